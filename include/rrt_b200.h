@@ -1,0 +1,222 @@
+/* rrt_b200.h — C-ABI of the B200-native hot path of the relativistic ray tracer.
+ *
+ * One data-parallel path is served: per-pixel Monte Carlo radiance estimation in which every ray
+ * (camera, bounce, shadow) is integrated as a Schwarzschild null geodesic in short chords and each
+ * chord is tested against the BVH.  Everything below is plain C: pointers and sizes, no C++/torch
+ * types, no exceptions.  All functions return 0 on success or a negative RRT_E_* code; the message
+ * is available from rrt_last_error().  There is no CPU fallback: without a CUDA device every
+ * compute entry point fails with RRT_E_CUDA.
+ *
+ * A context (rrt_ctx) is bound to ONE GPU and is driven by one host thread at a time.  Multi-GPU
+ * runs use one context (one process) per GPU; each renders the interleaved tiles it owns
+ * (rrt_set_tile_shard) into a zero-initialised frame and the caller combines the frames with a
+ * single sum-reduce (NCCL) — see INTEGRATION.md.
+ *
+ * Reference interfaces replaced (paths relative to /root/reference/pathtracer):
+ *   PathTracer::set_scene  + build_accel   src/pathtracer.cpp:95-117,304-328   -> rrt_upload_scene
+ *   BVHAccel::BVHAccel / construct_bvh     src/bvh.cpp:14-19,49-96             -> rrt_upload_scene
+ *   PathTracer::set_camera                 src/pathtracer.cpp:119-134          -> rrt_set_camera
+ *   global_black_hole / -B flag            src/static_scene/blackhole.cpp:5, src/main.cpp:139-145 -> rrt_set_blackhole
+ *   PathTracer::set_frame_size             src/pathtracer.cpp:136-149          -> rrt_set_frame
+ *   render_cell / cell_tl / cell_br        src/pathtracer.cpp:256-274          -> rrt_set_cell
+ *   start_raytracing + worker_thread + raytrace_tile + raytrace_pixel
+ *                                          src/pathtracer.cpp:224-282,549-644; src/part1_code.cpp:125-163 -> rrt_render[_device]
+ *   BVHAccel::intersect(ray[,isect])       src/bvh.h:86-109, src/bvh.cpp:99-138 -> rrt_trace_rays
+ *   BlackHole::next_micro_ray              src/static_scene/blackhole.cpp:17-40 -> rrt_geodesic
+ *   Camera::generate_ray                   src/part1_code.cpp:182-187           -> rrt_generate_rays
+ *   BSDF::f / sample_f                     src/bsdf.cpp:33-171, src/part1_code.cpp:167-173 -> rrt_bsdf_sample, rrt_bsdf_eval
+ *   SceneLight::sample_L                   src/static_scene/light.cpp:17-92     -> rrt_light_sample
+ *   HDRImageBuffer::toColor                src/image.h:183-198,53-62            -> rrt_tonemap
+ */
+#ifndef RRT_B200_H
+#define RRT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RRT_ABI_VERSION 1
+
+/* error codes */
+#define RRT_OK 0
+#define RRT_E_ARG (-1)     /* bad argument / wrong state */
+#define RRT_E_CUDA (-2)    /* CUDA runtime error or no device */
+#define RRT_E_STATE (-3)   /* scene/camera/frame not set */
+#define RRT_E_IO (-4)      /* scene file problem */
+
+typedef struct rrt_ctx rrt_ctx;
+
+/* BSDF kinds (reference classes in src/bsdf.h:118-258) */
+enum {
+  RRT_MAT_DIFFUSE = 0,    /* a = reflectance */
+  RRT_MAT_MIRROR = 1,     /* a = reflectance */
+  RRT_MAT_GLASS = 2,      /* a = reflectance, b = transmittance, ior */
+  RRT_MAT_MICROFACET = 3, /* a = eta, b = k, alpha */
+  RRT_MAT_EMISSION = 4,   /* a = radiance */
+  RRT_MAT_REFRACTION = 5  /* b = transmittance, ior; reference stub: f = 0, sample_f = 0 (src/bsdf.cpp:100-106) */
+};
+
+typedef struct rrt_material {
+  int32_t type;
+  float a[3];
+  float b[3];
+  float alpha;
+  float ior;
+} rrt_material; /* 36 bytes */
+
+/* light kinds (reference classes in src/static_scene/light.h) */
+enum {
+  RRT_LIGHT_DIRECTIONAL = 0, /* direction = dirToLight (unit, already negated) */
+  RRT_LIGHT_HEMISPHERE = 1,  /* InfiniteHemisphereLight: fixed sampleToWorld (src/static_scene/light.cpp:27-32) */
+  RRT_LIGHT_POINT = 2,       /* position */
+  RRT_LIGHT_AREA = 3,        /* position, direction, dim_x, dim_y, area */
+  RRT_LIGHT_NULL = 4         /* Spot/Sphere/Mesh lights: reference stubs returning zero radiance (light.cpp:61-115) */
+};
+
+typedef struct rrt_light {
+  int32_t type;
+  float radiance[3];
+  double position[3];
+  double direction[3];
+  double dim_x[3];
+  double dim_y[3];
+  float area;
+  int32_t is_delta; /* SceneLight::is_delta_light() */
+} rrt_light; /* 120 bytes */
+
+/* Scene in the reference's primitive order (the order PathTracer::build_accel collects them,
+ * src/pathtracer.cpp:311-316).  Geometry is the reference's own doubles.  The library copies
+ * everything; the caller keeps ownership. */
+typedef struct rrt_scene {
+  uint32_t n_prims;
+  const uint8_t* prim_kind;   /* [n_prims] 0 = triangle, 1 = sphere */
+  const uint32_t* prim_index; /* [n_prims] index into the triangle or sphere arrays */
+  uint32_t n_tris;
+  const double* tri_pos;  /* [n_tris*9] p0,p1,p2 in Triangle's (v1,v2,v3) order */
+  const double* tri_nrm;  /* [n_tris*9] vertex normals n0,n1,n2 (not necessarily unit) */
+  const int32_t* tri_mat; /* [n_tris] */
+  uint32_t n_spheres;
+  const double* sph;      /* [n_spheres*4] centre xyz, radius */
+  const int32_t* sph_mat; /* [n_spheres] */
+  uint32_t n_mats;
+  const rrt_material* mats;
+  uint32_t n_lights;
+  const rrt_light* lights;
+} rrt_scene;
+
+/* Camera after Application::load/resize (src/camera.cpp:22-40,68-74,96-119).  c2w holds the three
+ * COLUMNS of the reference Matrix3x3 (c2w[3*j+i] = entries[j][i]).  Fov in degrees. */
+typedef struct rrt_camera {
+  double pos[3];
+  double c2w[9];
+  double hFov, vFov;
+  double nClip, fClip;
+  double lensRadius, focalDistance; /* used only with rrt_params.thin_lens */
+} rrt_camera;
+
+#define RRT_MODE_FLAT 0    /* BVHAccel::intersect_micro semantics: straight rays, min_t/max_t honoured */
+#define RRT_MODE_LITERAL 1 /* reference-literal: every ray bent, caller's min_t/max_t discarded (src/bvh.cpp:103-113) */
+
+typedef struct rrt_params {
+  int32_t ns_aa;            /* -s */
+  int32_t max_ray_depth;    /* -m */
+  int32_t ns_area_light;    /* -l */
+  int32_t samples_per_batch;/* -a batch (default 32) */
+  float max_tolerance;      /* -a tol (default 0.05) */
+  int32_t direct_hemisphere_sample; /* -H */
+  int32_t thin_lens;        /* THIN_LENS compile switch of the reference, run-time here */
+  uint64_t seed;            /* Philox key */
+  int32_t max_paths_in_flight; /* 0 = library default; wavefront chunk size */
+  int32_t reserved;
+} rrt_params;
+
+typedef struct rrt_stats {
+  double seconds;          /* device time of the whole render (CUDA events) */
+  double trace_seconds;    /* device time inside the geodesic+BVH trace kernels */
+  uint64_t paths;          /* est_radiance_global_illumination calls (= sum of sample counts) */
+  uint64_t rays;           /* BVHAccel::intersect calls (camera + bounce + shadow) */
+  uint64_t geodesic_steps; /* BlackHole::next_micro_ray calls (literal mode) or straight segments (flat) */
+  uint64_t node_visits;    /* 64-byte BVH node records fetched */
+  uint64_t tri_tests;      /* 80-byte triangle records tested */
+  uint64_t sphere_tests;   /* sphere records tested */
+  uint64_t kernel_launches;/* kernels of this library launched during the render */
+  uint64_t trace_launches; /* of which trace kernels */
+  uint64_t algorithmic_bytes; /* 64*node_visits + 80*tri_tests + 32*sphere_tests + 160*rays */
+} rrt_stats;
+
+/* Result of one BVHAccel::intersect(ray, &isect) call. */
+typedef struct rrt_hit {
+  int32_t status; /* 0 = miss, 1 = hit, 2 = swallowed by the hole (reference returns false) */
+  int32_t prim;   /* index in the reference primitive order, -1 if none */
+  int32_t chord;  /* index of the geodesic chord that produced the result (0 in flat mode) */
+  int32_t steps;  /* next_micro_ray calls made for this ray */
+  double t;       /* ray parameter within that chord (Ray::max_t after the hit) */
+  double hit_p[3];
+  double w_out[3];
+  double n[3];    /* as stored by the reference: un-normalised for triangles */
+} rrt_hit; /* 96 bytes */
+
+/* ---- lifecycle ---- */
+int rrt_abi_version(void);
+int rrt_device_count(void);
+int rrt_create(rrt_ctx** out, int device);
+void rrt_destroy(rrt_ctx* ctx);
+const char* rrt_last_error(const rrt_ctx* ctx); /* ctx may be NULL: last creation error */
+
+/* ---- configuration (host buffers) ---- */
+int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* scene);
+int rrt_set_camera(rrt_ctx* ctx, const rrt_camera* cam);
+int rrt_set_blackhole(rrt_ctx* ctx, const double centre[3], double r, double delta_theta, int mode);
+int rrt_set_frame(rrt_ctx* ctx, int width, int height);
+/* cell render (-p x y dx dy); w<=0 restores the full frame */
+int rrt_set_cell(rrt_ctx* ctx, int x, int y, int w, int h);
+/* interleaved tile ownership for multi-GPU: tile (tx,ty) belongs to rank (tx + ty*ntx) % world */
+int rrt_set_tile_shard(rrt_ctx* ctx, int tile_size, int rank, int world);
+
+/* ---- the hot path ---- */
+/* Blocking.  hdr_rgb: [W*H*3] float, row 0 = image bottom (sampleBuffer layout, src/pathtracer.cpp:575);
+ * sample_counts: [W*H] int (sampleCountBuffer).  Pixels not owned by this shard are written as 0.
+ * Either output may be NULL.  Host buffers; the copies are inside the call. */
+int rrt_render(rrt_ctx* ctx, const rrt_params* p, float* hdr_rgb, int32_t* sample_counts, rrt_stats* stats);
+/* Same, results left on the device: d_rgbn is a CUDA device pointer to [W*H] float4 (mean r,g,b, sample
+ * count as float), d_counts a device pointer to [W*H] int32 or NULL.  Runs on `stream` (a cudaStream_t
+ * passed as void*, NULL = the context's own stream) and synchronises it before returning. */
+int rrt_render_device(rrt_ctx* ctx, const rrt_params* p, void* d_rgbn, void* d_counts, void* stream, rrt_stats* stats);
+
+/* ---- parity hooks: the same device code the render uses, on caller-supplied inputs ---- */
+/* n rays, o/d: [n*3] doubles; min_t/max_t may be NULL (0, +inf); used only in flat mode. any_hit != 0
+ * gives BVHAccel::intersect(ray) (shadow-ray form): only status is meaningful. */
+int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, const double* min_t,
+                   const double* max_t, int any_hit, rrt_hit* out, rrt_stats* stats);
+/* First nsteps chords of each ray: seg_out [n*nsteps*7] = origin xyz, unit direction xyz, length. */
+int rrt_geodesic(rrt_ctx* ctx, int64_t n, const double* o, const double* d, int nsteps, double* seg_out);
+/* Camera::generate_ray for n normalised sensor positions xy [n*2] -> o,d [n*3]. */
+int rrt_generate_rays(rrt_ctx* ctx, int64_t n, const double* xy, double* o, double* d);
+/* BSDF::sample_f of material `mat` for n outgoing directions wo [n*3] with uniforms u [n*4] in [0,1)
+ * (u0,u1 = 2-D sample, u2 = glass coin).  Outputs f [n*3] float, wi [n*3] double, pdf [n] float. */
+int rrt_bsdf_sample(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const double* u, float* f,
+                    double* wi, float* pdf);
+/* BSDF::f */
+int rrt_bsdf_eval(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const double* wi, float* f);
+/* SceneLight::sample_L of light `light` from n points p [n*3] with uniforms u [n*2]:
+ * radiance [n*3] float, wi [n*3] double, dist [n] float, pdf [n] float. */
+int rrt_light_sample(rrt_ctx* ctx, int light, int64_t n, const double* p, const double* u,
+                     float* radiance, double* wi, float* dist, float* pdf);
+/* Philox4x32-10 block for (key = seed, counter = c0..c3) as the render uses it: out [n*4] uint32. */
+int rrt_philox(rrt_ctx* ctx, uint64_t seed, int64_t n, const uint32_t* counters, uint32_t* out);
+/* toColor: [n*3] float HDR -> [n] RGBA8 (alpha 0xFF), on the device. */
+int rrt_tonemap(rrt_ctx* ctx, int64_t n, const float* hdr_rgb, uint32_t* rgba);
+
+/* ---- introspection ---- */
+/* BVH facts after rrt_upload_scene: nodes, leaves, depth; dfs_rank [n_prims] (may be NULL) receives, for
+ * every primitive in reference order, its position in the reference BVH's depth-first leaf order. */
+int rrt_bvh_info(rrt_ctx* ctx, int32_t* n_nodes, int32_t* n_leaves, int32_t* depth, uint32_t* dfs_rank);
+/* number of geodesic chords per ray: count of j >= 0 with j*delta_theta < 2*pi (src/bvh.cpp:105) */
+int rrt_chords_per_ray(rrt_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RRT_B200_H */
