@@ -141,6 +141,9 @@ static Ctx load(const char* dae, int W, int H, AppConfig cfg = AppConfig()) {
   c.app->init();
   c.app->load(si);
   delete si;
+  // Optional: RRT_PROBE_SCREENDIST_SCALE=k multiplies Camera::screenDist before the resize, so that a small test
+  // frame covers the same field of view as a k-times larger one (the reference's -r only crops, src/camera.cpp:68-74).
+  if (const char* k = getenv("RRT_PROBE_SCREENDIST_SCALE")) c.app->camera.screenDist *= atof(k);
   if (W && H) c.app->resize(W, H);
   // set_up_pathtracer (src/application.cpp:622-628) silences nothing; keep stdout clean for callers
   FILE* saved = stdout; stdout = fopen("/dev/null", "w");
@@ -369,7 +372,7 @@ static int cmd_order(int, char**) {
 // out = W*H x [r g b count] doubles (row 0 = bottom, sampleBuffer layout) followed by
 // [total_rays, total_isects, total_draws, seconds].
 static int cmd_render(int argc, char** argv) {
-  if (argc < 13) return 1;
+  if (argc < 12) return 1;
   parse_bh(argc, argv);
   AppConfig cfg;
   int W = atoi(argv[3]), H = atoi(argv[4]);

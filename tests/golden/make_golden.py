@@ -1,0 +1,268 @@
+#!/usr/bin/env python
+"""Regenerates tests/golden/* from the reference's own code (oracle/_ref/ref_probe[_flat], built by
+oracle/build_ref.sh from /root/reference).  Runs only in the build container; the fixtures it writes are
+committed so that the GPU box (no /root/reference) can check against them.
+
+    python tests/golden/make_golden.py [kat] [render] [scenes]
+
+Inputs are seeded numpy draws; outputs are what the reference's BVHAccel::intersect, BlackHole::next_micro_ray,
+Camera::generate_ray, BSDF::f/sample_f, SceneLight::sample_L and PathTracer::raytrace_pixel return for them.
+"""
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = os.path.join(ROOT, "oracle", "_ref")
+DAE = os.path.join(REF, "dae")
+PROBE = {"bh": os.path.join(REF, "ref_probe"), "flat": os.path.join(REF, "ref_probe_flat")}
+RAND_MAX = 2147483647
+TMP = tempfile.mkdtemp(prefix="rrt_golden_")
+
+
+def run(args, env=None):
+    e = dict(os.environ)
+    e.update(env or {})
+    subprocess.check_call([str(a) for a in args], env=e, stdout=subprocess.DEVNULL)
+
+
+def probe(mode, cmd, *args, env=None):
+    run([PROBE[mode], cmd] + list(args), env)
+
+
+def tmpf(name):
+    return os.path.join(TMP, name)
+
+
+def wr(name, a):
+    p = tmpf(name)
+    np.ascontiguousarray(a, np.float64).tofile(p)
+    return p
+
+
+def rd(name, cols):
+    return np.fromfile(tmpf(name), np.float64).reshape(-1, cols)
+
+
+# ---------------------------------------------------------------- scenes
+SCENES = {  # name -> (dae, W, H, screenDist scale)
+    "cbspheres_lambertian_480x360": ("CBspheres_lambertian.dae", 480, 360, None),
+    "cbspheres_480x360": ("CBspheres.dae", 480, 360, None),
+    "cbspheres_microfacet_480x360": ("CBspheres_microfacet_al_ag.dae", 480, 360, None),
+    "cbgems_480x360": ("CBgems.dae", 480, 360, None),
+    "cbempty_480x360": ("CBempty.dae", 480, 360, None),
+    "cbbunny_microfacet_480x360": ("CBbunny_microfacet_cu.dae", 480, 360, None),
+    # small frames that still see the whole box: screenDist scaled by W/480
+    "cbspheres_lambertian_96x72": ("CBspheres_lambertian.dae", 96, 72, 0.2),
+    "cbspheres_96x72": ("CBspheres.dae", 96, 72, 0.2),
+    "cbspheres_microfacet_96x72": ("CBspheres_microfacet_al_ag.dae", 96, 72, 0.2),
+    "cbgems_96x72": ("CBgems.dae", 96, 72, 0.2),
+    "cbempty_96x72": ("CBempty.dae", 96, 72, 0.2),
+    "cbbunny_microfacet_96x72": ("CBbunny_microfacet_cu.dae", 96, 72, 0.2),
+}
+
+
+def scene_env(name):
+    k = SCENES[name][3]
+    return {"RRT_PROBE_SCREENDIST_SCALE": str(k)} if k else {}
+
+
+def make_scenes():
+    sys.path.insert(0, ROOT)
+    import importlib
+    sc = importlib.import_module("relativistic-ray-tracer_b200.scene")
+    for name, (dae, w, h, _) in SCENES.items():
+        out = tmpf(name + ".rrtscene")
+        probe("bh", "scene", os.path.join(DAE, dae), w, h, out, env=scene_env(name))
+        s = sc.SceneData.load(out)
+        raw = open(out, "rb").read()
+        dst = os.path.join(HERE, name + ".rrtscene")
+        if not name.endswith("_480x360"):  # same geometry as the 480x360 dump: keep only the camera block (24 doubles)
+            np.save(os.path.join(HERE, name + ".cam.npy"), np.frombuffer(raw, np.float64, 24, 40))
+            print("scene", name, "-> camera block only")
+            continue
+        if len(raw) > 256 * 1024:  # big meshes: compressed container of the same bytes
+            np.savez_compressed(dst + ".npz", raw=np.frombuffer(raw, np.uint8))
+            print("scene", name, s.n_prims, "prims ->", os.path.getsize(dst + ".npz"), "bytes (npz)")
+        else:
+            open(dst, "wb").write(raw)
+            print("scene", name, s.n_prims, "prims ->", len(raw), "bytes")
+
+
+# ---------------------------------------------------------------- KATs
+def unit(v):
+    return v / np.linalg.norm(v, axis=-1, keepdims=True)
+
+
+def kat_geodesic():
+    rng = np.random.default_rng(184)
+    n = 192
+    o = np.stack([rng.uniform(-1, 1, n), rng.uniform(0, 1.5, n), rng.uniform(-1, 5, n)], 1)
+    d = unit(rng.normal(size=(n, 3)))
+    c = np.array([0.0, 1.0, 0.0])
+    # rays aimed close to the hole (strong bending / capture), exactly radial rays (dy = 0 -> NaN chords), App. E ray
+    aim = c + rng.normal(scale=0.15, size=(48, 3))
+    o2 = np.stack([rng.uniform(-1, 1, 48), rng.uniform(0, 1.5, 48), rng.uniform(1, 5, 48)], 1)
+    d2 = unit(aim - o2)
+    o3 = np.array([[0.0, 1.0, 3.0], [0.0, 0.0, 0.0], [1.0, 1.0, 0.0]])
+    d3 = unit(c - o3)
+    o4 = np.array([[0.5, 0.0, 0.5]])
+    d4 = unit(np.array([[0.1, 1.49, 0.1]]) - o4)
+    O = np.concatenate([o, o2, o3, o4]); D = np.concatenate([d, d2, d3, d4])
+    rays = wr("geo_in.bin", np.concatenate([O, D], 1))
+    out = {}
+    for tag, bh, nsteps in (("default", None, 63), ("alt", (0.2, 0.8, -0.1, 0.05, 0.2), 32), ("r0", (0, 1, 0, 0, 0.1), 63)):
+        args = ["geodesic", rays, nsteps, tmpf("geo_out.bin")]
+        if bh:
+            args += ["-B"] + list(bh)
+        probe("bh", *args)
+        out["seg_" + tag] = rd("geo_out.bin", 8).reshape(len(O), nsteps, 8)
+        out["bh_" + tag] = np.array(bh if bh else (0, 1, 0, 0.1, 0.1), np.float64)
+    np.savez_compressed(os.path.join(HERE, "kat_geodesic.npz"), o=O, d=D, **out)
+    print("kat_geodesic", len(O), "rays")
+
+
+def kat_trace(scene, gw, gh, n_extra, seed, bh_alt=None):
+    dae, w, h, _ = SCENES[scene]
+    dae = os.path.join(DAE, dae)
+    env = scene_env(scene)
+    rng = np.random.default_rng(seed)
+    # camera rays through the reference's own generate_ray (pixel centres of a gw x gh grid + random jitter set)
+    gx, gy = np.meshgrid((np.arange(gw) + 0.5) / gw, (np.arange(gh) + 0.5) / gh)
+    xy = np.concatenate([np.stack([gx.ravel(), gy.ravel()], 1), rng.uniform(0, 1, (n_extra, 2))])
+    probe("bh", "camrays", dae, w, h, wr("xy.bin", xy), tmpf("cam.bin"), env=env)
+    cam = rd("cam.bin", 8)
+    res = {"xy": xy, "cam": cam}
+    for mode in ("flat", "bh"):
+        rays = cam.copy()
+        probe(mode, "trace", dae, w, h, wr("rays.bin", rays), tmpf("hit.bin"), env=env)
+        hit = rd("hit.bin", 16)
+        # secondary rays from the hit points: shadow-style (toward the light quad, max_t = float dist) and random bounces
+        ok = hit[:, 0] > 0
+        p = hit[ok, 2:5]
+        m = min(len(p), 3000)
+        sel = rng.choice(len(p), m, replace=False)
+        p = p[sel]
+        lp = np.stack([rng.uniform(-0.3, 0.3, m), np.full(m, 1.49), rng.uniform(-0.4, 0.4, m)], 1)
+        dl = lp - p
+        dist = np.sqrt(np.float32((dl * dl).sum(1))).astype(np.float32)
+        wi = dl / dist[:, None].astype(np.float64)
+        sh = np.concatenate([p + 1e-11 * wi, wi, np.zeros((m, 1)), dist[:, None].astype(np.float64)], 1)
+        wb = unit(rng.normal(size=(m, 3)))
+        bo = np.concatenate([p + 1e-11 * wb, wb, np.zeros((m, 1)), np.full((m, 1), np.inf)], 1)
+        sec = np.concatenate([sh, bo])
+        probe(mode, "trace", dae, w, h, wr("rays2.bin", sec), tmpf("hit2.bin"), env=env)
+        res["rays_" + mode] = np.concatenate([rays, sec])
+        res["hit_" + mode] = np.concatenate([hit, rd("hit2.bin", 16)])
+    if bh_alt:
+        probe("bh", "trace", dae, w, h, wr("rays.bin", cam), tmpf("hit.bin"), "-B", *bh_alt, env=env)
+        res["rays_alt"] = cam
+        res["hit_alt"] = rd("hit.bin", 16)
+        res["bh_alt"] = np.array(bh_alt, np.float64)
+    np.savez_compressed(os.path.join(HERE, "kat_trace_%s.npz" % scene), **res)
+    print("kat_trace", scene, {k: v.shape for k, v in res.items() if k.startswith("hit")})
+
+
+def kat_bsdf(scene, seed):
+    dae, w, h, _ = SCENES[scene]
+    dae = os.path.join(DAE, dae)
+    rng = np.random.default_rng(seed)
+    sys.path.insert(0, ROOT)
+    import importlib
+    sc = importlib.import_module("relativistic-ray-tracer_b200.scene")
+    s = sc.SceneData.load(os.path.join(HERE, scene + ".rrtscene"))
+    n = 512
+    out = {}
+    for mi in range(len(s.mats)):
+        wo = unit(rng.normal(size=(n, 3)))
+        wo[: n // 4, 2] = np.abs(wo[: n // 4, 2])  # more upper-hemisphere
+        wi = unit(rng.normal(size=(n, 3)))
+        wi[: n // 2, 2] = np.abs(wi[: n // 2, 2])
+        wo[: n // 2, 2] = np.abs(wo[: n // 2, 2])
+        r = rng.integers(0, RAND_MAX, (n, 4), endpoint=True).astype(np.float64)
+        r[0] = [0, 0, 0, 0]; r[1] = [RAND_MAX] * 4; r[2] = [0, RAND_MAX, 0, RAND_MAX]; r[3] = [RAND_MAX, 0, RAND_MAX, 0]
+        inp = np.concatenate([wo, wi, r], 1)
+        probe("bh", "bsdf", dae, w, h, mi, wr("bsdf_in.bin", inp), tmpf("bsdf_out.bin"))
+        out["in_%d" % mi] = inp
+        out["out_%d" % mi] = rd("bsdf_out.bin", 12)
+    np.savez_compressed(os.path.join(HERE, "kat_bsdf_%s.npz" % scene), **out)
+    print("kat_bsdf", scene, len(s.mats), "materials")
+
+
+def kat_light(scene, seed):
+    dae, w, h, _ = SCENES[scene]
+    dae = os.path.join(DAE, dae)
+    rng = np.random.default_rng(seed)
+    n = 512
+    p = np.stack([rng.uniform(-1, 1, n), rng.uniform(0, 1.6, n), rng.uniform(-1, 1, n)], 1)
+    r = rng.integers(0, RAND_MAX, (n, 2), endpoint=True).astype(np.float64)
+    r[0] = [0, 0]; r[1] = [RAND_MAX, RAND_MAX]
+    inp = np.concatenate([p, r], 1)
+    probe("bh", "light", dae, w, h, 0, wr("light_in.bin", inp), tmpf("light_out.bin"))
+    np.savez_compressed(os.path.join(HERE, "kat_light_%s.npz" % scene), inp=inp, out=rd("light_out.bin", 10))
+    print("kat_light", scene)
+
+
+def make_kat():
+    kat_geodesic()
+    kat_trace("cbspheres_lambertian_480x360", 96, 72, 2000, 1, bh_alt=(0.2, 0.8, -0.1, 0.05, 0.2))
+    kat_trace("cbgems_480x360", 64, 48, 1000, 2)
+    kat_trace("cbbunny_microfacet_480x360", 96, 72, 2000, 3)
+    for i, sname in enumerate(("cbspheres_lambertian_480x360", "cbspheres_480x360", "cbspheres_microfacet_480x360")):
+        kat_bsdf(sname, 10 + i)
+    kat_light("cbspheres_lambertian_480x360", 20)
+    kat_light("cbempty_480x360", 21)
+
+
+# ---------------------------------------------------------------- renders (reference raytrace_pixel, Philox-fed rand)
+RENDERS = {  # name -> (scene, mode, spp, l, m, batch, tol, seed, extra args)
+    "c1_flat_lambertian": ("cbspheres_lambertian_96x72", "flat", 16, 4, 5, 32, 0.05, 1, []),
+    "c2_bh_lambertian": ("cbspheres_lambertian_96x72", "bh", 8, 4, 5, 32, 0.05, 2, []),
+    "bh_glass_mirror": ("cbspheres_96x72", "bh", 8, 2, 6, 32, 0.05, 3, []),
+    "flat_glass_mirror": ("cbspheres_96x72", "flat", 16, 2, 8, 32, 0.05, 4, []),
+    "flat_microfacet": ("cbspheres_microfacet_96x72", "flat", 16, 2, 5, 32, 0.05, 5, []),
+    "bh_microfacet": ("cbspheres_microfacet_96x72", "bh", 4, 1, 4, 32, 0.05, 6, []),
+    "flat_gems": ("cbgems_96x72", "flat", 8, 2, 8, 32, 0.05, 7, []),
+    "flat_bunny_microfacet": ("cbbunny_microfacet_96x72", "flat", 8, 2, 5, 32, 0.05, 8, []),
+    "bh_bunny_microfacet": ("cbbunny_microfacet_96x72", "bh", 2, 1, 3, 32, 0.05, 9, []),
+    "flat_adaptive": ("cbspheres_lambertian_96x72", "flat", 64, 2, 4, 8, 0.2, 10, []),
+    "bh_adaptive": ("cbspheres_lambertian_96x72", "bh", 32, 1, 3, 8, 0.3, 11, []),
+    "flat_depth0": ("cbspheres_lambertian_96x72", "flat", 4, 1, 0, 32, 0.05, 12, []),
+    "flat_depth1": ("cbspheres_lambertian_96x72", "flat", 4, 4, 1, 32, 0.05, 13, []),
+    "bh_depth1_spp1": ("cbspheres_lambertian_96x72", "bh", 1, 4, 1, 32, 0.05, 14, []),
+    "flat_pointlight": ("cbempty_96x72", "flat", 8, 1, 4, 32, 0.05, 15, []),
+    "flat_hemisphere": ("cbspheres_lambertian_96x72", "flat", 8, 4, 3, 32, 0.05, 16, ["hemi"]),
+    "bh_alt_hole": ("cbspheres_lambertian_96x72", "bh", 4, 2, 4, 32, 0.05, 17, ["-B", 0.2, 0.8, -0.1, 0.05, 0.2]),
+}
+
+
+def make_render(only=None):
+    for name, (scene, mode, spp, l, m, batch, tol, seed, extra) in RENDERS.items():
+        if only and name not in only:
+            continue
+        dae, w, h, _ = SCENES[scene]
+        out = tmpf("render.bin")
+        probe(mode, "render", os.path.join(DAE, dae), w, h, spp, l, m, batch, tol, seed, out, *extra, env=scene_env(scene))
+        a = np.fromfile(out, np.float64)
+        img = a[: w * h * 4].reshape(h, w, 4)
+        tail = a[w * h * 4:]
+        np.savez_compressed(os.path.join(HERE, "render_%s.npz" % name), hdr=img[..., :3].astype(np.float32),
+                            counts=img[..., 3].astype(np.int32), scene=scene, mode=mode,
+                            params=np.array([spp, l, m, batch, tol, seed], np.float64),
+                            hemi=np.array("hemi" in extra), bh=np.array([x for x in extra if not isinstance(x, str)], np.float64),
+                            draws=tail[2])
+        print("render", name, "mean radiance %.5f  paths %d" % (img[..., :3].mean(), img[..., 3].sum()))
+
+
+if __name__ == "__main__":
+    what = sys.argv[1:] or ["scenes", "kat", "render"]
+    if "scenes" in what:
+        make_scenes()
+    if "kat" in what:
+        make_kat()
+    if "render" in what:
+        make_render([w for w in what if w in RENDERS] or None)
