@@ -158,12 +158,21 @@ typedef struct rrt_hit {
   double n[3];    /* as stored by the reference: un-normalised for triangles */
 } rrt_hit; /* 96 bytes */
 
+/* tuning / instrumentation switches for rrt_set_option */
+enum {
+  RRT_OPT_BVH_TOPOLOGY = 0, /* 0 = the reference's midpoint-split tree shape (default), 1 = binned SAH; takes effect at the next rrt_upload_scene */
+  RRT_OPT_COUNTERS = 1,     /* 1 (default) = trace kernels count rays / chords / node visits / primitive tests for rrt_stats */
+  RRT_OPT_WORK_BYTES = 2,   /* upper bound for the wavefront work buffers in bytes (default 12 GiB) */
+  RRT_OPT_TRACE_KERNEL = 3  /* trace kernel variant, see DESIGN.md (0 = default) */
+};
+
 /* ---- lifecycle ---- */
 int rrt_abi_version(void);
 int rrt_device_count(void);
 int rrt_create(rrt_ctx** out, int device);
 void rrt_destroy(rrt_ctx* ctx);
 const char* rrt_last_error(const rrt_ctx* ctx); /* ctx may be NULL: last creation error */
+int rrt_set_option(rrt_ctx* ctx, int option, int64_t value);
 
 /* ---- configuration (host buffers) ---- */
 int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* scene);
@@ -190,7 +199,8 @@ int rrt_render_device(rrt_ctx* ctx, const rrt_params* p, void* d_rgbn, void* d_c
  * gives BVHAccel::intersect(ray) (shadow-ray form): only status is meaningful. */
 int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, const double* min_t,
                    const double* max_t, int any_hit, rrt_hit* out, rrt_stats* stats);
-/* First nsteps chords of each ray: seg_out [n*nsteps*7] = origin xyz, unit direction xyz, length. */
+/* First nsteps chords of each ray: seg_out [n*nsteps*8] = origin xyz, unit direction xyz, length, and 1.0 when the
+ * chord crosses the horizon (the reference's capture test, src/bvh.cpp:107), else 0.0. */
 int rrt_geodesic(rrt_ctx* ctx, int64_t n, const double* o, const double* d, int nsteps, double* seg_out);
 /* Camera::generate_ray for n normalised sensor positions xy [n*2] -> o,d [n*3]. */
 int rrt_generate_rays(rrt_ctx* ctx, int64_t n, const double* xy, double* o, double* d);
@@ -213,6 +223,9 @@ int rrt_tonemap(rrt_ctx* ctx, int64_t n, const float* hdr_rgb, uint32_t* rgba);
 /* BVH facts after rrt_upload_scene: nodes, leaves, depth; dfs_rank [n_prims] (may be NULL) receives, for
  * every primitive in reference order, its position in the reference BVH's depth-first leaf order. */
 int rrt_bvh_info(rrt_ctx* ctx, int32_t* n_nodes, int32_t* n_leaves, int32_t* depth, uint32_t* dfs_rank);
+/* Host-only (no device needed): runs the BVH construction rrt_upload_scene uses.  info[0..5] = reference-shape nodes,
+ * leaves, depth, flattened interior nodes, leaf records, root child code; dfs_rank as in rrt_bvh_info (may be NULL). */
+int rrt_bvh_build_host(const rrt_scene* scene, int topology, int32_t info[6], uint32_t* dfs_rank);
 /* number of geodesic chords per ray: count of j >= 0 with j*delta_theta < 2*pi (src/bvh.cpp:105) */
 int rrt_chords_per_ray(rrt_ctx* ctx);
 

@@ -1,0 +1,623 @@
+// rrt_api.cu — the C-ABI of include/rrt_b200.h: context, uploads, the wavefront render loop, parity hooks.
+// Host code here only orchestrates; every number is produced by the kernels in rrt_kernels.cuh.
+// There is no CPU fallback: without a CUDA device rrt_create fails with RRT_E_CUDA.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "rrt_bvh.h"
+#include "rrt_kernels.cuh"
+
+static thread_local std::string g_create_error;
+
+struct DevBuf {
+  void* p = nullptr; size_t bytes = 0;
+  cudaError_t ensure(size_t need) {
+    if (need <= bytes) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; bytes = 0;
+    cudaError_t e = cudaMalloc(&p, need ? need : 16);
+    if (e == cudaSuccess) bytes = need;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+  template <class T> T* as() const { return (T*)p; }
+};
+
+struct rrt_ctx {
+  int device = 0, sm_count = 148;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  // configuration
+  bool have_scene = false, have_cam = false;
+  DevScene ds; DevHole bh; DevCamera cam;
+  rrt::FlatBvh bvh;
+  int n_lights = 0, n_delta_lights = 0;
+  int W = 0, H = 0;
+  int cell_x = 0, cell_y = 0, cell_w = 0, cell_h = 0;
+  int tile = 32, rank = 0, world = 1;
+  int64_t opt[16];
+  // device memory
+  DevBuf d_nodes, d_leaf, d_nrm, d_kind, d_index, d_pmat, d_sph, d_mats, d_lights;
+  DevBuf d_work, d_px, d_act, d_blk, d_cnt, d_out_rgb, d_out_cnt, d_out_rgbn, d_hook_in, d_hook_out;
+  std::vector<cudaEvent_t> events;
+  size_t events_used = 0;
+  uint32_t* h_pinned = nullptr;  // small pinned scratch for counts
+};
+
+#define CK(call)                                                                                           \
+  do {                                                                                                     \
+    cudaError_t e_ = (call);                                                                               \
+    if (e_ != cudaSuccess) {                                                                               \
+      char b_[512]; snprintf(b_, sizeof b_, "%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      ctx->err = b_; return RRT_E_CUDA;                                                                    \
+    }                                                                                                      \
+  } while (0)
+#define FAIL(code, msg) do { ctx->err = (msg); return (code); } while (0)
+
+static int chords_for(double dtheta) {
+  int j = 0;
+  while (j * dtheta < 2 * M_PI && j < (1 << 20)) ++j;  /* reference src/bvh.cpp:105 */
+  return j;
+}
+
+extern "C" {
+
+int rrt_abi_version(void) { return RRT_ABI_VERSION; }
+
+int rrt_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+  return n;
+}
+
+const char* rrt_last_error(const rrt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int rrt_create(rrt_ctx** out, int device) {
+  if (!out) { g_create_error = "rrt_create: out is NULL"; return RRT_E_ARG; }
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    g_create_error = std::string("rrt_create: no CUDA device (") + (e != cudaSuccess ? cudaGetErrorString(e) : "count = 0") +
+                     "); this library has no CPU fallback";
+    return RRT_E_CUDA;
+  }
+  if (device < 0 || device >= n) { g_create_error = "rrt_create: device index out of range"; return RRT_E_ARG; }
+  if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); return RRT_E_CUDA; }
+  rrt_ctx* ctx = new rrt_ctx();
+  ctx->device = device;
+  memset(ctx->opt, 0, sizeof ctx->opt);
+  ctx->opt[RRT_OPT_COUNTERS] = 1;
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+      (e = cudaMallocHost((void**)&ctx->h_pinned, 4096)) != cudaSuccess) {
+    g_create_error = cudaGetErrorString(e); delete ctx; return RRT_E_CUDA;
+  }
+  ctx->sm_count = prop.multiProcessorCount;
+  memset(&ctx->ds, 0, sizeof ctx->ds); memset(&ctx->cam, 0, sizeof ctx->cam);
+  /* global_black_hole(nullptr, Vector3D(0, 1, 0), 0.1, 0.1)  (reference src/static_scene/blackhole.cpp:5) */
+  ctx->bh.cx = 0; ctx->bh.cy = 1; ctx->bh.cz = 0; ctx->bh.r = 0.1; ctx->bh.r2 = 0.1 * 0.1; ctx->bh.h = 0.1;
+  ctx->bh.cos_h = cos(0.1); ctx->bh.sin_h = sin(0.1); ctx->bh.mode = RRT_MODE_LITERAL; ctx->bh.nchords = chords_for(0.1);
+  *out = ctx;
+  return RRT_OK;
+}
+
+void rrt_destroy(rrt_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  DevBuf* bufs[] = {&ctx->d_nodes, &ctx->d_leaf, &ctx->d_nrm, &ctx->d_kind, &ctx->d_index, &ctx->d_pmat, &ctx->d_sph, &ctx->d_mats, &ctx->d_lights,
+                    &ctx->d_work, &ctx->d_px, &ctx->d_act, &ctx->d_blk, &ctx->d_cnt, &ctx->d_out_rgb, &ctx->d_out_cnt, &ctx->d_out_rgbn,
+                    &ctx->d_hook_in, &ctx->d_hook_out};
+  for (DevBuf* b : bufs) b->release();
+  for (cudaEvent_t ev : ctx->events) cudaEventDestroy(ev);
+  if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+int rrt_set_option(rrt_ctx* ctx, int option, int64_t value) {
+  if (!ctx) return RRT_E_ARG;
+  if (option < 0 || option >= 16) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
+  ctx->opt[option] = value;
+  return RRT_OK;
+}
+
+static int upload(rrt_ctx* ctx, DevBuf& b, const void* src, size_t bytes) {
+  CK(b.ensure(bytes));
+  if (bytes) CK(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  return RRT_OK;
+}
+
+int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
+  if (!ctx || !s) return RRT_E_ARG;
+  CK(cudaSetDevice(ctx->device));
+  if (s->n_prims && (!s->prim_kind || !s->prim_index)) FAIL(RRT_E_ARG, "rrt_upload_scene: primitive arrays missing");
+  if ((s->n_tris && (!s->tri_pos || !s->tri_nrm || !s->tri_mat)) || (s->n_spheres && (!s->sph || !s->sph_mat)))
+    FAIL(RRT_E_ARG, "rrt_upload_scene: geometry arrays missing");
+  if (s->n_prims >= (1u << 28)) FAIL(RRT_E_ARG, "rrt_upload_scene: more than 2^28 primitives");
+  for (uint32_t p = 0; p < s->n_prims; ++p) {
+    uint32_t k = s->prim_kind[p], idx = s->prim_index[p];
+    if (k > 1 || idx >= (k == 0 ? s->n_tris : s->n_spheres)) FAIL(RRT_E_ARG, "rrt_upload_scene: primitive table out of range");
+    int32_t m = k == 0 ? s->tri_mat[idx] : s->sph_mat[idx];
+    if (m < 0 || (uint32_t)m >= s->n_mats) FAIL(RRT_E_ARG, "rrt_upload_scene: material index out of range");
+  }
+  rrt::build_bvh(s, (int)ctx->opt[RRT_OPT_BVH_TOPOLOGY], &ctx->bvh);
+  const rrt::FlatBvh& b = ctx->bvh;
+  int tree_depth = 0;
+  {  /* depth of the flattened tree bounds the traversal stack */
+    std::vector<std::pair<int, int>> st;
+    if (b.root >= 0) st.push_back({b.root, 1});
+    while (!st.empty()) {
+      auto [nd, dp] = st.back(); st.pop_back();
+      tree_depth = std::max(tree_depth, dp);
+      int32_t c[2]; memcpy(c, &b.nodes[16 * (size_t)nd + 12], 8);
+      for (int k = 0; k < 2; ++k) if (c[k] >= 0) st.push_back({c[k], dp + 1});
+    }
+  }
+  if (tree_depth >= RRT_STACK) FAIL(RRT_E_ARG, "rrt_upload_scene: BVH deeper than the traversal stack; set RRT_OPT_BVH_TOPOLOGY = 1");
+  CK(cudaStreamSynchronize(ctx->stream));
+  int rc;
+  if ((rc = upload(ctx, ctx->d_nodes, b.nodes.data(), b.nodes.size() * 4))) return rc;
+  if ((rc = upload(ctx, ctx->d_leaf, b.leaf.data(), b.leaf.size() * 8))) return rc;
+  if ((rc = upload(ctx, ctx->d_nrm, s->tri_nrm, 72 * (size_t)s->n_tris))) return rc;
+  if ((rc = upload(ctx, ctx->d_kind, s->prim_kind, s->n_prims))) return rc;
+  if ((rc = upload(ctx, ctx->d_index, s->prim_index, 4 * (size_t)s->n_prims))) return rc;
+  if ((rc = upload(ctx, ctx->d_pmat, b.prim_mat.data(), 4 * (size_t)s->n_prims))) return rc;
+  if ((rc = upload(ctx, ctx->d_sph, s->sph, 32 * (size_t)s->n_spheres))) return rc;
+  if ((rc = upload(ctx, ctx->d_mats, s->mats, sizeof(rrt_material) * (size_t)s->n_mats))) return rc;
+  if ((rc = upload(ctx, ctx->d_lights, s->lights, sizeof(rrt_light) * (size_t)s->n_lights))) return rc;
+  CK(cudaStreamSynchronize(ctx->stream));
+  DevScene& d = ctx->ds;
+  d.nodes = ctx->d_nodes.as<float4>(); d.leaf = ctx->d_leaf.as<double2>(); d.tri_nrm = ctx->d_nrm.as<double>();
+  d.prim_kind = ctx->d_kind.as<uint8_t>(); d.prim_index = ctx->d_index.as<uint32_t>(); d.prim_mat = ctx->d_pmat.as<int32_t>();
+  d.sph = ctx->d_sph.as<double>(); d.mats = ctx->d_mats.as<rrt_material>(); d.lights = ctx->d_lights.as<rrt_light>();
+  d.n_prims = (int)s->n_prims; d.n_mats = (int)s->n_mats; d.n_lights = (int)s->n_lights; d.root = b.root;
+  for (int k = 0; k < 3; ++k) { d.root_lo[k] = b.root_lo[k]; d.root_hi[k] = b.root_hi[k]; }
+  ctx->n_lights = (int)s->n_lights; ctx->n_delta_lights = 0;
+  for (uint32_t i = 0; i < s->n_lights; ++i) if (s->lights[i].is_delta) ctx->n_delta_lights++;
+  ctx->have_scene = true;
+  return RRT_OK;
+}
+
+int rrt_set_camera(rrt_ctx* ctx, const rrt_camera* cam) {
+  if (!ctx || !cam) return RRT_E_ARG;
+  memcpy(ctx->cam.pos, cam->pos, sizeof cam->pos); memcpy(ctx->cam.c2w, cam->c2w, sizeof cam->c2w);
+  ctx->cam.hFov = cam->hFov; ctx->cam.vFov = cam->vFov; ctx->cam.nClip = cam->nClip; ctx->cam.fClip = cam->fClip;
+  ctx->cam.lensRadius = cam->lensRadius; ctx->cam.focalDistance = cam->focalDistance;
+  ctx->have_cam = true;
+  return RRT_OK;
+}
+
+int rrt_set_blackhole(rrt_ctx* ctx, const double c[3], double r, double dtheta, int mode) {
+  if (!ctx || !c) return RRT_E_ARG;
+  if (mode != RRT_MODE_FLAT && mode != RRT_MODE_LITERAL) FAIL(RRT_E_ARG, "rrt_set_blackhole: unknown mode");
+  ctx->bh.cx = c[0]; ctx->bh.cy = c[1]; ctx->bh.cz = c[2]; ctx->bh.r = r; ctx->bh.r2 = r * r; ctx->bh.h = dtheta;
+  ctx->bh.cos_h = cos(dtheta); ctx->bh.sin_h = sin(dtheta);  /* host libm, as the reference evaluates them (src/static_scene/blackhole.cpp:34-35) */
+  ctx->bh.mode = mode; ctx->bh.nchords = chords_for(dtheta);
+  return RRT_OK;
+}
+
+int rrt_set_frame(rrt_ctx* ctx, int w, int h) {
+  if (!ctx) return RRT_E_ARG;
+  if (w <= 0 || h <= 0 || (int64_t)w * h >= (1ll << 31)) FAIL(RRT_E_ARG, "rrt_set_frame: bad size");
+  ctx->W = w; ctx->H = h; ctx->cell_w = 0;
+  return RRT_OK;
+}
+
+int rrt_set_cell(rrt_ctx* ctx, int x, int y, int w, int h) {
+  if (!ctx) return RRT_E_ARG;
+  ctx->cell_x = x; ctx->cell_y = y; ctx->cell_w = w; ctx->cell_h = h;
+  return RRT_OK;
+}
+
+int rrt_set_tile_shard(rrt_ctx* ctx, int tile, int rank, int world) {
+  if (!ctx) return RRT_E_ARG;
+  if (tile <= 0 || world <= 0 || rank < 0 || rank >= world) FAIL(RRT_E_ARG, "rrt_set_tile_shard: bad arguments");
+  ctx->tile = tile; ctx->rank = rank; ctx->world = world;
+  return RRT_OK;
+}
+
+int rrt_bvh_build_host(const rrt_scene* scene, int topology, int32_t info[6], uint32_t* dfs_rank) {
+  if (!scene || !info) return RRT_E_ARG;
+  rrt::FlatBvh b;
+  rrt::build_bvh(scene, topology, &b);
+  info[0] = b.ref_nodes; info[1] = b.ref_leaves; info[2] = b.ref_depth; info[3] = b.n_nodes; info[4] = (int32_t)(b.leaf.size() / 10); info[5] = b.root;
+  if (dfs_rank && !b.dfs_rank.empty()) memcpy(dfs_rank, b.dfs_rank.data(), 4 * b.dfs_rank.size());
+  return RRT_OK;
+}
+
+int rrt_chords_per_ray(rrt_ctx* ctx) { return ctx ? ctx->bh.nchords : RRT_E_ARG; }
+
+int rrt_bvh_info(rrt_ctx* ctx, int32_t* n_nodes, int32_t* n_leaves, int32_t* depth, uint32_t* dfs_rank) {
+  if (!ctx) return RRT_E_ARG;
+  if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_bvh_info: no scene");
+  if (n_nodes) *n_nodes = ctx->bvh.ref_nodes;
+  if (n_leaves) *n_leaves = ctx->bvh.ref_leaves;
+  if (depth) *depth = ctx->bvh.ref_depth;
+  if (dfs_rank) memcpy(dfs_rank, ctx->bvh.dfs_rank.data(), 4 * ctx->bvh.dfs_rank.size());
+  return RRT_OK;
+}
+
+}  // extern "C"
+
+/* ---------------------------------------------------------------- render */
+static cudaEvent_t next_event(rrt_ctx* ctx) {
+  if (ctx->events_used == ctx->events.size()) {
+    cudaEvent_t ev; cudaEventCreate(&ev); ctx->events.push_back(ev);
+  }
+  return ctx->events[ctx->events_used++];
+}
+
+template <class Keep>
+static int compact(rrt_ctx* ctx, Keep keep, const uint32_t* in, uint32_t n, uint32_t* out, uint32_t* n_out) {
+  uint32_t nblocks = (n + RRT_CBLOCK - 1) / RRT_CBLOCK;
+  if (n == 0) { *n_out = 0; return RRT_OK; }
+  CK(ctx->d_blk.ensure(4 * (size_t)(nblocks + 1)));
+  uint32_t* blk = ctx->d_blk.as<uint32_t>();
+  k_compact_count<<<nblocks, RRT_CBLOCK, 0, ctx->stream>>>(keep, in, n, blk);
+  k_compact_scan<<<1, 1024, 0, ctx->stream>>>(blk, nblocks, blk + nblocks);
+  k_compact_scatter<<<nblocks, RRT_CBLOCK, 0, ctx->stream>>>(keep, in, n, blk, out);
+  CK(cudaMemcpyAsync(ctx->h_pinned, blk + nblocks, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  *n_out = ctx->h_pinned[0];
+  return RRT_OK;
+}
+
+static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_counts, float4* d_rgbn, cudaStream_t user_stream, rrt_stats* stats) {
+  if (!ctx->have_scene || !ctx->have_cam || ctx->W <= 0) FAIL(RRT_E_STATE, "rrt_render: scene, camera and frame must be set first");
+  if (p->ns_aa <= 0 || p->max_ray_depth < 0 || p->ns_area_light <= 0 || p->samples_per_batch <= 0) FAIL(RRT_E_ARG, "rrt_render: bad parameters");
+  CK(cudaSetDevice(ctx->device));
+  (void)user_stream;
+  cudaStream_t st = ctx->stream;
+  const bool count = ctx->opt[RRT_OPT_COUNTERS] != 0;
+  const size_t npix = (size_t)ctx->W * ctx->H;
+
+  RenderK rk;
+  rk.W = ctx->W; rk.H = ctx->H; rk.ns_aa = p->ns_aa; rk.D = p->max_ray_depth; rk.ns_area_light = p->ns_area_light; rk.batch = p->samples_per_batch;
+  rk.tol = p->max_tolerance; rk.hemi = p->direct_hemisphere_sample != 0; rk.thin_lens = p->thin_lens != 0; rk.seed = p->seed;
+  if (rk.hemi) rk.S = rk.total = ctx->n_lights * p->ns_area_light;
+  else rk.S = rk.total = ctx->n_delta_lights + (ctx->n_lights - ctx->n_delta_lights) * p->ns_area_light;
+  if (rk.D == 0) rk.S = 0;
+  const int S = std::max(rk.S, 1);
+  const int nb_max = std::min(rk.batch, rk.ns_aa);
+  const int iters = std::max(rk.D, 1);
+
+  /* ---- work buffers: capacity from the in-flight budget */
+  const size_t per_path = 2 * (8 * 8 + 4 + 4 + 4 + 12) + 4 + 72 + 12 + 1 + 12 + (size_t)S * (56 + 4 + 4 + 16);
+  size_t want = p->max_paths_in_flight > 0 ? (size_t)p->max_paths_in_flight : (size_t)4 << 20;
+  size_t budget = (size_t)(ctx->opt[RRT_OPT_WORK_BYTES] > 0 ? ctx->opt[RRT_OPT_WORK_BYTES] : (int64_t)12 << 30);
+  want = std::min(want, std::max<size_t>(budget / per_path, 1024));
+  size_t pix_per_chunk = std::max<size_t>(want / nb_max, 1);
+  pix_per_chunk = std::min(pix_per_chunk, npix);
+  const size_t cap = pix_per_chunk * nb_max, capS = cap * S;
+  if (capS >= ((size_t)1 << 31)) FAIL(RRT_E_ARG, "rrt_render: max_paths_in_flight x light samples exceeds 2^31");
+  rk.cap = (int)cap;
+
+  Queues q; memset(&q, 0, sizeof q);
+  size_t off = 0;
+  auto carve = [&](size_t bytes) { size_t o = off; off += align_up(bytes); return o; };
+  size_t o_ray[2], o_slot[2], o_rngn[2], o_flags[2], o_beta[2];
+  for (int b = 0; b < 2; ++b) { o_ray[b] = carve(64 * cap); o_slot[b] = carve(4 * cap); o_rngn[b] = carve(4 * cap); o_flags[b] = carve(4 * cap); o_beta[b] = carve(12 * cap); }
+  size_t o_hprim = carve(4 * cap), o_hgeo = carve(72 * cap), o_dbeta = carve(12 * cap), o_vflag = carve(cap), o_sray = carve(56 * capS),
+         o_scidx = carve(4 * capS), o_sres = carve(4 * capS), o_scon = carve(16 * capS), o_L = carve(12 * cap);
+  q.ctl_stride = iters + 2;
+  size_t o_ctl = carve(4 * 4 * (size_t)q.ctl_stride);
+  CK(ctx->d_work.ensure(off));
+  char* wb = ctx->d_work.as<char>();
+  for (int b = 0; b < 2; ++b) {
+    q.ray[b] = (double*)(wb + o_ray[b]); q.slot[b] = (uint32_t*)(wb + o_slot[b]); q.rngn[b] = (uint32_t*)(wb + o_rngn[b]);
+    q.flags[b] = (uint32_t*)(wb + o_flags[b]); q.beta[b] = (float*)(wb + o_beta[b]);
+  }
+  q.h_prim = (int*)(wb + o_hprim); q.h_geo = (double*)(wb + o_hgeo); q.dbeta = (float*)(wb + o_dbeta); q.vflag = (uint8_t*)(wb + o_vflag);
+  q.sray = (double*)(wb + o_sray); q.s_cidx = (uint32_t*)(wb + o_scidx); q.s_res = (int*)(wb + o_sres); q.s_contrib = (float4*)(wb + o_scon);
+  q.Lsample = (float*)(wb + o_L); q.ctl = (int*)(wb + o_ctl);
+  const size_t ctl_bytes = 4 * 4 * (size_t)q.ctl_stride;
+
+  /* ---- per-pixel accumulators and the active list */
+  PixelAcc px;
+  {
+    size_t o_sum = 0, o_s1 = align_up(12 * npix), o_s2 = o_s1 + align_up(8 * npix), o_n = o_s2 + align_up(8 * npix), o_done = o_n + align_up(4 * npix),
+           total = o_done + align_up(npix);
+    CK(ctx->d_px.ensure(total));
+    char* pb = ctx->d_px.as<char>();
+    px.sum = (float*)(pb + o_sum); px.s1 = (double*)(pb + o_s1); px.s2 = (double*)(pb + o_s2); px.n = (int*)(pb + o_n); px.done = (uint8_t*)(pb + o_done);
+    CK(cudaMemsetAsync(pb, 0, total, st));
+  }
+  CK(ctx->d_act.ensure(2 * 4 * npix));
+  uint32_t* act[2] = {ctx->d_act.as<uint32_t>(), ctx->d_act.as<uint32_t>() + npix};
+  CK(ctx->d_cnt.ensure(sizeof(Counters)));
+  Counters* gcnt = ctx->d_cnt.as<Counters>();
+  CK(cudaMemsetAsync(gcnt, 0, sizeof(Counters), st));
+
+  ctx->events_used = 0;
+  cudaEvent_t ev_begin = next_event(ctx), ev_end = next_event(ctx);
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> trace_ev;
+  CK(cudaEventRecord(ev_begin, st));
+
+  KeepOwned own;
+  own.W = ctx->W; own.tile = ctx->tile; own.ntx = (ctx->W + ctx->tile - 1) / ctx->tile; own.rank = ctx->rank; own.world = ctx->world;
+  own.x0 = 0; own.y0 = 0; own.x1 = ctx->W; own.y1 = ctx->H;
+  if (ctx->cell_w > 0) {
+    own.x0 = std::max(ctx->cell_x, 0); own.y0 = std::max(ctx->cell_y, 0);
+    own.x1 = std::min(ctx->cell_x + ctx->cell_w, ctx->W); own.y1 = std::min(ctx->cell_y + ctx->cell_h, ctx->H);
+  }
+  uint32_t n_act = 0;
+  int rc = compact(ctx, own, nullptr, (uint32_t)npix, act[0], &n_act);
+  if (rc) return rc;
+
+  const int grid_trace = ctx->sm_count * 4, grid_small = ctx->sm_count * 8;
+  uint64_t launches = 3, trace_launches = 0;
+  int a = 0;
+  for (int base_sample = 0; base_sample < rk.ns_aa && n_act > 0;) {
+    const int nb = std::min(rk.batch, rk.ns_aa - base_sample);
+    for (size_t c0 = 0; c0 < n_act; c0 += pix_per_chunk) {
+      const int npx = (int)std::min(pix_per_chunk, (size_t)n_act - c0);
+      const uint32_t* chunk = act[a] + c0;
+      CK(cudaMemsetAsync(q.ctl, 0, ctl_bytes, st));
+      k_generate<<<grid_small, 256, 0, st>>>(ctx->cam, rk, q, chunk, npx, base_sample, nb);
+      launches++;
+      for (int it = 0; it < iters; ++it) {
+        const int cur = it & 1;
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, st)); }
+        if (count) k_trace_closest<true><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt);
+        else k_trace_closest<false><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt);
+        if (stats) { CK(cudaEventRecord(e1, st)); trace_ev.push_back({e0, e1}); }
+        k_shade<<<grid_small, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, rk, q, chunk, base_sample, nb, it);
+        launches += 2; trace_launches++;
+        if (rk.D >= 1 && rk.S > 0) {
+          if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, st)); }
+          int* scount = q.ctl + q.ctl_stride + it; int* scursor = q.ctl + 3 * q.ctl_stride + it;
+          if (rk.hemi) {
+            if (count) k_trace_shadow<false, true><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
+            else k_trace_shadow<false, false><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
+          } else {
+            if (count) k_trace_shadow<true, true><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
+            else k_trace_shadow<true, false><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
+          }
+          if (stats) { CK(cudaEventRecord(e1, st)); trace_ev.push_back({e0, e1}); }
+          k_accumulate<<<grid_small, 256, 0, st>>>(ctx->ds, rk, q, it);
+          launches += 2; trace_launches++;
+        }
+        if (it + 1 < iters && (it & 3) == 3) {  /* long depth budgets: stop once every path has died */
+          CK(cudaMemcpyAsync(ctx->h_pinned, q.ctl + it + 1, 4, cudaMemcpyDeviceToHost, st));
+          CK(cudaStreamSynchronize(st));
+          if (ctx->h_pinned[0] == 0) break;
+        }
+      }
+      k_resolve<<<grid_small, 256, 0, st>>>(rk, q, px, chunk, npx, nb);
+      launches++;
+    }
+    base_sample += nb;
+    if (base_sample < rk.ns_aa) {
+      KeepActive ka; ka.done = px.done;
+      uint32_t n_next = 0;
+      rc = compact(ctx, ka, act[a], n_act, act[a ^ 1], &n_next);
+      if (rc) return rc;
+      launches += 3;
+      a ^= 1; n_act = n_next;
+    }
+  }
+  k_finalize<<<grid_small, 256, 0, st>>>(px, npix, d_rgb, d_counts, d_rgbn, gcnt);
+  launches++;
+  CK(cudaEventRecord(ev_end, st));
+  CK(cudaStreamSynchronize(st));
+  CK(cudaGetLastError());
+  if (stats) {
+    memset(stats, 0, sizeof *stats);
+    float ms = 0; CK(cudaEventElapsedTime(&ms, ev_begin, ev_end));
+    stats->seconds = ms * 1e-3;
+    double tms = 0;
+    for (auto& pr : trace_ev) { float t = 0; CK(cudaEventElapsedTime(&t, pr.first, pr.second)); tms += t; }
+    stats->trace_seconds = tms * 1e-3;
+    Counters hc;
+    CK(cudaMemcpy(&hc, gcnt, sizeof hc, cudaMemcpyDeviceToHost));
+    stats->rays = hc.rays; stats->geodesic_steps = hc.steps; stats->node_visits = hc.nodes; stats->tri_tests = hc.tris; stats->sphere_tests = hc.sph;
+    stats->kernel_launches = launches; stats->trace_launches = trace_launches;
+    stats->algorithmic_bytes = 64 * hc.nodes + 80 * hc.tris + 32 * hc.sph + 160 * hc.rays;
+    stats->paths = hc.paths; /* sum of sample counts */
+  }
+  return RRT_OK;
+}
+
+extern "C" {
+
+int rrt_render(rrt_ctx* ctx, const rrt_params* p, float* hdr_rgb, int32_t* sample_counts, rrt_stats* stats) {
+  if (!ctx || !p) return RRT_E_ARG;
+  const size_t npix = (size_t)ctx->W * ctx->H;
+  CK(cudaSetDevice(ctx->device));
+  CK(ctx->d_out_rgb.ensure(12 * npix)); CK(ctx->d_out_cnt.ensure(4 * npix));
+  int rc = render_impl(ctx, p, ctx->d_out_rgb.as<float>(), ctx->d_out_cnt.as<int>(), nullptr, nullptr, stats);
+  if (rc) return rc;
+  if (hdr_rgb) CK(cudaMemcpy(hdr_rgb, ctx->d_out_rgb.p, 12 * npix, cudaMemcpyDeviceToHost));
+  if (sample_counts) CK(cudaMemcpy(sample_counts, ctx->d_out_cnt.p, 4 * npix, cudaMemcpyDeviceToHost));
+  return RRT_OK;
+}
+
+int rrt_render_device(rrt_ctx* ctx, const rrt_params* p, void* d_rgbn, void* d_counts, void* stream, rrt_stats* stats) {
+  if (!ctx || !p) return RRT_E_ARG;
+  if (stream) CK(cudaStreamSynchronize((cudaStream_t)stream));
+  return render_impl(ctx, p, nullptr, (int*)d_counts, (float4*)d_rgbn, (cudaStream_t)stream, stats);
+}
+
+/* ---------------------------------------------------------------- parity hooks */
+struct HookIO {  // stage host arrays on the device, fetch results back
+  rrt_ctx* ctx; size_t in_off = 0, out_off = 0;
+  std::vector<std::pair<size_t, std::pair<void*, size_t>>> outs;
+};
+
+static int hook_begin(rrt_ctx* ctx, size_t in_bytes, size_t out_bytes) {
+  CK(cudaSetDevice(ctx->device));
+  CK(ctx->d_hook_in.ensure(in_bytes + 4096)); CK(ctx->d_hook_out.ensure(out_bytes + 4096));
+  return RRT_OK;
+}
+static void* hook_in(rrt_ctx* ctx, size_t& off, const void* src, size_t bytes) {
+  if (!src) return nullptr;
+  char* dst = ctx->d_hook_in.as<char>() + off;
+  cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream);
+  off += align_up(bytes);
+  return dst;
+}
+static void* hook_out(rrt_ctx* ctx, size_t& off, size_t bytes) {
+  char* dst = ctx->d_hook_out.as<char>() + off;
+  off += align_up(bytes);
+  return dst;
+}
+static int grid_for(long long n, int block) { long long g = (n + block - 1) / block; return (int)std::max<long long>(1, std::min<long long>(g, 65535)); }
+
+int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, const double* min_t, const double* max_t, int any_hit, rrt_hit* out,
+                   rrt_stats* stats) {
+  if (!ctx || n < 0 || (n && (!o || !d || !out))) return RRT_E_ARG;
+  if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_trace_rays: no scene");
+  if (stats) memset(stats, 0, sizeof *stats);
+  if (n == 0) return RRT_OK;
+  int rc = hook_begin(ctx, 64 * (size_t)n + 4096, sizeof(rrt_hit) * (size_t)n + 256);
+  if (rc) return rc;
+  size_t io = 0, oo = 0;
+  double* d_o = (double*)hook_in(ctx, io, o, 24 * (size_t)n); double* d_d = (double*)hook_in(ctx, io, d, 24 * (size_t)n);
+  double* d_mn = (double*)hook_in(ctx, io, min_t, 8 * (size_t)n); double* d_mx = (double*)hook_in(ctx, io, max_t, 8 * (size_t)n);
+  rrt_hit* d_out = (rrt_hit*)hook_out(ctx, oo, sizeof(rrt_hit) * (size_t)n);
+  Counters* gc = (Counters*)hook_out(ctx, oo, sizeof(Counters));
+  CK(cudaMemsetAsync(gc, 0, sizeof(Counters), ctx->stream));
+  cudaEvent_t e0, e1; ctx->events_used = 0; e0 = next_event(ctx); e1 = next_event(ctx);
+  CK(cudaEventRecord(e0, ctx->stream));
+  int grid = grid_for(n, RRT_BLOCK);
+  if (any_hit) k_hook_trace<true><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, n, d_o, d_d, d_mn, d_mx, d_out, gc);
+  else k_hook_trace<false><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, n, d_o, d_d, d_mn, d_mx, d_out, gc);
+  CK(cudaEventRecord(e1, ctx->stream));
+  CK(cudaMemcpyAsync(out, d_out, sizeof(rrt_hit) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
+  if (stats) {
+    Counters hc; CK(cudaMemcpy(&hc, gc, sizeof hc, cudaMemcpyDeviceToHost));
+    float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+    stats->seconds = stats->trace_seconds = ms * 1e-3;
+    stats->rays = hc.rays; stats->geodesic_steps = hc.steps; stats->node_visits = hc.nodes; stats->tri_tests = hc.tris; stats->sphere_tests = hc.sph;
+    stats->kernel_launches = stats->trace_launches = 1;
+    stats->algorithmic_bytes = 64 * hc.nodes + 80 * hc.tris + 32 * hc.sph + 160 * hc.rays;
+  }
+  return RRT_OK;
+}
+
+int rrt_geodesic(rrt_ctx* ctx, int64_t n, const double* o, const double* d, int nsteps, double* seg_out) {
+  if (!ctx || n < 0 || nsteps < 0 || (n && (!o || !d || !seg_out))) return RRT_E_ARG;
+  if (n == 0 || nsteps == 0) return RRT_OK;
+  size_t ob = 64 * (size_t)n * nsteps;
+  int rc = hook_begin(ctx, 48 * (size_t)n + 1024, ob);
+  if (rc) return rc;
+  size_t io = 0, oo = 0;
+  double* d_o = (double*)hook_in(ctx, io, o, 24 * (size_t)n); double* d_d = (double*)hook_in(ctx, io, d, 24 * (size_t)n);
+  double* d_s = (double*)hook_out(ctx, oo, ob);
+  k_hook_geodesic<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->bh, n, d_o, d_d, nsteps, d_s);
+  CK(cudaMemcpyAsync(seg_out, d_s, ob, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
+  return RRT_OK;
+}
+
+int rrt_generate_rays(rrt_ctx* ctx, int64_t n, const double* xy, double* o, double* d) {
+  if (!ctx || n < 0 || (n && (!xy || !o || !d))) return RRT_E_ARG;
+  if (!ctx->have_cam) FAIL(RRT_E_STATE, "rrt_generate_rays: no camera");
+  if (n == 0) return RRT_OK;
+  int rc = hook_begin(ctx, 16 * (size_t)n, 48 * (size_t)n + 1024);
+  if (rc) return rc;
+  size_t io = 0, oo = 0;
+  double* d_xy = (double*)hook_in(ctx, io, xy, 16 * (size_t)n);
+  double* d_o = (double*)hook_out(ctx, oo, 24 * (size_t)n); double* d_d = (double*)hook_out(ctx, oo, 24 * (size_t)n);
+  k_hook_camera<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->cam, n, d_xy, d_o, d_d);
+  CK(cudaMemcpyAsync(o, d_o, 24 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(d, d_d, 24 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
+  return RRT_OK;
+}
+
+static int bsdf_hook(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const double* wi_in, const double* u, float* f, double* wi, float* pdf) {
+  if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_bsdf: no scene");
+  if (mat < 0 || mat >= ctx->ds.n_mats) FAIL(RRT_E_ARG, "rrt_bsdf: material index out of range");
+  if (n == 0) return RRT_OK;
+  int rc = hook_begin(ctx, 80 * (size_t)n + 2048, 40 * (size_t)n + 2048);
+  if (rc) return rc;
+  size_t io = 0, oo = 0;
+  double* d_wo = (double*)hook_in(ctx, io, wo, 24 * (size_t)n); double* d_wi_in = (double*)hook_in(ctx, io, wi_in, 24 * (size_t)n);
+  double* d_u = (double*)hook_in(ctx, io, u, 32 * (size_t)n);
+  float* d_f = (float*)hook_out(ctx, oo, 12 * (size_t)n); double* d_wi = (double*)hook_out(ctx, oo, 24 * (size_t)n); float* d_pdf = (float*)hook_out(ctx, oo, 4 * (size_t)n);
+  k_hook_bsdf<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->ds.mats, mat, n, d_wo, d_wi_in, d_u, d_f, d_wi, d_pdf);
+  CK(cudaMemcpyAsync(f, d_f, 12 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (wi) CK(cudaMemcpyAsync(wi, d_wi, 24 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (pdf) CK(cudaMemcpyAsync(pdf, d_pdf, 4 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
+  return RRT_OK;
+}
+
+int rrt_bsdf_sample(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const double* u, float* f, double* wi, float* pdf) {
+  if (!ctx || n < 0 || (n && (!wo || !u || !f || !wi || !pdf))) return RRT_E_ARG;
+  return bsdf_hook(ctx, mat, n, wo, nullptr, u, f, wi, pdf);
+}
+
+int rrt_bsdf_eval(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const double* wi, float* f) {
+  if (!ctx || n < 0 || (n && (!wo || !wi || !f))) return RRT_E_ARG;
+  return bsdf_hook(ctx, mat, n, wo, wi, nullptr, f, nullptr, nullptr);
+}
+
+int rrt_light_sample(rrt_ctx* ctx, int light, int64_t n, const double* p, const double* u, float* radiance, double* wi, float* dist, float* pdf) {
+  if (!ctx || n < 0 || (n && (!p || !u || !radiance || !wi || !dist || !pdf))) return RRT_E_ARG;
+  if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_light_sample: no scene");
+  if (light < 0 || light >= ctx->ds.n_lights) FAIL(RRT_E_ARG, "rrt_light_sample: light index out of range");
+  if (n == 0) return RRT_OK;
+  int rc = hook_begin(ctx, 40 * (size_t)n + 1024, 44 * (size_t)n + 2048);
+  if (rc) return rc;
+  size_t io = 0, oo = 0;
+  double* d_p = (double*)hook_in(ctx, io, p, 24 * (size_t)n); double* d_u = (double*)hook_in(ctx, io, u, 16 * (size_t)n);
+  float* d_rad = (float*)hook_out(ctx, oo, 12 * (size_t)n); double* d_wi = (double*)hook_out(ctx, oo, 24 * (size_t)n);
+  float* d_dist = (float*)hook_out(ctx, oo, 4 * (size_t)n); float* d_pdf = (float*)hook_out(ctx, oo, 4 * (size_t)n);
+  k_hook_light<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->ds.lights, light, n, d_p, d_u, d_rad, d_wi, d_dist, d_pdf);
+  CK(cudaMemcpyAsync(radiance, d_rad, 12 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(wi, d_wi, 24 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(dist, d_dist, 4 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(pdf, d_pdf, 4 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
+  return RRT_OK;
+}
+
+int rrt_philox(rrt_ctx* ctx, uint64_t seed, int64_t n, const uint32_t* counters, uint32_t* out) {
+  if (!ctx || n < 0 || (n && (!counters || !out))) return RRT_E_ARG;
+  if (n == 0) return RRT_OK;
+  int rc = hook_begin(ctx, 16 * (size_t)n, 16 * (size_t)n);
+  if (rc) return rc;
+  size_t io = 0, oo = 0;
+  uint32_t* d_c = (uint32_t*)hook_in(ctx, io, counters, 16 * (size_t)n);
+  uint32_t* d_o = (uint32_t*)hook_out(ctx, oo, 16 * (size_t)n);
+  k_hook_philox<<<grid_for(n, 128), 128, 0, ctx->stream>>>(seed, n, d_c, d_o);
+  CK(cudaMemcpyAsync(out, d_o, 16 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
+  return RRT_OK;
+}
+
+int rrt_tonemap(rrt_ctx* ctx, int64_t n, const float* hdr_rgb, uint32_t* rgba) {
+  if (!ctx || n < 0 || (n && (!hdr_rgb || !rgba))) return RRT_E_ARG;
+  if (n == 0) return RRT_OK;
+  int rc = hook_begin(ctx, 12 * (size_t)n, 4 * (size_t)n);
+  if (rc) return rc;
+  size_t io = 0, oo = 0;
+  float* d_h = (float*)hook_in(ctx, io, hdr_rgb, 12 * (size_t)n);
+  uint32_t* d_o = (uint32_t*)hook_out(ctx, oo, 4 * (size_t)n);
+  k_tonemap<<<grid_for(n, 256), 256, 0, ctx->stream>>>(n, d_h, d_o);
+  CK(cudaMemcpyAsync(rgba, d_o, 4 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
+  return RRT_OK;
+}
+
+}  // extern "C"

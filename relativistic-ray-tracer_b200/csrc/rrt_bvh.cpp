@@ -1,0 +1,226 @@
+// rrt_bvh.cpp — see rrt_bvh.h.  Host code, runs once per rrt_upload_scene.
+#include "rrt_bvh.h"
+
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+
+namespace rrt {
+namespace {
+
+struct Box { double lo[3], hi[3]; };
+struct TNode { Box bb; int l, r, start, count; };
+struct Tree { std::vector<TNode> nodes; std::vector<uint32_t> order; int leaves = 0, depth = 0; };
+
+inline void box_reset(Box& b) { for (int k = 0; k < 3; ++k) { b.lo[k] = INFINITY; b.hi[k] = -INFINITY; } }
+inline void box_expand(Box& b, const Box& o) {
+  for (int k = 0; k < 3; ++k) { b.lo[k] = fmin(b.lo[k], o.lo[k]); b.hi[k] = fmax(b.hi[k], o.hi[k]); }
+}
+inline double box_area(const Box& b) {
+  double x = b.hi[0] - b.lo[0], y = b.hi[1] - b.lo[1], z = b.hi[2] - b.lo[2];
+  if (!(x >= 0 && y >= 0 && z >= 0)) return 0.0;
+  return 2.0 * (x * y + y * z + z * x);
+}
+
+struct Builder {
+  const rrt_scene* s;
+  std::vector<Box> pbox;        // Primitive::get_bbox (reference src/static_scene/triangle.cpp:11-19, sphere.h:30-32)
+  std::vector<double> pcen;     // 3 per prim: BBox::centroid() = (min + max) / 2, i.e. 0.5 * (min + max)  (src/bbox.h:98-100)
+  std::vector<uint32_t> tmp;
+
+  void prepare() {
+    uint32_t n = s->n_prims;
+    pbox.resize(n); pcen.resize(3 * (size_t)n); tmp.resize(n);
+    for (uint32_t p = 0; p < n; ++p) {
+      Box b;
+      if (s->prim_kind[p] == 0) {
+        const double* q = s->tri_pos + 9 * (size_t)s->prim_index[p];
+        for (int k = 0; k < 3; ++k) b.lo[k] = b.hi[k] = q[k];
+        for (int v = 1; v < 3; ++v)
+          for (int k = 0; k < 3; ++k) { b.lo[k] = fmin(b.lo[k], q[3 * v + k]); b.hi[k] = fmax(b.hi[k], q[3 * v + k]); }
+      } else {
+        const double* c = s->sph + 4 * (size_t)s->prim_index[p];
+        for (int k = 0; k < 3; ++k) { b.lo[k] = c[k] - c[3]; b.hi[k] = c[k] + c[3]; }
+      }
+      pbox[p] = b;
+      const double half = 1.0 / 2;
+      for (int k = 0; k < 3; ++k) pcen[3 * (size_t)p + k] = half * (b.lo[k] + b.hi[k]);
+    }
+  }
+
+  Box bounds(const uint32_t* prims, uint32_t n) const {
+    Box b; box_reset(b);
+    for (uint32_t i = 0; i < n; ++i) box_expand(b, pbox[prims[i]]);
+    return b;
+  }
+
+  // construct_bvh (reference src/bvh.cpp:49-96).  prims[0..n) is reordered in place (stable partition, as the
+  // reference's push_back into left/right vectors is).
+  int build_ref(Tree& t, uint32_t* prims, uint32_t n, uint32_t base, int depth) {
+    int me = (int)t.nodes.size();
+    t.nodes.push_back(TNode());
+    Box bb = bounds(prims, n);
+    t.nodes[me].bb = bb; t.nodes[me].l = t.nodes[me].r = -1; t.nodes[me].start = t.nodes[me].count = 0;
+    if (depth > t.depth) t.depth = depth;
+    if (n <= 4) {
+      t.nodes[me].start = (int)base; t.nodes[me].count = (int)n; t.leaves++;
+      return me;
+    }
+    double ex = bb.hi[0] - bb.lo[0], ey = bb.hi[1] - bb.lo[1], ez = bb.hi[2] - bb.lo[2];
+    int axis = (ex > ey && ex > ez) ? 0 : (ey > ex && ey > ez) ? 1 : 2;
+    const double half = 1.0 / 2;
+    double mid = half * (bb.lo[axis] + bb.hi[axis]);
+    uint32_t nl = 0, nr = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+      if (pcen[3 * (size_t)prims[i] + axis] < mid) prims[nl++] = prims[i];   // nl <= i: safe in place
+      else tmp[nr++] = prims[i];
+    }
+    if (nl == 0 || nr == 0) {
+      // both vectors are rebuilt from the ORIGINAL order: first half left, rest right; the in-place pass above kept
+      // the original order in whichever side received everything
+      if (nl == 0) memcpy(prims, tmp.data(), sizeof(uint32_t) * n);
+      nl = n / 2; nr = n - nl;
+    } else {
+      memcpy(prims + nl, tmp.data(), sizeof(uint32_t) * nr);
+    }
+    int l = build_ref(t, prims, nl, base, depth + 1);
+    int r = build_ref(t, prims + nl, nr, base + nl, depth + 1);
+    t.nodes[me].l = l; t.nodes[me].r = r;
+    return me;
+  }
+
+  // binned SAH (16 bins per axis); leaves of <= 4 primitives like the reference
+  int build_sah(Tree& t, uint32_t* prims, uint32_t n, uint32_t base, int depth) {
+    int me = (int)t.nodes.size();
+    t.nodes.push_back(TNode());
+    Box bb = bounds(prims, n);
+    t.nodes[me].bb = bb; t.nodes[me].l = t.nodes[me].r = -1; t.nodes[me].start = t.nodes[me].count = 0;
+    if (depth > t.depth) t.depth = depth;
+    if (n <= 4) {
+      t.nodes[me].start = (int)base; t.nodes[me].count = (int)n; t.leaves++;
+      return me;
+    }
+    const int NB = 16;
+    double clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (uint32_t i = 0; i < n; ++i)
+      for (int k = 0; k < 3; ++k) { double c = pcen[3 * (size_t)prims[i] + k]; clo[k] = fmin(clo[k], c); chi[k] = fmax(chi[k], c); }
+    double best = INFINITY; int best_axis = -1, best_bin = -1;
+    for (int axis = 0; axis < 3; ++axis) {
+      double w = chi[axis] - clo[axis];
+      if (!(w > 0)) continue;
+      Box bbx[NB]; uint32_t cnt[NB];
+      for (int b = 0; b < NB; ++b) { box_reset(bbx[b]); cnt[b] = 0; }
+      double scale = NB / w;
+      for (uint32_t i = 0; i < n; ++i) {
+        int b = (int)((pcen[3 * (size_t)prims[i] + axis] - clo[axis]) * scale);
+        if (b >= NB) b = NB - 1; if (b < 0) b = 0;
+        box_expand(bbx[b], pbox[prims[i]]); cnt[b]++;
+      }
+      double ra[NB]; uint32_t rc[NB]; Box acc; box_reset(acc); uint32_t c = 0;
+      for (int b = NB - 1; b > 0; --b) { box_expand(acc, bbx[b]); c += cnt[b]; ra[b] = box_area(acc); rc[b] = c; }
+      box_reset(acc); c = 0;
+      for (int b = 0; b < NB - 1; ++b) {
+        box_expand(acc, bbx[b]); c += cnt[b];
+        if (c == 0 || rc[b + 1] == 0) continue;
+        double cost = box_area(acc) * c + ra[b + 1] * rc[b + 1];
+        if (cost < best) { best = cost; best_axis = axis; best_bin = b; }
+      }
+    }
+    uint32_t nl = 0, nr = 0;
+    if (best_axis >= 0) {
+      double w = chi[best_axis] - clo[best_axis], scale = NB / w;
+      for (uint32_t i = 0; i < n; ++i) {
+        int b = (int)((pcen[3 * (size_t)prims[i] + best_axis] - clo[best_axis]) * scale);
+        if (b >= NB) b = NB - 1; if (b < 0) b = 0;
+        if (b <= best_bin) prims[nl++] = prims[i]; else tmp[nr++] = prims[i];
+      }
+      memcpy(prims + nl, tmp.data(), sizeof(uint32_t) * nr);
+    }
+    if (nl == 0 || nr == 0) { nl = n / 2; nr = n - nl; }
+    int l = build_sah(t, prims, nl, base, depth + 1);
+    int r = build_sah(t, prims + nl, nr, base + nl, depth + 1);
+    t.nodes[me].l = l; t.nodes[me].r = r;
+    return me;
+  }
+};
+
+inline float round_down(double x) { float f = (float)x; if ((double)f > x) f = nextafterf(f, -INFINITY); return f; }
+inline float round_up(double x) { float f = (float)x; if ((double)f < x) f = nextafterf(f, INFINITY); return f; }
+
+inline int32_t as_i32(float f) { int32_t i; memcpy(&i, &f, 4); return i; }
+inline float as_f32(int32_t i) { float f; memcpy(&f, &i, 4); return f; }
+
+}  // namespace
+
+int build_bvh(const rrt_scene* s, int topology, FlatBvh* out) {
+  *out = FlatBvh();
+  uint32_t n = s->n_prims;
+  out->dfs_rank.assign(n, 0);
+  out->prim_mat.resize(n);
+  for (uint32_t p = 0; p < n; ++p) out->prim_mat[p] = s->prim_kind[p] == 0 ? s->tri_mat[s->prim_index[p]] : s->sph_mat[s->prim_index[p]];
+  if (n == 0) { out->root = -1; /* ~(-1) = 0: an empty leaf */ return 0; }
+  Builder b; b.s = s; b.prepare();
+
+  Tree ref; ref.order.resize(n);
+  for (uint32_t i = 0; i < n; ++i) ref.order[i] = i;
+  ref.nodes.reserve(n);
+  b.build_ref(ref, ref.order.data(), n, 0, 0);
+  for (uint32_t i = 0; i < n; ++i) out->dfs_rank[ref.order[i]] = i;
+  out->ref_nodes = (int)ref.nodes.size(); out->ref_leaves = ref.leaves; out->ref_depth = ref.depth;
+
+  Tree own;
+  const Tree* t = &ref;
+  if (topology == 1) {
+    own.order.resize(n);
+    for (uint32_t i = 0; i < n; ++i) own.order[i] = i;
+    own.nodes.reserve(n);
+    b.build_sah(own, own.order.data(), n, 0, 0);
+    t = &own;
+  }
+
+  // leaf records in the tree's leaf order
+  out->leaf.assign(10 * (size_t)n, 0.0);
+  for (uint32_t i = 0; i < n; ++i) {
+    uint32_t p = t->order[i];
+    double* r = &out->leaf[10 * (size_t)i];
+    uint32_t kind = s->prim_kind[p];
+    if (kind == 0) {
+      const double* q = s->tri_pos + 9 * (size_t)s->prim_index[p];
+      for (int k = 0; k < 3; ++k) { r[k] = q[k]; r[3 + k] = q[3 + k] - q[k]; r[6 + k] = q[6 + k] - q[k]; }
+    } else {
+      const double* c = s->sph + 4 * (size_t)s->prim_index[p];
+      r[0] = c[0]; r[1] = c[1]; r[2] = c[2]; r[3] = c[3] * c[3]; /* Sphere::r2 = r * r (reference src/static_scene/sphere.h:27) */
+    }
+    uint32_t w[2] = {p, (out->dfs_rank[p] << 1) | kind};
+    memcpy(&r[9], w, 8);
+  }
+
+  // flatten: interior nodes in depth-first preorder
+  auto child_code = [&](int ni, std::vector<int>& remap) -> int32_t {
+    const TNode& c = t->nodes[ni];
+    if (c.l < 0) return ~(int32_t)(((uint32_t)c.start << 3) | (uint32_t)c.count);
+    return remap[ni];
+  };
+  std::vector<int> remap(t->nodes.size(), -1);
+  int ninner = 0;
+  for (size_t i = 0; i < t->nodes.size(); ++i) if (t->nodes[i].l >= 0) remap[i] = ninner++;  // vector order IS preorder
+  out->n_nodes = ninner;
+  out->nodes.assign(16 * (size_t)(ninner > 0 ? ninner : 1), 0.f);
+  for (size_t i = 0; i < t->nodes.size(); ++i) {
+    const TNode& nd = t->nodes[i];
+    if (nd.l < 0) continue;
+    float* q = &out->nodes[16 * (size_t)remap[i]];
+    const Box& L = t->nodes[nd.l].bb; const Box& R = t->nodes[nd.r].bb;
+    q[0] = round_down(L.lo[0]); q[1] = round_down(L.lo[1]); q[2] = round_down(L.lo[2]); q[3] = round_up(L.hi[0]);
+    q[4] = round_up(L.hi[1]); q[5] = round_up(L.hi[2]); q[6] = round_down(R.lo[0]); q[7] = round_down(R.lo[1]);
+    q[8] = round_down(R.lo[2]); q[9] = round_up(R.hi[0]); q[10] = round_up(R.hi[1]); q[11] = round_up(R.hi[2]);
+    q[12] = as_f32(child_code(nd.l, remap)); q[13] = as_f32(child_code(nd.r, remap)); q[14] = 0.f; q[15] = 0.f;
+  }
+  out->root = child_code(0, remap);
+  for (int k = 0; k < 3; ++k) { out->root_lo[k] = t->nodes[0].bb.lo[k]; out->root_hi[k] = t->nodes[0].bb.hi[k]; }
+  (void)as_i32;
+  return 0;
+}
+
+}  // namespace rrt

@@ -1,0 +1,39 @@
+// rrt_bvh.h — host-side BVH construction and flattening for the device traversal.
+//
+// Replaces BVHAccel::BVHAccel / construct_bvh (reference src/bvh.cpp:14-19,49-96) and the heap-allocated
+// BVHNode tree (reference src/bvh.h:24-41).  Two things come out of the build:
+//   1. the reference's own tree shape (midpoint split on the strictly largest axis, leaves of <= 4 primitives,
+//      index halving when a side is empty) — needed because the reference keeps the LAST primitive in its
+//      depth-first order among equal-t hits (src/static_scene/triangle.cpp:43-45, src/bvh.cpp:120-135), so every
+//      primitive carries its depth-first rank and the device breaks ties toward the higher rank;
+//   2. the flattened arrays the kernels read: 64-byte interior nodes holding BOTH children's boxes (outward
+//      rounded floats) and 80-byte leaf records holding the reference's doubles.
+#pragma once
+#include <stdint.h>
+#include <vector>
+#include "../../include/rrt_b200.h"
+
+namespace rrt {
+
+// 64-byte node = 4 x float4:
+//   q0 = (L.min.x, L.min.y, L.min.z, L.max.x)   q1 = (L.max.y, L.max.z, R.min.x, R.min.y)
+//   q2 = (R.min.z, R.max.x, R.max.y, R.max.z)   q3 = (left, right, 0, 0) as int32
+// child >= 0: interior node index; child < 0: leaf, ~child = (first record << 3) | record count.
+// 80-byte leaf record = 9 doubles + 2 x uint32:
+//   triangle: p0, e1 = p1 - p0, e2 = p2 - p0     sphere: centre, r*r, 0...
+//   word0 = primitive index in reference order; word1 = (depth-first rank << 1) | kind (0 triangle, 1 sphere)
+struct FlatBvh {
+  std::vector<float> nodes;       // 16 floats per node
+  std::vector<double> leaf;       // 10 doubles per record
+  std::vector<uint32_t> dfs_rank; // [n_prims]
+  std::vector<int32_t> prim_mat;  // [n_prims] material of each primitive
+  int32_t root = -1;              // child code of the root (0 if interior, leaf code if the whole scene is one leaf)
+  double root_lo[3] = {0, 0, 0}, root_hi[3] = {0, 0, 0};
+  int n_nodes = 0;                // interior nodes in the flattened array
+  int ref_nodes = 0, ref_leaves = 0, ref_depth = 0; // shape of the reference tree (nodes incl. leaves)
+};
+
+// topology: 0 = reference shape (midpoint split), 1 = binned SAH (own shape; ranks still come from the reference shape)
+int build_bvh(const rrt_scene* s, int topology, FlatBvh* out);
+
+}  // namespace rrt

@@ -1,0 +1,589 @@
+// rrt_kernels.cuh — the wavefront kernels: generate, trace (geodesic-advance + intersect), shade / BSDF-sample,
+// accumulate, resolve, plus the stable compaction used for the active-pixel list.
+//
+// Queues are SoA arrays of capacity `cap` (the stride between components).  A path is identified by its
+// SLOT = pixel_in_chunk * samples_this_round + sample_in_round, which never changes; queue POSITIONS change
+// every bounce because the shade kernel compacts survivors with warp ballot + one atomic per warp.
+#pragma once
+#include "rrt_trace.cuh"
+#include "rrt_shade.cuh"
+
+#define RRT_BLOCK 128
+
+struct RenderK {      // per-render constants (reference PathTracer members, src/pathtracer.cpp:32-85)
+  int W, H;
+  int ns_aa, D, ns_area_light, batch;
+  float tol;
+  int hemi, thin_lens;
+  unsigned long long seed;
+  int S;              // light samples taken per shaded vertex (slots in the contribution table)
+  int total;          // divisor of the direct estimate (reference src/part1_code.cpp:17,56)
+  int cap;            // queue capacity = SoA stride
+};
+
+struct Queues {
+  double* ray[2];       // 8 x cap: o.xyz d.xyz tmin tmax          (extension rays, ping-pong)
+  uint32_t* slot[2];    // path slot
+  uint32_t* rngn[2];    // draws consumed so far
+  uint32_t* flags[2];   // bit0: previous vertex was a delta BSDF
+  float* beta[2];       // 3 x cap: throughput
+  int* h_prim;          // closest-hit result per queue position: prim >= 0, -1 miss, -2 captured
+  double* h_geo;        // 9 x cap: hit_p, w_out, n
+  float* dbeta;         // 3 x cap: throughput at the vertex whose direct light is pending
+  uint8_t* vflag;       // bit0: vertex took light samples
+  double* sray;         // 7 x capS: shadow rays o d tmax
+  uint32_t* s_cidx;     // contribution-table index of each shadow ray
+  int* s_res;           // capS: -2 no ray, -1 unoccluded, >= 0 prim hit
+  float4* s_contrib;    // capS: contribution (rgb), w = cos term (hemisphere mode)
+  float* Lsample;       // 3 x cap: radiance of each path slot
+  int* ctl;             // [4][D+2]: queue counts, shadow counts, trace cursors, shadow cursors
+  int ctl_stride;
+};
+
+struct PixelAcc {      // per-pixel state across adaptive rounds (reference src/part1_code.cpp:125-163)
+  float* sum;          // 3 x npix
+  double* s1; double* s2;
+  int* n;              // samples taken
+  uint8_t* done;       // adaptive stop reached
+};
+
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+
+/* warp-aggregated append from possibly divergent code: one atomic per converged group */
+__device__ __forceinline__ int append_pos(int* counter) {
+  unsigned m = __activemask();
+  int leader = __ffs(m) - 1;
+  int rank = __popc(m & ((1u << lane_id()) - 1u));
+  int base = 0;
+  if (lane_id() == leader) base = atomicAdd(counter, __popc(m));
+  base = __shfl_sync(m, base, leader);
+  return base + rank;
+}
+
+__device__ __forceinline__ void flush_counters(const Counters& c, Counters* g) {
+  unsigned long long v[5] = {c.rays, c.steps, c.nodes, c.tris, c.sph};
+  unsigned long long* dst = (unsigned long long*)g;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    unsigned long long x = v[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane_id() == 0 && x) atomicAdd(dst + k, x);
+  }
+}
+
+/* ---------------------------------------------------------------- BVHAccel::intersect for one ray */
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ void trace_ray(const DevScene& sc, const DevHole& bh, d3 o, d3 d, double tmin, double tmax, bool want_geo,
+                                          Hit& hit, int* stack, Counters& cnt) {
+  hit.status = 0; hit.prim = -1; hit.chord = 0; hit.steps = 0; hit.t = 0.0;
+  if (COUNT) cnt.rays++;
+  Seg s; Best best;
+  bool found = false;
+  if (bh.mode == RRT_MODE_FLAT) {
+    s.o = o; s.d = d; s.tmin = tmin; s.tmax = tmax;
+    hit.steps = 1;
+    if (COUNT) cnt.steps++;
+    found = traverse<ANY, COUNT>(sc, s, best, stack, RRT_BLOCK, cnt);
+  } else {
+    double len = 0.0;
+    int j = 0;
+    for (; j < bh.nchords; ++j) {
+      next_micro_ray(bh, o, d, len);
+      if (COUNT) cnt.steps++;
+      if (horizon_hit(bh, o, d, len)) { hit.status = 2; hit.chord = j; hit.steps = j + 1; return; }
+      s.o = o; s.d = d; s.tmin = 0.0; s.tmax = len;
+      if (traverse<ANY, COUNT>(sc, s, best, stack, RRT_BLOCK, cnt)) { found = true; break; }
+    }
+    hit.chord = found ? j : j - 1; hit.steps = found ? j + 1 : j;
+  }
+  if (!found) return;
+  hit.status = 1; hit.prim = best.prim; hit.t = best.t;
+  if (!want_geo) return;
+  hit.p = vadd(s.o, vmul(s.d, best.t));
+  hit.w_out = vneg(s.d);
+  uint32_t idx = sc.prim_index[best.prim];
+  if (best.kind == 0) {
+    const double* N = sc.tri_nrm + 9 * (size_t)idx;
+    double b0 = 1 - best.b1 - best.b2;
+    hit.n = vadd(vadd(smul(b0, D3(N[0], N[1], N[2])), smul(best.b1, D3(N[3], N[4], N[5]))), smul(best.b2, D3(N[6], N[7], N[8])));
+  } else {
+    const double* c = sc.sph + 4 * (size_t)idx;
+    hit.n = vunit(vsub(vadd(s.o, vmul(s.d, best.t)), D3(c[0], c[1], c[2])));
+  }
+}
+
+/* ---------------------------------------------------------------- generate: Camera::generate_ray per path slot
+ * (reference src/part1_code.cpp:125-145,182-187) */
+__global__ void __launch_bounds__(256) k_generate(const __grid_constant__ DevCamera cam, const __grid_constant__ RenderK rk,
+                                                  const __grid_constant__ Queues q, const uint32_t* __restrict__ act, int npix, int base_sample, int nb) {
+  int npaths = npix * nb;
+  for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < npaths; slot += gridDim.x * blockDim.x) {
+    uint32_t pixel = act[slot / nb];
+    uint32_t sample = (uint32_t)(base_sample + slot % nb);
+    int x = (int)(pixel % (uint32_t)rk.W), y = (int)(pixel / (uint32_t)rk.W);
+    Rng g = rng_make(rk.seed, pixel, sample, 0);
+    double sx = x, sy = y;
+    if (rk.ns_aa == 1) { sx += 0.5; sy += 0.5; }
+    else { double jx, jy; rng_grid2(g, jx, jy); sx += jx; sy += jy; }
+    d3 o, d;
+    if (rk.thin_lens) {
+      double lx, ly; rng_grid2(g, lx, ly);
+      generate_ray_thin_lens(cam, sx / rk.W, sy / rk.H, lx, ly * 2 * RRT_PI, o, d);
+    } else generate_ray(cam, sx / rk.W, sy / rk.H, o, d);
+    double* r = q.ray[0];
+    size_t c = (size_t)rk.cap;
+    r[slot] = o.x; r[c + slot] = o.y; r[2 * c + slot] = o.z; r[3 * c + slot] = d.x; r[4 * c + slot] = d.y; r[5 * c + slot] = d.z;
+    r[6 * c + slot] = cam.nClip; r[7 * c + slot] = cam.fClip;
+    q.slot[0][slot] = (uint32_t)slot; q.rngn[0][slot] = g.n; q.flags[0][slot] = 0;
+    q.beta[0][slot] = 1.f; q.beta[0][c + slot] = 1.f; q.beta[0][2 * c + slot] = 1.f;
+    q.Lsample[slot] = 0.f; q.Lsample[c + slot] = 0.f; q.Lsample[2 * c + slot] = 0.f;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) q.ctl[0] = npaths;
+}
+
+/* ---------------------------------------------------------------- trace: closest hit for the extension queue.
+ * Persistent warps pull 32 rays at a time from a device-side cursor. */
+template <bool COUNT>
+__global__ void __launch_bounds__(RRT_BLOCK, 4) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+                                                                const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
+                                                                int* cursor, int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt) {
+  __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
+  int* stack = stack_mem + threadIdx.x;
+  Counters cnt = {0, 0, 0, 0, 0, 0};
+  const int n = *count_ptr;
+  while (true) {
+    int base = 0;
+    if (lane_id() == 0) base = atomicAdd(cursor, 32);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) break;
+    int i = base + lane_id();
+    if (i < n) {
+      d3 o = D3(ray[i], ray[cap + i], ray[2 * cap + i]), d = D3(ray[3 * cap + i], ray[4 * cap + i], ray[5 * cap + i]);
+      Hit h;
+      trace_ray<false, COUNT>(sc, bh, o, d, ray[6 * cap + i], ray[7 * cap + i], true, h, stack, cnt);
+      h_prim[i] = h.status == 1 ? h.prim : (h.status == 2 ? -2 : -1);
+      if (h.status == 1) {
+        h_geo[i] = h.p.x; h_geo[cap + i] = h.p.y; h_geo[2 * cap + i] = h.p.z;
+        h_geo[3 * cap + i] = h.w_out.x; h_geo[4 * cap + i] = h.w_out.y; h_geo[5 * cap + i] = h.w_out.z;
+        h_geo[6 * cap + i] = h.n.x; h_geo[7 * cap + i] = h.n.y; h_geo[8 * cap + i] = h.n.z;
+      }
+    }
+    __syncwarp();
+  }
+  if (COUNT) flush_counters(cnt, gcnt);
+}
+
+/* shadow rays: BVHAccel::intersect(ray) (any hit), or closest hit when the hemisphere estimator needs the emitter */
+template <bool ANY, bool COUNT>
+__global__ void __launch_bounds__(RRT_BLOCK, 4) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+                                                               const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
+                                                               int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt) {
+  __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
+  int* stack = stack_mem + threadIdx.x;
+  Counters cnt = {0, 0, 0, 0, 0, 0};
+  const int n = *count_ptr;
+  while (true) {
+    int base = 0;
+    if (lane_id() == 0) base = atomicAdd(cursor, 32);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) break;
+    int i = base + lane_id();
+    if (i < n) {
+      d3 o = D3(ray[i], ray[cap + i], ray[2 * cap + i]), d = D3(ray[3 * cap + i], ray[4 * cap + i], ray[5 * cap + i]);
+      Hit h;
+      trace_ray<ANY, COUNT>(sc, bh, o, d, 0.0, ray[6 * cap + i], false, h, stack, cnt);
+      res[cidx[i]] = h.status == 1 ? h.prim : -1;
+    }
+    __syncwarp();
+  }
+  if (COUNT) flush_counters(cnt, gcnt);
+}
+
+/* ---------------------------------------------------------------- shade: est_radiance_global_illumination /
+ * at_least_one_bounce_radiance / estimate_direct_lighting_* unrolled over the wavefront
+ * (reference src/part1_code.cpp:15-123).  `it` = vertex index along the path (0 = camera hit); the reference's
+ * recursion depth at this vertex is D - it. */
+__global__ void __launch_bounds__(RRT_BLOCK) k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+                                                     const __grid_constant__ RenderK rk, const __grid_constant__ Queues q,
+                                                     const uint32_t* __restrict__ act, int base_sample, int nb, int it) {
+  const int cur = it & 1, nxt = cur ^ 1;
+  const size_t cap = (size_t)rk.cap;
+  const int count = q.ctl[it];
+  int* next_count = q.ctl + (it + 1);
+  int* sh_count = q.ctl + q.ctl_stride + it;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  for (int base = warp * 32; base < count; base += nwarps * 32) {
+    const int i = base + lane_id();
+    bool ext = false;
+    d3 eo = D3(0, 0, 0), ed = D3(0, 0, 0);
+    f3 ebeta = F3(0, 0, 0);
+    uint32_t slot = 0, en = 0, eflags = 0;
+    if (i < count) {
+      const int prim = q.h_prim[i];
+      q.vflag[i] = 0;
+      if (prim >= 0) {
+        slot = q.slot[cur][i];
+        const uint32_t flags = q.flags[cur][i];
+        const f3 beta = F3(q.beta[cur][i], q.beta[cur][cap + i], q.beta[cur][2 * cap + i]);
+        const rrt_material m = sc.mats[sc.prim_mat[prim]];
+        const f3 Le = mat_emission(m);
+        if (it == 0) { q.Lsample[slot] = Le.r; q.Lsample[cap + slot] = Le.g; q.Lsample[2 * cap + slot] = Le.b; }
+        else if (flags & 1u) {
+          f3 a = s_mul(Le, beta);
+          q.Lsample[slot] += a.r; q.Lsample[cap + slot] += a.g; q.Lsample[2 * cap + slot] += a.b;
+        }
+        if (rk.D >= 1) {
+          const uint32_t pixel = act[slot / (uint32_t)nb];
+          Rng g = rng_make(rk.seed, pixel, (uint32_t)(base_sample + slot % (uint32_t)nb), q.rngn[cur][i]);
+          const d3 hit_p = D3(q.h_geo[i], q.h_geo[cap + i], q.h_geo[2 * cap + i]);
+          const d3 wo_world = D3(q.h_geo[3 * cap + i], q.h_geo[4 * cap + i], q.h_geo[5 * cap + i]);
+          const d3 nrm = D3(q.h_geo[6 * cap + i], q.h_geo[7 * cap + i], q.h_geo[8 * cap + i]);
+          d3 o2w[3]; make_coord_space(o2w, nrm);
+          const d3 w_out = mat_tmul(o2w, wo_world);
+          const bool delta = mat_is_delta(m);
+          if (rk.D == 1 || !delta) {
+            /* one_bounce_radiance: light samples -> shadow queue, contributions -> table row i */
+            q.vflag[i] = 1;
+            q.dbeta[i] = beta.r; q.dbeta[cap + i] = beta.g; q.dbeta[2 * cap + i] = beta.b;
+            int k = 0;
+            if (rk.hemi) {
+              /* estimate_direct_lighting_hemisphere (reference src/part1_code.cpp:15-31) */
+              for (; k < rk.S; ++k) {
+                d3 w_in = hemisphere_sample(g);
+                d3 wi_world = mat_mul(o2w, w_in);
+                f3 f = bsdf_f(m, w_out, w_in);
+                const size_t ci = (size_t)i * rk.S + k;
+                q.s_contrib[ci] = make_float4(f.r, f.g, f.b, (float)w_in.z);
+                q.s_res[ci] = -1;
+                int pos = append_pos(sh_count);
+                const size_t cs = cap * (size_t)rk.S;
+                d3 so = vadd(hit_p, smul(RRT_EPS_D, wi_world));
+                q.sray[pos] = so.x; q.sray[cs + pos] = so.y; q.sray[2 * cs + pos] = so.z;
+                q.sray[3 * cs + pos] = wi_world.x; q.sray[4 * cs + pos] = wi_world.y; q.sray[5 * cs + pos] = wi_world.z;
+                q.sray[6 * cs + pos] = INFINITY;
+                q.s_cidx[pos] = (uint32_t)ci;
+              }
+            } else {
+              /* estimate_direct_lighting_importance (reference src/part1_code.cpp:33-57) */
+              for (int li = 0; li < sc.n_lights; ++li) {
+                const rrt_light& l = sc.lights[li];
+                const int ns = l.is_delta ? 1 : rk.ns_area_light;
+                for (int s = 0; s < ns; ++s, ++k) {
+                  d3 wi_world; float dist, pdf;
+                  f3 Li = light_sample_L(l, hit_p, wi_world, dist, pdf, g);
+                  const size_t ci = (size_t)i * rk.S + k;
+                  q.s_res[ci] = -2;
+                  if (l.type == RRT_LIGHT_NULL) continue;
+                  d3 w_in = mat_tmul(o2w, wi_world);
+                  if (w_in.z < 0) continue;
+                  f3 c = s_divf(s_mulf(s_mul(Li, bsdf_f(m, w_out, w_in)), (float)w_in.z), pdf);
+                  q.s_contrib[ci] = make_float4(c.r, c.g, c.b, 0.f);
+                  q.s_res[ci] = -1;
+                  int pos = append_pos(sh_count);
+                  const size_t cs = cap * (size_t)rk.S;
+                  d3 so = vadd(hit_p, smul(RRT_EPS_D, wi_world));
+                  q.sray[pos] = so.x; q.sray[cs + pos] = so.y; q.sray[2 * cs + pos] = so.z;
+                  q.sray[3 * cs + pos] = wi_world.x; q.sray[4 * cs + pos] = wi_world.y; q.sray[5 * cs + pos] = wi_world.z;
+                  q.sray[6 * cs + pos] = (double)dist;
+                  q.s_cidx[pos] = (uint32_t)ci;
+                }
+              }
+            }
+          }
+          if (rk.D >= 2) {
+            /* at_least_one_bounce_radiance (reference src/part1_code.cpp:82-97): Russian roulette, BSDF sample */
+            const int depth = rk.D - it;
+            const double prob = 0.7;
+            if (depth == rk.D || (depth > 1 && rng_uniform(g) < prob)) {
+              d3 w_in; float pdf;
+              f3 f = bsdf_sample_f(m, w_out, w_in, pdf, g);
+              if (pdf != 0.0f) {
+                ed = mat_mul(o2w, w_in);
+                eo = vadd(hit_p, smul(RRT_EPS_D, ed));
+                ebeta = s_divf(s_divf(s_mulf(s_mul(beta, f), (float)fabs(w_in.z)), pdf), (float)prob);
+                en = g.n; eflags = delta ? 1u : 0u;
+                ext = true;
+              }
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+    /* compaction of survivors: warp ballot + prefix, one atomic per warp */
+    unsigned mask = __ballot_sync(0xffffffffu, ext);
+    if (mask) {
+      int wbase = 0;
+      if (lane_id() == 0) wbase = atomicAdd(next_count, __popc(mask));
+      wbase = __shfl_sync(0xffffffffu, wbase, 0);
+      if (ext) {
+        int pos = wbase + __popc(mask & ((1u << lane_id()) - 1u));
+        double* r = q.ray[nxt];
+        r[pos] = eo.x; r[cap + pos] = eo.y; r[2 * cap + pos] = eo.z; r[3 * cap + pos] = ed.x; r[4 * cap + pos] = ed.y; r[5 * cap + pos] = ed.z;
+        r[6 * cap + pos] = 0.0; r[7 * cap + pos] = INFINITY;
+        q.slot[nxt][pos] = slot; q.rngn[nxt][pos] = en; q.flags[nxt][pos] = eflags;
+        q.beta[nxt][pos] = ebeta.r; q.beta[nxt][cap + pos] = ebeta.g; q.beta[nxt][2 * cap + pos] = ebeta.b;
+      }
+    }
+  }
+}
+
+/* ---------------------------------------------------------------- accumulate: fold the shadow-ray verdicts of vertex
+ * `it` into each path's radiance, in the reference's sample order */
+__global__ void __launch_bounds__(256) k_accumulate(const __grid_constant__ DevScene sc, const __grid_constant__ RenderK rk,
+                                                    const __grid_constant__ Queues q, int it) {
+  const int cur = it & 1;
+  const size_t cap = (size_t)rk.cap;
+  const int count = q.ctl[it];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+    if (!(q.vflag[i] & 1)) continue;
+    f3 L = F3(0, 0, 0);
+    for (int k = 0; k < rk.S; ++k) {
+      const size_t ci = (size_t)i * rk.S + k;
+      const int r = q.s_res[ci];
+      if (rk.hemi) {
+        if (r >= 0) {
+          float4 c = q.s_contrib[ci];
+          f3 Le = mat_emission(sc.mats[sc.prim_mat[r]]);
+          L = s_add(L, s_mulf(s_mul(Le, F3(c.x, c.y, c.z)), c.w));
+        }
+      } else if (r == -1) {
+        float4 c = q.s_contrib[ci];
+        L = s_add(L, F3(c.x, c.y, c.z));
+      }
+    }
+    if (rk.hemi) L = s_divf(s_mulf(s_mulf(L, 2.f), (float)RRT_PI), (float)rk.total);
+    else L = s_divf(L, (float)rk.total);
+    const f3 beta = F3(q.dbeta[i], q.dbeta[cap + i], q.dbeta[2 * cap + i]);
+    const uint32_t slot = q.slot[cur][i];
+    f3 a = s_mul(L, beta);
+    q.Lsample[slot] += a.r; q.Lsample[cap + slot] += a.g; q.Lsample[2 * cap + slot] += a.b;
+  }
+}
+
+/* ---------------------------------------------------------------- resolve: add a round's samples to their pixel in
+ * sample order and apply the adaptive stop rule (reference src/part1_code.cpp:141-161) */
+__global__ void __launch_bounds__(256) k_resolve(const __grid_constant__ RenderK rk, const __grid_constant__ Queues q, const __grid_constant__ PixelAcc px,
+                                                 const uint32_t* __restrict__ act, int npix, int nb) {
+  const size_t cap = (size_t)rk.cap, np = (size_t)rk.W * rk.H;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += gridDim.x * blockDim.x) {
+    const uint32_t pixel = act[p];
+    f3 ret = F3(px.sum[pixel], px.sum[np + pixel], px.sum[2 * np + pixel]);
+    double s1 = px.s1[pixel], s2 = px.s2[pixel];
+    int n = px.n[pixel];
+    for (int s = 0; s < nb; ++s) {
+      const size_t slot = (size_t)p * nb + s;
+      f3 L = F3(q.Lsample[slot], q.Lsample[cap + slot], q.Lsample[2 * cap + slot]);
+      ret = s_add(ret, L);
+      double illum = s_illum(L);
+      s1 += illum; s2 += illum * illum;
+    }
+    n += nb;
+    if (n % rk.batch == 0) {
+      double avg = s1 / n, sd = sqrt((s2 - avg * s1) / (n - 1));
+      if (1.96 * sd / sqrt((double)n) <= rk.tol * avg) px.done[pixel] = 1;
+    }
+    if (n >= rk.ns_aa) px.done[pixel] = 1;
+    px.sum[pixel] = ret.r; px.sum[np + pixel] = ret.g; px.sum[2 * np + pixel] = ret.b;
+    px.s1[pixel] = s1; px.s2[pixel] = s2; px.n[pixel] = n;
+  }
+}
+
+/* mean radiance and sample count per pixel (reference src/part1_code.cpp:161-162) */
+__global__ void __launch_bounds__(256) k_finalize(const __grid_constant__ PixelAcc px, size_t npix, float* __restrict__ rgb, int* __restrict__ counts,
+                                                  float4* __restrict__ rgbn, Counters* gcnt) {
+  unsigned long long paths = 0;
+  for (size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x; p < npix; p += (size_t)gridDim.x * blockDim.x) {
+    int n = px.n[p];
+    paths += (unsigned long long)n;
+    f3 s = F3(px.sum[p], px.sum[npix + p], px.sum[2 * npix + p]);
+    f3 m = n > 0 ? s_divf(s, (float)n) : F3(0, 0, 0);
+    if (rgb) { rgb[3 * p] = m.r; rgb[3 * p + 1] = m.g; rgb[3 * p + 2] = m.b; }
+    if (counts) counts[p] = n;
+    if (rgbn) rgbn[p] = make_float4(m.r, m.g, m.b, (float)n);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) paths += __shfl_xor_sync(0xffffffffu, paths, o);
+  if (lane_id() == 0 && paths) atomicAdd(&gcnt->paths, paths);
+}
+
+/* ---------------------------------------------------------------- stable compaction (ballot + prefix), three passes:
+ * per-block counts, one-block exclusive scan of the counts, scatter.  keep(i) decides. */
+#define RRT_CBLOCK 1024
+struct KeepOwned {  // pixel belongs to this shard and to the render cell
+  int W, x0, y0, x1, y1, tile, ntx, rank, world;
+  __device__ bool operator()(uint32_t p, uint32_t) const {
+    int x = (int)(p % (uint32_t)W), y = (int)(p / (uint32_t)W);
+    if (x < x0 || x >= x1 || y < y0 || y >= y1) return false;
+    return ((x / tile) + (y / tile) * ntx) % world == rank;
+  }
+};
+struct KeepActive {  // pixel has not reached its stop rule
+  const uint8_t* done;
+  __device__ bool operator()(uint32_t, uint32_t v) const { return !done[v]; }
+};
+
+template <class Keep>
+__global__ void __launch_bounds__(RRT_CBLOCK) k_compact_count(Keep keep, const uint32_t* __restrict__ in, uint32_t n, uint32_t* __restrict__ block_counts) {
+  __shared__ uint32_t wsum[32];
+  uint32_t i = blockIdx.x * RRT_CBLOCK + threadIdx.x;
+  bool k = i < n && keep(i, in ? in[i] : i);
+  unsigned m = __ballot_sync(0xffffffffu, k);
+  if (lane_id() == 0) wsum[threadIdx.x >> 5] = __popc(m);
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    uint32_t v = wsum[threadIdx.x];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (threadIdx.x == 0) block_counts[blockIdx.x] = v;
+  }
+}
+__global__ void __launch_bounds__(1024) k_compact_scan(uint32_t* __restrict__ block_counts, uint32_t nblocks, uint32_t* __restrict__ total) {
+  __shared__ uint32_t wsum[32];
+  __shared__ uint32_t carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < nblocks; base += 1024) {
+    uint32_t i = base + threadIdx.x;
+    uint32_t v = i < nblocks ? block_counts[i] : 0, x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane_id() >= o) x += y; }
+    if (lane_id() == 31) wsum[threadIdx.x >> 5] = x;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      uint32_t w = wsum[threadIdx.x], z = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, z, o); if (lane_id() >= o) z += y; }
+      wsum[threadIdx.x] = z - w;
+    }
+    __syncthreads();
+    uint32_t excl = carry + wsum[threadIdx.x >> 5] + x - v;
+    if (i < nblocks) block_counts[i] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = excl + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+template <class Keep>
+__global__ void __launch_bounds__(RRT_CBLOCK) k_compact_scatter(Keep keep, const uint32_t* __restrict__ in, uint32_t n, const uint32_t* __restrict__ block_offsets,
+                                                                uint32_t* __restrict__ out) {
+  __shared__ uint32_t wsum[32];
+  uint32_t i = blockIdx.x * RRT_CBLOCK + threadIdx.x;
+  uint32_t v = i < n ? (in ? in[i] : i) : 0;
+  bool k = i < n && keep(i, v);
+  unsigned m = __ballot_sync(0xffffffffu, k);
+  if (lane_id() == 0) wsum[threadIdx.x >> 5] = __popc(m);
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    uint32_t w = wsum[threadIdx.x], z = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, z, o); if (lane_id() >= o) z += y; }
+    wsum[threadIdx.x] = z - w;
+  }
+  __syncthreads();
+  if (k) out[block_offsets[blockIdx.x] + wsum[threadIdx.x >> 5] + __popc(m & ((1u << lane_id()) - 1u))] = v;
+}
+
+/* ---------------------------------------------------------------- parity hooks (one thread per item) */
+template <bool ANY>
+__global__ void __launch_bounds__(RRT_BLOCK, 4) k_hook_trace(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, long long n,
+                                                            const double* __restrict__ o, const double* __restrict__ d, const double* __restrict__ tmin,
+                                                            const double* __restrict__ tmax, rrt_hit* __restrict__ out, Counters* gcnt) {
+  __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
+  int* stack = stack_mem + threadIdx.x;
+  Counters cnt = {0, 0, 0, 0, 0, 0};
+  long long nround = (n + 31) / 32 * 32;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nround; i += (long long)gridDim.x * blockDim.x) {
+    if (i < n) {
+      Hit h; h.p = h.w_out = h.n = D3(0, 0, 0);
+      trace_ray<ANY, true>(sc, bh, D3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), D3(d[3 * i], d[3 * i + 1], d[3 * i + 2]), tmin ? tmin[i] : 0.0,
+                           tmax ? tmax[i] : (double)INFINITY, !ANY, h, stack, cnt);
+      rrt_hit r;
+      r.status = h.status; r.prim = (h.status == 1 && !ANY) ? h.prim : -1; r.chord = h.chord; r.steps = h.steps;
+      r.t = h.status == 1 ? h.t : 0.0;
+      bool geo = h.status == 1 && !ANY;
+      r.hit_p[0] = geo ? h.p.x : 0; r.hit_p[1] = geo ? h.p.y : 0; r.hit_p[2] = geo ? h.p.z : 0;
+      r.w_out[0] = geo ? h.w_out.x : 0; r.w_out[1] = geo ? h.w_out.y : 0; r.w_out[2] = geo ? h.w_out.z : 0;
+      r.n[0] = geo ? h.n.x : 0; r.n[1] = geo ? h.n.y : 0; r.n[2] = geo ? h.n.z : 0;
+      out[i] = r;
+    }
+  }
+  flush_counters(cnt, gcnt);
+}
+
+__global__ void k_hook_geodesic(const __grid_constant__ DevHole bh, long long n, const double* __restrict__ o, const double* __restrict__ d, int nsteps,
+                                double* __restrict__ seg) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    d3 ro = D3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), rd = D3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+    double len = 0.0;
+    for (int j = 0; j < nsteps; ++j) {
+      next_micro_ray(bh, ro, rd, len);
+      double* s = seg + ((size_t)i * nsteps + j) * 8;
+      s[0] = ro.x; s[1] = ro.y; s[2] = ro.z; s[3] = rd.x; s[4] = rd.y; s[5] = rd.z; s[6] = len;
+      s[7] = horizon_hit(bh, ro, rd, len) ? 1.0 : 0.0;
+    }
+  }
+}
+
+__global__ void k_hook_camera(const __grid_constant__ DevCamera cam, long long n, const double* __restrict__ xy, double* __restrict__ o, double* __restrict__ d) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    d3 ro, rd; generate_ray(cam, xy[2 * i], xy[2 * i + 1], ro, rd);
+    o[3 * i] = ro.x; o[3 * i + 1] = ro.y; o[3 * i + 2] = ro.z; d[3 * i] = rd.x; d[3 * i + 1] = rd.y; d[3 * i + 2] = rd.z;
+  }
+}
+
+__global__ void k_hook_bsdf(const rrt_material* __restrict__ mats, int mat, long long n, const double* __restrict__ wo, const double* __restrict__ wi_in,
+                            const double* __restrict__ u, float* __restrict__ f, double* __restrict__ wi, float* __restrict__ pdf) {
+  const rrt_material m = mats[mat];
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    d3 w = D3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]);
+    f3 s;
+    if (u) {  /* sample_f */
+      Rng g = rng_make(0, 0, 0, 0); g.fixed = u + 4 * i;
+      d3 r = D3(0, 0, 0); float p = 0;
+      s = bsdf_sample_f(m, w, r, p, g);
+      wi[3 * i] = r.x; wi[3 * i + 1] = r.y; wi[3 * i + 2] = r.z; pdf[i] = p;
+    } else s = bsdf_f(m, w, D3(wi_in[3 * i], wi_in[3 * i + 1], wi_in[3 * i + 2]));
+    f[3 * i] = s.r; f[3 * i + 1] = s.g; f[3 * i + 2] = s.b;
+  }
+}
+
+__global__ void k_hook_light(const rrt_light* __restrict__ lights, int light, long long n, const double* __restrict__ p, const double* __restrict__ u,
+                             float* __restrict__ rad, double* __restrict__ wi, float* __restrict__ dist, float* __restrict__ pdf) {
+  const rrt_light l = lights[light];
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    Rng g = rng_make(0, 0, 0, 0); g.fixed = u + 2 * i;
+    d3 w; float ds = 0, pd = 0;
+    f3 s = light_sample_L(l, D3(p[3 * i], p[3 * i + 1], p[3 * i + 2]), w, ds, pd, g);
+    rad[3 * i] = s.r; rad[3 * i + 1] = s.g; rad[3 * i + 2] = s.b;
+    wi[3 * i] = w.x; wi[3 * i + 1] = w.y; wi[3 * i + 2] = w.z; dist[i] = ds; pdf[i] = pd;
+  }
+}
+
+__global__ void k_hook_philox(unsigned long long seed, long long n, const uint32_t* __restrict__ ctr, uint32_t* __restrict__ out) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    uint32_t c0 = ctr[4 * i], c1 = ctr[4 * i + 1], c2 = ctr[4 * i + 2], c3 = ctr[4 * i + 3];
+    philox4x32_10(c0, c1, c2, c3, (uint32_t)seed, (uint32_t)(seed >> 32));
+    out[4 * i] = c0; out[4 * i + 1] = c1; out[4 * i + 2] = c2; out[4 * i + 3] = c3;
+  }
+}
+
+/* HDRImageBuffer::toColor + ImageBuffer::update_pixel (reference src/image.h:183-198,53-62): gamma 2.2, level 1,
+ * upper clamp only, truncation to 8 bits, alpha 0xFF */
+__global__ void k_tonemap(long long n, const float* __restrict__ hdr, uint32_t* __restrict__ rgba) {
+  const float one_over_gamma = 1.0f / 2.2f;
+  const float exposure = (float)sqrt(pow(2.0, (double)1.0f));
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    uint32_t p = 0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      float c = powf(hdr[3 * i + k] * exposure, one_over_gamma);
+      float v = c < 1.f ? c : 1.f;
+      if (!(v >= 0.f)) v = 0.f;
+      p |= ((uint32_t)(v * 255)) << (8 * k);
+    }
+    rgba[i] = p | 0xFF000000u;
+  }
+}

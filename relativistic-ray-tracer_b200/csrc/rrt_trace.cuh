@@ -1,0 +1,201 @@
+// rrt_trace.cuh — device side of BVHAccel::intersect: the Schwarzschild chord stepper, the horizon test and
+// the BVH traversal of one chord.  Reference: src/bvh.cpp:99-138, src/static_scene/blackhole.cpp:13-40,
+// src/static_scene/sphere.cpp:10-53, src/static_scene/triangle.cpp:25-55, src/bbox.cpp:10-25.
+//
+// Exactness contract (DESIGN.md "Numerics"): chord recurrence, horizon test and primitive tests are IEEE
+// double in the reference's operation order (bit-identical results); interior-node slab tests are
+// CONSERVATIVE (never reject a box the reference accepts), so which leaves get tested may be a superset
+// of the reference's, and the primitive tests alone decide the hit.  Equal-t ties go to the primitive
+// with the higher reference depth-first rank (the reference keeps the last one it visits).
+#pragma once
+#include "rrt_math.cuh"
+#include "../../include/rrt_b200.h"
+
+#define RRT_STACK 48  /* traversal stack entries per thread (shared memory); tree depth bound */
+
+struct DevScene {
+  const float4* nodes;        // 4 float4 per interior node
+  const double2* leaf;        // 5 double2 per leaf record
+  const double* tri_nrm;      // 9 per triangle: vertex normals
+  const uint8_t* prim_kind;   // [n_prims]
+  const uint32_t* prim_index; // [n_prims]
+  const int32_t* prim_mat;    // [n_prims]
+  const double* sph;          // 4 per sphere
+  const rrt_material* mats;
+  const rrt_light* lights;
+  int32_t n_prims, n_mats, n_lights, root;
+  double root_lo[3], root_hi[3];
+};
+
+struct DevHole {            // global_black_hole (reference src/static_scene/blackhole.cpp:5) + per-frame constants
+  double cx, cy, cz, r, r2, h, cos_h, sin_h;
+  int32_t mode, nchords;
+};
+
+struct Counters { unsigned long long rays, steps, nodes, tris, sph, paths; };
+
+struct Hit {
+  int status;   // 0 miss, 1 hit, 2 captured
+  int prim, chord, steps;
+  double t;
+  d3 p, w_out, n;
+};
+
+// one chord (or, in flat mode, the whole ray)
+struct Seg { d3 o, d; double tmin, tmax; };
+
+// best hit so far inside a chord
+struct Best { double t, b1, b2; int prim; int rank; int kind; };
+
+/* BlackHole::f (reference src/static_scene/blackhole.cpp:13-15) */
+__device__ __forceinline__ double bh_f(double r, double u) { return -u + 3.0 * r * u * u / 2.0; }
+
+/* BlackHole::next_micro_ray (reference src/static_scene/blackhole.cpp:17-40).  In: previous chord (o, d, len).
+ * Out: next chord.  The conserved plane (x_axis, y_axis) is re-derived from the chord each call, exactly as the
+ * reference does; nothing but (o, d, len) is carried. */
+__device__ __forceinline__ void next_micro_ray(const DevHole& bh, d3& o, d3& d, double& len) {
+  const double h = bh.h;
+  d3 c = D3(bh.cx, bh.cy, bh.cz);
+  d3 p = vadd(o, vmul(d, len));
+  d3 x_axis = vsub(p, c);
+  double dist = vnorm(x_axis);
+  double u = 1.0 / dist;              /* both `1. / norm()` in normalize() and `u = 1 / d` */
+  x_axis = D3(x_axis.x * u, x_axis.y * u, x_axis.z * u);
+  double dx = vdot(d, x_axis);
+  d3 y_axis = vsub(d, smul(dx, x_axis));
+  double dy = vnorm(y_axis);
+  double rdy = 1.0 / dy;
+  y_axis = D3(y_axis.x * rdy, y_axis.y * rdy, y_axis.z * rdy);
+  double up = -u * dx / dy;
+  double f1 = bh_f(bh.r, u);
+  double f2 = bh_f(bh.r, u + up * h / 2.0);
+  double f3 = bh_f(bh.r, u + up * h / 2.0 + f1 * h * h / 4.0);
+  u += up * h + (f1 + f2 + f3) * h * h / 6.0;
+  double dn = 1.0 / u;
+  double next_x = dn * bh.cos_h;
+  double next_y = dn * bh.sin_h;
+  d3 q = vsub(vadd(vadd(c, smul(next_x, x_axis)), smul(next_y, y_axis)), p);
+  double l = vnorm(q);
+  double rl = 1.0 / l;
+  o = p; d = D3(q.x * rl, q.y * rl, q.z * rl); len = l;
+}
+
+/* Sphere::test + the range logic of Sphere::intersect (reference src/static_scene/sphere.cpp:10-53) for the horizon:
+ * true when the chord [0, len] crosses the sphere of radius^2 r2 about c. */
+__device__ __forceinline__ bool horizon_hit(const DevHole& bh, d3 o, d3 d, double len) {
+  d3 tmp = vsub(o, D3(bh.cx, bh.cy, bh.cz));
+  double b = 2 * vdot(tmp, d), c = vnorm2(tmp) - bh.r2, disc = b * b - 4 * c;
+  if (disc < 0) return false;
+  double sq = sqrt(disc);
+  double t1 = (-b - sq) / 2, t2 = (-b + sq) / 2;
+  return (0.0 <= t1 && t1 <= len) || (0.0 <= t2 && t2 <= len);
+}
+
+/* Conservative version of BBox::intersect (reference src/bbox.cpp:10-25).  The reference divides by d six times;
+ * here the three reciprocals are formed once per chord and the result is widened by 2^-40 relative, far more than
+ * the two roundings that separate (b - o) * (1/d) from (b - o) / d, so every box the reference accepts is accepted.
+ * min/max keep the reference's argument order, hence its NaN behaviour for rays lying in a slab plane.
+ * Requires tmin >= 0 (true for chords and for every ray the estimator makes).  Returns the entry distance. */
+__device__ __forceinline__ bool box_hit(float lox, float loy, float loz, float hix, float hiy, float hiz, const d3& o,
+                                        const d3& inv, double seg_tmin, double seg_tmax, double& tnear) {
+  const double GROW = 1.0 + 9.094947017729282e-13, SHRINK = 1.0 - 9.094947017729282e-13;
+  double tx0 = ((double)lox - o.x) * inv.x, tx1 = ((double)hix - o.x) * inv.x;
+  double ty0 = ((double)loy - o.y) * inv.y, ty1 = ((double)hiy - o.y) * inv.y;
+  double tz0 = ((double)loz - o.z) * inv.z, tz1 = ((double)hiz - o.z) * inv.z;
+  double tmn = cmax(cmax(cmin(tx0, tx1), cmin(ty0, ty1)), cmin(tz0, tz1));
+  double tmx = cmin(cmin(cmax(tx0, tx1), cmax(ty0, ty1)), cmax(tz0, tz1));
+  tmn = tmn * (tmn > 0 ? SHRINK : GROW);
+  tmx = tmx * GROW;
+  tnear = tmn;
+  return tmn <= tmx && tmn <= seg_tmax && tmx >= seg_tmin;
+}
+
+/* Triangle::intersect and Sphere::intersect on one 80-byte leaf record.  Accepts when the reference would and the
+ * hit is at least as close as the best so far (ties: higher depth-first rank wins). */
+template <bool COUNT>
+__device__ __forceinline__ bool leaf_record_test(const double2* __restrict__ rec, const Seg& s, Best& best, Counters& cnt) {
+  double2 a0 = __ldg(rec + 0), a1 = __ldg(rec + 1), a2 = __ldg(rec + 2), a3 = __ldg(rec + 3), a4 = __ldg(rec + 4);
+  unsigned long long tag = (unsigned long long)__double_as_longlong(a4.y);
+  int prim = (int)(uint32_t)tag;
+  uint32_t rk = (uint32_t)(tag >> 32);
+  int kind = (int)(rk & 1u), rank = (int)(rk >> 1);
+  double t, b1 = 0.0, b2 = 0.0;
+  if (kind == 0) {
+    if (COUNT) cnt.tris++;
+    d3 p0 = D3(a0.x, a0.y, a1.x), e1 = D3(a1.y, a2.x, a2.y), e2 = D3(a3.x, a3.y, a4.x);
+    d3 sv = vsub(s.o, p0);
+    d3 s1 = vcross(s.d, e2), s2 = vcross(sv, e1);
+    double inv = 1. / vdot(s1, e1);
+    t = vdot(s2, e2) * inv; b1 = vdot(s1, sv) * inv; b2 = vdot(s2, s.d) * inv;
+    double b0 = 1 - b1 - b2;
+    if (!(s.tmin <= t && t <= best.t && b0 >= 0 && b1 >= 0 && b2 >= 0)) return false;
+  } else {
+    if (COUNT) cnt.sph++;
+    d3 tmp = vsub(s.o, D3(a0.x, a0.y, a1.x));
+    double b = 2 * vdot(tmp, s.d), c = vnorm2(tmp) - a1.y, disc = b * b - 4 * c;
+    if (disc < 0) return false;
+    double sq = sqrt(disc);
+    double t1 = (-b - sq) / 2, t2 = (-b + sq) / 2;
+    if (s.tmin <= t1 && t1 <= best.t) t = t1;
+    else if (s.tmin <= t2 && t2 <= best.t) t = t2;
+    else return false;
+  }
+  if (t == best.t && rank < best.rank) return false;
+  best.t = t; best.b1 = b1; best.b2 = b2; best.prim = prim; best.rank = rank; best.kind = kind;
+  return true;
+}
+
+/* BVHAccel::intersect_micro (reference src/bvh.cpp:115-138) as an iterative, near-child-first traversal with a
+ * per-thread stack in shared memory.  ANY = shadow-ray form (stop at the first accepted primitive). */
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt) {
+  best.t = s.tmax; best.rank = -1; best.prim = -1; best.kind = 0; best.b1 = best.b2 = 0.0;
+  d3 inv = D3(1.0 / s.d.x, 1.0 / s.d.y, 1.0 / s.d.z);
+  bool found = false;
+  {
+    /* root box in full double precision */
+    double tx0 = (sc.root_lo[0] - s.o.x) * inv.x, tx1 = (sc.root_hi[0] - s.o.x) * inv.x;
+    double ty0 = (sc.root_lo[1] - s.o.y) * inv.y, ty1 = (sc.root_hi[1] - s.o.y) * inv.y;
+    double tz0 = (sc.root_lo[2] - s.o.z) * inv.z, tz1 = (sc.root_hi[2] - s.o.z) * inv.z;
+    double tmn = cmax(cmax(cmin(tx0, tx1), cmin(ty0, ty1)), cmin(tz0, tz1));
+    double tmx = cmin(cmin(cmax(tx0, tx1), cmax(ty0, ty1)), cmax(tz0, tz1));
+    const double GROW = 1.0 + 9.094947017729282e-13, SHRINK = 1.0 - 9.094947017729282e-13;
+    tmn = tmn * (tmn > 0 ? SHRINK : GROW); tmx = tmx * GROW;
+    if (!(tmn <= tmx && tmn <= s.tmax && tmx >= s.tmin)) return false;
+  }
+  int cur = sc.root;
+  int sp = 0;
+  while (true) {
+    if (cur < 0) {
+      uint32_t bits = (uint32_t)~cur;
+      uint32_t first = bits >> 3, count = bits & 7u;
+      for (uint32_t k = 0; k < count; ++k) {
+        if (leaf_record_test<COUNT>(sc.leaf + 5 * (size_t)(first + k), s, best, cnt)) {
+          found = true;
+          if (ANY) return true;
+        }
+      }
+      if (sp == 0) break;
+      cur = stack[(--sp) * stride];
+      continue;
+    }
+    const float4* nd = sc.nodes + 4 * (size_t)cur;
+    float4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2), q3 = __ldg(nd + 3);
+    if (COUNT) cnt.nodes++;
+    double tl, tr;
+    bool hl = box_hit(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, s.o, inv, s.tmin, best.t, tl);
+    bool hr = box_hit(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, s.o, inv, s.tmin, best.t, tr);
+    int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
+    if (hl && hr) {
+      if (tr < tl) { int t = cl; cl = cr; cr = t; }
+      stack[(sp++) * stride] = cr;
+      cur = cl;
+    } else if (hl) cur = cl;
+    else if (hr) cur = cr;
+    else {
+      if (sp == 0) break;
+      cur = stack[(--sp) * stride];
+    }
+  }
+  return found;
+}

@@ -1,0 +1,283 @@
+"""GPU parity tests proper: the CUDA path (through the C-ABI, csrc/librrt_b200.so) against
+  (a) the golden vectors produced by the reference's own objects (tests/golden/, made by make_golden.py), and
+  (b) the CPU oracle (oracle/rrt_oracle.c) on the same seeded inputs.
+Tolerances (BASELINE.json north_star): BVH hit / miss / primitive id bit-exact, t within 1e-5 relative; geodesic
+endpoints and directions within 1e-4 relative; images RMSE <= 1 % of mean radiance.  What this implementation
+actually delivers is stricter and is what the asserts state: chords, hit points and normals are BIT-identical
+(IEEE double, same operation order, no FMA), BSDF / light values agree to libm rounding.
+"""
+import numpy as np
+import pytest
+
+from util import RAND_MAX, golden, hits_from_probe, load_scene, sc
+from test_oracle_render import RENDERS, setup_from_golden
+
+pytestmark = pytest.mark.gpu
+
+
+def same(a, b):
+    a = np.asarray(a); b = np.asarray(b)
+    return bool(np.all((a == b) | (np.isnan(a) & np.isnan(b))))
+
+
+@pytest.fixture(scope="module")
+def api():
+    import importlib
+    return importlib.import_module("relativistic-ray-tracer_b200.api")
+
+
+@pytest.fixture(scope="module")
+def orc():
+    from oracle import orc as o
+    return o
+
+
+def make_ctx(api, scene_name):
+    c = api.Context(0)
+    c.upload_scene(load_scene(scene_name))
+    return c
+
+
+def test_philox_known_answers(api):
+    c = api.Context(0)
+    assert [hex(x) for x in c.philox(0, [[0, 0, 0, 0]])[0]] == ["0x6627e8d5", "0xe169c58d", "0xbc57ac4c", "0x9b00dbd8"]
+    assert [hex(x) for x in c.philox(0xFFFFFFFFFFFFFFFF, [[0xFFFFFFFF] * 4])[0]] == ["0x408f276d", "0x41c83b0e", "0xa20bc7c6", "0x6d5451fd"]
+    assert [hex(x) for x in c.philox(0x299F31D0A4093822, [[0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344]])[0]] == \
+        ["0xd16cfe09", "0x94fdcceb", "0x5001e420", "0x24126ea1"]
+
+
+@pytest.mark.parametrize("tag", ["default", "alt", "r0"])
+def test_geodesic_chords_bit_exact(api, tag):
+    g = golden("kat_geodesic")
+    c = make_ctx(api, "cbempty_480x360")
+    bh = g["bh_" + tag]
+    c.set_blackhole(bh[:3], bh[3], bh[4], sc.MODE_LITERAL)
+    ref = g["seg_" + tag]
+    got = c.geodesic(g["o"], g["d"], ref.shape[1])
+    assert same(got, ref)  # north_star asks for 1e-4 relative; delivered: identical bits, NaN chords of radial rays included
+    assert c.chords_per_ray() == (63 if bh[4] == 0.1 else 32)
+
+
+@pytest.mark.parametrize("topology", [0, 1])
+@pytest.mark.parametrize("scene", ["cbspheres_lambertian_480x360", "cbgems_480x360", "cbbunny_microfacet_480x360"])
+@pytest.mark.parametrize("mode", ["flat", "bh", "alt"])
+def test_bvh_intersect_matches_reference(api, scene, mode, topology):
+    g = golden("kat_trace_" + scene)
+    if "hit_" + mode not in g.files:
+        pytest.skip("no alt-hole vectors for this scene")
+    c = api.Context(0)
+    c.set_option(api.OPT_BVH_TOPOLOGY, topology)
+    c.upload_scene(load_scene(scene))
+    if mode == "flat":
+        c.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_FLAT)
+    elif mode == "alt":
+        bh = g["bh_alt"]; c.set_blackhole(bh[:3], bh[3], bh[4], sc.MODE_LITERAL)
+    rays = g["rays_" + mode]; ref = hits_from_probe(g["hit_" + mode])
+    got, st = c.trace_rays(rays[:, 0:3], rays[:, 3:6], rays[:, 6], rays[:, 7])
+    assert np.array_equal(got["status"] == 1, ref["hit"])                    # hit / miss: exact
+    h = ref["hit"]
+    assert np.array_equal(got["prim"][h], ref["prim"][h])                    # primitive id: exact
+    assert same(got["hit_p"][h], ref["hit_p"][h]) and same(got["w_out"][h], ref["w_out"][h]) and same(got["n"][h], ref["n"][h])
+    anyh, _ = c.trace_rays(rays[:, 0:3], rays[:, 3:6], rays[:, 6], rays[:, 7], any_hit=True)
+    assert np.array_equal(anyh["status"] == 1, ref["any"])
+    assert st["rays"] == len(rays)
+
+
+@pytest.mark.parametrize("scene,mode", [("cbspheres_lambertian_480x360", "bh"), ("cbbunny_microfacet_480x360", "flat"),
+                                        ("cbbunny_microfacet_480x360", "bh")])
+def test_trace_matches_oracle_records(api, orc, scene, mode):
+    """full rrt_hit records (status incl. capture, chord index, step count, t) against the CPU oracle"""
+    g = golden("kat_trace_" + scene)
+    s = load_scene(scene)
+    c = api.Context(0); c.upload_scene(s)
+    o = orc.Oracle(s)
+    m = sc.MODE_FLAT if mode == "flat" else sc.MODE_LITERAL
+    c.set_blackhole((0, 1, 0), 0.1, 0.1, m); o.set_blackhole((0, 1, 0), 0.1, 0.1, m)
+    rays = g["rays_" + mode]
+    got, gst = c.trace_rays(rays[:, 0:3], rays[:, 3:6], rays[:, 6], rays[:, 7])
+    ref, ost = o.trace_rays(rays[:, 0:3], rays[:, 3:6], rays[:, 6], rays[:, 7])
+    for f in ("status", "prim", "chord", "steps"):
+        assert np.array_equal(got[f], ref[f]), f
+    assert same(got["t"], ref["t"])  # north_star: 1e-5 relative; delivered: identical
+    assert gst["geodesic_steps"] == ost["geodesic_steps"] and gst["rays"] == ost["rays"]
+    assert (got["status"] == 2).sum() > 0 or mode == "flat"
+
+
+def test_camera_rays(api):
+    g = golden("kat_trace_cbspheres_lambertian_480x360")
+    c = make_ctx(api, "cbspheres_lambertian_480x360")
+    o, d = c.generate_rays(g["xy"])
+    assert same(o, g["cam"][:, 0:3])
+    np.testing.assert_allclose(d, g["cam"][:, 3:6], rtol=0, atol=4e-16)  # tan() is CUDA libm, not glibc
+
+
+@pytest.mark.parametrize("scene", ["cbspheres_lambertian_480x360", "cbspheres_480x360", "cbspheres_microfacet_480x360"])
+def test_bsdf_f_and_sample_f(api, scene):
+    g = golden("kat_bsdf_" + scene)
+    s = load_scene(scene)
+    c = api.Context(0); c.upload_scene(s)
+    for mi in range(len(s.mats)):
+        inp, ref = g["in_%d" % mi], g["out_%d" % mi]
+        u = inp[:, 6:10] / RAND_MAX
+        f, wi, pdf = c.bsdf_sample(mi, inp[:, 0:3], u)
+        fe = c.bsdf_eval(mi, inp[:, 0:3], inp[:, 3:6])
+        # float results: a few float ulps (double libm differences are rounded away except at float ties)
+        np.testing.assert_allclose(fe, ref[:, 0:3], rtol=2e-6, atol=1e-30, err_msg="%s mat %d f" % (scene, mi))
+        live = ref[:, 9] != 0
+        assert np.array_equal(pdf != 0, live)
+        np.testing.assert_allclose(f[live], ref[live, 3:6], rtol=2e-6, atol=1e-30, err_msg="%s mat %d sample_f" % (scene, mi))
+        np.testing.assert_allclose(pdf[live], ref[live, 9], rtol=2e-6, err_msg="%s mat %d pdf" % (scene, mi))
+        np.testing.assert_allclose(wi[live], ref[live, 6:9], rtol=0, atol=1e-13, err_msg="%s mat %d wi" % (scene, mi))
+
+
+@pytest.mark.parametrize("scene", ["cbspheres_lambertian_480x360", "cbempty_480x360"])
+def test_light_sample_L(api, scene):
+    g = golden("kat_light_" + scene)
+    c = make_ctx(api, scene)
+    inp, ref = g["inp"], g["out"]
+    rad, wi, dist, pdf = c.light_sample(0, inp[:, 0:3], inp[:, 3:5] / RAND_MAX)
+    assert same(rad.astype(np.float64), ref[:, 0:3]) and same(wi, ref[:, 3:6])  # no transcendental on this path: exact
+    assert same(dist.astype(np.float64), ref[:, 6]) and same(pdf.astype(np.float64), ref[:, 7])
+
+
+def test_tonemap_matches_oracle(api, orc):
+    rng = np.random.default_rng(5)
+    hdr = np.concatenate([rng.uniform(0, 2, (4000, 3)), [[0, 0, 0], [1, 1, 1], [0.5, 10, 1e-6]]]).astype(np.float32)
+    got = api.Context(0).tonemap(hdr).view(np.uint8).reshape(-1, 4).astype(int)
+    ref = orc.tonemap(hdr).view(np.uint8).reshape(-1, 4).astype(int)
+    assert np.abs(got - ref).max() <= 1  # powf: CUDA vs glibc, at most one 8-bit level at a truncation boundary
+    assert (got != ref).mean() < 0.01
+
+
+def image_report(hdr, ref):
+    rel = np.abs(hdr - ref) / np.maximum(np.abs(ref), 1e-3)
+    pix = rel.max(-1)
+    rmse = float(np.sqrt(np.mean((hdr.astype(np.float64) - ref) ** 2)))
+    return pix, rmse
+
+
+@pytest.mark.parametrize("name", RENDERS)
+def test_render_matches_reference_image(api, orc, name):
+    """Same Philox stream as the golden image rendered by the reference's raytrace_pixel: images agree path by path.
+    A path can only differ where a CUDA-libm direction differs from glibc's in the last bit AND that flips a hit;
+    the asserts allow 0.5 % of pixels to do so and bound the whole-image error far below the 1 % RMSE target."""
+    g = golden("render_" + name)
+    s = load_scene(str(g["scene"]))
+    c = api.Context(0); c.upload_scene(s)
+    p = setup_from_golden(g, c)
+    hdr, cnt, st = c.render(p)
+    ref = g["hdr"]
+    pix, rmse = image_report(hdr, ref)
+    assert (cnt != g["counts"]).mean() <= 0.005, "adaptive stop decisions differ"
+    assert (pix > 1e-4).mean() <= 0.005, "fraction of pixels off by more than 1e-4 relative: %g" % (pix > 1e-4).mean()
+    assert rmse <= 0.01 * float(ref.mean()) + 1e-12
+    assert st["paths"] == int(cnt.sum())
+    # the same work as the CPU oracle does on this input: ray and chord counts agree to the rare libm-flipped path
+    o = orc.Oracle(s)
+    po = setup_from_golden(g, o)
+    _, _, ost = o.render(po)
+    assert abs(st["rays"] - ost["rays"]) <= 1e-3 * ost["rays"] + 2
+    assert abs(st["geodesic_steps"] - ost["geodesic_steps"]) <= 1e-3 * ost["geodesic_steps"] + 64
+
+
+def c2_setup(api, w=480, h=360):
+    s = load_scene("cbspheres_lambertian_480x360")
+    if (w, h) != (480, 360):
+        s.set_screen_size(w, h)
+    c = api.Context(0); c.upload_scene(s)
+    c.set_frame(w, h)
+    return c, s
+
+
+def test_c2_full_size_properties(api):
+    """BASELINE config 2 at full size: size-independent properties instead of a CPU run."""
+    c, s = c2_setup(api)
+    p = sc.make_params(ns_aa=16, max_ray_depth=5, ns_area_light=4, seed=7)
+    hdr, cnt, st = c.render(p)
+    assert np.isfinite(hdr).all() and (hdr >= 0).all()
+    assert (cnt == 16).all() and st["paths"] == 480 * 360 * 16          # spp < batch: no adaptive stop
+    assert st["rays"] > st["paths"] and st["geodesic_steps"] > st["rays"]
+    hdr2, cnt2, st2 = c.render(p)
+    assert np.array_equal(hdr, hdr2) and st2["rays"] == st["rays"] and st2["geodesic_steps"] == st["geodesic_steps"]  # deterministic
+    # a different chunking of the wavefront must not change a single bit
+    p2 = sc.make_params(ns_aa=16, max_ray_depth=5, ns_area_light=4, seed=7, max_paths_in_flight=300000)
+    hdr3, _, st3 = c.render(p2)
+    assert np.array_equal(hdr, hdr3) and st3["rays"] == st["rays"]
+    # interleaved tile shards: the union of the ranks' frames is the single-GPU frame (multi-GPU contract)
+    acc = np.zeros_like(hdr); accn = np.zeros_like(cnt)
+    for r in range(3):
+        c.set_tile_shard(32, r, 3)
+        hr, cr, _ = c.render(p)
+        assert ((hr != 0).any(-1) <= (cr > 0)).all()
+        acc += hr; accn += cr
+    c.set_tile_shard(32, 0, 1)
+    assert np.array_equal(acc, hdr) and np.array_equal(accn, cnt)
+    # cell render (-p): pixels outside the cell stay zero, inside equal the full frame
+    c.set_cell(100, 50, 64, 40)
+    hc, cc, _ = c.render(p)
+    c.set_cell(0, 0, 0, 0)
+    assert np.array_equal(hc[50:90, 100:164], hdr[50:90, 100:164]) and cc.sum() == 64 * 40 * 16
+    hc[50:90, 100:164] = 0
+    assert not hc.any()
+
+
+def test_c1_flat_full_size_against_oracle_stats(api, orc):
+    """BASELINE config 1 (flat space) at 480x360, 1 spp: per-pixel agreement with the CPU oracle."""
+    c, s = c2_setup(api)
+    o = orc.Oracle(s)
+    c.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_FLAT); o.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_FLAT)
+    o.set_frame(480, 360)
+    p = sc.make_params(ns_aa=2, max_ray_depth=5, ns_area_light=4, seed=3)
+    hdr, cnt, st = c.render(p)
+    ref, rcnt, ost = o.render(p)
+    pix, rmse = image_report(hdr, ref)
+    assert np.array_equal(cnt, rcnt)
+    assert (pix > 1e-4).mean() <= 0.002 and rmse <= 0.01 * float(ref.mean())
+    assert abs(st["rays"] - ost["rays"]) <= 1e-3 * ost["rays"]
+
+
+def test_adaptive_rounds_match_oracle(api, orc):
+    """spp > batch: several adaptive rounds, active-pixel compaction between them"""
+    s = load_scene("cbspheres_lambertian_96x72")
+    c = api.Context(0); c.upload_scene(s); c.set_frame(96, 72)
+    o = orc.Oracle(s); o.set_frame(96, 72)
+    p = sc.make_params(ns_aa=40, max_ray_depth=3, ns_area_light=1, samples_per_batch=8, max_tolerance=0.25, seed=21)
+    hdr, cnt, st = c.render(p)
+    ref, rcnt, _ = o.render(p)
+    assert (cnt != rcnt).mean() <= 0.005
+    assert set(np.unique(cnt)) <= {8, 16, 24, 32, 40} and len(np.unique(cnt)) >= 3
+    pix, rmse = image_report(hdr, ref)
+    assert (pix > 1e-4).mean() <= 0.01 and rmse <= 0.01 * float(ref.mean())
+
+
+def test_empty_and_degenerate_inputs(api):
+    c = make_ctx(api, "cbempty_480x360")
+    hits, st = c.trace_rays(np.zeros((0, 3)), np.zeros((0, 3)))
+    assert len(hits) == 0 and st["rays"] == 0
+    # radial ray: NaN chords, never hits, walks all chords (reference src/static_scene/blackhole.cpp:24-27)
+    hits, st = c.trace_rays([[0.0, 1.0, 3.0]], [[0.0, 0.0, -1.0]])
+    assert hits["status"][0] == 0 and hits["steps"][0] == 63
+    # a scene with no primitives at all
+    e = sc.SceneData(np.zeros(0, np.uint8), np.zeros(0, np.uint32), np.zeros((0, 9)), np.zeros((0, 9)), np.zeros(0, np.int32),
+                     np.zeros((0, 4)), np.zeros(0, np.int32), np.zeros(0, sc.MAT_DTYPE), np.zeros(0, sc.LIGHT_DTYPE), load_scene("cbempty_480x360").camera)
+    c2 = api.Context(0); c2.upload_scene(e); c2.set_frame(16, 8)
+    hdr, cnt, st = c2.render(sc.make_params(ns_aa=2, max_ray_depth=2))
+    assert not hdr.any() and (cnt == 2).all()
+    with pytest.raises(api.RrtError):
+        api.Context(0).render(sc.make_params())  # nothing set: RRT_E_STATE, loudly
+
+
+def test_pathtracer_mirror_state_machine(api, tmp_path):
+    s = load_scene("cbspheres_lambertian_96x72")
+    pt = api.PathTracer(ns_aa=4, max_ray_depth=3, ns_area_light=2, seed=5)
+    assert pt.state == pt.INIT
+    pt.start_raytracing()          # wrong state: silently ignored, as the reference does
+    assert pt.state == pt.INIT
+    pt.set_scene(s); pt.set_camera(s)
+    assert pt.state == pt.READY
+    pt.set_frame_size(96, 72)
+    out = tmp_path / "img.png"
+    pt.render_to_file(str(out))
+    assert pt.state == pt.DONE and out.exists() and (tmp_path / "img_rate.png").exists()
+    assert pt.sampleBuffer.mean() > 0.05 and (pt.sampleCountBuffer == 4).all()
+    assert pt.bvh.ctx.bvh_info()["n_nodes"] == 7
