@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the hot path (per-pixel Monte Carlo radiance estimation with Schwarzschild ray
+bending) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|bunny_bh]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+One step = one full render of the workload.  Default workload = BASELINE.json configs[1] ("C2"):
+CBspheres_lambertian.dae 480x360, -s 16 -l 4 -m 5, black hole on (the reference's default hole).  The scene is the
+committed flattened copy of that .dae (tests/golden/*.rrtscene, written by the reference's own COLLADA loader).
+At N GPUs the frame is tile-sharded (16x16 interleaved tiles), every rank renders 16*N samples per pixel of its
+tiles (per-GPU work fixed => "scaling": "weak") and the per-rank float4 frames are combined with ONE NCCL reduce.
+
+Prints ONE JSON line (rank 0).  `value` = Mpaths/s with everything resident in HBM; `e2e` = the same through the
+public host-buffer API (scene upload + render + frame read-back inside the timed region).
+--impl reference times the reference's own CPU path tracer (oracle/_ref/ref_bh, built from /root/reference by
+oracle/build_ref.sh; falls back to the OpenMP oracle port when that binary is absent) on the host cores.
+"""
+import argparse
+import importlib
+import json
+import os
+import re
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np
+
+WORKLOADS = {
+    # name: (scene fixture, dae for the reference binary, W, H, spp, l, m, mode, description)
+    "c2": ("cbspheres_lambertian_480x360", "CBspheres_lambertian.dae", 480, 360, 16, 4, 5, "bh",
+           "C2: CBspheres_lambertian.dae 480x360 -s 16 -l 4 -m 5, Schwarzschild hole on (0,1,0) r=0.1 dtheta=0.1"),
+    "c1": ("cbspheres_lambertian_480x360", "CBspheres_lambertian.dae", 480, 360, 16, 4, 5, "flat",
+           "C1: CBspheres_lambertian.dae 480x360 -s 16 -l 4 -m 5, flat spacetime"),
+    "c3": ("cbbunny_microfacet_480x360", "CBbunny_microfacet_cu.dae", 1280, 720, 256, 4, 5, "flat",
+           "C3: CBbunny_microfacet_cu.dae 1280x720 -s 256 -l 4 -m 5, flat spacetime"),
+    "bunny_bh": ("cbbunny_microfacet_480x360", "CBbunny_microfacet_cu.dae", 1920, 1080, 16, 4, 5, "bh",
+                 "C4 substitute (CBdragon.dae is not in the reference tree): CBbunny_microfacet_cu.dae 1920x1080 -s 16 -l 4 -m 5, hole on"),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for k, nm in enumerate(names):
+                if len(r) > 3 + k and r[3 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        sm_load = sorted(sm)[len(sm) // 2:] if sm else []  # upper half = samples taken under load
+        return {"sm_mhz": float(np.median(sm_load)) if sm_load else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU arms
+def run_reference_binary(wl, spp, threads):
+    """One run of the UNMODIFIED reference CPU path tracer (oracle/_ref/ref_bh or ref_flat).  Returns (paths, seconds, rays)."""
+    fixture, dae, W, H, _, l, m, mode, _ = WORKLOADS[wl]
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_bh" if mode == "bh" else "ref_flat")
+    scene = os.path.join(ROOT, "oracle", "_ref", "dae", dae)
+    if not (os.path.exists(exe) and os.path.exists(scene)):
+        return None
+    with tempfile.TemporaryDirectory() as td:
+        out = os.path.join(td, "o.png")
+        cmd = [exe, "-t", str(threads), "-s", str(spp), "-l", str(l), "-m", str(m), "-r", str(W), str(H), "-f", out, scene]
+        t0 = time.perf_counter()
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        wall = time.perf_counter() - t0
+    txt = r.stdout
+    ms = re.findall(r"100%! \(([0-9.]+)s\)", txt)          # reference src/pathtracer.cpp:636
+    rays = re.findall(r"BVH traced (\d+) rays", txt)       # reference src/pathtracer.cpp:637
+    secs = float(ms[-1]) if ms else wall
+    return W * H * spp, secs, int(rays[-1]) if rays else 0
+
+
+def run_oracle_port(wl, spp):
+    from util import load_scene, sc
+    from oracle import orc
+    fixture, _, W, H, _, l, m, mode, _ = WORKLOADS[wl]
+    s = load_scene(fixture)
+    if (W, H) != (480, 360):
+        s.set_screen_size(W, H)
+    o = orc.Oracle(s)
+    o.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
+    o.set_frame(W, H)
+    t0 = time.perf_counter()
+    _, cnt, st = o.render(sc.make_params(ns_aa=spp, max_ray_depth=m, ns_area_light=l, seed=1))
+    return int(cnt.sum()), time.perf_counter() - t0, st["rays"]
+
+
+def cpu_sample(wl, spp=1):
+    cores = os.cpu_count() or 1
+    res = run_reference_binary(wl, spp, cores)
+    if res is not None:
+        paths, secs, rays = res
+        return {"value": paths / secs / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "reference",
+                "sample": "reference binary (oracle/_ref) -t %d, same frame at -s %d: %d paths in %.2f s, %d rays" % (cores, spp, paths, secs, rays)}
+    paths, secs, rays = run_oracle_port(wl, spp)
+    return {"value": paths / secs / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
+            "sample": "oracle port (OpenMP, %d threads), same frame at %d spp: %d paths in %.2f s, %d rays" % (cores, spp, paths, secs, rays)}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = args.workload
+    times, paths = [], 0
+    last = None
+    for i in range(args.warmup + args.steps):
+        last = cpu_sample(wl, 1)
+        m = re.search(r"(\d+) paths in ([0-9.]+) s", last["sample"])
+        if i >= args.warmup:
+            paths += int(m.group(1)); times.append(float(m.group(2)))
+    total = sum(times)
+    v = paths / total / 1e6
+    last["value"] = v
+    print(json.dumps({"impl": "reference", "metric": "Mpaths/s", "value": v, "unit": "Mpaths/s", "n_gpus": args.gpus, "steps": args.steps,
+                      "warmup": args.warmup, "ms_per_step": 1e3 * total / max(args.steps, 1), "higher_is_better": True, "scaling": "weak",
+                      "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                      "config": {"workload": WORKLOADS[wl][8], "sample": "each step = the same frame at 1 spp on the host cores"},
+                      "cpu_baseline": last, "e2e": {"value": v, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--spp", type=int, default=0, help="override samples per pixel")
+    ap.add_argument("--topology", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    from util import load_scene, sc
+    api = importlib.import_module("relativistic-ray-tracer_b200.api")
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    fixture, _, W, H, spp, l, m, mode, desc = WORKLOADS[args.workload]
+    if args.spp:
+        spp = args.spp
+    spp_job = spp * world                       # weak scaling: per-GPU paths fixed
+    s = load_scene(fixture)
+    if (W, H) != (480, 360):
+        s.set_screen_size(W, H)
+    ctx = api.Context(local)
+    ctx.set_option(api.OPT_BVH_TOPOLOGY, args.topology)
+    ctx.upload_scene(s)
+    ctx.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
+    ctx.set_frame(W, H)
+    ctx.set_tile_shard(16, rank, world)
+    # spp <= 32 keeps the reference's default adaptive batch (32) from ever triggering; above it the batch is the job's
+    # spp so that every rank traces exactly W*H*spp/N paths (stated in config)
+    batch = 32 if spp_job <= 32 else spp_job
+    params = sc.make_params(ns_aa=spp_job, max_ray_depth=m, ns_area_light=l, samples_per_batch=batch, seed=1)
+
+    frame = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def step_device():
+        st = ctx.render_device(params, frame.data_ptr(), 0, 0, want_stats=True)
+        if world > 1:
+            dist.reduce(frame, dst=0, op=dist.ReduceOp.SUM)
+        return st
+
+    for _ in range(args.warmup):
+        step_device()
+    # ---- instrumented pass (counters on) for the algorithmic-byte and work figures; deterministic, so it describes
+    # the timed passes exactly.  Timed passes run with counters off.
+    st_count = step_device()
+    ctx.set_option(api.OPT_COUNTERS, 0)
+    step_device()
+
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    trace_s, render_s, launches, trace_launches = 0.0, 0.0, 0, 0
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    for k in range(args.steps):
+        flush.zero_()                    # L2 flush between timed iterations (outside the events)
+        torch.cuda.synchronize()
+        ev[k][0].record()
+        st = step_device()
+        ev[k][1].record()
+        trace_s += st["trace_seconds"]; render_s += st["seconds"]; launches += st["kernel_launches"]; trace_launches += st["trace_launches"]
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    total_ms = sum(a.elapsed_time(b) for a, b in ev)
+    clk = clocks.stop() if rank == 0 else None
+
+    # ---- e2e: public host-buffer API; scene upload (pinned host arrays -> HBM, BVH build) + render + frame read-back
+    hdr = np.empty((H, W, 3), np.float32); cnt = np.empty((H, W), np.int32)
+    hdr_t = torch.from_numpy(hdr).pin_memory(); cnt_t = torch.from_numpy(cnt).pin_memory()
+    hdr_p, cnt_p = hdr_t.numpy(), cnt_t.numpy()
+    h2d = int(s.prim_kind.nbytes + s.prim_index.nbytes + s.tri_pos.nbytes + s.tri_nrm.nbytes + s.tri_mat.nbytes + s.sph.nbytes + s.sph_mat.nbytes +
+              s.mats.nbytes + s.lights.nbytes + 18 * 8 + 48)
+    d2h = int(hdr.nbytes + cnt.nbytes)
+    host_frame = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()
+
+    def step_e2e():
+        ctx.upload_scene(s)
+        if world == 1:
+            ctx.render(params, hdr_p, cnt_p, want_stats=False)
+        else:
+            ctx.render_device(params, frame.data_ptr(), 0, 0, want_stats=False)
+            dist.reduce(frame, dst=0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                host_frame.copy_(frame, non_blocking=False)
+    step_e2e()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+
+    t = torch.tensor([total_ms, e2e_s, trace_s, float(st_count["paths"]), float(st_count["geodesic_steps"]), float(st_count["rays"]),
+                      float(st_count["algorithmic_bytes"])], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        total_ms, e2e_s, trace_s = float(mx[0]), float(mx[1]), float(mx[2])
+        paths, steps_geo, rays, alg_bytes = float(sm[3]), float(sm[4]), float(sm[5]), float(sm[6])
+    else:
+        paths, steps_geo, rays, alg_bytes = [float(x) for x in t[3:7]]
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    secs = total_ms * 1e-3
+    peak, peak_src = peaks()
+    # roofline of the dominant kernel (trace: geodesic-advance + BVH intersect): rank-0 algorithmic bytes / rank-0 trace time
+    my_bytes = float(st_count["algorithmic_bytes"])
+    my_trace_s = float(t[2]) / max(args.steps, 1)
+    achieved = my_bytes / my_trace_s / 1e9 if my_trace_s > 0 else 0.0
+    line = {
+        "metric": "Mpaths/s", "value": paths * args.steps / secs / 1e6, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "frame": [W, H], "spp": spp_job, "ns_area_light": l, "max_ray_depth": m, "samples_per_batch": batch,
+                   "parallelism": "tile%d" % world, "bvh_topology": args.topology, "l2": "flushed between timed iterations (256 MiB write)",
+                   "scaling_rule": "frame fixed, spp = %d x n_gpus, 16x16 interleaved tiles, one NCCL reduce per frame" % spp},
+        "geodesic_steps_per_s": steps_geo * args.steps / secs, "rays_per_s": rays * args.steps / secs,
+        "paths_per_step": paths, "geodesic_steps_per_step": steps_geo, "rays_per_step": rays,
+        "e2e": {"value": paths * args.steps / e2e_s / 1e6, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "kernel": "k_trace_closest + k_trace_shadow (geodesic advance + BVH intersect)", "peak_source": peak_src,
+                     "algorithmic_bytes_per_step": my_bytes, "trace_ms_per_step": my_trace_s * 1e3,
+                     "trace_launches_per_step": trace_launches / max(args.steps, 1),
+                     "trace_share_of_step": trace_s / (render_s if render_s > 0 else 1.0),
+                     "note": "scene is L1/L2 resident for this workload (7-node BVH): the kernel is FP64-pipe bound, see DESIGN.md"},
+        "clocks": clk,
+    }
+    if not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_sample(args.workload, 1)
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
