@@ -93,6 +93,8 @@ int rrt_create(rrt_ctx** out, int device) {
   ctx->device = device;
   memset(ctx->opt, 0, sizeof ctx->opt);
   ctx->opt[RRT_OPT_COUNTERS] = 1;
+  ctx->opt[RRT_OPT_LEAF_SIZE] = 2;
+  ctx->opt[RRT_OPT_BVH_TOPOLOGY] = 1;
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaMallocHost((void**)&ctx->h_pinned, 4096)) != cudaSuccess) {
@@ -147,7 +149,7 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
     int32_t m = k == 0 ? s->tri_mat[idx] : s->sph_mat[idx];
     if (m < 0 || (uint32_t)m >= s->n_mats) FAIL(RRT_E_ARG, "rrt_upload_scene: material index out of range");
   }
-  rrt::build_bvh(s, (int)ctx->opt[RRT_OPT_BVH_TOPOLOGY], &ctx->bvh);
+  rrt::build_bvh(s, (int)ctx->opt[RRT_OPT_BVH_TOPOLOGY], (int)ctx->opt[RRT_OPT_LEAF_SIZE], &ctx->bvh);
   const rrt::FlatBvh& b = ctx->bvh;
   int tree_depth = 0;
   {  /* depth of the flattened tree bounds the traversal stack */
@@ -178,7 +180,7 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   d.prim_kind = ctx->d_kind.as<uint8_t>(); d.prim_index = ctx->d_index.as<uint32_t>(); d.prim_mat = ctx->d_pmat.as<int32_t>();
   d.sph = ctx->d_sph.as<double>(); d.mats = ctx->d_mats.as<rrt_material>(); d.lights = ctx->d_lights.as<rrt_light>();
   d.n_prims = (int)s->n_prims; d.n_mats = (int)s->n_mats; d.n_lights = (int)s->n_lights; d.root = b.root;
-  for (int k = 0; k < 3; ++k) { d.root_lo[k] = b.root_lo[k]; d.root_hi[k] = b.root_hi[k]; }
+  for (int k = 0; k < 3; ++k) { d.root_lo[k] = rrt::round_down_f(b.root_lo[k]); d.root_hi[k] = rrt::round_up_f(b.root_hi[k]); }
   ctx->n_lights = (int)s->n_lights; ctx->n_delta_lights = 0;
   for (uint32_t i = 0; i < s->n_lights; ++i) if (s->lights[i].is_delta) ctx->n_delta_lights++;
   ctx->have_scene = true;
@@ -226,7 +228,7 @@ int rrt_set_tile_shard(rrt_ctx* ctx, int tile, int rank, int world) {
 int rrt_bvh_build_host(const rrt_scene* scene, int topology, int32_t info[6], uint32_t* dfs_rank) {
   if (!scene || !info) return RRT_E_ARG;
   rrt::FlatBvh b;
-  rrt::build_bvh(scene, topology, &b);
+  rrt::build_bvh(scene, topology, 2, &b);
   info[0] = b.ref_nodes; info[1] = b.ref_leaves; info[2] = b.ref_depth; info[3] = b.n_nodes; info[4] = (int32_t)(b.leaf.size() / 10); info[5] = b.root;
   if (dfs_rank && !b.dfs_rank.empty()) memcpy(dfs_rank, b.dfs_rank.data(), 4 * b.dfs_rank.size());
   return RRT_OK;
@@ -449,7 +451,7 @@ int rrt_render_device(rrt_ctx* ctx, const rrt_params* p, void* d_rgbn, void* d_c
 }
 
 /* ---------------------------------------------------------------- parity hooks */
-struct HookIO {  // stage host arrays on the device, fetch results back
+struct HookStage {  // stage host arrays on the device, fetch results back
   rrt_ctx* ctx; size_t in_off = 0, out_off = 0;
   std::vector<std::pair<size_t, std::pair<void*, size_t>>> outs;
 };
@@ -479,19 +481,22 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
   if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_trace_rays: no scene");
   if (stats) memset(stats, 0, sizeof *stats);
   if (n == 0) return RRT_OK;
-  int rc = hook_begin(ctx, 64 * (size_t)n + 4096, sizeof(rrt_hit) * (size_t)n + 256);
+  if (n >= ((int64_t)1 << 30)) FAIL(RRT_E_ARG, "rrt_trace_rays: at most 2^30 rays per call");
+  int rc = hook_begin(ctx, 64 * (size_t)n + 4096, sizeof(rrt_hit) * (size_t)n + 1024);
   if (rc) return rc;
   size_t io = 0, oo = 0;
   double* d_o = (double*)hook_in(ctx, io, o, 24 * (size_t)n); double* d_d = (double*)hook_in(ctx, io, d, 24 * (size_t)n);
   double* d_mn = (double*)hook_in(ctx, io, min_t, 8 * (size_t)n); double* d_mx = (double*)hook_in(ctx, io, max_t, 8 * (size_t)n);
   rrt_hit* d_out = (rrt_hit*)hook_out(ctx, oo, sizeof(rrt_hit) * (size_t)n);
   Counters* gc = (Counters*)hook_out(ctx, oo, sizeof(Counters));
+  int* d_cursor = (int*)hook_out(ctx, oo, 256);
   CK(cudaMemsetAsync(gc, 0, sizeof(Counters), ctx->stream));
+  CK(cudaMemsetAsync(d_cursor, 0, 4, ctx->stream));
   cudaEvent_t e0, e1; ctx->events_used = 0; e0 = next_event(ctx); e1 = next_event(ctx);
   CK(cudaEventRecord(e0, ctx->stream));
-  int grid = grid_for(n, RRT_BLOCK);
-  if (any_hit) k_hook_trace<true><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, n, d_o, d_d, d_mn, d_mx, d_out, gc);
-  else k_hook_trace<false><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, n, d_o, d_d, d_mn, d_mx, d_out, gc);
+  int grid = (int)std::min<int64_t>((n + RRT_BLOCK - 1) / RRT_BLOCK, (int64_t)ctx->sm_count * 4);
+  if (any_hit) k_hook_trace<true><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc);
+  else k_hook_trace<false><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc);
   CK(cudaEventRecord(e1, ctx->stream));
   CK(cudaMemcpyAsync(out, d_out, sizeof(rrt_hit) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));

@@ -28,6 +28,7 @@ struct Builder {
   std::vector<Box> pbox;        // Primitive::get_bbox (reference src/static_scene/triangle.cpp:11-19, sphere.h:30-32)
   std::vector<double> pcen;     // 3 per prim: BBox::centroid() = (min + max) / 2, i.e. 0.5 * (min + max)  (src/bbox.h:98-100)
   std::vector<uint32_t> tmp;
+  uint32_t max_leaf = 4;
 
   void prepare() {
     uint32_t n = s->n_prims;
@@ -97,7 +98,7 @@ struct Builder {
     Box bb = bounds(prims, n);
     t.nodes[me].bb = bb; t.nodes[me].l = t.nodes[me].r = -1; t.nodes[me].start = t.nodes[me].count = 0;
     if (depth > t.depth) t.depth = depth;
-    if (n <= 4) {
+    if (n <= max_leaf) {
       t.nodes[me].start = (int)base; t.nodes[me].count = (int)n; t.leaves++;
       return me;
     }
@@ -114,7 +115,8 @@ struct Builder {
       double scale = NB / w;
       for (uint32_t i = 0; i < n; ++i) {
         int b = (int)((pcen[3 * (size_t)prims[i] + axis] - clo[axis]) * scale);
-        if (b >= NB) b = NB - 1; if (b < 0) b = 0;
+        if (b >= NB) b = NB - 1;
+        if (b < 0) b = 0;
         box_expand(bbx[b], pbox[prims[i]]); cnt[b]++;
       }
       double ra[NB]; uint32_t rc[NB]; Box acc; box_reset(acc); uint32_t c = 0;
@@ -132,7 +134,8 @@ struct Builder {
       double w = chi[best_axis] - clo[best_axis], scale = NB / w;
       for (uint32_t i = 0; i < n; ++i) {
         int b = (int)((pcen[3 * (size_t)prims[i] + best_axis] - clo[best_axis]) * scale);
-        if (b >= NB) b = NB - 1; if (b < 0) b = 0;
+        if (b >= NB) b = NB - 1;
+        if (b < 0) b = 0;
         if (b <= best_bin) prims[nl++] = prims[i]; else tmp[nr++] = prims[i];
       }
       memcpy(prims + nl, tmp.data(), sizeof(uint32_t) * nr);
@@ -153,7 +156,10 @@ inline float as_f32(int32_t i) { float f; memcpy(&f, &i, 4); return f; }
 
 }  // namespace
 
-int build_bvh(const rrt_scene* s, int topology, FlatBvh* out) {
+float round_down_f(double x) { return round_down(x); }
+float round_up_f(double x) { return round_up(x); }
+
+int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out) {
   *out = FlatBvh();
   uint32_t n = s->n_prims;
   out->dfs_rank.assign(n, 0);
@@ -161,6 +167,7 @@ int build_bvh(const rrt_scene* s, int topology, FlatBvh* out) {
   for (uint32_t p = 0; p < n; ++p) out->prim_mat[p] = s->prim_kind[p] == 0 ? s->tri_mat[s->prim_index[p]] : s->sph_mat[s->prim_index[p]];
   if (n == 0) { out->root = -1; /* ~(-1) = 0: an empty leaf */ return 0; }
   Builder b; b.s = s; b.prepare();
+  b.max_leaf = (uint32_t)(max_leaf < 1 ? 1 : max_leaf > 7 ? 7 : max_leaf);
 
   Tree ref; ref.order.resize(n);
   for (uint32_t i = 0; i < n; ++i) ref.order[i] = i;

@@ -33,7 +33,11 @@ struct FlatBvh {
   int ref_nodes = 0, ref_leaves = 0, ref_depth = 0; // shape of the reference tree (nodes incl. leaves)
 };
 
-// topology: 0 = reference shape (midpoint split), 1 = binned SAH (own shape; ranks still come from the reference shape)
-int build_bvh(const rrt_scene* s, int topology, FlatBvh* out);
+// topology: 0 = reference shape (midpoint split, leaves <= 4), 1 = binned SAH with leaves of <= max_leaf primitives
+// (own shape; ranks still come from the reference shape).  max_leaf is clamped to 1..7 and ignored for topology 0.
+int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out);
+// outward float rounding used for every box the device sees
+float round_down_f(double x);
+float round_up_f(double x);
 
 }  // namespace rrt

@@ -72,47 +72,6 @@ __device__ __forceinline__ void flush_counters(const Counters& c, Counters* g) {
   }
 }
 
-/* ---------------------------------------------------------------- BVHAccel::intersect for one ray */
-template <bool ANY, bool COUNT>
-__device__ __forceinline__ void trace_ray(const DevScene& sc, const DevHole& bh, d3 o, d3 d, double tmin, double tmax, bool want_geo,
-                                          Hit& hit, int* stack, Counters& cnt) {
-  hit.status = 0; hit.prim = -1; hit.chord = 0; hit.steps = 0; hit.t = 0.0;
-  if (COUNT) cnt.rays++;
-  Seg s; Best best;
-  bool found = false;
-  if (bh.mode == RRT_MODE_FLAT) {
-    s.o = o; s.d = d; s.tmin = tmin; s.tmax = tmax;
-    hit.steps = 1;
-    if (COUNT) cnt.steps++;
-    found = traverse<ANY, COUNT>(sc, s, best, stack, RRT_BLOCK, cnt);
-  } else {
-    double len = 0.0;
-    int j = 0;
-    for (; j < bh.nchords; ++j) {
-      next_micro_ray(bh, o, d, len);
-      if (COUNT) cnt.steps++;
-      if (horizon_hit(bh, o, d, len)) { hit.status = 2; hit.chord = j; hit.steps = j + 1; return; }
-      s.o = o; s.d = d; s.tmin = 0.0; s.tmax = len;
-      if (traverse<ANY, COUNT>(sc, s, best, stack, RRT_BLOCK, cnt)) { found = true; break; }
-    }
-    hit.chord = found ? j : j - 1; hit.steps = found ? j + 1 : j;
-  }
-  if (!found) return;
-  hit.status = 1; hit.prim = best.prim; hit.t = best.t;
-  if (!want_geo) return;
-  hit.p = vadd(s.o, vmul(s.d, best.t));
-  hit.w_out = vneg(s.d);
-  uint32_t idx = sc.prim_index[best.prim];
-  if (best.kind == 0) {
-    const double* N = sc.tri_nrm + 9 * (size_t)idx;
-    double b0 = 1 - best.b1 - best.b2;
-    hit.n = vadd(vadd(smul(b0, D3(N[0], N[1], N[2])), smul(best.b1, D3(N[3], N[4], N[5]))), smul(best.b2, D3(N[6], N[7], N[8])));
-  } else {
-    const double* c = sc.sph + 4 * (size_t)idx;
-    hit.n = vunit(vsub(vadd(s.o, vmul(s.d, best.t)), D3(c[0], c[1], c[2])));
-  }
-}
-
 /* ---------------------------------------------------------------- generate: Camera::generate_ray per path slot
  * (reference src/part1_code.cpp:125-145,182-187) */
 __global__ void __launch_bounds__(256) k_generate(const __grid_constant__ DevCamera cam, const __grid_constant__ RenderK rk,
@@ -142,63 +101,7 @@ __global__ void __launch_bounds__(256) k_generate(const __grid_constant__ DevCam
   if (blockIdx.x == 0 && threadIdx.x == 0) q.ctl[0] = npaths;
 }
 
-/* ---------------------------------------------------------------- trace: closest hit for the extension queue.
- * Persistent warps pull 32 rays at a time from a device-side cursor. */
-template <bool COUNT>
-__global__ void __launch_bounds__(RRT_BLOCK, 4) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
-                                                                const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
-                                                                int* cursor, int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt) {
-  __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
-  int* stack = stack_mem + threadIdx.x;
-  Counters cnt = {0, 0, 0, 0, 0, 0};
-  const int n = *count_ptr;
-  while (true) {
-    int base = 0;
-    if (lane_id() == 0) base = atomicAdd(cursor, 32);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= n) break;
-    int i = base + lane_id();
-    if (i < n) {
-      d3 o = D3(ray[i], ray[cap + i], ray[2 * cap + i]), d = D3(ray[3 * cap + i], ray[4 * cap + i], ray[5 * cap + i]);
-      Hit h;
-      trace_ray<false, COUNT>(sc, bh, o, d, ray[6 * cap + i], ray[7 * cap + i], true, h, stack, cnt);
-      h_prim[i] = h.status == 1 ? h.prim : (h.status == 2 ? -2 : -1);
-      if (h.status == 1) {
-        h_geo[i] = h.p.x; h_geo[cap + i] = h.p.y; h_geo[2 * cap + i] = h.p.z;
-        h_geo[3 * cap + i] = h.w_out.x; h_geo[4 * cap + i] = h.w_out.y; h_geo[5 * cap + i] = h.w_out.z;
-        h_geo[6 * cap + i] = h.n.x; h_geo[7 * cap + i] = h.n.y; h_geo[8 * cap + i] = h.n.z;
-      }
-    }
-    __syncwarp();
-  }
-  if (COUNT) flush_counters(cnt, gcnt);
-}
-
-/* shadow rays: BVHAccel::intersect(ray) (any hit), or closest hit when the hemisphere estimator needs the emitter */
-template <bool ANY, bool COUNT>
-__global__ void __launch_bounds__(RRT_BLOCK, 4) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
-                                                               const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
-                                                               int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt) {
-  __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
-  int* stack = stack_mem + threadIdx.x;
-  Counters cnt = {0, 0, 0, 0, 0, 0};
-  const int n = *count_ptr;
-  while (true) {
-    int base = 0;
-    if (lane_id() == 0) base = atomicAdd(cursor, 32);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= n) break;
-    int i = base + lane_id();
-    if (i < n) {
-      d3 o = D3(ray[i], ray[cap + i], ray[2 * cap + i]), d = D3(ray[3 * cap + i], ray[4 * cap + i], ray[5 * cap + i]);
-      Hit h;
-      trace_ray<ANY, COUNT>(sc, bh, o, d, 0.0, ray[6 * cap + i], false, h, stack, cnt);
-      res[cidx[i]] = h.status == 1 ? h.prim : -1;
-    }
-    __syncwarp();
-  }
-  if (COUNT) flush_counters(cnt, gcnt);
-}
+#include "rrt_wavetrace.cuh"
 
 /* ---------------------------------------------------------------- shade: est_radiance_global_illumination /
  * at_least_one_bounce_radiance / estimate_direct_lighting_* unrolled over the wavefront
@@ -487,32 +390,6 @@ __global__ void __launch_bounds__(RRT_CBLOCK) k_compact_scatter(Keep keep, const
 }
 
 /* ---------------------------------------------------------------- parity hooks (one thread per item) */
-template <bool ANY>
-__global__ void __launch_bounds__(RRT_BLOCK, 4) k_hook_trace(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, long long n,
-                                                            const double* __restrict__ o, const double* __restrict__ d, const double* __restrict__ tmin,
-                                                            const double* __restrict__ tmax, rrt_hit* __restrict__ out, Counters* gcnt) {
-  __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
-  int* stack = stack_mem + threadIdx.x;
-  Counters cnt = {0, 0, 0, 0, 0, 0};
-  long long nround = (n + 31) / 32 * 32;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nround; i += (long long)gridDim.x * blockDim.x) {
-    if (i < n) {
-      Hit h; h.p = h.w_out = h.n = D3(0, 0, 0);
-      trace_ray<ANY, true>(sc, bh, D3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), D3(d[3 * i], d[3 * i + 1], d[3 * i + 2]), tmin ? tmin[i] : 0.0,
-                           tmax ? tmax[i] : (double)INFINITY, !ANY, h, stack, cnt);
-      rrt_hit r;
-      r.status = h.status; r.prim = (h.status == 1 && !ANY) ? h.prim : -1; r.chord = h.chord; r.steps = h.steps;
-      r.t = h.status == 1 ? h.t : 0.0;
-      bool geo = h.status == 1 && !ANY;
-      r.hit_p[0] = geo ? h.p.x : 0; r.hit_p[1] = geo ? h.p.y : 0; r.hit_p[2] = geo ? h.p.z : 0;
-      r.w_out[0] = geo ? h.w_out.x : 0; r.w_out[1] = geo ? h.w_out.y : 0; r.w_out[2] = geo ? h.w_out.z : 0;
-      r.n[0] = geo ? h.n.x : 0; r.n[1] = geo ? h.n.y : 0; r.n[2] = geo ? h.n.z : 0;
-      out[i] = r;
-    }
-  }
-  flush_counters(cnt, gcnt);
-}
-
 __global__ void k_hook_geodesic(const __grid_constant__ DevHole bh, long long n, const double* __restrict__ o, const double* __restrict__ d, int nsteps,
                                 double* __restrict__ seg) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {

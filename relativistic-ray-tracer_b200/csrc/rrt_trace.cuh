@@ -3,7 +3,7 @@
 // src/static_scene/sphere.cpp:10-53, src/static_scene/triangle.cpp:25-55, src/bbox.cpp:10-25.
 //
 // Exactness contract (DESIGN.md "Numerics"): chord recurrence, horizon test and primitive tests are IEEE
-// double in the reference's operation order (bit-identical results); interior-node slab tests are
+// double in the reference's operation order (bit-identical results); interior-node slab tests are FP32 and
 // CONSERVATIVE (never reject a box the reference accepts), so which leaves get tested may be a superset
 // of the reference's, and the primitive tests alone decide the hit.  Equal-t ties go to the primitive
 // with the higher reference depth-first rank (the reference keeps the last one it visits).
@@ -24,7 +24,7 @@ struct DevScene {
   const rrt_material* mats;
   const rrt_light* lights;
   int32_t n_prims, n_mats, n_lights, root;
-  double root_lo[3], root_hi[3];
+  float root_lo[3], root_hi[3];   // root box, rounded outward
 };
 
 struct DevHole {            // global_black_hole (reference src/static_scene/blackhole.cpp:5) + per-frame constants
@@ -91,23 +91,54 @@ __device__ __forceinline__ bool horizon_hit(const DevHole& bh, d3 o, d3 d, doubl
   return (0.0 <= t1 && t1 <= len) || (0.0 <= t2 && t2 <= len);
 }
 
-/* Conservative version of BBox::intersect (reference src/bbox.cpp:10-25).  The reference divides by d six times;
- * here the three reciprocals are formed once per chord and the result is widened by 2^-40 relative, far more than
- * the two roundings that separate (b - o) * (1/d) from (b - o) / d, so every box the reference accepts is accepted.
- * min/max keep the reference's argument order, hence its NaN behaviour for rays lying in a slab plane.
- * Requires tmin >= 0 (true for chords and for every ray the estimator makes).  Returns the entry distance. */
-__device__ __forceinline__ bool box_hit(float lox, float loy, float loz, float hix, float hiy, float hiz, const d3& o,
-                                        const d3& inv, double seg_tmin, double seg_tmax, double& tnear) {
-  const double GROW = 1.0 + 9.094947017729282e-13, SHRINK = 1.0 - 9.094947017729282e-13;
-  double tx0 = ((double)lox - o.x) * inv.x, tx1 = ((double)hix - o.x) * inv.x;
-  double ty0 = ((double)loy - o.y) * inv.y, ty1 = ((double)hiy - o.y) * inv.y;
-  double tz0 = ((double)loz - o.z) * inv.z, tz1 = ((double)hiz - o.z) * inv.z;
-  double tmn = cmax(cmax(cmin(tx0, tx1), cmin(ty0, ty1)), cmin(tz0, tz1));
-  double tmx = cmin(cmin(cmax(tx0, tx1), cmax(ty0, ty1)), cmax(tz0, tz1));
-  tmn = tmn * (tmn > 0 ? SHRINK : GROW);
-  tmx = tmx * GROW;
-  tnear = tmn;
-  return tmn <= tmx && tmn <= seg_tmax && tmx >= seg_tmin;
+/* Conservative FP32 version of BBox::intersect (reference src/bbox.cpp:10-25).  The reference evaluates
+ * t = (plane - o) / d in double for the six planes; here one chord-constant context holds o and 1/d rounded to float
+ * and every plane parameter is widened by a rigorous bound on what those roundings can do, so that every box the
+ * reference accepts is accepted here (the reverse need not hold: the exact primitive tests decide the hit):
+ *   t_f = fl((b - o_f) * i_f),  o_f = fl(o), i_f = fl(1 / fl(d))
+ *   |t - t_f| <= |t_f| * 4u + |o - o_f| * |1/d| * (1 + 4u),  u = 2^-24
+ * widened to |t_f| * 2^-20 + A with A = 2^-23 * |o_f| * |i_f| per axis (2x slack on the origin term, 4x on the
+ * relative term).  Direction components below 1e-30 are flushed to a signed zero (i_f = +-inf, A = inf), which
+ * removes the float-denormal case from the analysis; NaN parameters are dropped by fminf/fmaxf, which only ever
+ * widens the interval.  Node boxes are already rounded outward from the reference's doubles on the host.
+ * Requires tmin >= 0 (true for chords and for every ray the estimator makes). */
+struct BoxCtx {
+  float ox, oy, oz, ix, iy, iz, ax, ay, az, tmin;
+  bool nx, ny, nz;   /* direction component negative: the near plane is the box maximum */
+};
+__device__ __forceinline__ void boxctx_axis(double o, double d, float& of, float& inv, float& a, bool& neg) {
+  float df = (float)d;
+  if (fabsf(df) < 1e-30f) df = copysignf(0.f, df);
+  of = (float)o; inv = 1.0f / df;
+  a = 1.1920929e-7f * fabsf(of) * fabsf(inv);
+  neg = __float_as_int(df) < 0;
+}
+__device__ __forceinline__ void boxctx_make(const d3& o, const d3& d, double tmin, BoxCtx& c) {
+  boxctx_axis(o.x, d.x, c.ox, c.ix, c.ax, c.nx);
+  boxctx_axis(o.y, d.y, c.oy, c.iy, c.ay, c.ny);
+  boxctx_axis(o.z, d.z, c.oz, c.iz, c.az, c.nz);
+  c.tmin = __double2float_rd(tmin);
+}
+__device__ __forceinline__ bool box_hit(float lox, float loy, float loz, float hix, float hiy, float hiz, const BoxCtx& c, float tmaxf,
+                                        float& tnear) {
+  const float R = 9.5367431640625e-7f; /* 2^-20 */
+  float tnx = __fmaf_rn((c.nx ? hix : lox) - c.ox, c.ix, -c.ax), tfx = __fmaf_rn((c.nx ? lox : hix) - c.ox, c.ix, c.ax);
+  float tny = __fmaf_rn((c.ny ? hiy : loy) - c.oy, c.iy, -c.ay), tfy = __fmaf_rn((c.ny ? loy : hiy) - c.oy, c.iy, c.ay);
+  float tnz = __fmaf_rn((c.nz ? hiz : loz) - c.oz, c.iz, -c.az), tfz = __fmaf_rn((c.nz ? loz : hiz) - c.oz, c.iz, c.az);
+  float tn = fmaxf(fmaxf(tnx, tny), tnz), tf = fminf(fminf(tfx, tfy), tfz);
+  tn = __fmaf_rn(fabsf(tn), -R, tn);
+  tf = __fmaf_rn(fabsf(tf), R, tf);
+  tnear = tn;
+  return tn <= tf && tn <= tmaxf && tf >= c.tmin;
+}
+
+/* True when x * (1 / det) is certainly a negative, non-zero number: opposite signs and both magnitudes far enough
+ * from the ends of the exponent range that the product can neither underflow to (-)0 nor involve inf/NaN.  Used to
+ * reject a triangle before the division; anything this test does not cover takes the literal path below. */
+__device__ __forceinline__ bool surely_negative(double x, double det) {
+  int hx = __double2hiint(x), hd = __double2hiint(det);
+  unsigned ex = ((unsigned)hx >> 20) & 0x7ffu, ed = ((unsigned)hd >> 20) & 0x7ffu;
+  return ((hx ^ hd) < 0) && (ex - 523u < 1524u) && (ed - 1u < 1523u);
 }
 
 /* Triangle::intersect and Sphere::intersect on one 80-byte leaf record.  Accepts when the reference would and the
@@ -123,10 +154,19 @@ __device__ __forceinline__ bool leaf_record_test(const double2* __restrict__ rec
   if (kind == 0) {
     if (COUNT) cnt.tris++;
     d3 p0 = D3(a0.x, a0.y, a1.x), e1 = D3(a1.y, a2.x, a2.y), e2 = D3(a3.x, a3.y, a4.x);
+    /* same products as the reference; the three sign tests only skip work whose outcome is already decided */
+    d3 s1 = vcross(s.d, e2);
+    double det = vdot(s1, e1);
     d3 sv = vsub(s.o, p0);
-    d3 s1 = vcross(s.d, e2), s2 = vcross(sv, e1);
-    double inv = 1. / vdot(s1, e1);
-    t = vdot(s2, e2) * inv; b1 = vdot(s1, sv) * inv; b2 = vdot(s2, s.d) * inv;
+    double x1 = vdot(s1, sv);
+    if (surely_negative(x1, det)) return false;   /* b1 < 0 */
+    d3 s2 = vcross(sv, e1);
+    double x2 = vdot(s2, s.d);
+    if (surely_negative(x2, det)) return false;   /* b2 < 0 */
+    double xt = vdot(s2, e2);
+    if (surely_negative(xt, det)) return false;   /* t < 0 <= min_t */
+    double inv = 1. / det;
+    t = xt * inv; b1 = x1 * inv; b2 = x2 * inv;
     double b0 = 1 - b1 - b2;
     if (!(s.tmin <= t && t <= best.t && b0 >= 0 && b1 >= 0 && b2 >= 0)) return false;
   } else {
@@ -150,19 +190,11 @@ __device__ __forceinline__ bool leaf_record_test(const double2* __restrict__ rec
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt) {
   best.t = s.tmax; best.rank = -1; best.prim = -1; best.kind = 0; best.b1 = best.b2 = 0.0;
-  d3 inv = D3(1.0 / s.d.x, 1.0 / s.d.y, 1.0 / s.d.z);
+  BoxCtx bc; boxctx_make(s.o, s.d, s.tmin, bc);
+  float tmaxf = __double2float_ru(best.t);
   bool found = false;
-  {
-    /* root box in full double precision */
-    double tx0 = (sc.root_lo[0] - s.o.x) * inv.x, tx1 = (sc.root_hi[0] - s.o.x) * inv.x;
-    double ty0 = (sc.root_lo[1] - s.o.y) * inv.y, ty1 = (sc.root_hi[1] - s.o.y) * inv.y;
-    double tz0 = (sc.root_lo[2] - s.o.z) * inv.z, tz1 = (sc.root_hi[2] - s.o.z) * inv.z;
-    double tmn = cmax(cmax(cmin(tx0, tx1), cmin(ty0, ty1)), cmin(tz0, tz1));
-    double tmx = cmin(cmin(cmax(tx0, tx1), cmax(ty0, ty1)), cmax(tz0, tz1));
-    const double GROW = 1.0 + 9.094947017729282e-13, SHRINK = 1.0 - 9.094947017729282e-13;
-    tmn = tmn * (tmn > 0 ? SHRINK : GROW); tmx = tmx * GROW;
-    if (!(tmn <= tmx && tmn <= s.tmax && tmx >= s.tmin)) return false;
-  }
+  float tl, tr;
+  if (!box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tl)) return false;
   int cur = sc.root;
   int sp = 0;
   while (true) {
@@ -173,6 +205,7 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best&
         if (leaf_record_test<COUNT>(sc.leaf + 5 * (size_t)(first + k), s, best, cnt)) {
           found = true;
           if (ANY) return true;
+          tmaxf = __double2float_ru(best.t);
         }
       }
       if (sp == 0) break;
@@ -182,9 +215,8 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best&
     const float4* nd = sc.nodes + 4 * (size_t)cur;
     float4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2), q3 = __ldg(nd + 3);
     if (COUNT) cnt.nodes++;
-    double tl, tr;
-    bool hl = box_hit(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, s.o, inv, s.tmin, best.t, tl);
-    bool hr = box_hit(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, s.o, inv, s.tmin, best.t, tr);
+    bool hl = box_hit(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, bc, tmaxf, tl);
+    bool hr = box_hit(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, bc, tmaxf, tr);
     int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
     if (hl && hr) {
       if (tr < tl) { int t = cl; cl = cr; cr = t; }

@@ -1,0 +1,186 @@
+// rrt_wavetrace.cuh — the trace kernel: BVHAccel::intersect (reference src/bvh.cpp:99-138) for a queue of rays.
+//
+// Persistent warps.  Rays need anywhere from 1 to 63 chords, so a warp that waited for its slowest ray would idle
+// most lanes (measured on the first version: 9-12 active threads per instruction).  Here every LANE owns one ray
+// and replaces it the moment it finishes: the warp reserves RRT_POOL consecutive queue entries with one atomic,
+// hands them to free lanes with ballot + popc, and only goes back to the global cursor when its pool is empty.
+// One loop trip = at most one chord per lane: geodesic advance, horizon test, BVH traversal of that chord.
+//
+// IO policies say where rays come from and where results go (extension queue, shadow queue, parity hook), so the
+// three kernels run the same loop.
+#pragma once
+#include "rrt_trace.cuh"
+
+#ifndef RRT_BLOCK
+#define RRT_BLOCK 128
+#endif
+#define RRT_POOL 128  /* queue entries a warp reserves per atomic */
+
+__device__ __forceinline__ int wt_lane() { return threadIdx.x & 31; }
+
+/* hit geometry as Triangle::intersect / Sphere::intersect store it (reference src/static_scene/triangle.cpp:46-52,
+ * sphere.cpp:44-50): hit_p = o + d t, w_out = -d, n = barycentric blend of the vertex normals (NOT normalised) or
+ * the unit sphere normal */
+__device__ __forceinline__ void fill_geo(const DevScene& sc, const Seg& s, const Best& best, Hit& hit) {
+  hit.p = vadd(s.o, vmul(s.d, best.t));
+  hit.w_out = vneg(s.d);
+  uint32_t idx = sc.prim_index[best.prim];
+  if (best.kind == 0) {
+    const double* N = sc.tri_nrm + 9 * (size_t)idx;
+    double b0 = 1 - best.b1 - best.b2;
+    hit.n = vadd(vadd(smul(b0, D3(N[0], N[1], N[2])), smul(best.b1, D3(N[3], N[4], N[5]))), smul(best.b2, D3(N[6], N[7], N[8])));
+  } else {
+    const double* c = sc.sph + 4 * (size_t)idx;
+    hit.n = vunit(vsub(vadd(s.o, vmul(s.d, best.t)), D3(c[0], c[1], c[2])));
+  }
+}
+
+struct ClosestIO {   // extension queue -> hit records for the shade kernel
+  const double* ray; size_t cap; int* h_prim; double* h_geo;
+  static constexpr bool GEO = true;
+  __device__ __forceinline__ void load(int i, d3& o, d3& d, double& tmin, double& tmax) const {
+    o = D3(ray[i], ray[cap + i], ray[2 * cap + i]); d = D3(ray[3 * cap + i], ray[4 * cap + i], ray[5 * cap + i]);
+    tmin = ray[6 * cap + i]; tmax = ray[7 * cap + i];
+  }
+  __device__ __forceinline__ void store(int i, const Hit& h) const {
+    h_prim[i] = h.status == 1 ? h.prim : (h.status == 2 ? -2 : -1);
+    if (h.status == 1) {
+      h_geo[i] = h.p.x; h_geo[cap + i] = h.p.y; h_geo[2 * cap + i] = h.p.z;
+      h_geo[3 * cap + i] = h.w_out.x; h_geo[4 * cap + i] = h.w_out.y; h_geo[5 * cap + i] = h.w_out.z;
+      h_geo[6 * cap + i] = h.n.x; h_geo[7 * cap + i] = h.n.y; h_geo[8 * cap + i] = h.n.z;
+    }
+  }
+};
+
+struct ShadowIO {    // shadow queue -> verdict in the contribution table
+  const double* ray; size_t cap; const uint32_t* cidx; int* res;
+  static constexpr bool GEO = false;
+  __device__ __forceinline__ void load(int i, d3& o, d3& d, double& tmin, double& tmax) const {
+    o = D3(ray[i], ray[cap + i], ray[2 * cap + i]); d = D3(ray[3 * cap + i], ray[4 * cap + i], ray[5 * cap + i]);
+    tmin = 0.0; tmax = ray[6 * cap + i];
+  }
+  __device__ __forceinline__ void store(int i, const Hit& h) const { res[cidx[i]] = h.status == 1 ? h.prim : -1; }
+};
+
+template <bool ANY>
+struct HookIO {      // rrt_trace_rays: host-layout arrays in, rrt_hit out
+  const double* o; const double* d; const double* tmin; const double* tmax; rrt_hit* out;
+  static constexpr bool GEO = !ANY;
+  __device__ __forceinline__ void load(int i, d3& ro, d3& rd, double& mn, double& mx) const {
+    ro = D3(o[3 * (size_t)i], o[3 * (size_t)i + 1], o[3 * (size_t)i + 2]); rd = D3(d[3 * (size_t)i], d[3 * (size_t)i + 1], d[3 * (size_t)i + 2]);
+    mn = tmin ? tmin[i] : 0.0; mx = tmax ? tmax[i] : (double)INFINITY;
+  }
+  __device__ __forceinline__ void store(int i, const Hit& h) const {
+    rrt_hit r;
+    bool geo = h.status == 1 && !ANY;
+    r.status = h.status; r.prim = geo ? h.prim : -1; r.chord = h.chord; r.steps = h.steps;
+    r.t = h.status == 1 ? h.t : 0.0;
+    r.hit_p[0] = geo ? h.p.x : 0; r.hit_p[1] = geo ? h.p.y : 0; r.hit_p[2] = geo ? h.p.z : 0;
+    r.w_out[0] = geo ? h.w_out.x : 0; r.w_out[1] = geo ? h.w_out.y : 0; r.w_out[2] = geo ? h.w_out.z : 0;
+    r.n[0] = geo ? h.n.x : 0; r.n[1] = geo ? h.n.y : 0; r.n[2] = geo ? h.n.z : 0;
+    out[i] = r;
+  }
+};
+
+__device__ __forceinline__ void wt_flush_counters(const Counters& c, Counters* g) {
+  unsigned long long v[5] = {c.rays, c.steps, c.nodes, c.tris, c.sph};
+  unsigned long long* dst = (unsigned long long*)g;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    unsigned long long x = v[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (wt_lane() == 0 && x) atomicAdd(dst + k, x);
+  }
+}
+
+template <bool ANY, bool COUNT, class IO>
+__device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHole& bh, const IO& io, const int n, int* cursor, Counters* gcnt) {
+  __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
+  int* stack = stack_mem + threadIdx.x;
+  Counters cnt = {0, 0, 0, 0, 0, 0};
+  const bool flat = bh.mode == RRT_MODE_FLAT;
+  const unsigned lt_mask = (1u << wt_lane()) - 1u;
+  int pool_next = 0, pool_end = 0;   /* warp-uniform */
+  bool more = true;                  /* warp-uniform: the global queue may still have entries */
+  bool has = false;
+  int idx = 0, j = 0;
+  d3 o = D3(0, 0, 0), d = D3(0, 0, 0);
+  double len = 0.0, tmin = 0.0, tmax = 0.0;
+  while (true) {
+    /* ---- hand queue entries to the lanes that have none */
+    unsigned need = __ballot_sync(0xffffffffu, !has);
+    while (need) {
+      if (pool_next >= pool_end) {
+        if (!more) break;
+        int base = 0;
+        if (wt_lane() == 0) base = atomicAdd(cursor, RRT_POOL);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) { more = false; break; }
+        pool_next = base; pool_end = min(base + RRT_POOL, n);
+      }
+      const int avail = pool_end - pool_next;
+      const int rank = __popc(need & lt_mask);
+      if (!has && rank < avail) {
+        idx = pool_next + rank;
+        io.load(idx, o, d, tmin, tmax);
+        has = true; j = 0; len = 0.0;
+        if (COUNT) cnt.rays++;
+      }
+      pool_next += min(__popc(need), avail);
+      need = __ballot_sync(0xffffffffu, !has);
+    }
+    if (!__any_sync(0xffffffffu, has)) break;
+    /* ---- one chord for every lane that holds a ray */
+    if (has) {
+      Hit h; h.status = -1;
+      Seg s; Best best;
+      if (flat) { s.o = o; s.d = d; s.tmin = tmin; s.tmax = tmax; }
+      else {
+        next_micro_ray(bh, o, d, len);
+        s.o = o; s.d = d; s.tmin = 0.0; s.tmax = len;
+        if (horizon_hit(bh, o, d, len)) { h.status = 2; h.prim = -1; h.chord = j; h.steps = j + 1; h.t = 0.0; }
+      }
+      if (COUNT) cnt.steps++;
+      if (h.status < 0) {
+        if (traverse<ANY, COUNT>(sc, s, best, stack, RRT_BLOCK, cnt)) {
+          h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
+          if (IO::GEO) fill_geo(sc, s, best, h);
+        } else {
+          ++j;
+          if (flat || j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = flat ? 0 : j - 1; h.steps = flat ? 1 : j; h.t = 0.0; }
+        }
+      }
+      if (h.status >= 0) { io.store(idx, h); has = false; }
+    }
+    __syncwarp();
+  }
+  if (COUNT) wt_flush_counters(cnt, gcnt);
+}
+
+/* extension rays: closest hit */
+template <bool COUNT>
+__global__ void __launch_bounds__(RRT_BLOCK, 4) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+                                                                const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
+                                                                int* cursor, int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt) {
+  ClosestIO io; io.ray = ray; io.cap = cap; io.h_prim = h_prim; io.h_geo = h_geo;
+  trace_persistent<false, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
+}
+
+/* shadow rays: BVHAccel::intersect(ray) (any hit), or closest hit when the hemisphere estimator needs the emitter */
+template <bool ANY, bool COUNT>
+__global__ void __launch_bounds__(RRT_BLOCK, 4) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+                                                               const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
+                                                               int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt) {
+  ShadowIO io; io.ray = ray; io.cap = cap; io.cidx = cidx; io.res = res;
+  trace_persistent<ANY, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
+}
+
+/* parity hook: the same loop on caller-supplied rays */
+template <bool ANY>
+__global__ void __launch_bounds__(RRT_BLOCK, 4) k_hook_trace(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, int n,
+                                                            const double* __restrict__ o, const double* __restrict__ d, const double* __restrict__ tmin,
+                                                            const double* __restrict__ tmax, rrt_hit* __restrict__ out, int* cursor, Counters* gcnt) {
+  HookIO<ANY> io; io.o = o; io.d = d; io.tmin = tmin; io.tmax = tmax; io.out = out;
+  trace_persistent<ANY, true>(sc, bh, io, n, cursor, gcnt);
+}
