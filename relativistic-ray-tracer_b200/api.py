@@ -20,7 +20,7 @@ import numpy as np
 from . import scene as _sc
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "librrt_b200.so")
+LIB_PATH = os.environ.get("RRT_B200_LIB") or os.path.join(_HERE, "csrc", "librrt_b200.so")  # env override: A/B builds only
 _LIB = None
 
 OPT_BVH_TOPOLOGY, OPT_COUNTERS, OPT_WORK_BYTES, OPT_TRACE_KERNEL, OPT_LEAF_SIZE = 0, 1, 2, 3, 4

@@ -273,6 +273,25 @@ static int compact(rrt_ctx* ctx, Keep keep, const uint32_t* in, uint32_t n, uint
 
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
+/* trace-kernel dispatch: COUNT (instrumented) x variant (RRT_OPT_TRACE_KERNEL: 0 chord-lockstep, 1 vote-scheduled) */
+static void launch_closest(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, const double* ray, size_t cap, const int* cnt_ptr, int* cursor, int* h_prim,
+                           double* h_geo, Counters* gc) {
+  const bool v1 = ctx->opt[RRT_OPT_TRACE_KERNEL] == 1;
+  if (count) { if (v1) k_trace_closest<true, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc);
+               else k_trace_closest<true, 0><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc); }
+  else { if (v1) k_trace_closest<false, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc);
+         else k_trace_closest<false, 0><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc); }
+}
+template <bool ANY>
+static void launch_shadow(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, const double* ray, size_t cap, const int* cnt_ptr, int* cursor,
+                          const uint32_t* cidx, int* res, Counters* gc) {
+  const bool v1 = ctx->opt[RRT_OPT_TRACE_KERNEL] == 1;
+  if (count) { if (v1) k_trace_shadow<ANY, true, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc);
+               else k_trace_shadow<ANY, true, 0><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc); }
+  else { if (v1) k_trace_shadow<ANY, false, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc);
+         else k_trace_shadow<ANY, false, 0><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc); }
+}
+
 static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_counts, float4* d_rgbn, cudaStream_t user_stream, rrt_stats* stats) {
   if (!ctx->have_scene || !ctx->have_cam || ctx->W <= 0) FAIL(RRT_E_STATE, "rrt_render: scene, camera and frame must be set first");
   if (p->ns_aa <= 0 || p->max_ray_depth < 0 || p->ns_area_light <= 0 || p->samples_per_batch <= 0) FAIL(RRT_E_ARG, "rrt_render: bad parameters");
@@ -355,7 +374,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   int rc = compact(ctx, own, nullptr, (uint32_t)npix, act[0], &n_act);
   if (rc) return rc;
 
-  const int grid_trace = ctx->sm_count * 4, grid_small = ctx->sm_count * 8;
+  const int grid_trace = ctx->sm_count * RRT_MINB, grid_small = ctx->sm_count * 8;
   uint64_t launches = 3, trace_launches = 0;
   int a = 0;
   for (int base_sample = 0; base_sample < rk.ns_aa && n_act > 0;) {
@@ -370,21 +389,15 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
         const int cur = it & 1;
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, st)); }
-        if (count) k_trace_closest<true><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt);
-        else k_trace_closest<false><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt);
+        launch_closest(ctx, count, grid_trace, st, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt);
         if (stats) { CK(cudaEventRecord(e1, st)); trace_ev.push_back({e0, e1}); }
         k_shade<<<grid_small, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, rk, q, chunk, base_sample, nb, it);
         launches += 2; trace_launches++;
         if (rk.D >= 1 && rk.S > 0) {
           if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, st)); }
           int* scount = q.ctl + q.ctl_stride + it; int* scursor = q.ctl + 3 * q.ctl_stride + it;
-          if (rk.hemi) {
-            if (count) k_trace_shadow<false, true><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
-            else k_trace_shadow<false, false><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
-          } else {
-            if (count) k_trace_shadow<true, true><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
-            else k_trace_shadow<true, false><<<grid_trace, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
-          }
+          if (rk.hemi) launch_shadow<false>(ctx, count, grid_trace, st, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
+          else launch_shadow<true>(ctx, count, grid_trace, st, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
           if (stats) { CK(cudaEventRecord(e1, st)); trace_ev.push_back({e0, e1}); }
           k_accumulate<<<grid_small, 256, 0, st>>>(ctx->ds, rk, q, it);
           launches += 2; trace_launches++;
@@ -495,8 +508,11 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
   cudaEvent_t e0, e1; ctx->events_used = 0; e0 = next_event(ctx); e1 = next_event(ctx);
   CK(cudaEventRecord(e0, ctx->stream));
   int grid = (int)std::min<int64_t>((n + RRT_BLOCK - 1) / RRT_BLOCK, (int64_t)ctx->sm_count * 4);
-  if (any_hit) k_hook_trace<true><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc);
-  else k_hook_trace<false><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc);
+  const bool v1 = ctx->opt[RRT_OPT_TRACE_KERNEL] == 1;
+  if (any_hit) { if (v1) k_hook_trace<true, 1><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc);
+                 else k_hook_trace<true, 0><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc); }
+  else { if (v1) k_hook_trace<false, 1><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc);
+         else k_hook_trace<false, 0><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc); }
   CK(cudaEventRecord(e1, ctx->stream));
   CK(cudaMemcpyAsync(out, d_out, sizeof(rrt_hit) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));

@@ -11,7 +11,9 @@
 #include "rrt_math.cuh"
 #include "../../include/rrt_b200.h"
 
-#define RRT_STACK 48  /* traversal stack entries per thread (shared memory); tree depth bound */
+#ifndef RRT_STACK
+#define RRT_STACK 40
+#endif  /* traversal stack entries per thread (shared memory); tree depth bound */
 
 struct DevScene {
   const float4* nodes;        // 4 float4 per interior node
@@ -95,36 +97,44 @@ __device__ __forceinline__ bool horizon_hit(const DevHole& bh, d3 o, d3 d, doubl
  * t = (plane - o) / d in double for the six planes; here one chord-constant context holds o and 1/d rounded to float
  * and every plane parameter is widened by a rigorous bound on what those roundings can do, so that every box the
  * reference accepts is accepted here (the reverse need not hold: the exact primitive tests decide the hit):
- *   t_f = fl((b - o_f) * i_f),  o_f = fl(o), i_f = fl(1 / fl(d))
- *   |t - t_f| <= |t_f| * 4u + |o - o_f| * |1/d| * (1 + 4u),  u = 2^-24
- * widened to |t_f| * 2^-20 + A with A = 2^-23 * |o_f| * |i_f| per axis (2x slack on the origin term, 4x on the
- * relative term).  Direction components below 1e-30 are flushed to a signed zero (i_f = +-inf, A = inf), which
+ *   o_f = fl(o), i_f = fl(1 / fl(d)); the per-plane formula and its error bound are with boxctx_axis below.
+ * Direction components below 1e-30 are flushed to a signed zero (i_f = +-inf; the constants become inf or NaN), which
  * removes the float-denormal case from the analysis; NaN parameters are dropped by fminf/fmaxf, which only ever
  * widens the interval.  Node boxes are already rounded outward from the reference's doubles on the host.
  * Requires tmin >= 0 (true for chords and for every ray the estimator makes). */
 struct BoxCtx {
-  float ox, oy, oz, ix, iy, iz, ax, ay, az, tmin;
-  bool nx, ny, nz;   /* direction component negative: the near plane is the box maximum */
+  float ix, iy, iz;          /* fl(1 / fl(d)) */
+  float nx_, ny_, nz_;       /* near-plane constants:  -(fl(o_f * i_f)) - A */
+  float fx_, fy_, fz_;       /* far-plane constants:   -(fl(o_f * i_f)) + A */
+  float tmin;
+  bool nx, ny, nz;           /* direction component negative: the near plane is the box maximum */
 };
-__device__ __forceinline__ void boxctx_axis(double o, double d, float& of, float& inv, float& a, bool& neg) {
+/* Plane parameter in one FFMA: t_f = fl(b * i_f - c), c = fl(o_f * i_f).  Against the exact t = (b - o) / d:
+ *   |t - t_f| <= |t_f| * 3u  +  (|o - o_f| |1/d| + |c - o_f i_f|) (1 + 3u)  <=  |t_f| * 3u + 2u |o_f| |i_f| (1 + ...)
+ * (u = 2^-24), widened to |t_f| * 2^-20 + A with A = 2^-22 |o_f| |i_f|: 2x slack on the absolute term, 5x on the
+ * relative one. */
+__device__ __forceinline__ void boxctx_axis(double o, double d, float& inv, float& cn, float& cf, bool& neg) {
   float df = (float)d;
   if (fabsf(df) < 1e-30f) df = copysignf(0.f, df);
-  of = (float)o; inv = 1.0f / df;
-  a = 1.1920929e-7f * fabsf(of) * fabsf(inv);
+  float of = (float)o;
+  inv = 1.0f / df;
+  float c = of * inv;
+  float a = 2.3841858e-7f * fabsf(of) * fabsf(inv);
+  cn = -c - a; cf = -c + a;
   neg = __float_as_int(df) < 0;
 }
 __device__ __forceinline__ void boxctx_make(const d3& o, const d3& d, double tmin, BoxCtx& c) {
-  boxctx_axis(o.x, d.x, c.ox, c.ix, c.ax, c.nx);
-  boxctx_axis(o.y, d.y, c.oy, c.iy, c.ay, c.ny);
-  boxctx_axis(o.z, d.z, c.oz, c.iz, c.az, c.nz);
+  boxctx_axis(o.x, d.x, c.ix, c.nx_, c.fx_, c.nx);
+  boxctx_axis(o.y, d.y, c.iy, c.ny_, c.fy_, c.ny);
+  boxctx_axis(o.z, d.z, c.iz, c.nz_, c.fz_, c.nz);
   c.tmin = __double2float_rd(tmin);
 }
 __device__ __forceinline__ bool box_hit(float lox, float loy, float loz, float hix, float hiy, float hiz, const BoxCtx& c, float tmaxf,
                                         float& tnear) {
   const float R = 9.5367431640625e-7f; /* 2^-20 */
-  float tnx = __fmaf_rn((c.nx ? hix : lox) - c.ox, c.ix, -c.ax), tfx = __fmaf_rn((c.nx ? lox : hix) - c.ox, c.ix, c.ax);
-  float tny = __fmaf_rn((c.ny ? hiy : loy) - c.oy, c.iy, -c.ay), tfy = __fmaf_rn((c.ny ? loy : hiy) - c.oy, c.iy, c.ay);
-  float tnz = __fmaf_rn((c.nz ? hiz : loz) - c.oz, c.iz, -c.az), tfz = __fmaf_rn((c.nz ? loz : hiz) - c.oz, c.iz, c.az);
+  float tnx = __fmaf_rn(c.nx ? hix : lox, c.ix, c.nx_), tfx = __fmaf_rn(c.nx ? lox : hix, c.ix, c.fx_);
+  float tny = __fmaf_rn(c.ny ? hiy : loy, c.iy, c.ny_), tfy = __fmaf_rn(c.ny ? loy : hiy, c.iy, c.fy_);
+  float tnz = __fmaf_rn(c.nz ? hiz : loz, c.iz, c.nz_), tfz = __fmaf_rn(c.nz ? loz : hiz, c.iz, c.fz_);
   float tn = fmaxf(fmaxf(tnx, tny), tnz), tf = fminf(fminf(tfx, tfy), tfz);
   tn = __fmaf_rn(fabsf(tn), -R, tn);
   tf = __fmaf_rn(fabsf(tf), R, tf);

@@ -15,6 +15,9 @@
 #define RRT_BLOCK 128
 #endif
 #define RRT_POOL 128  /* queue entries a warp reserves per atomic */
+#ifndef RRT_MINB
+#define RRT_MINB 6     /* resident blocks per SM the trace kernels are compiled for */
+#endif
 
 __device__ __forceinline__ int wt_lane() { return threadIdx.x & 31; }
 
@@ -94,6 +97,7 @@ __device__ __forceinline__ void wt_flush_counters(const Counters& c, Counters* g
   }
 }
 
+/* ---------------------------------------------------------------- variant 0 (default): chord-lockstep loop */
 template <bool ANY, bool COUNT, class IO>
 __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHole& bh, const IO& io, const int n, int* cursor, Counters* gcnt) {
   __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
@@ -158,29 +162,167 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
   if (COUNT) wt_flush_counters(cnt, gcnt);
 }
 
+/* ---------------------------------------------------------------- variant 1: vote-scheduled state machine (measured
+ * SLOWER than variant 0 on C2, 62.9 vs 48.2 ms per frame: kept for A/B).
+ * The lockstep loop above still loses lanes INSIDE a chord: traversals have different lengths and lanes that reach a
+ * leaf run the FP64 primitive test while their neighbours wait (ncu on variant 0: 13-18 active threads per
+ * instruction, DMUL/DADD at 13-14).  Here every lane is in one of three work states — STEP (advance the geodesic by
+ * one chord and set up its traversal), NODE (visit one interior node), LEAF (test one leaf record) — and each trip
+ * of the loop the warp votes and executes only the block most lanes are waiting for.  A block therefore never runs
+ * for fewer than a third of the lanes that have work, and the expensive FP64 blocks run nearly full. */
+template <bool ANY, bool COUNT, class IO>
+__device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& bh, const IO& io, const int n, int* cursor, Counters* gcnt) {
+  __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
+  int* stack = stack_mem + threadIdx.x;
+  enum { ST_IDLE = 0, ST_FREE = 1, ST_STEP = 2, ST_NODE = 3, ST_LEAF = 4 };
+  Counters cnt = {0, 0, 0, 0, 0, 0};
+  const bool flat = bh.mode == RRT_MODE_FLAT;
+  const unsigned lt_mask = (1u << wt_lane()) - 1u;
+  int pool_next = 0, pool_end = 0;
+  bool more = true;
+  int state = ST_FREE;
+  int idx = 0, j = 0, cur = 0, sp = 0;
+  uint32_t lf_next = 0, lf_end = 0;
+  bool found = false;
+  float tmaxf = 0.f;
+  Seg s; s.o = s.d = D3(0, 0, 0); s.tmin = s.tmax = 0.0;
+  Best best; best.t = 0.0; best.b1 = best.b2 = 0.0; best.prim = -1; best.rank = -1; best.kind = 0;
+  BoxCtx bc; bc.ix = bc.iy = bc.iz = bc.nx_ = bc.ny_ = bc.nz_ = bc.fx_ = bc.fy_ = bc.fz_ = bc.tmin = 0.f; bc.nx = bc.ny = bc.nz = false;
+
+  auto finish = [&](int status) {
+    Hit h; h.status = status; h.prim = status == 1 ? best.prim : -1; h.t = status == 1 ? best.t : 0.0;
+    if (status == 0) { h.chord = flat ? 0 : j - 1; h.steps = flat ? 1 : j; }
+    else { h.chord = j; h.steps = j + 1; }
+    if (IO::GEO && status == 1) fill_geo(sc, s, best, h);
+    io.store(idx, h);
+    state = ST_FREE;
+  };
+  auto chord_done = [&]() {   /* traversal of the current chord is exhausted */
+    if (found) finish(1);
+    else { ++j; if (flat || j >= bh.nchords) finish(0); else state = ST_STEP; }
+  };
+  auto enter = [&](int node) {  /* next thing to visit */
+    cur = node;
+    if (node < 0) { uint32_t bits = (uint32_t)~node; lf_next = bits >> 3; lf_end = lf_next + (bits & 7u); state = lf_next < lf_end ? ST_LEAF : ST_NODE; }
+    else state = ST_NODE;
+  };
+  auto pop_or_done = [&]() {
+    if (sp == 0) chord_done();
+    else enter(stack[(--sp) * RRT_BLOCK]);
+  };
+
+  while (true) {
+    /* ---- refill free lanes from the warp pool */
+    unsigned need = __ballot_sync(0xffffffffu, state == ST_FREE);
+    while (need) {
+      if (pool_next >= pool_end) {
+        if (!more) break;
+        int base = 0;
+        if (wt_lane() == 0) base = atomicAdd(cursor, RRT_POOL);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) { more = false; break; }
+        pool_next = base; pool_end = min(base + RRT_POOL, n);
+      }
+      const int avail = pool_end - pool_next;
+      const int rank = __popc(need & lt_mask);
+      if (state == ST_FREE && rank < avail) {
+        idx = pool_next + rank;
+        io.load(idx, s.o, s.d, s.tmin, s.tmax);
+        if (!flat) { s.tmin = 0.0; s.tmax = 0.0; }
+        j = 0; state = ST_STEP;
+        if (COUNT) cnt.rays++;
+      }
+      pool_next += min(__popc(need), avail);
+      need = __ballot_sync(0xffffffffu, state == ST_FREE);
+    }
+    if (state == ST_FREE) state = ST_IDLE;   /* queue exhausted */
+    /* ---- vote */
+    const int nS = __popc(__ballot_sync(0xffffffffu, state == ST_STEP));
+    const int nN = __popc(__ballot_sync(0xffffffffu, state == ST_NODE));
+    const int nL = __popc(__ballot_sync(0xffffffffu, state == ST_LEAF));
+    if ((nS | nN | nL) == 0) break;
+    if (nN >= nL && nN >= nS) {
+      if (state == ST_NODE) {
+        if (cur < 0) pop_or_done();   /* empty leaf */
+        else {
+          const float4* nd = sc.nodes + 4 * (size_t)cur;
+          float4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2), q3 = __ldg(nd + 3);
+          if (COUNT) cnt.nodes++;
+          float tl, tr;
+          bool hl = box_hit(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, bc, tmaxf, tl);
+          bool hr = box_hit(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, bc, tmaxf, tr);
+          int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
+          if (hl && hr) {
+            if (tr < tl) { int t = cl; cl = cr; cr = t; }
+            stack[(sp++) * RRT_BLOCK] = cr;
+            enter(cl);
+          } else if (hl) enter(cl);
+          else if (hr) enter(cr);
+          else pop_or_done();
+        }
+      }
+    } else if (nL >= nS) {
+      if (state == ST_LEAF) {
+        bool acc = leaf_record_test<COUNT>(sc.leaf + 5 * (size_t)lf_next, s, best, cnt);
+        ++lf_next;
+        if (acc) {
+          found = true;
+          if (ANY) finish(1);
+          else tmaxf = __double2float_ru(best.t);
+        }
+        if (state == ST_LEAF && lf_next >= lf_end) pop_or_done();
+      }
+    } else {
+      if (state == ST_STEP) {
+        bool captured = false;
+        if (!flat) {
+          next_micro_ray(bh, s.o, s.d, s.tmax);
+          captured = horizon_hit(bh, s.o, s.d, s.tmax);
+        }
+        if (COUNT) cnt.steps++;
+        if (captured) finish(2);
+        else {
+          best.t = s.tmax; best.rank = -1; best.prim = -1; best.kind = 0; best.b1 = best.b2 = 0.0;
+          found = false; sp = 0;
+          boxctx_make(s.o, s.d, s.tmin, bc);
+          tmaxf = __double2float_ru(best.t);
+          float tr;
+          if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tr)) enter(sc.root);
+          else chord_done();
+        }
+      }
+    }
+    __syncwarp();
+  }
+  if (COUNT) wt_flush_counters(cnt, gcnt);
+}
+
 /* extension rays: closest hit */
-template <bool COUNT>
-__global__ void __launch_bounds__(RRT_BLOCK, 4) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+template <bool COUNT, int V>
+__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                 const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
                                                                 int* cursor, int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt) {
   ClosestIO io; io.ray = ray; io.cap = cap; io.h_prim = h_prim; io.h_geo = h_geo;
-  trace_persistent<false, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
+  if (V == 1) trace_sched<false, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
+  else trace_persistent<false, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
 }
 
 /* shadow rays: BVHAccel::intersect(ray) (any hit), or closest hit when the hemisphere estimator needs the emitter */
-template <bool ANY, bool COUNT>
-__global__ void __launch_bounds__(RRT_BLOCK, 4) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+template <bool ANY, bool COUNT, int V>
+__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
                                                                int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt) {
   ShadowIO io; io.ray = ray; io.cap = cap; io.cidx = cidx; io.res = res;
-  trace_persistent<ANY, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
+  if (V == 1) trace_sched<ANY, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
+  else trace_persistent<ANY, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
 }
 
 /* parity hook: the same loop on caller-supplied rays */
-template <bool ANY>
-__global__ void __launch_bounds__(RRT_BLOCK, 4) k_hook_trace(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, int n,
+template <bool ANY, int V>
+__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB) k_hook_trace(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, int n,
                                                             const double* __restrict__ o, const double* __restrict__ d, const double* __restrict__ tmin,
                                                             const double* __restrict__ tmax, rrt_hit* __restrict__ out, int* cursor, Counters* gcnt) {
   HookIO<ANY> io; io.o = o; io.d = d; io.tmin = tmin; io.tmax = tmax; io.out = out;
-  trace_persistent<ANY, true>(sc, bh, io, n, cursor, gcnt);
+  if (V == 1) trace_sched<ANY, true>(sc, bh, io, n, cursor, gcnt);
+  else trace_persistent<ANY, true>(sc, bh, io, n, cursor, gcnt);
 }

@@ -58,15 +58,17 @@ def test_geodesic_chords_bit_exact(api, tag):
     assert c.chords_per_ray() == (63 if bh[4] == 0.1 else 32)
 
 
-@pytest.mark.parametrize("topology", [0, 1])
+@pytest.mark.parametrize("topology,leaf,variant", [(0, 4, 1), (1, 2, 1), (1, 1, 0), (1, 4, 0)])
 @pytest.mark.parametrize("scene", ["cbspheres_lambertian_480x360", "cbgems_480x360", "cbbunny_microfacet_480x360"])
 @pytest.mark.parametrize("mode", ["flat", "bh", "alt"])
-def test_bvh_intersect_matches_reference(api, scene, mode, topology):
+def test_bvh_intersect_matches_reference(api, scene, mode, topology, leaf, variant):
     g = golden("kat_trace_" + scene)
     if "hit_" + mode not in g.files:
         pytest.skip("no alt-hole vectors for this scene")
     c = api.Context(0)
     c.set_option(api.OPT_BVH_TOPOLOGY, topology)
+    c.set_option(api.OPT_LEAF_SIZE, leaf)
+    c.set_option(api.OPT_TRACE_KERNEL, variant)
     c.upload_scene(load_scene(scene))
     if mode == "flat":
         c.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_FLAT)
@@ -199,6 +201,14 @@ def test_c2_full_size_properties(api):
     assert st["rays"] > st["paths"] and st["geodesic_steps"] > st["rays"]
     hdr2, cnt2, st2 = c.render(p)
     assert np.array_equal(hdr, hdr2) and st2["rays"] == st["rays"] and st2["geodesic_steps"] == st["geodesic_steps"]  # deterministic
+    # the other trace-kernel variant and the other BVH shape must not change a single bit either
+    c.set_option(api.OPT_TRACE_KERNEL, 1)
+    hv, _, stv = c.render(p)
+    c.set_option(api.OPT_TRACE_KERNEL, 0)
+    assert np.array_equal(hdr, hv) and stv["rays"] == st["rays"] and stv["geodesic_steps"] == st["geodesic_steps"]
+    c0 = api.Context(0); c0.set_option(api.OPT_BVH_TOPOLOGY, 0); c0.upload_scene(s); c0.set_frame(480, 360)
+    h0, _, st0 = c0.render(p)
+    assert np.array_equal(hdr, h0) and st0["rays"] == st["rays"]
     # a different chunking of the wavefront must not change a single bit
     p2 = sc.make_params(ns_aa=16, max_ray_depth=5, ns_area_light=4, seed=7, max_paths_in_flight=300000)
     hdr3, _, st3 = c.render(p2)
