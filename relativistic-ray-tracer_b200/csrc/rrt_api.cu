@@ -42,7 +42,7 @@ struct rrt_ctx {
   int tile = 32, rank = 0, world = 1;
   int64_t opt[16];
   // device memory
-  DevBuf d_nodes, d_leaf, d_nrm, d_kind, d_index, d_pmat, d_sph, d_mats, d_lights;
+  DevBuf d_grid, d_nodes, d_leaf, d_nrm, d_kind, d_index, d_pmat, d_sph, d_mats, d_lights;
   DevBuf d_work, d_px, d_act, d_blk, d_cnt, d_out_rgb, d_out_cnt, d_out_rgbn, d_hook_in, d_hook_out;
   std::vector<cudaEvent_t> events;
   size_t events_used = 0;
@@ -94,6 +94,7 @@ int rrt_create(rrt_ctx** out, int device) {
   memset(ctx->opt, 0, sizeof ctx->opt);
   ctx->opt[RRT_OPT_COUNTERS] = 1;
   ctx->opt[RRT_OPT_LEAF_SIZE] = 2;
+  ctx->opt[RRT_OPT_CLEARANCE_GRID] = 0;   /* measured: no gain while chords of a warp are traversed in lockstep */
   ctx->opt[RRT_OPT_BVH_TOPOLOGY] = 1;
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
@@ -113,7 +114,7 @@ void rrt_destroy(rrt_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->d_nodes, &ctx->d_leaf, &ctx->d_nrm, &ctx->d_kind, &ctx->d_index, &ctx->d_pmat, &ctx->d_sph, &ctx->d_mats, &ctx->d_lights,
+  DevBuf* bufs[] = {&ctx->d_grid, &ctx->d_nodes, &ctx->d_leaf, &ctx->d_nrm, &ctx->d_kind, &ctx->d_index, &ctx->d_pmat, &ctx->d_sph, &ctx->d_mats, &ctx->d_lights,
                     &ctx->d_work, &ctx->d_px, &ctx->d_act, &ctx->d_blk, &ctx->d_cnt, &ctx->d_out_rgb, &ctx->d_out_cnt, &ctx->d_out_rgbn,
                     &ctx->d_hook_in, &ctx->d_hook_out};
   for (DevBuf* b : bufs) b->release();
@@ -150,6 +151,7 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
     if (m < 0 || (uint32_t)m >= s->n_mats) FAIL(RRT_E_ARG, "rrt_upload_scene: material index out of range");
   }
   rrt::build_bvh(s, (int)ctx->opt[RRT_OPT_BVH_TOPOLOGY], (int)ctx->opt[RRT_OPT_LEAF_SIZE], &ctx->bvh);
+  rrt::build_clearance_grid(s, (int)ctx->opt[RRT_OPT_CLEARANCE_GRID], &ctx->bvh);
   const rrt::FlatBvh& b = ctx->bvh;
   int tree_depth = 0;
   {  /* depth of the flattened tree bounds the traversal stack */
@@ -167,6 +169,7 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   int rc;
   if ((rc = upload(ctx, ctx->d_nodes, b.nodes.data(), b.nodes.size() * 4))) return rc;
   if ((rc = upload(ctx, ctx->d_leaf, b.leaf.data(), b.leaf.size() * 8))) return rc;
+  if ((rc = upload(ctx, ctx->d_grid, b.clearance.data(), b.clearance.size() * 4))) return rc;
   if ((rc = upload(ctx, ctx->d_nrm, s->tri_nrm, 72 * (size_t)s->n_tris))) return rc;
   if ((rc = upload(ctx, ctx->d_kind, s->prim_kind, s->n_prims))) return rc;
   if ((rc = upload(ctx, ctx->d_index, s->prim_index, 4 * (size_t)s->n_prims))) return rc;
@@ -179,6 +182,9 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   d.nodes = ctx->d_nodes.as<float4>(); d.leaf = ctx->d_leaf.as<double2>(); d.tri_nrm = ctx->d_nrm.as<double>();
   d.prim_kind = ctx->d_kind.as<uint8_t>(); d.prim_index = ctx->d_index.as<uint32_t>(); d.prim_mat = ctx->d_pmat.as<int32_t>();
   d.sph = ctx->d_sph.as<double>(); d.mats = ctx->d_mats.as<rrt_material>(); d.lights = ctx->d_lights.as<rrt_light>();
+  d.clearance = b.clearance.empty() ? nullptr : ctx->d_grid.as<float>();
+  d.gnx = b.grid_n[0]; d.gny = b.grid_n[1]; d.gnz = b.grid_n[2];
+  for (int k = 0; k < 3; ++k) { d.glo[k] = b.grid_lo[k]; d.ginv[k] = b.grid_inv_h[k]; }
   d.n_prims = (int)s->n_prims; d.n_mats = (int)s->n_mats; d.n_lights = (int)s->n_lights; d.root = b.root;
   for (int k = 0; k < 3; ++k) { d.root_lo[k] = rrt::round_down_f(b.root_lo[k]); d.root_hi[k] = rrt::round_up_f(b.root_hi[k]); }
   ctx->n_lights = (int)s->n_lights; ctx->n_delta_lights = 0;

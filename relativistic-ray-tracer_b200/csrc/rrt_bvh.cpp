@@ -2,6 +2,7 @@
 #include "rrt_bvh.h"
 
 #include <math.h>
+#include <cmath>
 #include <string.h>
 
 #include <algorithm>
@@ -228,6 +229,91 @@ int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out) {
   for (int k = 0; k < 3; ++k) { out->root_lo[k] = t->nodes[0].bb.lo[k]; out->root_hi[k] = t->nodes[0].bb.hi[k]; }
   (void)as_i32;
   return 0;
+}
+
+}  // namespace rrt
+
+namespace rrt {
+
+// Clearance grid.  Cells overlapped by a primitive's bounding box are "occupied".  For every cell c the value stored is
+//   clearance(c) = max(0, min over occupied c' of |centre(c) - centre(c')| - |cell diagonal|) * (1 - 1e-4) - 1e-4 * min cell side
+// Any point p of cell c and any point q of a primitive (which lies inside some occupied c') satisfy
+//   |p - q| >= |centre(c) - centre(c')| - half diagonal - half diagonal,
+// so a segment of length < clearance(c) that starts in c (or within 1e-4 cell sides of it: the device locates the cell in
+// float) cannot reach a primitive.  The minimum over occupied cells is an exact anisotropic distance transform done as
+// three 1-D min-plus passes.
+void build_clearance_grid(const rrt_scene* s, int res, FlatBvh* out) {
+  out->clearance.clear(); out->grid_n[0] = out->grid_n[1] = out->grid_n[2] = 0;
+  if (res <= 0 || s->n_prims == 0) return;
+  double lo[3], hi[3], ext[3], emax = 0;
+  for (int k = 0; k < 3; ++k) { lo[k] = out->root_lo[k]; hi[k] = out->root_hi[k]; }
+  for (int k = 0; k < 3; ++k) {
+    double pad = 1e-3 * fmax(hi[k] - lo[k], 1e-6) + 1e-9;   // keeps primitives on the box faces strictly inside
+    lo[k] -= pad; hi[k] += pad; ext[k] = hi[k] - lo[k]; emax = fmax(emax, ext[k]);
+  }
+  if (!(emax > 0) || !std::isfinite(emax)) return;
+  int n[3]; double h[3];
+  for (int k = 0; k < 3; ++k) {
+    n[k] = (int)ceil(res * ext[k] / emax); if (n[k] < 1) n[k] = 1; if (n[k] > res) n[k] = res;
+    h[k] = ext[k] / n[k];
+  }
+  const size_t N = (size_t)n[0] * n[1] * n[2];
+  const double BIG = 1e300;
+  std::vector<double> d2(N, BIG);   // squared centre distance to the nearest occupied cell
+  auto cell = [&](double x, int k) { int c = (int)floor((x - lo[k]) / h[k]); return c < 0 ? 0 : c >= n[k] ? n[k] - 1 : c; };
+  for (uint32_t p = 0; p < s->n_prims; ++p) {
+    double blo[3], bhi[3];
+    if (s->prim_kind[p] == 0) {
+      const double* q = s->tri_pos + 9 * (size_t)s->prim_index[p];
+      for (int k = 0; k < 3; ++k) { blo[k] = fmin(q[k], fmin(q[3 + k], q[6 + k])); bhi[k] = fmax(q[k], fmax(q[3 + k], q[6 + k])); }
+    } else {
+      const double* c = s->sph + 4 * (size_t)s->prim_index[p];
+      for (int k = 0; k < 3; ++k) { blo[k] = c[k] - fabs(c[3]); bhi[k] = c[k] + fabs(c[3]); }
+    }
+    int c0[3], c1[3];
+    for (int k = 0; k < 3; ++k) {   // one extra cell of margin on each side absorbs the floor() rounding at cell faces
+      c0[k] = cell(blo[k], k) - 1; c1[k] = cell(bhi[k], k) + 1;
+      if (c0[k] < 0) c0[k] = 0;
+      if (c1[k] >= n[k]) c1[k] = n[k] - 1;
+    }
+    for (int z = c0[2]; z <= c1[2]; ++z)
+      for (int y = c0[1]; y <= c1[1]; ++y)
+        for (int x = c0[0]; x <= c1[0]; ++x) d2[((size_t)z * n[1] + y) * n[0] + x] = 0.0;
+  }
+  // separable min-plus passes: d2(i) = min_j d2(j) + ((i - j) h)^2
+  std::vector<double> line, res_line;
+  for (int axis = 0; axis < 3; ++axis) {
+    const int L = n[axis];
+    const size_t stride = axis == 0 ? 1 : axis == 1 ? (size_t)n[0] : (size_t)n[0] * n[1];
+    line.assign(L, 0.0); res_line.assign(L, 0.0);
+    const int A = n[(axis + 1) % 3], B = n[(axis + 2) % 3];
+    const size_t sa = (axis + 1) % 3 == 0 ? 1 : (axis + 1) % 3 == 1 ? (size_t)n[0] : (size_t)n[0] * n[1];
+    const size_t sb = (axis + 2) % 3 == 0 ? 1 : (axis + 2) % 3 == 1 ? (size_t)n[0] : (size_t)n[0] * n[1];
+    for (int a = 0; a < A; ++a)
+      for (int b = 0; b < B; ++b) {
+        const size_t base = a * sa + b * sb;
+        for (int i = 0; i < L; ++i) line[i] = d2[base + i * stride];
+        for (int i = 0; i < L; ++i) {
+          double best = BIG;
+          for (int j = 0; j < L; ++j) {
+            if (line[j] >= BIG) continue;
+            double dd = (i - j) * h[axis];
+            double v = line[j] + dd * dd;
+            if (v < best) best = v;
+          }
+          res_line[i] = best;
+        }
+        for (int i = 0; i < L; ++i) d2[base + i * stride] = res_line[i];
+      }
+  }
+  const double diag = sqrt(h[0] * h[0] + h[1] * h[1] + h[2] * h[2]);
+  const double hmin = fmin(h[0], fmin(h[1], h[2]));
+  out->clearance.resize(N);
+  for (size_t i = 0; i < N; ++i) {
+    double c = d2[i] >= BIG ? 0.0 : (sqrt(d2[i]) - diag) * (1.0 - 1e-4) - 1e-4 * hmin;
+    out->clearance[i] = c > 0 ? round_down((float)c > c ? c * (1 - 1e-6) : c) : 0.f;
+  }
+  for (int k = 0; k < 3; ++k) { out->grid_n[k] = n[k]; out->grid_lo[k] = lo[k]; out->grid_inv_h[k] = 1.0 / h[k]; }
 }
 
 }  // namespace rrt

@@ -30,12 +30,20 @@ struct FlatBvh {
   int32_t root = -1;              // child code of the root (0 if interior, leaf code if the whole scene is one leaf)
   double root_lo[3] = {0, 0, 0}, root_hi[3] = {0, 0, 0};
   int n_nodes = 0;                // interior nodes in the flattened array
+  // clearance grid (see build_clearance_grid): per cell, a lower bound on the distance from ANY point of the cell to ANY primitive
+  std::vector<float> clearance;   // [gz][gy][gx]
+  int grid_n[3] = {0, 0, 0};
+  double grid_lo[3] = {0, 0, 0}, grid_inv_h[3] = {0, 0, 0};
   int ref_nodes = 0, ref_leaves = 0, ref_depth = 0; // shape of the reference tree (nodes incl. leaves)
 };
 
 // topology: 0 = reference shape (midpoint split, leaves <= 4), 1 = binned SAH with leaves of <= max_leaf primitives
 // (own shape; ranks still come from the reference shape).  max_leaf is clamped to 1..7 and ignored for topology 0.
 int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out);
+// Empty-space grid over the scene box, res cells along the longest axis (0 disables).  The device skips the BVH for a chord
+// whose length is below the clearance of the cell its origin lies in: no primitive can be within reach, so the
+// result is unchanged.
+void build_clearance_grid(const rrt_scene* s, int res, FlatBvh* out);
 // outward float rounding used for every box the device sees
 float round_down_f(double x);
 float round_up_f(double x);

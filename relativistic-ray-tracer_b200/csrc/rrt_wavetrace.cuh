@@ -136,27 +136,30 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
     }
     if (!__any_sync(0xffffffffu, has)) break;
     /* ---- one chord for every lane that holds a ray */
+    Hit h; h.status = -1;
+    Seg s; s.o = o; s.d = d; s.tmin = tmin; s.tmax = tmax;
+    Best best;
     if (has) {
-      Hit h; h.status = -1;
-      Seg s; Best best;
-      if (flat) { s.o = o; s.d = d; s.tmin = tmin; s.tmax = tmax; }
-      else {
+      if (!flat) {
         next_micro_ray(bh, o, d, len);
         s.o = o; s.d = d; s.tmin = 0.0; s.tmax = len;
         if (horizon_hit(bh, o, d, len)) { h.status = 2; h.prim = -1; h.chord = j; h.steps = j + 1; h.t = 0.0; }
       }
       if (COUNT) cnt.steps++;
-      if (h.status < 0) {
-        if (traverse<ANY, COUNT>(sc, s, best, stack, RRT_BLOCK, cnt)) {
-          h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
-          if (IO::GEO) fill_geo(sc, s, best, h);
-        } else {
-          ++j;
-          if (flat || j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = flat ? 0 : j - 1; h.steps = flat ? 1 : j; h.t = 0.0; }
-        }
-      }
-      if (h.status >= 0) { io.store(idx, h); has = false; }
     }
+    const bool want = has && h.status < 0 && !chord_is_clear(sc, s.o, s.tmax);
+    const bool live = has && h.status < 0;
+    const bool found = traverse<ANY, COUNT>(sc, s, best, stack, RRT_BLOCK, cnt, want);   /* whole warp, converged */
+    if (live) {
+      if (found) {
+        h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
+        if (IO::GEO) fill_geo(sc, s, best, h);
+      } else {
+        ++j;
+        if (flat || j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = flat ? 0 : j - 1; h.steps = flat ? 1 : j; h.t = 0.0; }
+      }
+    }
+    if (has && h.status >= 0) { io.store(idx, h); has = false; }
     __syncwarp();
   }
   if (COUNT) wt_flush_counters(cnt, gcnt);
@@ -284,11 +287,14 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
         else {
           best.t = s.tmax; best.rank = -1; best.prim = -1; best.kind = 0; best.b1 = best.b2 = 0.0;
           found = false; sp = 0;
-          boxctx_make(s.o, s.d, s.tmin, bc);
           tmaxf = __double2float_ru(best.t);
           float tr;
-          if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tr)) enter(sc.root);
-          else chord_done();
+          if (chord_is_clear(sc, s.o, s.tmax)) chord_done();
+          else {
+            boxctx_make(s.o, s.d, s.tmin, bc);
+            if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tr)) enter(sc.root);
+            else chord_done();
+          }
         }
       }
     }

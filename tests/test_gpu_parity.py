@@ -206,7 +206,8 @@ def test_c2_full_size_properties(api):
     hv, _, stv = c.render(p)
     c.set_option(api.OPT_TRACE_KERNEL, 0)
     assert np.array_equal(hdr, hv) and stv["rays"] == st["rays"] and stv["geodesic_steps"] == st["geodesic_steps"]
-    c0 = api.Context(0); c0.set_option(api.OPT_BVH_TOPOLOGY, 0); c0.upload_scene(s); c0.set_frame(480, 360)
+    c0 = api.Context(0); c0.set_option(api.OPT_BVH_TOPOLOGY, 0); c0.set_option(api.OPT_CLEARANCE_GRID, 0)   # reference tree shape, no empty-space grid
+    c0.upload_scene(s); c0.set_frame(480, 360)
     h0, _, st0 = c0.render(p)
     assert np.array_equal(hdr, h0) and st0["rays"] == st["rays"]
     # a different chunking of the wavefront must not change a single bit
