@@ -58,10 +58,10 @@ def test_geodesic_chords_bit_exact(api, tag):
     assert c.chords_per_ray() == (63 if bh[4] == 0.1 else 32)
 
 
-@pytest.mark.parametrize("topology,leaf,variant", [(0, 4, 1), (1, 2, 1), (1, 1, 0), (1, 4, 0)])
+@pytest.mark.parametrize("topology,leaf,variant,grid", [(0, 4, 1, 0), (1, 2, 1, 32), (1, 1, 0, 64), (1, 4, 0, 0), (1, 2, 0, 128)])
 @pytest.mark.parametrize("scene", ["cbspheres_lambertian_480x360", "cbgems_480x360", "cbbunny_microfacet_480x360"])
 @pytest.mark.parametrize("mode", ["flat", "bh", "alt"])
-def test_bvh_intersect_matches_reference(api, scene, mode, topology, leaf, variant):
+def test_bvh_intersect_matches_reference(api, scene, mode, topology, leaf, variant, grid):
     g = golden("kat_trace_" + scene)
     if "hit_" + mode not in g.files:
         pytest.skip("no alt-hole vectors for this scene")
@@ -69,6 +69,7 @@ def test_bvh_intersect_matches_reference(api, scene, mode, topology, leaf, varia
     c.set_option(api.OPT_BVH_TOPOLOGY, topology)
     c.set_option(api.OPT_LEAF_SIZE, leaf)
     c.set_option(api.OPT_TRACE_KERNEL, variant)
+    c.set_option(api.OPT_CLEARANCE_GRID, grid)
     c.upload_scene(load_scene(scene))
     if mode == "flat":
         c.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_FLAT)
@@ -206,7 +207,7 @@ def test_c2_full_size_properties(api):
     hv, _, stv = c.render(p)
     c.set_option(api.OPT_TRACE_KERNEL, 0)
     assert np.array_equal(hdr, hv) and stv["rays"] == st["rays"] and stv["geodesic_steps"] == st["geodesic_steps"]
-    c0 = api.Context(0); c0.set_option(api.OPT_BVH_TOPOLOGY, 0); c0.set_option(api.OPT_CLEARANCE_GRID, 0)   # reference tree shape, no empty-space grid
+    c0 = api.Context(0); c0.set_option(api.OPT_BVH_TOPOLOGY, 0); c0.set_option(api.OPT_CLEARANCE_GRID, 96)   # reference tree shape + empty-space grid
     c0.upload_scene(s); c0.set_frame(480, 360)
     h0, _, st0 = c0.render(p)
     assert np.array_equal(hdr, h0) and st0["rays"] == st["rays"]
