@@ -187,6 +187,16 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   for (int k = 0; k < 3; ++k) { d.glo[k] = b.grid_lo[k]; d.ginv[k] = b.grid_inv_h[k]; }
   d.n_prims = (int)s->n_prims; d.n_mats = (int)s->n_mats; d.n_lights = (int)s->n_lights; d.root = b.root;
   for (int k = 0; k < 3; ++k) { d.root_lo[k] = rrt::round_down_f(b.root_lo[k]); d.root_hi[k] = rrt::round_up_f(b.root_hi[k]); }
+  {
+    double r2 = 0.0;
+    for (int k = 0; k < 3; ++k) {
+      d.ctr[k] = 0.5 * ((double)d.root_lo[k] + (double)d.root_hi[k]);
+      double e = 0.5 * ((double)d.root_hi[k] - (double)d.root_lo[k]);
+      r2 += e * e;
+    }
+    d.rad = std::sqrt(r2) * 1.0001 + 1e-9;   /* only precision depends on it (rrt_trace.cuh boxctx_make) */
+    if (!(d.rad < 1e300)) { d.rad = 0.0; d.ctr[0] = d.ctr[1] = d.ctr[2] = 0.0; }
+  }
   ctx->n_lights = (int)s->n_lights; ctx->n_delta_lights = 0;
   for (uint32_t i = 0; i < s->n_lights; ++i) if (s->lights[i].is_delta) ctx->n_delta_lights++;
   ctx->have_scene = true;

@@ -27,6 +27,7 @@ struct DevScene {
   const rrt_light* lights;
   int32_t n_prims, n_mats, n_lights, root;
   float root_lo[3], root_hi[3];   // root box, rounded outward
+  double ctr[3], rad;             // sphere around the root box (far-chord origin shift, boxctx_make)
   // clearance grid (rrt_bvh.h): lower bound on the distance from any point of a cell to any primitive
   const float* clearance;
   int gnx, gny, gnz;
@@ -116,22 +117,49 @@ struct BoxCtx {
 /* Plane parameter in one FFMA: t_f = fl(b * i_f - c), c = fl(o_f * i_f).  Against the exact t = (b - o) / d:
  *   |t - t_f| <= |t_f| * 3u  +  (|o - o_f| |1/d| + |c - o_f i_f|) (1 + 3u)  <=  |t_f| * 3u + 2u |o_f| |i_f| (1 + ...)
  * (u = 2^-24), widened to |t_f| * 2^-20 + A with A = 2^-22 |o_f| |i_f|: 2x slack on the absolute term, 5x on the
- * relative one. */
-__device__ __forceinline__ void boxctx_axis(double o, double d, float& inv, float& cn, float& cf, bool& neg) {
+ * relative one.  `slack` is an extra bound on |o - o_true| (far chords, below); it enters A as slack |i_f|. */
+__device__ __forceinline__ void boxctx_axis(double o, double d, float slack, float& inv, float& cn, float& cf, bool& neg) {
   float df = (float)d;
   if (fabsf(df) < 1e-30f) df = copysignf(0.f, df);
   float of = (float)o;
   inv = 1.0f / df;
   float c = of * inv;
-  float a = 2.3841858e-7f * fabsf(of) * fabsf(inv);
+  float a = __fmaf_rn(2.3841858e-7f, fabsf(of), slack) * fabsf(inv);
   cn = -c - a; cf = -c + a;
   neg = __float_as_int(df) < 0;
 }
-__device__ __forceinline__ void boxctx_make(const d3& o, const d3& d, double tmin, BoxCtx& c) {
-  boxctx_axis(o.x, d.x, c.ix, c.nx_, c.fx_, c.nx);
-  boxctx_axis(o.y, d.y, c.iy, c.ny_, c.fy_, c.ny);
-  boxctx_axis(o.z, d.z, c.iz, c.nz_, c.fz_, c.nz);
+/* Far chords.  The position uncertainty of the FP32 test is ~2^-20 |o|.  The reference's escaped rays jump between
+ * points up to ~1e7 units out on chords that pass close to the scene; from there every box near
+ * the chord would pass and one lane would walk the whole tree.  The slab test does not care where along the line the
+ * parameter is counted from, so such a chord is tested from q = o + T d with the range [tmin - T, tmax - T], T = the
+ * distance from o to the sphere around the root box.  q is computed in double; the bound on its rounding error,
+ * |q_i - (o_i + T d_i)| <= 2^-53 (|o_i| + 2T), enters the plane constants as `slack` (4x margin), and the shifted
+ * range ends are widened by 2^-50 relative before rounding outward to float.  Returns T (0: not shifted). */
+#define RRT_FAR_ORIGIN 512.0f
+__device__ __forceinline__ double boxctx_make(const DevScene& sc, const d3& o, const d3& d, double tmin, BoxCtx& c) {
+  d3 q = o;
+  double T = 0.0;
+  float slack = 0.f;
+  const float m = fmaxf(fmaxf(fabsf((float)o.x), fabsf((float)o.y)), fabsf((float)o.z));
   c.tmin = __double2float_rd(tmin);
+  if (m > RRT_FAR_ORIGIN && m < 1e30f) {
+    d3 w = vsub(o, D3(sc.ctr[0], sc.ctr[1], sc.ctr[2]));
+    T = fmax(sqrt(vnorm2(w)) - sc.rad, 0.0);
+    q = D3(o.x + T * d.x, o.y + T * d.y, o.z + T * d.z);
+    slack = __double2float_ru((3.0 * (double)m + T) * 4.45e-16);
+    double x = tmin - T;
+    c.tmin = __double2float_rd(x - fabs(x) * 8.9e-16);
+  }
+  boxctx_axis(q.x, d.x, slack, c.ix, c.nx_, c.fx_, c.nx);
+  boxctx_axis(q.y, d.y, slack, c.iy, c.ny_, c.fy_, c.ny);
+  boxctx_axis(q.z, d.z, slack, c.iz, c.nz_, c.fz_, c.nz);
+  return T;
+}
+/* upper end of the parameter range in the (possibly shifted) units of the box context, rounded up */
+__device__ __forceinline__ float boxctx_tmax(double tmax, double T) {
+  if (T == 0.0) return __double2float_ru(tmax);
+  double x = tmax - T;
+  return __double2float_ru(x + fabs(x) * 8.9e-16);
 }
 __device__ __forceinline__ bool box_hit(float lox, float loy, float loz, float hix, float hiy, float hiz, const BoxCtx& c, float tmaxf,
                                         float& tnear) {
@@ -225,9 +253,11 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best&
   float tmaxf = 0.f, tl, tr;
   bool found = false;
   int cur = DONE, sp = 0;
+  bool shifted = false;               /* far chord: box parameters count from o + T d, see boxctx_make */
   if (active) {
-    boxctx_make(s.o, s.d, s.tmin, bc);
-    tmaxf = __double2float_ru(best.t);
+    const double T = boxctx_make(sc, s.o, s.d, s.tmin, bc);
+    shifted = T != 0.0;
+    tmaxf = boxctx_tmax(best.t, T);
     if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tl)) cur = sc.root;
   }
   while (__any_sync(0xffffffffu, cur != DONE)) {
@@ -255,7 +285,7 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best&
         if (leaf_record_test<COUNT>(sc.leaf + 5 * (size_t)(first + k), s, best, cnt)) {
           found = true;
           if (ANY) { sp = 0; break; }
-          tmaxf = __double2float_ru(best.t);
+          if (!shifted) tmaxf = __double2float_ru(best.t);   /* shifted chords keep the chord-long range: rare, and conservative */
         }
       }
       if (sp) cur = stack[(--sp) * stride];

@@ -186,7 +186,7 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
   int state = ST_FREE;
   int idx = 0, j = 0, cur = 0, sp = 0;
   uint32_t lf_next = 0, lf_end = 0;
-  bool found = false;
+  bool found = false, shifted = false;
   float tmaxf = 0.f;
   Seg s; s.o = s.d = D3(0, 0, 0); s.tmin = s.tmax = 0.0;
   Best best; best.t = 0.0; best.b1 = best.b2 = 0.0; best.prim = -1; best.rank = -1; best.kind = 0;
@@ -271,7 +271,7 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
         if (acc) {
           found = true;
           if (ANY) finish(1);
-          else tmaxf = __double2float_ru(best.t);
+          else if (!shifted) tmaxf = __double2float_ru(best.t);
         }
         if (state == ST_LEAF && lf_next >= lf_end) pop_or_done();
       }
@@ -291,7 +291,9 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
           float tr;
           if (chord_is_clear(sc, s.o, s.tmax)) chord_done();
           else {
-            boxctx_make(s.o, s.d, s.tmin, bc);
+            const double T = boxctx_make(sc, s.o, s.d, s.tmin, bc);
+            shifted = T != 0.0;
+            tmaxf = boxctx_tmax(best.t, T);
             if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tr)) enter(sc.root);
             else chord_done();
           }

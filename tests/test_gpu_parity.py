@@ -106,6 +106,43 @@ def test_trace_matches_oracle_records(api, orc, scene, mode):
     assert (got["status"] == 2).sum() > 0 or mode == "flat"
 
 
+@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("mode", ["flat", "bh"])
+def test_far_origin_chords_match_oracle(api, orc, mode, variant):
+    """chords whose origin lies 1e2..1e7 units from the scene are box-tested from a shifted origin (rrt_trace.cuh boxctx_make):
+    same records as the oracle, for rays aimed into the scene and for the escaped rays of a 1080p frame"""
+    s = load_scene("cbbunny_microfacet_480x360")
+    c = api.Context(0); c.set_option(api.OPT_TRACE_KERNEL, variant); c.upload_scene(s)
+    o = orc.Oracle(s)
+    m = sc.MODE_FLAT if mode == "flat" else sc.MODE_LITERAL
+    c.set_blackhole((0, 1, 0), 0.1, 0.1, m); o.set_blackhole((0, 1, 0), 0.1, 0.1, m)
+    rng = np.random.default_rng(11)
+    n = 3000
+    target = np.c_[rng.uniform(-1, 1, n), rng.uniform(0, 2, n), rng.uniform(-1, 1, n)]
+    dirs = rng.normal(size=(n, 3)); dirs /= np.linalg.norm(dirs, axis=1)[:, None]
+    dirs[: n // 10, rng.integers(0, 3)] = 0.0                                  # some axis-parallel ones
+    dirs /= np.linalg.norm(dirs, axis=1)[:, None]
+    dist = 10.0 ** rng.uniform(2, 7, n)
+    org = target - dirs * dist[:, None]
+    if mode == "bh":                                                           # plus the escaped rays of a wide frame
+        s2 = load_scene("cbbunny_microfacet_480x360"); s2.set_screen_size(1920, 1080)
+        c2 = api.Context(0); c2.upload_scene(s2)
+        co, cd = c2.generate_rays(rng.uniform(0, 1, (3000, 2)))
+        org = np.r_[org, co]; dirs = np.r_[dirs, cd]
+    got, gst = c.trace_rays(org, dirs)
+    ref, ost = o.trace_rays(org, dirs)
+    for f in ("status", "prim", "chord", "steps"):
+        assert np.array_equal(got[f], ref[f]), f
+    assert same(got["t"], ref["t"])
+    if mode == "flat":
+        assert (got["status"] == 1).mean() > 0.5
+        # the shifted boxes prune: a far ray costs about what a near one does, not the whole tree
+        assert gst["node_visits"] < 400 * len(org)
+    anyh, _ = c.trace_rays(org, dirs, any_hit=True)
+    refany, _ = o.trace_rays(org, dirs, any_hit=True)
+    assert np.array_equal(anyh["status"], refany["status"])
+
+
 def test_camera_rays(api):
     g = golden("kat_trace_cbspheres_lambertian_480x360")
     c = make_ctx(api, "cbspheres_lambertian_480x360")
