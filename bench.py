@@ -191,6 +191,7 @@ def main():
     import torch.distributed as dist
     from util import load_scene, sc
     api = importlib.import_module("relativistic-ray-tracer_b200.api")
+    shard = importlib.import_module("relativistic-ray-tracer_b200.shard")
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -216,10 +217,10 @@ def main():
     ctx.upload_scene(s)
     ctx.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
     ctx.set_frame(W, H)
-    ctx.set_tile_shard(16, rank, world)
+    ctx.set_tile_shard(shard.DEFAULT_TILE, rank, world)
     # spp <= 32 keeps the reference's default adaptive batch (32) from ever triggering; above it the batch is the job's
     # spp so that every rank traces exactly W*H*spp/N paths (stated in config)
-    batch = 32 if spp_job <= 32 else spp_job
+    spp_job, batch = shard.weak_scaling_params(spp, world)
     params = sc.make_params(ns_aa=spp_job, max_ray_depth=m, ns_area_light=l, samples_per_batch=batch, seed=1)
 
     frame = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
@@ -227,8 +228,7 @@ def main():
 
     def step_device():
         st = ctx.render_device(params, frame.data_ptr(), 0, 0, want_stats=True)
-        if world > 1:
-            dist.reduce(frame, dst=0, op=dist.ReduceOp.SUM)
+        shard.assemble(frame)
         return st
 
     for _ in range(args.warmup):
@@ -275,7 +275,7 @@ def main():
             ctx.render(params, hdr_p, cnt_p, want_stats=False)
         else:
             ctx.render_device(params, frame.data_ptr(), 0, 0, want_stats=False)
-            dist.reduce(frame, dst=0, op=dist.ReduceOp.SUM)
+            shard.assemble(frame)
             if rank == 0:
                 host_frame.copy_(frame, non_blocking=False)
     step_e2e()

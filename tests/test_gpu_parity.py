@@ -14,6 +14,9 @@ from test_oracle_render import RENDERS, setup_from_golden
 
 pytestmark = pytest.mark.gpu
 
+import importlib
+shard = importlib.import_module("relativistic-ray-tracer_b200.shard")
+
 
 def same(a, b):
     a = np.asarray(a); b = np.asarray(b)
@@ -258,6 +261,7 @@ def test_c2_full_size_properties(api):
         c.set_tile_shard(32, r, 3)
         hr, cr, _ = c.render(p)
         assert ((hr != 0).any(-1) <= (cr > 0)).all()
+        assert np.array_equal(cr > 0, shard.tile_owner(480, 360, 32, 3) == r)   # device owner rule == host owner rule
         acc += hr; accn += cr
     c.set_tile_shard(32, 0, 1)
     assert np.array_equal(acc, hdr) and np.array_equal(accn, cnt)
