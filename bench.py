@@ -2,7 +2,7 @@
 """bench.py — headline benchmark of the hot path (per-pixel Monte Carlo radiance estimation with Schwarzschild ray
 bending) on B200.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|bunny_bh]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c5|bunny_bh]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 
 One step = one full render of the workload.  Default workload = BASELINE.json configs[1] ("C2"):
@@ -43,7 +43,24 @@ WORKLOADS = {
            "C3: CBbunny_microfacet_cu.dae 1280x720 -s 256 -l 4 -m 5, flat spacetime"),
     "bunny_bh": ("cbbunny_microfacet_480x360", "CBbunny_microfacet_cu.dae", 1920, 1080, 16, 4, 5, "bh",
                  "C4 substitute (CBdragon.dae is not in the reference tree): CBbunny_microfacet_cu.dae 1920x1080 -s 16 -l 4 -m 5, hole on"),
+    "c5": ("synth:c5", None, 3840, 2160, 4, 4, 5, "bh",
+           "C5 at reduced spp: procedural Cornell box + displaced UV sphere, 1,002,540 triangles (synth.py, seed 184), 3840x2160 -s 4 "
+           "(the config names 4096 spp) -l 4 -m 5, hole on; BVH nodes + FP64 leaf records = 115 MB"),
 }
+
+
+def workload_scene(wl):
+    """flattened scene of a workload at its frame size (fixture under tests/golden, or the procedural generator)"""
+    from util import load_scene
+    fixture, _, W, H = WORKLOADS[wl][:4]
+    if fixture.startswith("synth:"):
+        synth = importlib.import_module("relativistic-ray-tracer_b200.synth")
+        s = synth.c5_scene(load_scene("cbspheres_lambertian_480x360"))
+    else:
+        s = load_scene(fixture)
+    if (W, H) != (480, 360):
+        s.set_screen_size(W, H)
+    return s
 
 
 def peaks():
@@ -146,8 +163,8 @@ def run_reference_binary(wl, spp, threads):
     """One run of the UNMODIFIED reference CPU path tracer (oracle/_ref/ref_bh or ref_flat).  Returns (paths, seconds, rays)."""
     fixture, dae, W, H, _, l, m, mode, _ = WORKLOADS[wl]
     exe = os.path.join(ROOT, "oracle", "_ref", "ref_bh" if mode == "bh" else "ref_flat")
-    scene = os.path.join(ROOT, "oracle", "_ref", "dae", dae)
-    if not (os.path.exists(exe) and os.path.exists(scene)):
+    scene = os.path.join(ROOT, "oracle", "_ref", "dae", dae or "-")
+    if dae is None or not (os.path.exists(exe) and os.path.exists(scene)):
         return None
     with tempfile.TemporaryDirectory() as td:
         out = os.path.join(td, "o.png")
@@ -166,9 +183,7 @@ def run_oracle_port(wl, spp):
     from util import load_scene, sc
     from oracle import orc
     fixture, _, W, H, _, l, m, mode, _ = WORKLOADS[wl]
-    s = load_scene(fixture)
-    if (W, H) != (480, 360):
-        s.set_screen_size(W, H)
+    s = workload_scene(wl)
     o = orc.Oracle(s)
     o.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
     o.set_frame(W, H)
@@ -248,9 +263,7 @@ def main():
     if args.spp:
         spp = args.spp
     spp_job = spp * world                       # weak scaling: per-GPU paths fixed
-    s = load_scene(fixture)
-    if (W, H) != (480, 360):
-        s.set_screen_size(W, H)
+    s = workload_scene(args.workload)
     ctx = api.Context(local)
     ctx.set_option(api.OPT_BVH_TOPOLOGY, args.topology)
     ctx.set_option(api.OPT_LEAF_SIZE, args.leaf)
@@ -348,6 +361,8 @@ def main():
 
     secs = total_ms * 1e-3
     peak, peak_src = peaks()
+    binfo = api.bvh_build_host(s, args.topology) if s.n_prims <= 200000 else None
+    scene_bytes = (64 * binfo["flat_nodes"] + 80 * binfo["leaf_records"]) if binfo else 64 * (s.n_prims // 2) + 80 * s.n_prims
     # roofline of the dominant kernel (trace: geodesic-advance + BVH intersect): rank-0 algorithmic bytes / rank-0 trace time
     my_bytes = float(st_count["algorithmic_bytes"])
     my_trace_s = float(t[2]) / max(args.steps, 1)
@@ -367,7 +382,10 @@ def main():
                      "algorithmic_bytes_per_step": my_bytes, "trace_ms_per_step": my_trace_s * 1e3,
                      "trace_launches_per_step": trace_launches / max(args.steps, 1),
                      "trace_share_of_step": trace_s / (render_s if render_s > 0 else 1.0),
-                     "note": "scene is L1/L2 resident for this workload (7-node BVH): the kernel is FP64-pipe bound, see DESIGN.md"},
+                     "scene_bytes": scene_bytes,
+                     "note": ("BVH nodes + leaf records = %.1f MB: %s" % (scene_bytes / 1e6,
+                              "L1/L2 resident, the kernel is instruction-issue bound (FP64 + FP32 pipes), the fraction counts cache-served bytes; see DESIGN.md section 6"
+                              if scene_bytes < 100e6 else "exceeds the 126 MB L2 together with the ray queues; DRAM-served"))},
         "clocks": clk,
     }
     if not args.no_cpu_baseline:

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define RRT_ABI_VERSION 1
+#define RRT_ABI_VERSION 2
 
 /* error codes */
 #define RRT_OK 0
@@ -225,9 +225,10 @@ int rrt_tonemap(rrt_ctx* ctx, int64_t n, const float* hdr_rgb, uint32_t* rgba);
 /* BVH facts after rrt_upload_scene: nodes, leaves, depth; dfs_rank [n_prims] (may be NULL) receives, for
  * every primitive in reference order, its position in the reference BVH's depth-first leaf order. */
 int rrt_bvh_info(rrt_ctx* ctx, int32_t* n_nodes, int32_t* n_leaves, int32_t* depth, uint32_t* dfs_rank);
-/* Host-only (no device needed): runs the BVH construction rrt_upload_scene uses.  info[0..5] = reference-shape nodes,
- * leaves, depth, flattened interior nodes, leaf records, root child code; dfs_rank as in rrt_bvh_info (may be NULL). */
-int rrt_bvh_build_host(const rrt_scene* scene, int topology, int32_t info[6], uint32_t* dfs_rank);
+/* Host-only (no device needed): runs the BVH construction rrt_upload_scene uses.  info[0..7] = reference-shape nodes,
+ * leaves, depth, flattened interior nodes, leaf records, root child code, interior levels of the flattened tree, the
+ * device traversal stack size those levels must stay below; dfs_rank as in rrt_bvh_info (may be NULL). */
+int rrt_bvh_build_host(const rrt_scene* scene, int topology, int32_t info[8], uint32_t* dfs_rank);
 /* number of geodesic chords per ray: count of j >= 0 with j*delta_theta < 2*pi (src/bvh.cpp:105) */
 int rrt_chords_per_ray(rrt_ctx* ctx);
 

@@ -79,13 +79,13 @@ def _p(a):
 
 def bvh_build_host(scene, topology=0):
     """rrt_bvh_build_host: the host-side BVH construction, no device needed."""
-    info = (C.c_int32 * 6)()
+    info = (C.c_int32 * 8)()
     rank = np.zeros(max(scene.n_prims, 1), np.uint32)
     cs = scene.c_scene()
     rc = lib().rrt_bvh_build_host(C.byref(cs), int(topology), info, _p(rank))
     if rc != 0:
         raise RrtError("rrt_bvh_build_host failed (%d)" % rc)
-    return dict(n_nodes=info[0], n_leaves=info[1], depth=info[2], flat_nodes=info[3], leaf_records=info[4], root=info[5],
+    return dict(n_nodes=info[0], n_leaves=info[1], depth=info[2], flat_nodes=info[3], leaf_records=info[4], root=info[5], flat_depth=info[6], stack=info[7],
                 dfs_rank=rank[:scene.n_prims])
 
 

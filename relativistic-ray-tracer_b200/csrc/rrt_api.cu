@@ -137,6 +137,22 @@ static int upload(rrt_ctx* ctx, DevBuf& b, const void* src, size_t bytes) {
   return RRT_OK;
 }
 
+}  /* extern "C" */
+/* interior levels of the flattened tree = the most entries a traversal can have on its stack, plus one */
+static int flat_depth(const rrt::FlatBvh& b) {
+  int depth = 0;
+  std::vector<std::pair<int, int>> st;
+  if (b.root >= 0) st.push_back({b.root, 1});
+  while (!st.empty()) {
+    auto [nd, dp] = st.back(); st.pop_back();
+    depth = std::max(depth, dp);
+    int32_t c[2]; memcpy(c, &b.nodes[16 * (size_t)nd + 12], 8);
+    for (int k = 0; k < 2; ++k) if (c[k] >= 0) st.push_back({c[k], dp + 1});
+  }
+  return depth;
+}
+
+extern "C" {
 int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   if (!ctx || !s) return RRT_E_ARG;
   CK(cudaSetDevice(ctx->device));
@@ -153,17 +169,7 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   rrt::build_bvh(s, (int)ctx->opt[RRT_OPT_BVH_TOPOLOGY], (int)ctx->opt[RRT_OPT_LEAF_SIZE], &ctx->bvh);
   rrt::build_clearance_grid(s, (int)ctx->opt[RRT_OPT_CLEARANCE_GRID], &ctx->bvh);
   const rrt::FlatBvh& b = ctx->bvh;
-  int tree_depth = 0;
-  {  /* depth of the flattened tree bounds the traversal stack */
-    std::vector<std::pair<int, int>> st;
-    if (b.root >= 0) st.push_back({b.root, 1});
-    while (!st.empty()) {
-      auto [nd, dp] = st.back(); st.pop_back();
-      tree_depth = std::max(tree_depth, dp);
-      int32_t c[2]; memcpy(c, &b.nodes[16 * (size_t)nd + 12], 8);
-      for (int k = 0; k < 2; ++k) if (c[k] >= 0) st.push_back({c[k], dp + 1});
-    }
-  }
+  const int tree_depth = flat_depth(b);   /* bounds the traversal stack */
   if (tree_depth >= RRT_STACK) FAIL(RRT_E_ARG, "rrt_upload_scene: BVH deeper than the traversal stack; set RRT_OPT_BVH_TOPOLOGY = 1");
   CK(cudaStreamSynchronize(ctx->stream));
   int rc;
@@ -241,11 +247,12 @@ int rrt_set_tile_shard(rrt_ctx* ctx, int tile, int rank, int world) {
   return RRT_OK;
 }
 
-int rrt_bvh_build_host(const rrt_scene* scene, int topology, int32_t info[6], uint32_t* dfs_rank) {
+int rrt_bvh_build_host(const rrt_scene* scene, int topology, int32_t info[8], uint32_t* dfs_rank) {
   if (!scene || !info) return RRT_E_ARG;
   rrt::FlatBvh b;
   rrt::build_bvh(scene, topology, 2, &b);
   info[0] = b.ref_nodes; info[1] = b.ref_leaves; info[2] = b.ref_depth; info[3] = b.n_nodes; info[4] = (int32_t)(b.leaf.size() / 10); info[5] = b.root;
+  info[6] = flat_depth(b); info[7] = RRT_STACK;
   if (dfs_rank && !b.dfs_rank.empty()) memcpy(dfs_rank, b.dfs_rank.data(), 4 * b.dfs_rank.size());
   return RRT_OK;
 }

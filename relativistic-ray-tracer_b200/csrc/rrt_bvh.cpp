@@ -12,6 +12,7 @@ namespace {
 
 struct Box { double lo[3], hi[3]; };
 struct TNode { Box bb; int l, r, start, count; };
+static const int kMaxSahDepth = 38;   /* < RRT_STACK (rrt_trace.cuh), checked again at upload */
 struct Tree { std::vector<TNode> nodes; std::vector<uint32_t> order; int leaves = 0, depth = 0; };
 
 inline void box_reset(Box& b) { for (int k = 0; k < 3; ++k) { b.lo[k] = INFINITY; b.hi[k] = -INFINITY; } }
@@ -107,6 +108,27 @@ struct Builder {
     double clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (uint32_t i = 0; i < n; ++i)
       for (int k = 0; k < 3; ++k) { double c = pcen[3 * (size_t)prims[i] + k]; clo[k] = fmin(clo[k], c); chi[k] = fmax(chi[k], c); }
+    {
+      /* depth budget: the device traversal stack holds RRT_STACK (40) entries, one per level.  Once the levels a
+       * balanced subtree of n primitives still needs would no longer fit under kMaxSahDepth, split at the object median
+       * of the widest axis from here down, which bounds the depth by construction for any n < 2^28. */
+      int need = 0;
+      for (uint64_t cap = max_leaf ? max_leaf : 1; cap < n; cap <<= 1) ++need;
+      if (depth + need + 1 >= kMaxSahDepth) {
+        int axis = 0;
+        for (int k = 1; k < 3; ++k) if (chi[k] - clo[k] > chi[axis] - clo[axis]) axis = k;
+        uint32_t h = n / 2;
+        const double* pc = pcen.data();
+        std::nth_element(prims, prims + h, prims + n, [pc, axis](uint32_t a, uint32_t b) {
+          double ca = pc[3 * (size_t)a + axis], cb = pc[3 * (size_t)b + axis];
+          return ca < cb || (ca == cb && a < b);
+        });
+        int l = build_sah(t, prims, h, base, depth + 1);
+        int r = build_sah(t, prims + h, n - h, base + h, depth + 1);
+        t.nodes[me].l = l; t.nodes[me].r = r;
+        return me;
+      }
+    }
     double best = INFINITY; int best_axis = -1, best_bin = -1;
     for (int axis = 0; axis < 3; ++axis) {
       double w = chi[axis] - clo[axis];

@@ -289,6 +289,31 @@ def test_c1_flat_full_size_against_oracle_stats(api, orc):
     assert abs(st["rays"] - ost["rays"]) <= 1e-3 * ost["rays"]
 
 
+@pytest.mark.parametrize("mode", ["flat", "bh"])
+def test_procedural_mesh_scene_matches_oracle(api, orc, mode):
+    """C5's generator at a size the oracle finishes in seconds (18k triangles): hit records and a small render"""
+    synth = importlib.import_module("relativistic-ray-tracer_b200.synth")
+    s = synth.c5_scene(load_scene("cbspheres_lambertian_96x72"), 96, 97)
+    c = api.Context(0); c.upload_scene(s); c.set_frame(96, 72)
+    o = orc.Oracle(s); o.set_frame(96, 72)
+    m = sc.MODE_FLAT if mode == "flat" else sc.MODE_LITERAL
+    c.set_blackhole((0, 1, 0), 0.1, 0.1, m); o.set_blackhole((0, 1, 0), 0.1, 0.1, m)
+    rng = np.random.default_rng(5)
+    ro, rd = c.generate_rays(rng.uniform(0, 1, (4000, 2)))
+    got, gst = c.trace_rays(ro, rd)
+    ref, ost = o.trace_rays(ro, rd)
+    for f in ("status", "prim", "chord", "steps"):
+        assert np.array_equal(got[f], ref[f]), f
+    assert same(got["t"], ref["t"]) and same(got["hit_p"], ref["hit_p"]) and same(got["n"], ref["n"])
+    assert (got["prim"] >= 12).sum() > 100                     # the mesh is actually hit
+    p = sc.make_params(ns_aa=2, max_ray_depth=3, ns_area_light=2, seed=9)
+    hdr, cnt, st = c.render(p)
+    rimg, rcnt, rst = o.render(p)
+    pix, rmse = image_report(hdr, rimg)
+    assert np.array_equal(cnt, rcnt) and (pix > 1e-4).mean() <= 0.005 and rmse <= 0.01 * float(rimg.mean())
+    assert abs(st["rays"] - rst["rays"]) <= 2e-3 * rst["rays"]
+
+
 def test_adaptive_rounds_match_oracle(api, orc):
     """spp > batch: several adaptive rounds, active-pixel compaction between them"""
     s = load_scene("cbspheres_lambertian_96x72")
