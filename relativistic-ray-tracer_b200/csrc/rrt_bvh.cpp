@@ -3,9 +3,15 @@
 
 #include <math.h>
 #include <cmath>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <thread>
+#include <vector>
 
 namespace rrt {
 namespace {
@@ -25,12 +31,60 @@ inline double box_area(const Box& b) {
   return 2.0 * (x * y + y * z + z * x);
 }
 
+static double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+#define TICK(name) do { if (getenv("RRT_BVH_TIMING")) { double t_ = now_s(); fprintf(stderr, "[bvh] %-12s %.3f s\n", name, t_ - t0_); t0_ = t_; } } while (0)
 struct Builder {
   const rrt_scene* s;
   std::vector<Box> pbox;        // Primitive::get_bbox (reference src/static_scene/triangle.cpp:11-19, sphere.h:30-32)
   std::vector<double> pcen;     // 3 per prim: BBox::centroid() = (min + max) / 2, i.e. 0.5 * (min + max)  (src/bbox.h:98-100)
-  std::vector<uint32_t> tmp;
+  std::vector<uint32_t> tmp;    // partition scratch; a call on prims[base, base + n) uses tmp[base, base + n), so disjoint
+                                // subtrees can be built concurrently
   uint32_t max_leaf = 4;
+  struct Task { int node; uint32_t* prims; uint32_t n, base; int depth; };
+  std::vector<Task>* tasks = nullptr;
+  uint32_t grain = 0;
+
+  /* The top of the tree is built on the calling thread; subtrees of at most `grain` primitives are handed to worker
+   * threads, each into its own node array, and spliced under their placeholder afterwards.  The result is the tree the
+   * serial recursion builds (same splits, same primitive order); only the node array order differs, and the
+   * flattening below renumbers nodes in depth-first preorder anyway. */
+  template <class F>
+  void build_parallel(Tree& t, F build, uint32_t* prims, uint32_t n) {
+    unsigned hw = std::thread::hardware_concurrency();
+    unsigned nthreads = hw < 1 ? 1 : hw > 32 ? 32 : hw;
+    if (n < 65536 || nthreads == 1) { (this->*build)(t, prims, n, 0, 0); return; }
+    std::vector<Task> list;
+    tasks = &list; grain = std::max<uint32_t>(8192, n / (8 * nthreads));
+    double t0_ = now_s();
+    (this->*build)(t, prims, n, 0, 0);
+    tasks = nullptr;
+    TICK("  top");
+    std::vector<Tree> sub(list.size());
+    std::atomic<size_t> next{0};
+    auto work = [&]() {
+      for (size_t i; (i = next.fetch_add(1)) < list.size();) {
+        const Task& k = list[i];
+        sub[i].nodes.reserve(2 * (size_t)k.n / (max_leaf ? max_leaf : 1) + 16);
+        (this->*build)(sub[i], k.prims, k.n, k.base, k.depth);
+      }
+    };
+    std::vector<std::thread> pool;
+    for (unsigned w = 1; w < nthreads && w < list.size(); ++w) pool.emplace_back(work);
+    work();
+    for (auto& th : pool) th.join();
+    TICK("  subtrees");
+    for (size_t i = 0; i < list.size(); ++i) {
+      const std::vector<TNode>& L = sub[i].nodes;
+      const int me = list[i].node, off = (int)t.nodes.size();
+      auto map = [&](int j) { return j < 0 ? j : j == 0 ? me : off + j - 1; };
+      for (size_t j = 0; j < L.size(); ++j) {
+        TNode nd = L[j]; nd.l = map(nd.l); nd.r = map(nd.r);
+        if (j == 0) t.nodes[me] = nd; else t.nodes.push_back(nd);
+      }
+      t.leaves += sub[i].leaves;
+      if (sub[i].depth > t.depth) t.depth = sub[i].depth;
+    }
+  }
 
   void prepare() {
     uint32_t n = s->n_prims;
@@ -63,6 +117,11 @@ struct Builder {
   int build_ref(Tree& t, uint32_t* prims, uint32_t n, uint32_t base, int depth) {
     int me = (int)t.nodes.size();
     t.nodes.push_back(TNode());
+    if (tasks && n <= grain && depth > 0) {   /* subtree left to a worker thread (build_parallel) */
+      t.nodes[me].l = t.nodes[me].r = -1; t.nodes[me].start = t.nodes[me].count = 0;
+      tasks->push_back(Task{me, prims, n, base, depth});
+      return me;
+    }
     Box bb = bounds(prims, n);
     t.nodes[me].bb = bb; t.nodes[me].l = t.nodes[me].r = -1; t.nodes[me].start = t.nodes[me].count = 0;
     if (depth > t.depth) t.depth = depth;
@@ -77,15 +136,15 @@ struct Builder {
     uint32_t nl = 0, nr = 0;
     for (uint32_t i = 0; i < n; ++i) {
       if (pcen[3 * (size_t)prims[i] + axis] < mid) prims[nl++] = prims[i];   // nl <= i: safe in place
-      else tmp[nr++] = prims[i];
+      else tmp[base + nr++] = prims[i];
     }
     if (nl == 0 || nr == 0) {
       // both vectors are rebuilt from the ORIGINAL order: first half left, rest right; the in-place pass above kept
       // the original order in whichever side received everything
-      if (nl == 0) memcpy(prims, tmp.data(), sizeof(uint32_t) * n);
+      if (nl == 0) memcpy(prims, tmp.data() + base, sizeof(uint32_t) * n);
       nl = n / 2; nr = n - nl;
     } else {
-      memcpy(prims + nl, tmp.data(), sizeof(uint32_t) * nr);
+      memcpy(prims + nl, tmp.data() + base, sizeof(uint32_t) * nr);
     }
     int l = build_ref(t, prims, nl, base, depth + 1);
     int r = build_ref(t, prims + nl, nr, base + nl, depth + 1);
@@ -97,6 +156,11 @@ struct Builder {
   int build_sah(Tree& t, uint32_t* prims, uint32_t n, uint32_t base, int depth) {
     int me = (int)t.nodes.size();
     t.nodes.push_back(TNode());
+    if (tasks && n <= grain && depth > 0) {   /* subtree left to a worker thread (build_parallel) */
+      t.nodes[me].l = t.nodes[me].r = -1; t.nodes[me].start = t.nodes[me].count = 0;
+      tasks->push_back(Task{me, prims, n, base, depth});
+      return me;
+    }
     Box bb = bounds(prims, n);
     t.nodes[me].bb = bb; t.nodes[me].l = t.nodes[me].r = -1; t.nodes[me].start = t.nodes[me].count = 0;
     if (depth > t.depth) t.depth = depth;
@@ -130,18 +194,42 @@ struct Builder {
       }
     }
     double best = INFINITY; int best_axis = -1, best_bin = -1;
-    for (int axis = 0; axis < 3; ++axis) {
-      double w = chi[axis] - clo[axis];
-      if (!(w > 0)) continue;
-      Box bbx[NB]; uint32_t cnt[NB];
-      for (int b = 0; b < NB; ++b) { box_reset(bbx[b]); cnt[b] = 0; }
-      double scale = NB / w;
-      for (uint32_t i = 0; i < n; ++i) {
-        int b = (int)((pcen[3 * (size_t)prims[i] + axis] - clo[axis]) * scale);
-        if (b >= NB) b = NB - 1;
-        if (b < 0) b = 0;
-        box_expand(bbx[b], pbox[prims[i]]); cnt[b]++;
+    /* one pass over the primitives fills the bins of all three axes; large nodes (the serial top of the tree) split
+     * the pass over threads and merge the partial bins, which gives the same boxes and counts in any order */
+    struct Bins { Box bb[3][NB]; uint32_t cnt[3][NB]; };
+    double scale3[3]; bool use[3];
+    for (int k = 0; k < 3; ++k) { double w = chi[k] - clo[k]; use[k] = w > 0; scale3[k] = use[k] ? NB / w : 0.0; }
+    auto fill = [&](Bins& B, uint32_t i0, uint32_t i1) {
+      for (int k = 0; k < 3; ++k) for (int q = 0; q < NB; ++q) { box_reset(B.bb[k][q]); B.cnt[k][q] = 0; }
+      for (uint32_t i = i0; i < i1; ++i) {
+        const uint32_t p = prims[i];
+        const Box& pb = pbox[p];
+        for (int k = 0; k < 3; ++k) {
+          if (!use[k]) continue;
+          int q = (int)((pcen[3 * (size_t)p + k] - clo[k]) * scale3[k]);
+          if (q >= NB) q = NB - 1;
+          if (q < 0) q = 0;
+          box_expand(B.bb[k][q], pb); B.cnt[k][q]++;
+        }
       }
+    };
+    Bins bins;
+    unsigned parts = n >= 65536 ? std::min(16u, std::max(1u, std::thread::hardware_concurrency())) : 1;
+    if (parts > 1) {
+      std::vector<Bins> part(parts);
+      std::vector<std::thread> th;
+      for (unsigned w = 0; w < parts; ++w)
+        th.emplace_back([&, w]() { fill(part[w], (uint32_t)((uint64_t)n * w / parts), (uint32_t)((uint64_t)n * (w + 1) / parts)); });
+      for (auto& x : th) x.join();
+      bins = part[0];
+      for (unsigned w = 1; w < parts; ++w)
+        for (int k = 0; k < 3; ++k) for (int q = 0; q < NB; ++q) { box_expand(bins.bb[k][q], part[w].bb[k][q]); bins.cnt[k][q] += part[w].cnt[k][q]; }
+    } else {
+      fill(bins, 0, n);
+    }
+    for (int axis = 0; axis < 3; ++axis) {
+      if (!use[axis]) continue;
+      const Box* bbx = bins.bb[axis]; const uint32_t* cnt = bins.cnt[axis];
       double ra[NB]; uint32_t rc[NB]; Box acc; box_reset(acc); uint32_t c = 0;
       for (int b = NB - 1; b > 0; --b) { box_expand(acc, bbx[b]); c += cnt[b]; ra[b] = box_area(acc); rc[b] = c; }
       box_reset(acc); c = 0;
@@ -159,9 +247,9 @@ struct Builder {
         int b = (int)((pcen[3 * (size_t)prims[i] + best_axis] - clo[best_axis]) * scale);
         if (b >= NB) b = NB - 1;
         if (b < 0) b = 0;
-        if (b <= best_bin) prims[nl++] = prims[i]; else tmp[nr++] = prims[i];
+        if (b <= best_bin) prims[nl++] = prims[i]; else tmp[base + nr++] = prims[i];
       }
-      memcpy(prims + nl, tmp.data(), sizeof(uint32_t) * nr);
+      memcpy(prims + nl, tmp.data() + base, sizeof(uint32_t) * nr);
     }
     if (nl == 0 || nr == 0) { nl = n / 2; nr = n - nl; }
     int l = build_sah(t, prims, nl, base, depth + 1);
@@ -183,6 +271,7 @@ float round_down_f(double x) { return round_down(x); }
 float round_up_f(double x) { return round_up(x); }
 
 int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out) {
+  double t0_ = now_s();
   *out = FlatBvh();
   uint32_t n = s->n_prims;
   out->dfs_rank.assign(n, 0);
@@ -190,13 +279,15 @@ int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out) {
   for (uint32_t p = 0; p < n; ++p) out->prim_mat[p] = s->prim_kind[p] == 0 ? s->tri_mat[s->prim_index[p]] : s->sph_mat[s->prim_index[p]];
   if (n == 0) { out->root = -1; /* ~(-1) = 0: an empty leaf */ return 0; }
   Builder b; b.s = s; b.prepare();
+  TICK("prepare");
   b.max_leaf = (uint32_t)(max_leaf < 1 ? 1 : max_leaf > 7 ? 7 : max_leaf);
 
   Tree ref; ref.order.resize(n);
   for (uint32_t i = 0; i < n; ++i) ref.order[i] = i;
   ref.nodes.reserve(n);
-  b.build_ref(ref, ref.order.data(), n, 0, 0);
+  b.build_parallel(ref, &Builder::build_ref, ref.order.data(), n);
   for (uint32_t i = 0; i < n; ++i) out->dfs_rank[ref.order[i]] = i;
+  TICK("ref tree");
   out->ref_nodes = (int)ref.nodes.size(); out->ref_leaves = ref.leaves; out->ref_depth = ref.depth;
 
   Tree own;
@@ -205,10 +296,11 @@ int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out) {
     own.order.resize(n);
     for (uint32_t i = 0; i < n; ++i) own.order[i] = i;
     own.nodes.reserve(n);
-    b.build_sah(own, own.order.data(), n, 0, 0);
+    b.build_parallel(own, &Builder::build_sah, own.order.data(), n);
     t = &own;
   }
 
+  TICK("sah tree");
   // leaf records in the tree's leaf order
   out->leaf.assign(10 * (size_t)n, 0.0);
   for (uint32_t i = 0; i < n; ++i) {
@@ -226,6 +318,7 @@ int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out) {
     memcpy(&r[9], w, 8);
   }
 
+  TICK("leaf records");
   // flatten: interior nodes in depth-first preorder
   auto child_code = [&](int ni, std::vector<int>& remap) -> int32_t {
     const TNode& c = t->nodes[ni];
@@ -234,7 +327,15 @@ int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out) {
   };
   std::vector<int> remap(t->nodes.size(), -1);
   int ninner = 0;
-  for (size_t i = 0; i < t->nodes.size(); ++i) if (t->nodes[i].l >= 0) remap[i] = ninner++;  // vector order IS preorder
+  {  // interior nodes numbered in depth-first preorder (left subtree first): parents sit next to their near descendants
+    std::vector<int> st; st.push_back(0);
+    while (!st.empty()) {
+      int ni = st.back(); st.pop_back();
+      if (t->nodes[ni].l < 0) continue;
+      remap[ni] = ninner++;
+      st.push_back(t->nodes[ni].r); st.push_back(t->nodes[ni].l);
+    }
+  }
   out->n_nodes = ninner;
   out->nodes.assign(16 * (size_t)(ninner > 0 ? ninner : 1), 0.f);
   for (size_t i = 0; i < t->nodes.size(); ++i) {
@@ -250,6 +351,7 @@ int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out) {
   out->root = child_code(0, remap);
   for (int k = 0; k < 3; ++k) { out->root_lo[k] = t->nodes[0].bb.lo[k]; out->root_hi[k] = t->nodes[0].bb.hi[k]; }
   (void)as_i32;
+  TICK("flatten");
   return 0;
 }
 
