@@ -1,0 +1,122 @@
+// main.cpp — the reference's command line (src/main.cpp:28-40, 88-188) over the B200 path.
+//
+//   pathtracer [options] <scene.dae | scene.rrtscene>
+//     -s <INT>  -l <INT>  -m <INT>  -t <INT>  -a <INT> <FLOAT>  -H  -r <W> <H>  -p <x> <y> <dx> <dy>  -f <out.png>
+//     -b <FLOAT> -d <FLOAT> -c <camera settings file>  -B <x> <y> <z> <r> <dtheta>        exactly as the reference
+//   additions (not in the reference): -F (flat spacetime, the reference has no working switch), -S <seed>,
+//     -G <device>, --dump-scene <out.rrtscene> (load + flatten only: needs no GPU), --dump-camera <file>
+//   not available: -e <map.exr> (environment light is a "next" row), the interactive viewer (no graphics stack on
+//     this box): without -f the program renders to <scene>_screenshot_<time>.png instead of opening a window.
+// -t is accepted and ignored: the device replaces the worker threads.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+
+#include "rrt_host.h"
+
+using namespace rrt_host;
+
+static void usage(const char* binary) {
+  printf("Usage: %s [options] <scenefile>\n", binary);
+  printf("Program Options:\n");
+  printf("  -s  <INT>        Number of camera rays per pixel\n");
+  printf("  -l  <INT>        Number of samples per area light\n");
+  printf("  -t  <INT>        Number of render threads (ignored: the GPU renders)\n");
+  printf("  -m  <INT>        Maximum ray depth\n");
+  printf("  -a  <INT> <FLOAT> Samples per batch and tolerance for adaptive sampling\n");
+  printf("  -H               Enable uniform hemisphere sampling for direct lighting\n");
+  printf("  -f  <FILENAME>   Image (.png) file to save output to\n");
+  printf("  -r  <INT> <INT>  Width and height of output image\n");
+  printf("  -p  <x> <y> <dx> <dy> Render only this cell of the frame\n");
+  printf("  -c  <FILENAME>   Camera settings file\n");
+  printf("  -b  <FLOAT>      Lens radius      -d  <FLOAT>  Focal distance\n");
+  printf("  -B  <x> <y> <z> <r> <dtheta>  Black hole centre, Schwarzschild radius, angular step\n");
+  printf("  -F               Flat spacetime (no hole)      -S <INT> RNG seed      -G <INT> CUDA device\n");
+  printf("  --dump-scene <FILE>  write the flattened scene and exit (no GPU needed)\n");
+  printf("  -h               Print this help message\n\n");
+}
+
+int main(int argc, char** argv) {
+  size_t ns_aa = 1, max_ray_depth = 1, ns_area_light = 1, num_threads = 1, samples_per_batch = 32;
+  float max_tolerance = 0.05f;
+  bool hemisphere = false, write_to_file = false, flat = false;
+  double lens_radius = 0.25, focal_distance = 4.7;
+  size_t w = 0, h = 0, x = (size_t)-1, y = 0, dx = 0, dy = 0;
+  std::string filename, cam_settings, dump_scene, dump_camera, scene_path;
+  Vector3D bh_c(0, 1, 0); double bh_r = 0.1, bh_dtheta = 0.1;
+  unsigned long long seed = 0; int device = 0;
+
+  auto need = [&](int i, int k) { if (i + k >= argc) { usage(argv[0]); exit(1); } };
+  for (int i = 1; i < argc; ++i) {
+    std::string a = argv[i];
+    if (a == "-f") { need(i, 1); write_to_file = true; filename = argv[++i]; }
+    else if (a == "-r") { need(i, 2); w = (size_t)atoi(argv[i + 1]); h = (size_t)atoi(argv[i + 2]); i += 2; }
+    else if (a == "-p") { need(i, 4); x = (size_t)atoi(argv[i + 1]); y = (size_t)atoi(argv[i + 2]); dx = (size_t)atoi(argv[i + 3]); dy = (size_t)atoi(argv[i + 4]); i += 4; }
+    else if (a == "-s") { need(i, 1); ns_aa = (size_t)atoi(argv[++i]); }
+    else if (a == "-l") { need(i, 1); ns_area_light = (size_t)atoi(argv[++i]); }
+    else if (a == "-t") { need(i, 1); num_threads = (size_t)atoi(argv[++i]); }
+    else if (a == "-m") { need(i, 1); max_ray_depth = (size_t)atoi(argv[++i]); }
+    else if (a == "-b") { need(i, 1); lens_radius = atof(argv[++i]); }
+    else if (a == "-d") { need(i, 1); focal_distance = atof(argv[++i]); }
+    else if (a == "-c") { need(i, 1); cam_settings = argv[++i]; }
+    else if (a == "-a") { need(i, 2); samples_per_batch = (size_t)atoi(argv[i + 1]); max_tolerance = (float)atof(argv[i + 2]); i += 2; }
+    else if (a == "-H") hemisphere = true;
+    else if (a == "-B") {
+      need(i, 5);
+      bh_c = Vector3D(atof(argv[i + 1]), atof(argv[i + 2]), atof(argv[i + 3])); bh_r = atof(argv[i + 4]); bh_dtheta = atof(argv[i + 5]);
+      i += 5;
+    }
+    else if (a == "-F") flat = true;
+    else if (a == "-S") { need(i, 1); seed = strtoull(argv[++i], nullptr, 10); }
+    else if (a == "-G") { need(i, 1); device = atoi(argv[++i]); }
+    else if (a == "--dump-scene") { need(i, 1); dump_scene = argv[++i]; }
+    else if (a == "--dump-camera") { need(i, 1); dump_camera = argv[++i]; }
+    else if (a == "--write-test-png") {   // host self-check used by tests/test_host_cpp.py: a 5x3 gradient through write_png
+      need(i, 1);
+      uint32_t px[15];
+      for (uint32_t k = 0; k < 15; ++k) px[k] = 0xFF000000u | (k * 17u) | ((255u - k * 17u) << 8) | ((k * 5u) << 16);
+      return write_png(argv[i + 1], px, 5, 3) ? 0 : 2;
+    }
+    else if (a == "-e") { fprintf(stderr, "-e: environment light is not available in this build (DESIGN.md section 9)\n"); return 1; }
+    else if (a == "-h") { usage(argv[0]); return 1; }
+    else if (!a.empty() && a[0] == '-') { usage(argv[0]); return 1; }
+    else scene_path = a;
+  }
+  if (scene_path.empty()) { usage(argv[0]); return 1; }
+  (void)num_threads;
+
+  printf("[PathTracer] Input scene file: %s\n", scene_path.c_str());
+  std::string scene_file = scene_path.substr(scene_path.find_last_of('/') + 1);
+  scene_file = scene_file.substr(0, scene_file.find(".dae"));
+
+  FlatScene scene; Camera camera; std::string err;
+  bool is_dae = scene_path.size() >= 4 && scene_path.compare(scene_path.size() - 4, 4, ".dae") == 0;
+  bool ok = is_dae ? load_dae(scene_path, &scene, &camera, &err) : load_rrtscene(scene_path, &scene, &camera, &err);
+  if (!ok) { fprintf(stderr, "[PathTracer] %s\n", err.c_str()); return is_dae ? 0 : 2; }   // the reference exits 0 on a missing file
+  if (w && h) camera.set_screen_size(w, h);
+  if (!cam_settings.empty() && !camera.load_settings(cam_settings)) { fprintf(stderr, "[Camera] cannot load settings from %s\n", cam_settings.c_str()); return 2; }
+  if (!cam_settings.empty()) printf("[Camera] Loaded settings from %s\n", cam_settings.c_str());
+
+  if (!dump_camera.empty()) { if (!camera.dump_settings(dump_camera)) return 2; printf("[Camera] Dumped settings to %s\n", dump_camera.c_str()); }
+  if (!dump_scene.empty()) {
+    // like PathTracer::set_camera, the dump carries the lens parameters of the command line
+    camera.lensRadius = lens_radius; camera.focalDistance = focal_distance;
+    if (!save_rrtscene(dump_scene, scene, camera, &err)) { fprintf(stderr, "%s\n", err.c_str()); return 2; }
+    printf("[PathTracer] %s: %zu primitives (%zu triangles, %zu spheres), %zu materials, %zu lights\n", dump_scene.c_str(), scene.n_prims(),
+           scene.tri_mat.size(), scene.sph_mat.size(), scene.mats.size(), scene.lights.size());
+    return 0;
+  }
+
+  PathTracer pt(ns_aa, max_ray_depth, ns_area_light, 1, 1, 1, num_threads, samples_per_batch, max_tolerance, nullptr, hemisphere,
+                scene_file, lens_radius, focal_distance);
+  pt.set_device(device); pt.set_seed(seed); pt.set_blackhole(bh_c, bh_r, bh_dtheta, flat);
+  pt.set_camera(&camera);
+  pt.set_scene(&scene);
+  pt.set_frame_size(camera.screenW, camera.screenH);
+  if (!pt.error().empty()) { fprintf(stderr, "[PathTracer] %s\n", pt.error().c_str()); return 3; }
+  pt.render_to_file(write_to_file ? filename : std::string(""), x, y, dx, dy);
+  if (!pt.error().empty()) { fprintf(stderr, "[PathTracer] %s\n", pt.error().c_str()); return 3; }
+  return 0;
+}

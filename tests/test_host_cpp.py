@@ -1,0 +1,137 @@
+"""C++ host side above the C-ABI (host/): COLLADA loading with the reference loader's semantics, the flattened scene
+files, the PNG writer and the CLI's argument handling.  CPU only; the render itself is covered by the gpu tests.
+
+The .dae files are the reference's own (copied next to the reference binaries by oracle/build_ref.sh, git-ignored);
+the golden scenes under tests/golden/ were dumped from the reference's objects by oracle/ref_probe.cpp, so equality here
+means the C++ loader + half-edge emulation reproduce the reference's scene build bit for bit."""
+import importlib
+import os
+import struct
+import subprocess
+import zlib
+
+import numpy as np
+import pytest
+
+from util import ROOT, load_scene
+
+sc = importlib.import_module("relativistic-ray-tracer_b200.scene")
+HOST = os.path.join(ROOT, "host")
+EXE = os.path.join(HOST, "pathtracer")
+DAE = os.path.join(ROOT, "oracle", "_ref", "dae")
+
+
+@pytest.fixture(scope="module")
+def exe():
+    lib = os.path.join(ROOT, "relativistic-ray-tracer_b200", "csrc", "librrt_b200.so")
+    if not os.path.exists(lib):
+        subprocess.run(["make", "-C", os.path.dirname(lib)], check=True, capture_output=True)
+    subprocess.run(["make", "-C", HOST], check=True, capture_output=True)
+    return EXE
+
+
+PAIRS = [("CBspheres_lambertian.dae", "cbspheres_lambertian_480x360"), ("CBempty.dae", "cbempty_480x360"),
+         ("CBspheres.dae", "cbspheres_480x360"), ("CBspheres_microfacet_al_ag.dae", "cbspheres_microfacet_480x360"),
+         ("CBgems.dae", "cbgems_480x360"), ("CBbunny_microfacet_cu.dae", "cbbunny_microfacet_480x360")]
+
+
+@pytest.mark.parametrize("dae,gold", PAIRS)
+def test_dae_loader_reproduces_the_reference_scene(exe, tmp_path, dae, gold):
+    src = os.path.join(DAE, dae)
+    if not os.path.exists(src):
+        pytest.skip("reference .dae files not present (oracle/build_ref.sh copies them)")
+    out = str(tmp_path / "s.rrtscene")
+    r = subprocess.run([exe, "--dump-scene", out, "-r", "480", "360", src], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    a, b = sc.SceneData.load(out), load_scene(gold)
+    for f in ("prim_kind", "prim_index", "tri_pos", "tri_nrm", "tri_mat", "sph", "sph_mat"):
+        x, y = getattr(a, f), getattr(b, f)
+        assert x.shape == y.shape and np.array_equal(x, y), f
+    assert a.mats.tobytes() == b.mats.tobytes() and a.lights.tobytes() == b.lights.tobytes()
+    assert a.camera == b.camera
+
+
+def test_rrtscene_round_trip_through_the_cpp_reader_and_writer(exe, tmp_path):
+    b = load_scene("cbspheres_lambertian_480x360")
+    src = str(tmp_path / "in.rrtscene"); out = str(tmp_path / "out.rrtscene")
+    b.save(src)
+    r = subprocess.run([exe, "--dump-scene", out, "-b", str(b.camera["lensRadius"]), "-d", str(b.camera["focalDistance"]), src],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert open(src, "rb").read() == open(out, "rb").read()
+
+
+def test_resize_follows_the_reference_fov_rule(exe, tmp_path):
+    b = load_scene("cbspheres_lambertian_480x360")
+    src = str(tmp_path / "in.rrtscene"); out = str(tmp_path / "out.rrtscene")
+    b.save(src)
+    subprocess.run([exe, "--dump-scene", out, "-r", "1920", "1080", src], check=True, capture_output=True)
+    a = sc.SceneData.load(out)
+    b.set_screen_size(1920, 1080)
+    assert a.camera["hFov"] == b.camera["hFov"] and a.camera["vFov"] == b.camera["vFov"] and a.camera["screenW"] == 1920.0
+
+
+def test_png_writer(exe, tmp_path):
+    out = str(tmp_path / "t.png")
+    assert subprocess.run([exe, "--write-test-png", out]).returncode == 0
+    raw = open(out, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, chunks = 8, []
+    while pos < len(raw):
+        n, tag = struct.unpack(">I4s", raw[pos:pos + 8])
+        data = raw[pos + 8:pos + 8 + n]
+        assert struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(tag + data) & 0xFFFFFFFF
+        chunks.append((tag, data)); pos += 12 + n
+    assert [c[0] for c in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+    assert struct.unpack(">IIBBBBB", chunks[0][1]) == (5, 3, 8, 6, 0, 0, 0)
+    px = zlib.decompress(chunks[1][1])
+    assert len(px) == 3 * (1 + 5 * 4)
+    k = 7   # pixel (2, 1)
+    off = 1 * 21 + 1 + 2 * 4
+    assert tuple(px[off:off + 4]) == (k * 17, 255 - k * 17, k * 5, 255)
+
+
+def test_cli_errors(exe, tmp_path):
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 1 and "Usage" in r.stdout
+    r = subprocess.run([exe, "--dump-scene", str(tmp_path / "x"), str(tmp_path / "missing.dae")], capture_output=True, text=True)
+    assert r.returncode == 0 and "cannot open" in r.stderr            # the reference exits 0 when the scene cannot be read
+    bad = tmp_path / "bad.dae"; bad.write_text("<COLLADA><asset><up_axis>Y_UP</up_axis></asset><scene>")
+    r = subprocess.run([exe, "--dump-scene", str(tmp_path / "x"), str(bad)], capture_output=True, text=True)
+    assert "missing end tag" in r.stderr and not os.path.exists(tmp_path / "x")
+    r = subprocess.run([exe, "-e", "map.exr", "scene.dae"], capture_output=True, text=True)
+    assert r.returncode == 1 and "environment light" in r.stderr
+
+
+def test_minimal_collada_document(exe, tmp_path):
+    """a hand-written Y_UP file: one quad (kept as the single triangle (d, a, b) the reference makes of it), one sphere
+    without material (grey diffuse), a point light, no camera node"""
+    doc = """<?xml version="1.0"?><!-- c --><COLLADA><asset><up_axis>Y_UP</up_axis></asset>
+    <library_geometries>
+      <geometry id="g"><mesh><source id="g-pos"><float_array id="g-arr" count="12">0 0 0  1 0 0  1 1 0  0 1 0</float_array></source>
+        <vertices id="g-v"><input semantic="POSITION" source="#g-pos"/></vertices>
+        <polylist count="1"><input semantic="VERTEX" source="#g-v" offset="0"/><vcount>4</vcount><p>0 1 2 3</p></polylist></mesh></geometry>
+      <geometry id="s"><extra><technique profile="CGL"><sphere><radius>0.5</radius></sphere></technique></extra></geometry>
+    </library_geometries>
+    <library_lights><light id="L"><technique_common><point><color>1 2 3</color><constant_attenuation>1</constant_attenuation>
+      <linear_attenuation>0</linear_attenuation><quadratic_attenuation>0</quadratic_attenuation></point></technique_common></light></library_lights>
+    <library_visual_scenes><visual_scene id="vs">
+      <node id="n1" name="quad"><matrix>2 0 0 0  0 2 0 0  0 0 2 0  0 0 0 1</matrix><instance_geometry url="#g"/></node>
+      <node id="n2" name="ball"><matrix>1 0 0 5  0 1 0 0  0 0 1 0  0 0 0 1</matrix><instance_geometry url="#s"/></node>
+      <node id="n3" name="lamp"><matrix>1 0 0 0  0 1 0 7  0 0 1 0  0 0 0 1</matrix><instance_light url="#L"/></node>
+    </visual_scene></library_visual_scenes>
+    <scene><instance_visual_scene url="#vs"/></scene></COLLADA>"""
+    src = tmp_path / "m.dae"; src.write_text(doc)
+    out = str(tmp_path / "m.rrtscene")
+    r = subprocess.run([exe, "--dump-scene", out, str(src)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    a = sc.SceneData.load(out)
+    assert a.prim_kind.tolist() == [0, 1]
+    assert a.tri_pos[0].tolist() == [0, 2, 0, 0, 0, 0, 2, 0, 0]                  # (d, a, b), scaled by 2
+    # an isolated face: every vertex is a boundary vertex, and the reference's boundary walk (h->next()->twin()) steps
+    # onto the virtual boundary face, whose winding is reversed -- the normal comes out flipped, as in the reference
+    np.testing.assert_allclose(a.tri_nrm[0].reshape(3, 3), [[0, 0, -1]] * 3, atol=1e-15)
+    assert a.sph[0].tolist() == [5, 0, 0, 0.5]
+    assert [int(m["type"]) for m in a.mats] == [sc.MAT_DIFFUSE, sc.MAT_DIFFUSE] and a.mats[1]["a"].tolist() == [0.5, 0.5, 0.5]
+    assert int(a.lights[0]["type"]) == sc.LIGHT_POINT and a.lights[0]["position"].tolist() == [0, 7, 0] and a.lights[0]["radiance"].tolist() == [1, 2, 3]
+    assert a.camera["screenW"] == 800.0 and a.camera["screenH"] == 600.0         # Application::init's defaults

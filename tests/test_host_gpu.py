@@ -1,0 +1,87 @@
+"""The C++ host side end to end on the GPU: host/pathtracer (reference CLI flags) -> PathTracer -> C-ABI -> PNG,
+against the same render made through the Python binding."""
+import importlib
+import os
+import struct
+import subprocess
+import zlib
+
+import numpy as np
+import pytest
+
+from util import ROOT, load_scene, sc
+
+pytestmark = pytest.mark.gpu
+EXE = os.path.join(ROOT, "host", "pathtracer")
+
+
+def read_png(path):
+    raw = open(path, "rb").read()
+    pos, idat, w, h = 8, b"", 0, 0
+    while pos < len(raw):
+        n, tag = struct.unpack(">I4s", raw[pos:pos + 8])
+        if tag == b"IHDR":
+            w, h = struct.unpack(">II", raw[pos + 8:pos + 16])
+        if tag == b"IDAT":
+            idat += raw[pos + 8:pos + 8 + n]
+        pos += 12 + n
+    px = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 1 + 4 * w)
+    assert (px[:, 0] == 0).all()
+    return px[:, 1:].reshape(h, w, 4)
+
+
+@pytest.fixture(scope="module")
+def exe():
+    if not os.path.exists(EXE):
+        subprocess.run(["make", "-C", os.path.dirname(EXE)], check=True, capture_output=True)
+    return EXE
+
+
+@pytest.mark.parametrize("flags,mode", [([], sc.MODE_LITERAL), (["-F"], sc.MODE_FLAT), (["-B", "0.1", "0.9", "0", "0.15", "0.2"], "alt")])
+def test_cli_render_equals_python_binding(exe, tmp_path, flags, mode):
+    api = importlib.import_module("relativistic-ray-tracer_b200.api")
+    s = load_scene("cbspheres_lambertian_96x72")
+    src = str(tmp_path / "s.rrtscene"); out = str(tmp_path / "o.png")
+    s.save(src)
+    r = subprocess.run([exe, "-s", "4", "-l", "2", "-m", "3", "-t", "8", "-S", "5", "-f", out] + flags + [src], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "[PathTracer] Job completed." in r.stdout and "BVH traced" in r.stdout
+    c = api.Context(0); c.upload_scene(s); c.set_frame(96, 72)
+    if mode == "alt":
+        c.set_blackhole((0.1, 0.9, 0), 0.15, 0.2, sc.MODE_LITERAL)
+    else:
+        c.set_blackhole((0, 1, 0), 0.1, 0.1, mode)
+    hdr, cnt, st = c.render(sc.make_params(ns_aa=4, max_ray_depth=3, ns_area_light=2, seed=5))
+    rgba = c.tonemap(hdr).reshape(72, 96)[::-1]
+    want = np.ascontiguousarray(rgba).view(np.uint8).reshape(72, 96, 4).copy()
+    want[..., 3] = 255
+    got = read_png(out)
+    assert got.shape == want.shape and np.array_equal(got, want)
+    assert ("traced %d rays" % st["rays"]) in r.stdout
+    rate = read_png(out[:-4] + "_rate.png")
+    assert rate.shape == (72, 96, 4) and (rate[..., 0] == 255).all() and (rate[..., 2] == 0).all()   # every pixel took all its samples: red
+
+
+def test_cli_cell_render(exe, tmp_path):
+    api = importlib.import_module("relativistic-ray-tracer_b200.api")
+    s = load_scene("cbspheres_lambertian_96x72")
+    src = str(tmp_path / "s.rrtscene"); out = str(tmp_path / "cell.png")
+    s.save(src)
+    r = subprocess.run([exe, "-s", "2", "-l", "1", "-m", "2", "-p", "20", "10", "32", "24", "-f", out, src], capture_output=True, text=True)
+    assert r.returncode == 0 and "Cell job completed" in r.stdout, r.stdout + r.stderr
+    c = api.Context(0); c.upload_scene(s); c.set_frame(96, 72)
+    hdr, _, _ = c.render(sc.make_params(ns_aa=2, max_ray_depth=2, ns_area_light=1, seed=0))
+    rgba = c.tonemap(hdr).reshape(72, 96)[10:34, 20:52][::-1]
+    want = np.ascontiguousarray(rgba).view(np.uint8).reshape(24, 32, 4).copy(); want[..., 3] = 255
+    assert np.array_equal(read_png(out), want)
+
+
+def test_cli_loads_dae_when_present(exe, tmp_path):
+    dae = os.path.join(ROOT, "oracle", "_ref", "dae", "CBspheres_lambertian.dae")
+    if not os.path.exists(dae):
+        pytest.skip("reference .dae files not on this box")
+    out = str(tmp_path / "o.png")
+    r = subprocess.run([exe, "-s", "1", "-l", "1", "-m", "1", "-r", "64", "48", "-f", out, dae], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    img = read_png(out)
+    assert img.shape == (48, 64, 4) and img[..., :3].max() > 0
