@@ -165,7 +165,8 @@ enum {
   RRT_OPT_WORK_BYTES = 2,   /* upper bound for the wavefront work buffers in bytes (default 12 GiB) */
   RRT_OPT_TRACE_KERNEL = 3, /* trace kernel variant, see DESIGN.md (0 = default) */
   RRT_OPT_LEAF_SIZE = 4,    /* primitives per leaf for topology 1 (1..7, default 2); takes effect at the next rrt_upload_scene */
-  RRT_OPT_CLEARANCE_GRID = 5 /* cells along the longest axis of the empty-space grid (0 = off, the default); next rrt_upload_scene */
+  RRT_OPT_CLEARANCE_GRID = 5, /* cells along the longest axis of the empty-space grid (0 = off, the default); next rrt_upload_scene */
+  RRT_OPT_BVH_WIDTH = 6       /* children per node on the device: 2, 4, 8, or 0 (default) = 8 for scenes of <= 128 primitives, else 2; topology 0 and trace kernel 1 always use 2; next rrt_upload_scene */
 };
 
 /* ---- lifecycle ---- */

@@ -23,7 +23,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RRT_B200_LIB") or os.path.join(_HERE, "csrc", "librrt_b200.so")  # env override: A/B builds only
 _LIB = None
 
-OPT_BVH_TOPOLOGY, OPT_COUNTERS, OPT_WORK_BYTES, OPT_TRACE_KERNEL, OPT_LEAF_SIZE, OPT_CLEARANCE_GRID = 0, 1, 2, 3, 4, 5
+OPT_BVH_TOPOLOGY, OPT_COUNTERS, OPT_WORK_BYTES, OPT_TRACE_KERNEL, OPT_LEAF_SIZE, OPT_CLEARANCE_GRID, OPT_BVH_WIDTH = 0, 1, 2, 3, 4, 5, 6
 
 EXPORTS = ["rrt_abi_version", "rrt_device_count", "rrt_create", "rrt_destroy", "rrt_last_error", "rrt_set_option", "rrt_upload_scene",
            "rrt_set_camera", "rrt_set_blackhole", "rrt_set_frame", "rrt_set_cell", "rrt_set_tile_shard", "rrt_render", "rrt_render_device",
@@ -375,15 +375,18 @@ class PathTracer:
         self.save_sampling_rate_image(filename)
 
     def save_sampling_rate_image(self, filename):
-        """reference src/pathtracer.cpp:686-717: red = high sample count, blue = low."""
-        cnt = self.sampleCountBuffer.astype(np.float64)
-        h, w = cnt.shape
-        gmin, gmax = cnt.min(), cnt.max()
+        """reference src/pathtracer.cpp:686-717: rate = samples taken / ns_aa; blue (few) -> green (half) -> red (all)."""
+        h, w = self.sampleCountBuffer.shape
+        rate = (self.sampleCountBuffer.astype(np.float32) * np.float32(1.0)) / np.float32(self.ns_aa)
+        lo = rate <= 0.5
+        r_lo = ((0.5 - rate.astype(np.float64)) / 0.5).astype(np.float32)
+        r_hi = ((1.0 - rate.astype(np.float64)) / 0.5).astype(np.float32)
+        red = np.where(lo, np.float32(0), (1.0 - r_hi.astype(np.float64)).astype(np.float32))
+        green = np.where(lo, (1.0 - r_lo.astype(np.float64)).astype(np.float32), r_hi)
+        blue = np.where(lo, r_lo, np.float32(0))
+        chan = lambda c: (np.minimum(np.float32(1), c) * np.float32(255)).astype(np.uint32).astype(np.uint8)   # ImageBuffer::update_pixel
         out = np.zeros((h, w, 4), np.uint8)
-        rate = np.where(gmax > gmin, (cnt - gmin) / max(gmax - gmin, 1e-300), 0.0) if gmax > gmin else np.zeros_like(cnt)
-        out[..., 0] = (np.clip(rate, 0, 1) * 255).astype(np.uint8)
-        out[..., 2] = (np.clip(1 - rate, 0, 1) * 255).astype(np.uint8)
-        out[..., 3] = 255
+        out[..., 0], out[..., 1], out[..., 2], out[..., 3] = chan(red), chan(green), chan(blue), 255
         base, ext = os.path.splitext(filename)
         write_png(base + "_rate" + (ext or ".png"), np.ascontiguousarray(out[::-1]))
 

@@ -270,7 +270,7 @@ inline float as_f32(int32_t i) { float f; memcpy(&f, &i, 4); return f; }
 float round_down_f(double x) { return round_down(x); }
 float round_up_f(double x) { return round_up(x); }
 
-int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out) {
+int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out, int width) {
   double t0_ = now_s();
   *out = FlatBvh();
   uint32_t n = s->n_prims;
@@ -352,6 +352,69 @@ int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out) {
   for (int k = 0; k < 3; ++k) { out->root_lo[k] = t->nodes[0].bb.lo[k]; out->root_hi[k] = t->nodes[0].bb.hi[k]; }
   (void)as_i32;
   TICK("flatten");
+
+  // ---- wide form: every interior node adopts grandchildren (largest box first) until it has `width` children.
+  // Fewer, fatter nodes: a traversal makes fewer loop iterations with the same instruction stream in every lane, which
+  // is what a warp that walks 32 different chords in lockstep wants.  Leaves are untouched (same records, same order).
+  out->width = (width == 4 || width == 8) ? width : 2;
+  if (out->width > 2) {
+    const int W = out->width;
+    struct Pending { int wide_index; int bin_node; int depth; };
+    std::vector<Pending> todo;
+    auto leaf_code = [&](const TNode& c) { return ~(int32_t)(((uint32_t)c.start << 3) | (uint32_t)c.count); };
+    if (t->nodes[0].l < 0) { out->wide_root = leaf_code(t->nodes[0]); out->n_wide = 0; out->wide.assign(8 * (size_t)W, 0.f); }
+    else {
+      out->wide_root = 0; out->n_wide = 1;
+      todo.push_back({0, 0, 1});
+      size_t head = 0;
+      std::vector<std::vector<int>> kids;   // per wide node: binary-node indices of its children
+      kids.push_back({});
+      // breadth-first numbering keeps the top of the tree (visited by every chord) in a few cache lines
+      while (head < todo.size()) {
+        Pending cur = todo[head++];
+        if (cur.depth > out->wide_depth) out->wide_depth = cur.depth;
+        std::vector<int> ch = {t->nodes[cur.bin_node].l, t->nodes[cur.bin_node].r};
+        while ((int)ch.size() < W) {
+          int pick = -1; double best_area = -1.0;
+          for (size_t k = 0; k < ch.size(); ++k) {
+            const TNode& c = t->nodes[ch[k]];
+            if (c.l < 0) continue;
+            double a = box_area(c.bb);
+            if (a > best_area) { best_area = a; pick = (int)k; }
+          }
+          if (pick < 0) break;
+          int b = ch[pick];
+          ch[pick] = t->nodes[b].l;
+          ch.push_back(t->nodes[b].r);
+        }
+        kids[cur.wide_index] = ch;
+        for (int c : ch)
+          if (t->nodes[c].l >= 0) { todo.push_back({out->n_wide++, c, cur.depth + 1}); kids.push_back({}); }
+      }
+      out->wide.assign(8 * (size_t)W * out->n_wide, 0.f);
+      // second pass: child codes need the numbering above
+      std::vector<int> wide_of(t->nodes.size(), -1);
+      for (const Pending& pnd : todo) wide_of[pnd.bin_node] = pnd.wide_index;
+      for (const Pending& pnd : todo) {
+        float* q = &out->wide[8 * (size_t)W * pnd.wide_index];
+        const std::vector<int>& ch = kids[pnd.wide_index];
+        for (int k = 0; k < W; ++k) {
+          if (k < (int)ch.size()) {
+            const TNode& c = t->nodes[ch[k]];
+            q[0 * W + k] = round_down(c.bb.lo[0]); q[1 * W + k] = round_down(c.bb.lo[1]); q[2 * W + k] = round_down(c.bb.lo[2]);
+            q[3 * W + k] = round_up(c.bb.hi[0]); q[4 * W + k] = round_up(c.bb.hi[1]); q[5 * W + k] = round_up(c.bb.hi[2]);
+            q[6 * W + k] = as_f32(c.l < 0 ? leaf_code(c) : wide_of[ch[k]]);
+          } else {
+            q[0 * W + k] = q[1 * W + k] = q[2 * W + k] = INFINITY;
+            q[3 * W + k] = q[4 * W + k] = q[5 * W + k] = -INFINITY;
+            q[6 * W + k] = as_f32(kEmptyChild);
+          }
+          q[7 * W + k] = 0.f;
+        }
+      }
+    }
+    TICK("collapse");
+  }
   return 0;
 }
 

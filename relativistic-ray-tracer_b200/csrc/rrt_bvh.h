@@ -30,6 +30,14 @@ struct FlatBvh {
   int32_t root = -1;              // child code of the root (0 if interior, leaf code if the whole scene is one leaf)
   double root_lo[3] = {0, 0, 0}, root_hi[3] = {0, 0, 0};
   int n_nodes = 0;                // interior nodes in the flattened array
+  // wide form (see collapse in rrt_bvh.cpp): the binary tree collapsed into nodes of up to `width` children.
+  //   node = 8 * width floats: lo.x[width] lo.y[] lo.z[] hi.x[] hi.y[] hi.z[] (outward rounded), child code[width] as int32, pad[width]
+  //   child code as above; an unused slot holds kEmptyChild and an inverted box
+  std::vector<float> wide;        // 8 * width floats per node (256 B for width 8)
+  int width = 2;                  // 2 = `nodes` is what the device reads; 4 / 8 = `wide`
+  int n_wide = 0;
+  int wide_depth = 0;             // levels of wide interior nodes
+  int32_t wide_root = -1;
   // clearance grid (see build_clearance_grid): per cell, a lower bound on the distance from ANY point of the cell to ANY primitive
   std::vector<float> clearance;   // [gz][gy][gx]
   int grid_n[3] = {0, 0, 0};
@@ -37,9 +45,12 @@ struct FlatBvh {
   int ref_nodes = 0, ref_leaves = 0, ref_depth = 0; // shape of the reference tree (nodes incl. leaves)
 };
 
+static const int32_t kEmptyChild = (int32_t)0x80000000;   // not a valid leaf code: n_prims < 2^28
+
 // topology: 0 = reference shape (midpoint split, leaves <= 4), 1 = binned SAH with leaves of <= max_leaf primitives
 // (own shape; ranks still come from the reference shape).  max_leaf is clamped to 1..7 and ignored for topology 0.
-int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out);
+// width: 2 keeps the binary nodes; 4 or 8 also fills the wide form.
+int build_bvh(const rrt_scene* s, int topology, int max_leaf, FlatBvh* out, int width = 2);
 // Empty-space grid over the scene box, res cells along the longest axis (0 disables).  The device skips the BVH for a chord
 // whose length is below the clearance of the cell its origin lies in: no primitive can be within reach, so the
 // result is unchanged.

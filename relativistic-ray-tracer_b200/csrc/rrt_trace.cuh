@@ -13,6 +13,7 @@
 
 #ifndef RRT_STACK
 #define RRT_STACK 40
+#define RRT_SPILL 136   /* wide traversal: entries beyond the shared-memory stack go to local memory (never seen in practice) */
 #endif  /* traversal stack entries per thread (shared memory); tree depth bound */
 
 struct DevScene {
@@ -28,6 +29,9 @@ struct DevScene {
   int32_t n_prims, n_mats, n_lights, root;
   float root_lo[3], root_hi[3];   // root box, rounded outward
   double ctr[3], rad;             // sphere around the root box (far-chord origin shift, boxctx_make)
+  const float* wide;              // wide nodes (rrt_bvh.h): 8 * width floats each
+  int32_t wroot;                  // child code of the wide root
+  int width;                      // 2: `nodes`; 4 / 8: `wide`
   // clearance grid (rrt_bvh.h): lower bound on the distance from any point of a cell to any primitive
   const float* clearance;
   int gnx, gny, gnz;
@@ -122,7 +126,7 @@ __device__ __forceinline__ void boxctx_axis(double o, double d, float slack, flo
   float df = (float)d;
   if (fabsf(df) < 1e-30f) df = copysignf(0.f, df);
   float of = (float)o;
-  inv = 1.0f / df;
+  inv = __frcp_rn(df);   /* correctly rounded, like 1.0f / df, without the division's slow path */
   float c = of * inv;
   float a = __fmaf_rn(2.3841858e-7f, fabsf(of), slack) * fabsf(inv);
   cn = -c - a; cf = -c + a;
@@ -289,6 +293,85 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best&
         }
       }
       if (sp) cur = stack[(--sp) * stride];
+    }
+    __syncwarp();
+  }
+  return found;
+}
+
+/* The same traversal over WIDE nodes (rrt_bvh.h: the binary tree collapsed to up to W children per node, boxes stored
+ * as six arrays of W floats).  One node visit tests W boxes with one straight-line instruction stream: no per-box
+ * select (the near / far plane arrays are picked once per chord from the direction signs), no ordering network (the
+ * nearest hit child is kept in a register, the others are pushed as they come), and far fewer loop iterations, which
+ * is what keeps the 32 lanes of a warp together.  Shadow rays (ANY) push every hit child and pop: order is irrelevant.
+ * A visit can push up to W - 1 codes, so the stack bound is (W - 1) * depth + 1: the first RRT_STACK entries live in
+ * shared memory as before, anything beyond (never observed) in a local-memory array; rrt_upload_scene checks the bound. */
+template <bool ANY, bool COUNT, int W>
+__device__ __forceinline__ bool traverse_wide(const DevScene& sc, const Seg& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt, bool active) {
+  const int DONE = (int)0x80000000;   /* also the code of an unused child slot (kEmptyChild) */
+  const float R = 9.5367431640625e-7f; /* 2^-20 */
+  best.t = s.tmax; best.rank = -1; best.prim = -1; best.kind = 0; best.b1 = best.b2 = 0.0;
+  BoxCtx bc;
+  float tmaxf = 0.f, tl;
+  bool found = false, shifted = false;
+  int cur = DONE, sp = 0;
+  int spill[RRT_SPILL];
+  auto push = [&](int code) { if (sp < RRT_STACK) stack[sp * stride] = code; else spill[min(sp - RRT_STACK, RRT_SPILL - 1)] = code; ++sp; };
+  auto pop = [&]() -> int { --sp; return sp < RRT_STACK ? stack[sp * stride] : spill[min(sp - RRT_STACK, RRT_SPILL - 1)]; };
+  int onx = 0, ony = W, onz = 2 * W, ofx = 3 * W, ofy = 4 * W, ofz = 5 * W;   /* float offsets of the near / far plane arrays */
+  if (active) {
+    const double T = boxctx_make(sc, s.o, s.d, s.tmin, bc);
+    shifted = T != 0.0;
+    tmaxf = boxctx_tmax(best.t, T);
+    if (bc.nx) { onx = 3 * W; ofx = 0; }
+    if (bc.ny) { ony = 4 * W; ofy = W; }
+    if (bc.nz) { onz = 5 * W; ofz = 2 * W; }
+    if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tl)) cur = sc.wroot;
+  }
+  while (__any_sync(0xffffffffu, cur != DONE)) {
+    while (cur >= 0) {
+      const float* nd = sc.wide + (size_t)(8 * W) * (size_t)cur;
+      if (COUNT) cnt.nodes++;
+      int nearest = DONE;
+      float tbest = 0.f;
+      auto child = [&](float pnx, float pfx, float pny, float pfy, float pnz, float pfz, int code) {
+        float tn = fmaxf(fmaxf(__fmaf_rn(pnx, bc.ix, bc.nx_), __fmaf_rn(pny, bc.iy, bc.ny_)), __fmaf_rn(pnz, bc.iz, bc.nz_));
+        float tf = fminf(fminf(__fmaf_rn(pfx, bc.ix, bc.fx_), __fmaf_rn(pfy, bc.iy, bc.fy_)), __fmaf_rn(pfz, bc.iz, bc.fz_));
+        tn = __fmaf_rn(fabsf(tn), -R, tn);
+        tf = __fmaf_rn(fabsf(tf), R, tf);
+        if (tn <= tf && tn <= tmaxf && tf >= bc.tmin && code != DONE) {
+          if (ANY) push(code);
+          else if (nearest == DONE) { nearest = code; tbest = tn; }
+          else if (tn < tbest) { push(nearest); nearest = code; tbest = tn; }
+          else push(code);
+        }
+      };
+#pragma unroll
+      for (int g = 0; g < W / 4; ++g) {
+        const float4 a = __ldg((const float4*)(nd + onx) + g), b = __ldg((const float4*)(nd + ofx) + g);
+        const float4 c = __ldg((const float4*)(nd + ony) + g), d = __ldg((const float4*)(nd + ofy) + g);
+        const float4 e = __ldg((const float4*)(nd + onz) + g), f = __ldg((const float4*)(nd + ofz) + g);
+        const int4 k = __ldg((const int4*)(nd + 6 * W) + g);
+        child(a.x, b.x, c.x, d.x, e.x, f.x, k.x);
+        child(a.y, b.y, c.y, d.y, e.y, f.y, k.y);
+        child(a.z, b.z, c.z, d.z, e.z, f.z, k.z);
+        child(a.w, b.w, c.w, d.w, e.w, f.w, k.w);
+      }
+      cur = (!ANY && nearest != DONE) ? nearest : (sp ? pop() : DONE);
+    }
+    __syncwarp();
+    if (cur != DONE) {
+      uint32_t bits = (uint32_t)~cur;
+      uint32_t first = bits >> 3, count = bits & 7u;
+      cur = DONE;
+      for (uint32_t k = 0; k < count; ++k) {
+        if (leaf_record_test<COUNT>(sc.leaf + 5 * (size_t)(first + k), s, best, cnt)) {
+          found = true;
+          if (ANY) { sp = 0; break; }
+          if (!shifted) tmaxf = __double2float_ru(best.t);
+        }
+      }
+      if (sp) cur = pop();
     }
     __syncwarp();
   }

@@ -18,6 +18,9 @@
 #ifndef RRT_MINB
 #define RRT_MINB 6     /* resident blocks per SM the trace kernels are compiled for */
 #endif
+#ifndef RRT_MINB_WIDE
+#define RRT_MINB_WIDE 6   /* the same for the wide-node variants */
+#endif
 
 __device__ __forceinline__ int wt_lane() { return threadIdx.x & 31; }
 
@@ -98,7 +101,7 @@ __device__ __forceinline__ void wt_flush_counters(const Counters& c, Counters* g
 }
 
 /* ---------------------------------------------------------------- variant 0 (default): chord-lockstep loop */
-template <bool ANY, bool COUNT, class IO>
+template <bool ANY, bool COUNT, int W, class IO>
 __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHole& bh, const IO& io, const int n, int* cursor, Counters* gcnt) {
   __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
   int* stack = stack_mem + threadIdx.x;
@@ -149,7 +152,9 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
     }
     const bool want = has && h.status < 0 && !chord_is_clear(sc, s.o, s.tmax);
     const bool live = has && h.status < 0;
-    const bool found = traverse<ANY, COUNT>(sc, s, best, stack, RRT_BLOCK, cnt, want);   /* whole warp, converged */
+    bool found;                                                                            /* whole warp, converged */
+    if (W == 2) found = traverse<ANY, COUNT>(sc, s, best, stack, RRT_BLOCK, cnt, want);
+    else found = traverse_wide<ANY, COUNT, (W == 2 ? 4 : W)>(sc, s, best, stack, RRT_BLOCK, cnt, want);
     if (live) {
       if (found) {
         h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
@@ -307,30 +312,30 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
 
 /* extension rays: closest hit */
 template <bool COUNT, int V>
-__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+__global__ void __launch_bounds__(RRT_BLOCK, (V >= 4 ? RRT_MINB_WIDE : RRT_MINB)) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                 const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
                                                                 int* cursor, int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt) {
   ClosestIO io; io.ray = ray; io.cap = cap; io.h_prim = h_prim; io.h_geo = h_geo;
   if (V == 1) trace_sched<false, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
-  else trace_persistent<false, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
+  else trace_persistent<false, COUNT, (V == 0 ? 2 : V)>(sc, bh, io, *count_ptr, cursor, gcnt);
 }
 
 /* shadow rays: BVHAccel::intersect(ray) (any hit), or closest hit when the hemisphere estimator needs the emitter */
 template <bool ANY, bool COUNT, int V>
-__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+__global__ void __launch_bounds__(RRT_BLOCK, (V >= 4 ? RRT_MINB_WIDE : RRT_MINB)) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
                                                                int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt) {
   ShadowIO io; io.ray = ray; io.cap = cap; io.cidx = cidx; io.res = res;
   if (V == 1) trace_sched<ANY, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
-  else trace_persistent<ANY, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
+  else trace_persistent<ANY, COUNT, (V == 0 ? 2 : V)>(sc, bh, io, *count_ptr, cursor, gcnt);
 }
 
 /* parity hook: the same loop on caller-supplied rays */
 template <bool ANY, int V>
-__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB) k_hook_trace(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, int n,
+__global__ void __launch_bounds__(RRT_BLOCK, (V >= 4 ? RRT_MINB_WIDE : RRT_MINB)) k_hook_trace(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, int n,
                                                             const double* __restrict__ o, const double* __restrict__ d, const double* __restrict__ tmin,
                                                             const double* __restrict__ tmax, rrt_hit* __restrict__ out, int* cursor, Counters* gcnt) {
   HookIO<ANY> io; io.o = o; io.d = d; io.tmin = tmin; io.tmax = tmax; io.out = out;
   if (V == 1) trace_sched<ANY, true>(sc, bh, io, n, cursor, gcnt);
-  else trace_persistent<ANY, true>(sc, bh, io, n, cursor, gcnt);
+  else trace_persistent<ANY, true, (V == 0 ? 2 : V)>(sc, bh, io, n, cursor, gcnt);
 }

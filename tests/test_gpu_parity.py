@@ -61,10 +61,11 @@ def test_geodesic_chords_bit_exact(api, tag):
     assert c.chords_per_ray() == (63 if bh[4] == 0.1 else 32)
 
 
-@pytest.mark.parametrize("topology,leaf,variant,grid", [(0, 4, 1, 0), (1, 2, 1, 32), (1, 1, 0, 64), (1, 4, 0, 0), (1, 2, 0, 128)])
+@pytest.mark.parametrize("topology,leaf,variant,grid,width", [(0, 4, 1, 0, 2), (1, 2, 1, 32, 2), (1, 1, 0, 64, 4), (1, 4, 0, 0, 8), (1, 2, 0, 128, 2),
+                                                              (1, 2, 0, 0, 8), (1, 7, 0, 0, 4), (0, 4, 0, 0, 2)])
 @pytest.mark.parametrize("scene", ["cbspheres_lambertian_480x360", "cbgems_480x360", "cbbunny_microfacet_480x360"])
 @pytest.mark.parametrize("mode", ["flat", "bh", "alt"])
-def test_bvh_intersect_matches_reference(api, scene, mode, topology, leaf, variant, grid):
+def test_bvh_intersect_matches_reference(api, scene, mode, topology, leaf, variant, grid, width):
     g = golden("kat_trace_" + scene)
     if "hit_" + mode not in g.files:
         pytest.skip("no alt-hole vectors for this scene")
@@ -73,6 +74,7 @@ def test_bvh_intersect_matches_reference(api, scene, mode, topology, leaf, varia
     c.set_option(api.OPT_LEAF_SIZE, leaf)
     c.set_option(api.OPT_TRACE_KERNEL, variant)
     c.set_option(api.OPT_CLEARANCE_GRID, grid)
+    c.set_option(api.OPT_BVH_WIDTH, width)
     c.upload_scene(load_scene(scene))
     if mode == "flat":
         c.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_FLAT)
@@ -109,13 +111,13 @@ def test_trace_matches_oracle_records(api, orc, scene, mode):
     assert (got["status"] == 2).sum() > 0 or mode == "flat"
 
 
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant,width", [(0, 2), (1, 2), (0, 8), (0, 4)])
 @pytest.mark.parametrize("mode", ["flat", "bh"])
-def test_far_origin_chords_match_oracle(api, orc, mode, variant):
+def test_far_origin_chords_match_oracle(api, orc, mode, variant, width):
     """chords whose origin lies 1e2..1e7 units from the scene are box-tested from a shifted origin (rrt_trace.cuh boxctx_make):
     same records as the oracle, for rays aimed into the scene and for the escaped rays of a 1080p frame"""
     s = load_scene("cbbunny_microfacet_480x360")
-    c = api.Context(0); c.set_option(api.OPT_TRACE_KERNEL, variant); c.upload_scene(s)
+    c = api.Context(0); c.set_option(api.OPT_TRACE_KERNEL, variant); c.set_option(api.OPT_BVH_WIDTH, width); c.upload_scene(s)
     o = orc.Oracle(s)
     m = sc.MODE_FLAT if mode == "flat" else sc.MODE_LITERAL
     c.set_blackhole((0, 1, 0), 0.1, 0.1, m); o.set_blackhole((0, 1, 0), 0.1, 0.1, m)
@@ -251,6 +253,10 @@ def test_c2_full_size_properties(api):
     c0.upload_scene(s); c0.set_frame(480, 360)
     h0, _, st0 = c0.render(p)
     assert np.array_equal(hdr, h0) and st0["rays"] == st["rays"]
+    for width in (2, 4):                                                   # default is 8 children per node
+        cw = api.Context(0); cw.set_option(api.OPT_BVH_WIDTH, width); cw.upload_scene(s); cw.set_frame(480, 360)
+        hw, _, stw = cw.render(p)
+        assert np.array_equal(hdr, hw) and stw["rays"] == st["rays"] and stw["geodesic_steps"] == st["geodesic_steps"]
     # a different chunking of the wavefront must not change a single bit
     p2 = sc.make_params(ns_aa=16, max_ray_depth=5, ns_area_light=4, seed=7, max_paths_in_flight=300000)
     hdr3, _, st3 = c.render(p2)
