@@ -30,7 +30,7 @@ def lib():
         L.orc_create.restype = C.c_void_p
         L.orc_create.argtypes = [C.POINTER(_sc.Scene), C.POINTER(_sc.Camera)]
         for name in ("orc_destroy", "orc_set_camera", "orc_set_blackhole", "orc_set_frame", "orc_set_cell", "orc_set_tile_shard",
-                     "orc_bvh_info", "orc_geodesic", "orc_trace_rays", "orc_generate_rays", "orc_philox", "orc_tonemap"):
+                     "orc_bvh_info", "orc_geodesic", "orc_trace_rays", "orc_generate_rays", "orc_philox", "orc_tonemap", "orc_set_envmap"):
             getattr(L, name).restype = None
         _LIB = L
     return _LIB
@@ -64,6 +64,20 @@ class Oracle:
 
     def set_tile_shard(self, tile, rank, world):
         lib().orc_set_tile_shard(self.h, C.c_int(tile), C.c_int(rank), C.c_int(world))
+
+    def set_envmap(self, rgb):
+        """rgb: [h, w, 3] float32, row 0 = top (None clears)"""
+        if rgb is None:
+            lib().orc_set_envmap(self.h, C.c_int(0), C.c_int(0), None)
+            return
+        a = np.ascontiguousarray(rgb, np.float32)
+        lib().orc_set_envmap(self.h, C.c_int(a.shape[1]), C.c_int(a.shape[0]), _p(a))
+
+    def env_lookup(self, d):
+        d = np.ascontiguousarray(d, np.float64).reshape(-1, 3)
+        out = np.zeros((d.shape[0], 3), np.float32)
+        assert lib().orc_env_lookup(self.h, C.c_int64(d.shape[0]), _p(d), _p(out)) == 0
+        return out
 
     def chords_per_ray(self):
         return int(lib().orc_chords_per_ray(self.h))

@@ -41,6 +41,7 @@
 #include "static_scene/triangle.h"
 #include "static_scene/sphere.h"
 #include "static_scene/light.h"
+#include "static_scene/environment_light.h"
 #include "collada/collada.h"
 #undef private
 #undef protected
@@ -136,6 +137,20 @@ static Ctx load(const char* dae, int W, int H, AppConfig cfg = AppConfig()) {
   Ctx c; c.W = W; c.H = H;
   Collada::SceneInfo* si = new Collada::SceneInfo();
   if (Collada::ColladaParser::load(dae, si) < 0) { fprintf(stderr, "cannot load %s\n", dae); exit(2); }
+  // Optional: RRT_PROBE_ENVMAP=<file> gives the reference an environment map without going through an .exr file
+  // (none ships with the reference): the file is int32 w, int32 h, then w*h*3 float32 (row 0 = top, as load_exr fills
+  // the buffer, src/main.cpp:66-76).  EnvironmentLight's constructor writes probability_debug.png into the cwd.
+  if (const char* envf = getenv("RRT_PROBE_ENVMAP")) {
+    FILE* f = fopen(envf, "rb"); if (!f) { perror(envf); exit(2); }
+    int32_t wh[2]; if (fread(wh, 4, 2, f) != 2) exit(2);
+    std::vector<float> px((size_t)wh[0] * wh[1] * 3);
+    if (fread(px.data(), 4, px.size(), f) != px.size()) exit(2);
+    fclose(f);
+    HDRImageBuffer* env = new HDRImageBuffer();
+    env->resize(wh[0], wh[1]);
+    for (size_t i = 0; i < (size_t)wh[0] * wh[1]; ++i) env->data[i] = Spectrum(px[3 * i], px[3 * i + 1], px[3 * i + 2]);
+    cfg.pathtracer_envmap = env;
+  }
   // same call sequence as the headless path of main(): src/main.cpp:172-188
   c.app = new Application(cfg, false);
   c.app->init();
@@ -358,6 +373,24 @@ static int cmd_light(int argc, char** argv) {
   return 0;
 }
 
+// envdir: EnvironmentLight::sample_dir (src/static_scene/environment_light.cpp:145-147) for n directions.
+// in = n x [d3]; out = n x [L3].  Needs RRT_PROBE_ENVMAP.
+static int cmd_envdir(int argc, char** argv) {
+  if (argc < 7) return 1;
+  Ctx c = load(argv[2], atoi(argv[3]), atoi(argv[4]));
+  EnvironmentLight* env = c.pt->scene->lights.empty() ? nullptr : dynamic_cast<EnvironmentLight*>(c.pt->scene->lights.back());
+  if (!env) { fprintf(stderr, "no environment light (set RRT_PROBE_ENVMAP)\n"); return 2; }
+  std::vector<double> in = read_doubles(argv[5]);
+  size_t n = in.size() / 3;
+  std::vector<double> out(n * 3, 0.0);
+  for (size_t i = 0; i < n; ++i) {
+    Spectrum L = env->sample_dir(Ray(Vector3D(0, 0, 0), Vector3D(in[3 * i], in[3 * i + 1], in[3 * i + 2])));
+    out[3 * i] = L.r; out[3 * i + 1] = L.g; out[3 * i + 2] = L.b;
+  }
+  write_doubles(argv[6], out);
+  return 0;
+}
+
 // order: which of two consecutive rand() draws becomes .x of UniformGridSampler2D::get_sample()
 // (argument evaluation order is the compiler's choice, src/sampler.cpp:7-11).  Prints "x=first" or "x=second".
 static int cmd_order(int, char**) {
@@ -430,6 +463,7 @@ int main(int argc, char** argv) {
     else if (cmd == "camrays") rc = cmd_camrays(argc, argv);
     else if (cmd == "bsdf") rc = cmd_bsdf(argc, argv);
     else if (cmd == "light") rc = cmd_light(argc, argv);
+    else if (cmd == "envdir") rc = cmd_envdir(argc, argv);
     else if (cmd == "render") rc = cmd_render(argc, argv);
     else if (cmd == "order") rc = cmd_order(argc, argv);
   }

@@ -93,6 +93,10 @@ typedef struct orc_ctx {
   node_t* nodes; int n_nodes, cap_nodes, n_leaves, depth;
   uint32_t* order;  /* primitives in depth-first leaf order */
   uint64_t cnt_rays, cnt_steps, cnt_nodes, cnt_tris, cnt_sph; /* per-call counters (not thread safe: see orc_render) */
+  /* environment light (src/static_scene/environment_light.{h,cpp}): appended after the scene's lights (src/pathtracer.cpp:107-109) */
+  int env_w, env_h;
+  float* env;                         /* [h][w][3], row 0 = top */
+  double *env_pdf, *env_cond, *env_marg;
 } orc_ctx;
 
 static void* dup_mem(const void* p, size_t bytes) { void* q = malloc(bytes ? bytes : 1); if (bytes) memcpy(q, p, bytes); return q; }
@@ -180,7 +184,8 @@ orc_ctx* orc_create(const rrt_scene* s, const rrt_camera* cam) {
 void orc_destroy(orc_ctx* c) {
   if (!c) return;
   free(c->prim_kind); free(c->prim_index); free(c->tri_pos); free(c->tri_nrm); free(c->tri_mat); free(c->sph);
-  free(c->sph_mat); free(c->mats); free(c->lights); free(c->nodes); free(c->order); free(c);
+  free(c->sph_mat); free(c->mats); free(c->lights); free(c->nodes); free(c->order);
+  free(c->env); free(c->env_pdf); free(c->env_cond); free(c->env_marg); free(c);
 }
 
 void orc_set_camera(orc_ctx* c, const rrt_camera* cam) { c->cam = *cam; }
@@ -526,6 +531,80 @@ static spec bsdf_sample_f(const rrt_material* m, v3 wo, v3* wi, float* pdf, rng_
 }
 
 /* ------------------------------------------------------------------ lights: SceneLight::sample_L  (src/static_scene/light.cpp:17-92) */
+/* ---- EnvironmentLight ---- */
+/* init (src/static_scene/environment_light.cpp:21-49).  The reference accumulates into an uninitialised marginal_y
+ * (new double[h]); zero is what a fresh heap gives it and what is restated here. */
+void orc_set_envmap(orc_ctx* c, int w, int h, const float* rgb) {
+  free(c->env); free(c->env_pdf); free(c->env_cond); free(c->env_marg);
+  c->env = NULL; c->env_pdf = c->env_cond = c->env_marg = NULL; c->env_w = c->env_h = 0;
+  if (!rgb || w <= 0 || h <= 0) return;
+  c->env_w = w; c->env_h = h;
+  c->env = (float*)dup_mem(rgb, sizeof(float) * 3 * (size_t)w * h);
+  c->env_pdf = (double*)malloc(sizeof(double) * (size_t)w * h);
+  c->env_cond = (double*)malloc(sizeof(double) * (size_t)w * h);
+  c->env_marg = (double*)calloc((size_t)h, sizeof(double));
+  double sum = 0;
+  for (int j = 0; j < h; ++j)
+    for (int i = 0; i < w; ++i) {
+      c->env_pdf[(size_t)w * j + i] = s_illum(s3(rgb + 3 * ((size_t)w * j + i))) * sin(ORC_PI * (j + .5) / h);
+      sum += c->env_pdf[(size_t)w * j + i];
+    }
+  for (int j = 0; j < h; ++j) {
+    for (int i = 0; i < w; ++i) c->env_marg[j] += (c->env_pdf[(size_t)w * j + i] /= sum);
+    for (int i = 0; i < w; ++i) {
+      c->env_cond[(size_t)w * j + i] = c->env_pdf[(size_t)w * j + i] / c->env_marg[j];
+      if (i > 0) c->env_cond[(size_t)w * j + i] += c->env_cond[(size_t)w * j + i - 1];
+    }
+    if (j > 0) c->env_marg[j] += c->env_marg[j - 1];
+  }
+}
+
+/* bilerp (src/static_scene/environment_light.cpp:99-115) */
+static spec env_bilerp(const orc_ctx* c, double x, double y) {
+  const long w = c->env_w, h = c->env_h;
+  long right = lround(x), left, v = lround(y);
+  double u1 = right - x + .5, v1;
+  if (right == 0 || right == w) { left = w - 1; right = 0; } else left = right - 1;
+  if (v == 0) { v1 = v = 1; } else if (v == h) { v = h - 1; v1 = 0; } else v1 = v - y + .5;
+  size_t bottom = (size_t)w * (size_t)v, top = bottom - (size_t)w;
+  double u0 = 1 - u1;
+  spec tl = s3(c->env + 3 * (top + left)), tr = s3(c->env + 3 * (top + right));
+  spec bl = s3(c->env + 3 * (bottom + left)), br = s3(c->env + 3 * (bottom + right));
+  return s_add(s_mulf(s_add(s_mulf(tl, (float)u1), s_mulf(tr, (float)u0)), (float)v1),
+               s_mulf(s_add(s_mulf(bl, (float)u1), s_mulf(br, (float)u0)), (float)(1 - v1)));
+}
+
+/* sample_dir = bilerp(theta_phi_to_xy(dir_to_theta_phi(r.d)))  (:76-80, :60-65, :145-147) */
+static spec env_sample_dir(const orc_ctx* c, v3 d) {
+  v3 u = vunit(d);
+  double theta = acos(u.y), phi = atan2(-u.z, u.x) + ORC_PI;
+  double x = phi / 2. / ORC_PI * c->env_w, y = theta / ORC_PI * c->env_h;
+  return env_bilerp(c, x, y);
+}
+
+/* first index whose value is greater than key (std::upper_bound) */
+static int upper_bound_d(const double* a, int n, double key) {
+  int lo = 0, hi = n;
+  while (lo < hi) { int mid = lo + (hi - lo) / 2; if (!(key < a[mid])) lo = mid + 1; else hi = mid; }
+  return lo;
+}
+
+/* sample_L, ENV_HEMI == 0 (:118-133).  A draw of exactly 1.0 would index one past the tables in the reference
+ * (upper_bound returns h or w); clamped here, as on the device. */
+static spec env_sample_L(const orc_ctx* c, v3* wi, float* dist, float* pdf, rng_t* g) {
+  const int w = c->env_w, h = c->env_h;
+  *dist = INFINITY;
+  double sx, sy; rng_grid2(g, &sx, &sy);
+  int y = upper_bound_d(c->env_marg, h, sy); if (y > h - 1) y = h - 1;
+  const double* cond = c->env_cond + (size_t)w * y;
+  int x = upper_bound_d(cond, w, sx); if (x > w - 1) x = w - 1;
+  double phi = (double)x / w * 2.0 * ORC_PI, theta = (double)y / h * ORC_PI;     /* xy_to_theta_phi (:67-74) */
+  double dy = cos(theta), dx = cos(phi - ORC_PI) * sin(theta), dz = -sin(phi - ORC_PI) * sin(theta);   /* theta_phi_to_dir (:82-91) */
+  *wi = V(dx, dy, dz);
+  *pdf = (float)(c->env_pdf[(size_t)w * y + x] * w * h / (2 * ORC_PI * ORC_PI * sin(theta)));
+  return env_bilerp(c, (double)x, (double)y);
+}
+
 static spec light_sample_L(const rrt_light* l, v3 p, v3* wi, float* dist, float* pdf, rng_t* g) {
   switch (l->type) {
     case RRT_LIGHT_DIRECTIONAL:
@@ -607,14 +686,15 @@ static spec direct_importance(est_t* e, const isect_t* isect) {
   const rrt_material* m = prim_material(c, isect->prim);
   spec L_out = S(0, 0, 0);
   int total = 0;
-  for (uint32_t li = 0; li < c->n_lights; ++li) {
-    const rrt_light* l = &c->lights[li];
-    int ns = l->is_delta ? 1 : e->p->ns_area_light;
+  const uint32_t n_all = c->n_lights + (c->env ? 1u : 0u);
+  for (uint32_t li = 0; li < n_all; ++li) {
+    const rrt_light* l = li < c->n_lights ? &c->lights[li] : NULL;   /* NULL: the environment light, last in the list */
+    int ns = (l && l->is_delta) ? 1 : e->p->ns_area_light;
     total += ns;
     for (int i = 0; i < ns; ++i) {
       v3 wi_world; float dist, pdf;
-      spec sample = light_sample_L(l, isect->hit_p, &wi_world, &dist, &pdf, e->g);
-      if (l->type == RRT_LIGHT_NULL) continue; /* stub lights return zero radiance */
+      spec sample = l ? light_sample_L(l, isect->hit_p, &wi_world, &dist, &pdf, e->g) : env_sample_L(c, &wi_world, &dist, &pdf, e->g);
+      if (l && l->type == RRT_LIGHT_NULL) continue; /* stub lights return zero radiance */
       v3 w_in = mat_tmul(o2w, wi_world);
       if (w_in.z < 0) continue;
       ray_t sr; sr.o = vadd(isect->hit_p, smul(ORC_EPS_D, wi_world)); sr.d = wi_world; sr.min_t = 0.0; sr.max_t = dist;
@@ -654,10 +734,11 @@ static spec at_least_one_bounce(est_t* e, int depth, const isect_t* isect) {
   return L_out;
 }
 
-/* est_radiance_global_illumination  (src/part1_code.cpp:103-123), ILLUM == 2; no environment light (-e is a "next" row) */
+/* est_radiance_global_illumination  (src/part1_code.cpp:103-123), ILLUM == 2 */
 static spec est_radiance(est_t* e, const ray_t* r) {
   isect_t isect;
-  if (bvh_intersect(e->c, r, &isect, NULL, NULL, NULL, e->cnt) != 1) return S(0, 0, 0);
+  if (bvh_intersect(e->c, r, &isect, NULL, NULL, NULL, e->cnt) != 1)   /* a miss OR a capture; the ray's own, unbent direction */
+    return e->c->env ? env_sample_dir(e->c, r->d) : S(0, 0, 0);
   spec Le = mat_emission(prim_material(e->c, isect.prim));
   if (e->p->max_ray_depth == 0) return Le;
   if (e->p->max_ray_depth == 1) return s_add(Le, one_bounce(e, &isect));
@@ -811,13 +892,24 @@ int orc_bsdf_eval(const orc_ctx* c, int mat, int64_t n, const double* wo, const 
 }
 int orc_light_sample(const orc_ctx* c, int light, int64_t n, const double* p, const double* u, float* radiance, double* wi,
                      float* dist, float* pdf) {
-  if (light < 0 || light >= (int)c->n_lights) return RRT_E_ARG;
+  const int is_env = c->env && light == (int)c->n_lights;   /* the environment light is the last light */
+  if (light < 0 || (light >= (int)c->n_lights && !is_env)) return RRT_E_ARG;
   for (int64_t i = 0; i < n; ++i) {
     rng_t g; memset(&g, 0, sizeof g); g.fixed = u + 2 * i;
     v3 w; float ds = 0, pd = 0;
-    spec s = light_sample_L(&c->lights[light], V(p[3 * i], p[3 * i + 1], p[3 * i + 2]), &w, &ds, &pd, &g);
+    spec s = is_env ? env_sample_L(c, &w, &ds, &pd, &g) : light_sample_L(&c->lights[light], V(p[3 * i], p[3 * i + 1], p[3 * i + 2]), &w, &ds, &pd, &g);
     radiance[3 * i] = s.r; radiance[3 * i + 1] = s.g; radiance[3 * i + 2] = s.b;
     wi[3 * i] = w.x; wi[3 * i + 1] = w.y; wi[3 * i + 2] = w.z; dist[i] = ds; pdf[i] = pd;
+  }
+  return 0;
+}
+
+/* EnvironmentLight::sample_dir for n directions d [n*3] -> radiance [n*3] */
+int orc_env_lookup(const orc_ctx* c, int64_t n, const double* d, float* radiance) {
+  if (!c->env) return RRT_E_STATE;
+  for (int64_t i = 0; i < n; ++i) {
+    spec s = env_sample_dir(c, V(d[3 * i], d[3 * i + 1], d[3 * i + 2]));
+    radiance[3 * i] = s.r; radiance[3 * i + 1] = s.g; radiance[3 * i + 2] = s.b;
   }
   return 0;
 }

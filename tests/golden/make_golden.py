@@ -27,7 +27,7 @@ TMP = tempfile.mkdtemp(prefix="rrt_golden_")
 def run(args, env=None):
     e = dict(os.environ)
     e.update(env or {})
-    subprocess.check_call([str(a) for a in args], env=e, stdout=subprocess.DEVNULL)
+    subprocess.check_call([str(a) for a in args], env=e, stdout=subprocess.DEVNULL, cwd=TMP)   # cwd: EnvironmentLight drops a debug png there
 
 
 def probe(mode, cmd, *args, env=None):
@@ -207,6 +207,49 @@ def kat_light(scene, seed):
     print("kat_light", scene)
 
 
+# ---------------------------------------------------------------- environment map (the reference ships none)
+def synthetic_envmap(w=64, h=32, seed=30):
+    """smooth sky gradient + a bright sun + seeded texture, strictly positive (a black row would put 0/0 into the
+    reference's conditional table); [h, w, 3] float32, row 0 = top"""
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:h, 0:w]
+    sky = np.stack([0.25 + 0.5 * y / h, 0.35 + 0.3 * (1 - y / h), 0.6 + 0.3 * np.cos(2 * np.pi * x / w)], -1)
+    sun = 40.0 * np.exp(-(((x - 0.7 * w) / 2.5) ** 2 + ((y - 0.3 * h) / 2.0) ** 2))
+    tex = rng.uniform(0.0, 0.15, (h, w, 3))
+    return (sky + sun[..., None] * np.array([1.0, 0.9, 0.7]) + tex).astype(np.float32)
+
+
+def envmap_file(env):
+    p = tmpf("env.bin")
+    with open(p, "wb") as f:
+        f.write(np.array([env.shape[1], env.shape[0]], np.int32).tobytes()); f.write(np.ascontiguousarray(env, np.float32).tobytes())
+    return p
+
+
+def kat_envmap(scene, seed):
+    """EnvironmentLight::sample_L (as the last light of the scene) and ::sample_dir for seeded inputs"""
+    sys.path.insert(0, ROOT)
+    import importlib
+    sc = importlib.import_module("relativistic-ray-tracer_b200.scene")
+    dae, w, h, _ = SCENES[scene]
+    n_lights = len(sc.SceneData.load(os.path.join(HERE, scene + ".rrtscene")).lights)
+    env = synthetic_envmap()
+    e = {"RRT_PROBE_ENVMAP": envmap_file(env)}
+    rng = np.random.default_rng(seed)
+    n = 2048
+    p = np.stack([rng.uniform(-1, 1, n), rng.uniform(0, 1.6, n), rng.uniform(-1, 1, n)], 1)
+    r = rng.integers(0, RAND_MAX, (n, 2), endpoint=True).astype(np.float64)
+    r[0] = [0, 0]; r[1] = [RAND_MAX - 1, RAND_MAX - 1]; r[2] = [0, RAND_MAX - 1]; r[3] = [RAND_MAX - 1, 0]
+    inp = np.concatenate([p, r], 1)
+    probe("bh", "light", os.path.join(DAE, dae), w, h, n_lights, wr("env_in.bin", inp), tmpf("env_out.bin"), env=e)
+    d = unit(rng.normal(size=(n, 3)))
+    d[:6] = [[0, 1, 0], [0, -1, 0], [1, 0, 0], [-1, 0, 0], [0, 0, 1], [0, 0, -1]]
+    probe("bh", "envdir", os.path.join(DAE, dae), w, h, wr("envdir_in.bin", d), tmpf("envdir_out.bin"), env=e)
+    np.savez_compressed(os.path.join(HERE, "kat_envmap.npz"), env=env, scene=scene, light_index=n_lights, inp=inp, out=rd("env_out.bin", 10),
+                        dirs=d, dir_out=rd("envdir_out.bin", 3))
+    print("kat_envmap", scene)
+
+
 def make_kat():
     kat_geodesic()
     kat_trace("cbspheres_lambertian_480x360", 96, 72, 2000, 1, bh_alt=(0.2, 0.8, -0.1, 0.05, 0.2))
@@ -216,6 +259,7 @@ def make_kat():
         kat_bsdf(sname, 10 + i)
     kat_light("cbspheres_lambertian_480x360", 20)
     kat_light("cbempty_480x360", 21)
+    kat_envmap("cbspheres_lambertian_480x360", 22)
 
 
 # ---------------------------------------------------------------- renders (reference raytrace_pixel, Philox-fed rand)
@@ -237,6 +281,10 @@ RENDERS = {  # name -> (scene, mode, spp, l, m, batch, tol, seed, extra args)
     "flat_pointlight": ("cbempty_96x72", "flat", 8, 1, 4, 32, 0.05, 15, []),
     "flat_hemisphere": ("cbspheres_lambertian_96x72", "flat", 8, 4, 3, 32, 0.05, 16, ["hemi"]),
     "bh_alt_hole": ("cbspheres_lambertian_96x72", "bh", 4, 2, 4, 32, 0.05, 17, ["-B", 0.2, 0.8, -0.1, 0.05, 0.2]),
+    # environment light (-e): synthetic_envmap() handed to the reference through RRT_PROBE_ENVMAP
+    "flat_envmap": ("cbspheres_lambertian_96x72", "flat", 8, 2, 4, 32, 0.05, 18, ["env"]),
+    "bh_envmap": ("cbspheres_lambertian_96x72", "bh", 4, 2, 3, 32, 0.05, 19, ["env"]),
+    "bh_envmap_gems": ("cbgems_96x72", "bh", 4, 1, 5, 32, 0.05, 20, ["env"]),
 }
 
 
@@ -246,14 +294,17 @@ def make_render(only=None):
             continue
         dae, w, h, _ = SCENES[scene]
         out = tmpf("render.bin")
-        probe(mode, "render", os.path.join(DAE, dae), w, h, spp, l, m, batch, tol, seed, out, *extra, env=scene_env(scene))
+        env = scene_env(scene)
+        if "env" in extra:
+            env = dict(env); env["RRT_PROBE_ENVMAP"] = envmap_file(synthetic_envmap())
+        probe(mode, "render", os.path.join(DAE, dae), w, h, spp, l, m, batch, tol, seed, out, *[x for x in extra if x != "env"], env=env)
         a = np.fromfile(out, np.float64)
         img = a[: w * h * 4].reshape(h, w, 4)
         tail = a[w * h * 4:]
         np.savez_compressed(os.path.join(HERE, "render_%s.npz" % name), hdr=img[..., :3].astype(np.float32),
                             counts=img[..., 3].astype(np.int32), scene=scene, mode=mode,
                             params=np.array([spp, l, m, batch, tol, seed], np.float64),
-                            hemi=np.array("hemi" in extra), bh=np.array([x for x in extra if not isinstance(x, str)], np.float64),
+                            hemi=np.array("hemi" in extra), envmap=np.array("env" in extra), bh=np.array([x for x in extra if not isinstance(x, str)], np.float64),
                             draws=tail[2])
         print("render", name, "mean radiance %.5f  paths %d" % (img[..., :3].mean(), img[..., 3].sum()))
 

@@ -107,3 +107,17 @@ def test_light_sample_L(scene):
     rad, wi, dist, pdf = orc.Oracle(s).light_sample(0, inp[:, 0:3], inp[:, 3:5] / RAND_MAX)
     assert same(rad.astype(np.float64), ref[:, 0:3]) and same(wi, ref[:, 3:6])
     assert same(dist.astype(np.float64), ref[:, 6]) and same(pdf.astype(np.float64), ref[:, 7])
+
+
+def test_environment_light_sample_L_and_sample_dir():
+    """EnvironmentLight (reference src/static_scene/environment_light.cpp) as the last light of the scene: importance
+    sampling through the marginal / conditional tables, and the direction lookup used for camera rays that miss"""
+    g = golden("kat_envmap")
+    o = orc.Oracle(load_scene(str(g["scene"])))
+    o.set_envmap(g["env"])
+    inp, ref = g["inp"], g["out"]
+    rad, wi, dist, pdf = o.light_sample(int(g["light_index"]), inp[:, 0:3], inp[:, 3:5] / RAND_MAX)
+    assert same(rad.astype(np.float64), ref[:, 0:3]) and same(wi, ref[:, 3:6])
+    assert np.isinf(dist).all() and np.isinf(ref[:, 6]).all() and same(pdf.astype(np.float64), ref[:, 7])
+    assert (ref[:, 8] == 2).all() and (ref[:, 9] == 0).all()      # two draws per sample, not a delta light
+    assert same(o.env_lookup(g["dirs"]).astype(np.float64), g["dir_out"])
