@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define RRT_ABI_VERSION 2
+#define RRT_ABI_VERSION 3
 
 /* error codes */
 #define RRT_OK 0
@@ -184,6 +184,12 @@ int rrt_set_blackhole(rrt_ctx* ctx, const double centre[3], double r, double del
 int rrt_set_frame(rrt_ctx* ctx, int width, int height);
 /* cell render (-p x y dx dy); w<=0 restores the full frame */
 int rrt_set_cell(rrt_ctx* ctx, int x, int y, int w, int h);
+/* Environment light, the reference's -e <map.exr> (src/main.cpp:42-79, src/static_scene/environment_light.cpp):
+ * rgb = [height*width*3] floats, row 0 = top of the lat-long map (theta = 0 is +y).  The light is appended after the
+ * scene's lights, is importance sampled for direct lighting, and camera rays that hit nothing (or fall into the
+ * hole) return the map's radiance along their own, unbent direction.  rgb == NULL removes it.  Survives
+ * rrt_upload_scene.  Maps with an all-black row are not usable (the reference divides by that row's marginal). */
+int rrt_set_envmap(rrt_ctx* ctx, int width, int height, const float* rgb);
 /* interleaved tile ownership for multi-GPU: tile (tx,ty) belongs to rank (tx + ty*ntx) % world */
 int rrt_set_tile_shard(rrt_ctx* ctx, int tile_size, int rank, int world);
 
@@ -218,6 +224,9 @@ int rrt_bsdf_eval(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const doub
 int rrt_light_sample(rrt_ctx* ctx, int light, int64_t n, const double* p, const double* u,
                      float* radiance, double* wi, float* dist, float* pdf);
 /* Philox4x32-10 block for (key = seed, counter = c0..c3) as the render uses it: out [n*4] uint32. */
+/* EnvironmentLight::sample_dir for n directions dir [n*3] -> radiance [n*3]; the light itself is sampled through
+ * rrt_light_sample with light == the scene's light count. */
+int rrt_env_lookup(rrt_ctx* ctx, int64_t n, const double* dir, float* radiance);
 int rrt_philox(rrt_ctx* ctx, uint64_t seed, int64_t n, const uint32_t* counters, uint32_t* out);
 /* toColor: [n*3] float HDR -> [n] RGBA8 (alpha 0xFF), on the device. */
 int rrt_tonemap(rrt_ctx* ctx, int64_t n, const float* hdr_rgb, uint32_t* rgba);

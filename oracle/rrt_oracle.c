@@ -665,7 +665,7 @@ static spec direct_hemisphere(est_t* e, const isect_t* isect) {
   v3 o2w[3]; make_coord_space(o2w, isect->n);
   v3 w_out = mat_tmul(o2w, isect->w_out);
   const rrt_material* m = prim_material(c, isect->prim);
-  int num_samples = (int)c->n_lights * e->p->ns_area_light;
+  int num_samples = (int)(c->n_lights + (c->env ? 1u : 0u)) * e->p->ns_area_light;   /* scene->lights.size() counts the environment light */
   spec L_out = S(0, 0, 0);
   for (int i = 0; i < num_samples; ++i) {
     v3 w_in = hemisphere_sample(e->g);

@@ -28,7 +28,7 @@ OPT_BVH_TOPOLOGY, OPT_COUNTERS, OPT_WORK_BYTES, OPT_TRACE_KERNEL, OPT_LEAF_SIZE,
 EXPORTS = ["rrt_abi_version", "rrt_device_count", "rrt_create", "rrt_destroy", "rrt_last_error", "rrt_set_option", "rrt_upload_scene",
            "rrt_set_camera", "rrt_set_blackhole", "rrt_set_frame", "rrt_set_cell", "rrt_set_tile_shard", "rrt_render", "rrt_render_device",
            "rrt_trace_rays", "rrt_geodesic", "rrt_generate_rays", "rrt_bsdf_sample", "rrt_bsdf_eval", "rrt_light_sample", "rrt_philox",
-           "rrt_tonemap", "rrt_bvh_info", "rrt_bvh_build_host", "rrt_chords_per_ray"]
+           "rrt_tonemap", "rrt_bvh_info", "rrt_bvh_build_host", "rrt_chords_per_ray", "rrt_set_envmap", "rrt_env_lookup"]
 
 
 class RrtError(RuntimeError):
@@ -65,6 +65,8 @@ def lib():
         L.rrt_bsdf_eval.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rrt_light_sample.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rrt_philox.argtypes = [C.c_void_p, C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p]
+        L.rrt_set_envmap.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.rrt_env_lookup.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
         L.rrt_tonemap.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
         L.rrt_bvh_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_void_p]
         L.rrt_chords_per_ray.argtypes = [C.c_void_p]
@@ -207,6 +209,22 @@ class Context:
         self._ck(lib().rrt_light_sample(self.h, int(light), n, _p(p), _p(u), _p(rad), _p(wi), _p(dist), _p(pdf)))
         return rad, wi, dist, pdf
 
+    def set_envmap(self, rgb):
+        """environment light (-e): rgb [h, w, 3] float32, row 0 = top; None removes it"""
+        if rgb is None:
+            self._ck(lib().rrt_set_envmap(self.h, 0, 0, None))
+            return
+        a = np.ascontiguousarray(rgb, np.float32)
+        if a.ndim != 3 or a.shape[2] != 3:
+            raise ValueError("set_envmap: expected an [h, w, 3] array")
+        self._ck(lib().rrt_set_envmap(self.h, a.shape[1], a.shape[0], _p(a)))
+
+    def env_lookup(self, d):
+        d = np.ascontiguousarray(d, np.float64).reshape(-1, 3)
+        out = np.zeros((d.shape[0], 3), np.float32)
+        self._ck(lib().rrt_env_lookup(self.h, d.shape[0], _p(d), _p(out)))
+        return out
+
     def philox(self, seed, counters):
         counters = np.ascontiguousarray(counters, np.uint32).reshape(-1, 4)
         out = np.zeros_like(counters)
@@ -259,8 +277,7 @@ class PathTracer:
     def __init__(self, ns_aa=1, max_ray_depth=1, ns_area_light=1, ns_diff=1, ns_glsy=1, ns_refr=1, num_threads=1,
                  samples_per_batch=32, max_tolerance=0.05, envmap=None, direct_hemisphere_sample=False, filename="",
                  lensRadius=0.25, focalDistance=4.7, device=0, seed=0):
-        if envmap is not None:
-            raise NotImplementedError("environment light (-e) is a 'next' row, DESIGN.md")
+        self.envmap = envmap      # [h, w, 3] float array or None (reference: HDRImageBuffer*, src/pathtracer.cpp:61-65)
         self.ns_aa, self.max_ray_depth, self.ns_area_light = ns_aa, max_ray_depth, ns_area_light
         self.ns_diff, self.ns_glsy, self.ns_refr = ns_diff, ns_diff, ns_refr  # reference bug kept: ns_glsy = ns_diff (src/pathtracer.cpp:51)
         self.numWorkerThreads = num_threads  # accepted and ignored: the device replaces the worker pool
@@ -270,6 +287,8 @@ class PathTracer:
         self.seed = seed
         self.state = PathTracer.INIT
         self.ctx = Context(device)
+        if self.envmap is not None:
+            self.ctx.set_envmap(self.envmap)
         self.bvh = None
         self.scene = None
         self.camera_set = False

@@ -42,6 +42,8 @@ struct rrt_ctx {
   int tile = 32, rank = 0, world = 1;
   int64_t opt[16];
   // device memory
+  DevBuf d_env, d_env_pdf, d_env_cond, d_env_marg;
+  bool have_env = false;
   DevBuf d_grid, d_nodes, d_wide, d_leaf, d_nrm, d_kind, d_index, d_pmat, d_sph, d_mats, d_lights;
   DevBuf d_work, d_px, d_act, d_blk, d_cnt, d_out_rgb, d_out_cnt, d_out_rgbn, d_hook_in, d_hook_out;
   std::vector<cudaEvent_t> events;
@@ -115,7 +117,7 @@ void rrt_destroy(rrt_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->d_grid, &ctx->d_nodes, &ctx->d_wide, &ctx->d_leaf, &ctx->d_nrm, &ctx->d_kind, &ctx->d_index, &ctx->d_pmat, &ctx->d_sph, &ctx->d_mats, &ctx->d_lights,
+  DevBuf* bufs[] = {&ctx->d_env, &ctx->d_env_pdf, &ctx->d_env_cond, &ctx->d_env_marg, &ctx->d_grid, &ctx->d_nodes, &ctx->d_wide, &ctx->d_leaf, &ctx->d_nrm, &ctx->d_kind, &ctx->d_index, &ctx->d_pmat, &ctx->d_sph, &ctx->d_mats, &ctx->d_lights,
                     &ctx->d_work, &ctx->d_px, &ctx->d_act, &ctx->d_blk, &ctx->d_cnt, &ctx->d_out_rgb, &ctx->d_out_cnt, &ctx->d_out_rgbn,
                     &ctx->d_hook_in, &ctx->d_hook_out};
   for (DevBuf* b : bufs) b->release();
@@ -347,8 +349,9 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   RenderK rk;
   rk.W = ctx->W; rk.H = ctx->H; rk.ns_aa = p->ns_aa; rk.D = p->max_ray_depth; rk.ns_area_light = p->ns_area_light; rk.batch = p->samples_per_batch;
   rk.tol = p->max_tolerance; rk.hemi = p->direct_hemisphere_sample != 0; rk.thin_lens = p->thin_lens != 0; rk.seed = p->seed;
-  if (rk.hemi) rk.S = rk.total = ctx->n_lights * p->ns_area_light;
-  else rk.S = rk.total = ctx->n_delta_lights + (ctx->n_lights - ctx->n_delta_lights) * p->ns_area_light;
+  const int n_lights_all = ctx->n_lights + (ctx->have_env ? 1 : 0);   /* scene->lights.size(): the environment light counts */
+  if (rk.hemi) rk.S = rk.total = n_lights_all * p->ns_area_light;
+  else rk.S = rk.total = ctx->n_delta_lights + (n_lights_all - ctx->n_delta_lights) * p->ns_area_light;
   if (rk.D == 0) rk.S = 0;
   const int S = std::max(rk.S, 1);
   const int nb_max = std::min(rk.batch, rk.ns_aa);
@@ -635,7 +638,8 @@ int rrt_bsdf_eval(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const doub
 int rrt_light_sample(rrt_ctx* ctx, int light, int64_t n, const double* p, const double* u, float* radiance, double* wi, float* dist, float* pdf) {
   if (!ctx || n < 0 || (n && (!p || !u || !radiance || !wi || !dist || !pdf))) return RRT_E_ARG;
   if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_light_sample: no scene");
-  if (light < 0 || light >= ctx->ds.n_lights) FAIL(RRT_E_ARG, "rrt_light_sample: light index out of range");
+  const bool is_env = ctx->have_env && light == ctx->ds.n_lights;   /* the environment light is the last light */
+  if (light < 0 || (light >= ctx->ds.n_lights && !is_env)) FAIL(RRT_E_ARG, "rrt_light_sample: light index out of range");
   if (n == 0) return RRT_OK;
   int rc = hook_begin(ctx, 40 * (size_t)n + 1024, 44 * (size_t)n + 2048);
   if (rc) return rc;
@@ -643,11 +647,71 @@ int rrt_light_sample(rrt_ctx* ctx, int light, int64_t n, const double* p, const 
   double* d_p = (double*)hook_in(ctx, io, p, 24 * (size_t)n); double* d_u = (double*)hook_in(ctx, io, u, 16 * (size_t)n);
   float* d_rad = (float*)hook_out(ctx, oo, 12 * (size_t)n); double* d_wi = (double*)hook_out(ctx, oo, 24 * (size_t)n);
   float* d_dist = (float*)hook_out(ctx, oo, 4 * (size_t)n); float* d_pdf = (float*)hook_out(ctx, oo, 4 * (size_t)n);
-  k_hook_light<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->ds.lights, light, n, d_p, d_u, d_rad, d_wi, d_dist, d_pdf);
+  if (is_env) k_hook_env_sample<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->ds, n, d_u, d_rad, d_wi, d_dist, d_pdf);
+  else k_hook_light<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->ds.lights, light, n, d_p, d_u, d_rad, d_wi, d_dist, d_pdf);
   CK(cudaMemcpyAsync(radiance, d_rad, 12 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaMemcpyAsync(wi, d_wi, 24 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaMemcpyAsync(dist, d_dist, 4 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaMemcpyAsync(pdf, d_pdf, 4 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
+  return RRT_OK;
+}
+
+/* EnvironmentLight::EnvironmentLight + init (reference src/static_scene/environment_light.cpp:10-49): the map and its
+ * sampling tables (per-texel pdf, per-row conditional CDF, marginal CDF of the rows), built on the host in the reference's
+ * summation order and kept on the device. */
+int rrt_set_envmap(rrt_ctx* ctx, int width, int height, const float* rgb) {
+  if (!ctx) return RRT_E_ARG;
+  DevScene& d = ctx->ds;
+  if (!rgb || width <= 0 || height <= 0) {
+    ctx->have_env = false; d.env = nullptr; d.env_pdf = d.env_cond = d.env_marg = nullptr; d.env_w = d.env_h = 0;
+    return RRT_OK;
+  }
+  const size_t w = (size_t)width, h = (size_t)height;
+  if (w * h >= ((size_t)1 << 31)) FAIL(RRT_E_ARG, "rrt_set_envmap: map too large");
+  std::vector<double> pdf(w * h), cond(w * h), marg(h, 0.0);
+  double sum = 0;
+  for (size_t j = 0; j < h; ++j)
+    for (size_t i = 0; i < w; ++i) {
+      const float* q = rgb + 3 * (w * j + i);
+      const float illum = 0.2126f * q[0] + 0.7152f * q[1] + 0.0722f * q[2];
+      pdf[w * j + i] = illum * sin(3.14159265358979323 * ((int)j + .5) / (uint32_t)h);
+      sum += pdf[w * j + i];
+    }
+  for (size_t j = 0; j < h; ++j) {
+    for (size_t i = 0; i < w; ++i) marg[j] += (pdf[w * j + i] /= sum);
+    for (size_t i = 0; i < w; ++i) {
+      cond[w * j + i] = pdf[w * j + i] / marg[j];
+      if (i > 0) cond[w * j + i] += cond[w * j + i - 1];
+    }
+    if (j > 0) marg[j] += marg[j - 1];
+  }
+  CK(cudaStreamSynchronize(ctx->stream));
+  int rc;
+  if ((rc = upload(ctx, ctx->d_env, rgb, 12 * w * h))) return rc;
+  if ((rc = upload(ctx, ctx->d_env_pdf, pdf.data(), 8 * w * h))) return rc;
+  if ((rc = upload(ctx, ctx->d_env_cond, cond.data(), 8 * w * h))) return rc;
+  if ((rc = upload(ctx, ctx->d_env_marg, marg.data(), 8 * h))) return rc;
+  CK(cudaStreamSynchronize(ctx->stream));
+  d.env = ctx->d_env.as<float>(); d.env_pdf = ctx->d_env_pdf.as<double>(); d.env_cond = ctx->d_env_cond.as<double>();
+  d.env_marg = ctx->d_env_marg.as<double>(); d.env_w = width; d.env_h = height;
+  ctx->have_env = true;
+  return RRT_OK;
+}
+
+/* EnvironmentLight::sample_dir for n directions d [n*3] -> radiance [n*3] (parity hook) */
+int rrt_env_lookup(rrt_ctx* ctx, int64_t n, const double* dir, float* radiance) {
+  if (!ctx || n < 0 || (n && (!dir || !radiance))) return RRT_E_ARG;
+  if (!ctx->have_env) FAIL(RRT_E_STATE, "rrt_env_lookup: no environment map");
+  if (n == 0) return RRT_OK;
+  int rc = hook_begin(ctx, 24 * (size_t)n + 1024, 12 * (size_t)n + 1024);
+  if (rc) return rc;
+  size_t io = 0, oo = 0;
+  double* d_d = (double*)hook_in(ctx, io, dir, 24 * (size_t)n);
+  float* d_rad = (float*)hook_out(ctx, oo, 12 * (size_t)n);
+  k_hook_env_lookup<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->ds, n, d_d, d_rad);
+  CK(cudaMemcpyAsync(radiance, d_rad, 12 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   CK(cudaGetLastError());
   return RRT_OK;

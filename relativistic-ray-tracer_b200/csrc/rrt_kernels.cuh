@@ -125,6 +125,14 @@ __global__ void __launch_bounds__(RRT_BLOCK) k_shade(const __grid_constant__ Dev
     if (i < count) {
       const int prim = q.h_prim[i];
       q.vflag[i] = 0;
+      if (prim < 0 && it == 0 && sc.env) {
+        /* camera ray that hit nothing (or fell into the hole): the environment seen along its own, unbent direction
+         * (reference src/part1_code.cpp:106-107) */
+        const double* r = q.ray[cur];
+        const f3 Le = env_sample_dir(sc, D3(r[3 * cap + i], r[4 * cap + i], r[5 * cap + i]));
+        const uint32_t sl = q.slot[cur][i];
+        q.Lsample[sl] = Le.r; q.Lsample[cap + sl] = Le.g; q.Lsample[2 * cap + sl] = Le.b;
+      }
       if (prim >= 0) {
         slot = q.slot[cur][i];
         const uint32_t flags = q.flags[cur][i];
@@ -169,15 +177,17 @@ __global__ void __launch_bounds__(RRT_BLOCK) k_shade(const __grid_constant__ Dev
               }
             } else {
               /* estimate_direct_lighting_importance (reference src/part1_code.cpp:33-57) */
-              for (int li = 0; li < sc.n_lights; ++li) {
-                const rrt_light& l = sc.lights[li];
-                const int ns = l.is_delta ? 1 : rk.ns_area_light;
+              const int n_all = sc.n_lights + (sc.env ? 1 : 0);   /* the environment light is the last light (reference src/pathtracer.cpp:107-109) */
+              for (int li = 0; li < n_all; ++li) {
+                const bool is_env = li >= sc.n_lights;
+                const rrt_light& l = sc.lights[is_env ? 0 : li];
+                const int ns = (!is_env && l.is_delta) ? 1 : rk.ns_area_light;
                 for (int s = 0; s < ns; ++s, ++k) {
                   d3 wi_world; float dist, pdf;
-                  f3 Li = light_sample_L(l, hit_p, wi_world, dist, pdf, g);
+                  f3 Li = is_env ? env_sample_L(sc, wi_world, dist, pdf, g) : light_sample_L(l, hit_p, wi_world, dist, pdf, g);
                   const size_t ci = (size_t)i * rk.S + k;
                   q.s_res[ci] = -2;
-                  if (l.type == RRT_LIGHT_NULL) continue;
+                  if (!is_env && l.type == RRT_LIGHT_NULL) continue;
                   d3 w_in = mat_tmul(o2w, wi_world);
                   if (w_in.z < 0) continue;
                   f3 c = s_divf(s_mulf(s_mul(Li, bsdf_f(m, w_out, w_in)), (float)w_in.z), pdf);
@@ -424,6 +434,24 @@ __global__ void k_hook_bsdf(const rrt_material* __restrict__ mats, int mat, long
       wi[3 * i] = r.x; wi[3 * i + 1] = r.y; wi[3 * i + 2] = r.z; pdf[i] = p;
     } else s = bsdf_f(m, w, D3(wi_in[3 * i], wi_in[3 * i + 1], wi_in[3 * i + 2]));
     f[3 * i] = s.r; f[3 * i + 1] = s.g; f[3 * i + 2] = s.b;
+  }
+}
+
+/* parity hooks for the environment light: sample_L with caller-supplied uniforms, and sample_dir */
+__global__ void k_hook_env_sample(const __grid_constant__ DevScene sc, long long n, const double* __restrict__ u, float* __restrict__ rad,
+                                  double* __restrict__ wi, float* __restrict__ dist, float* __restrict__ pdf) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    Rng g = rng_make(0, 0, 0, 0); g.fixed = u + 2 * i;
+    d3 w; float ds = 0, pd = 0;
+    f3 s = env_sample_L(sc, w, ds, pd, g);
+    rad[3 * i] = s.r; rad[3 * i + 1] = s.g; rad[3 * i + 2] = s.b;
+    wi[3 * i] = w.x; wi[3 * i + 1] = w.y; wi[3 * i + 2] = w.z; dist[i] = ds; pdf[i] = pd;
+  }
+}
+__global__ void k_hook_env_lookup(const __grid_constant__ DevScene sc, long long n, const double* __restrict__ d, float* __restrict__ rad) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    f3 s = env_sample_dir(sc, D3(d[3 * i], d[3 * i + 1], d[3 * i + 2]));
+    rad[3 * i] = s.r; rad[3 * i + 1] = s.g; rad[3 * i + 2] = s.b;
   }
 }
 

@@ -188,3 +188,44 @@ __device__ __forceinline__ f3 light_sample_L(const rrt_light& l, d3 p, d3& wi, f
       wi = D3(0, 0, 0); dist = 0; pdf = 0; return F3(0, 0, 0);
   }
 }
+
+/* ---- EnvironmentLight (reference src/static_scene/environment_light.cpp), appended after the scene's lights ---- */
+/* bilerp (:99-115): the four texels around xy with the reference's wrap / clamp rules, weights narrowed to float */
+__device__ __forceinline__ f3 env_bilerp(const DevScene& sc, double x, double y) {
+  const long w = sc.env_w, h = sc.env_h;
+  long right = lround(x), left, v = lround(y);
+  double u1 = right - x + .5, v1;
+  if (right == 0 || right == w) { left = w - 1; right = 0; } else left = right - 1;
+  if (v == 0) { v = 1; v1 = 1; } else if (v == h) { v = h - 1; v1 = 0; } else v1 = v - y + .5;
+  size_t bottom = (size_t)w * (size_t)v, top = bottom - (size_t)w;
+  double u0 = 1 - u1;
+  f3 tl = s3(sc.env + 3 * (top + left)), tr = s3(sc.env + 3 * (top + right));
+  f3 bl = s3(sc.env + 3 * (bottom + left)), br = s3(sc.env + 3 * (bottom + right));
+  return s_add(s_mulf(s_add(s_mulf(tl, (float)u1), s_mulf(tr, (float)u0)), (float)v1),
+               s_mulf(s_add(s_mulf(bl, (float)u1), s_mulf(br, (float)u0)), (float)(1 - v1)));
+}
+/* sample_dir (:60-65, :76-80, :145-147): radiance from direction d */
+__device__ __forceinline__ f3 env_sample_dir(const DevScene& sc, d3 d) {
+  d3 u = vunit(d);
+  double theta = acos(u.y), phi = atan2(-u.z, u.x) + RRT_PI;
+  return env_bilerp(sc, phi / 2. / RRT_PI * sc.env_w, theta / RRT_PI * sc.env_h);
+}
+__device__ __forceinline__ int env_upper_bound(const double* __restrict__ a, int n, double key) {   /* std::upper_bound */
+  int lo = 0, hi = n;
+  while (lo < hi) { int mid = lo + (hi - lo) / 2; if (!(key < __ldg(a + mid))) lo = mid + 1; else hi = mid; }
+  return lo;
+}
+/* sample_L, ENV_HEMI == 0 (:118-133): row from the marginal, column from the row's conditional, direction of the
+ * texel CORNER, pdf from the texel.  An index one past the table (a draw of exactly 1.0) is clamped. */
+__device__ __forceinline__ f3 env_sample_L(const DevScene& sc, d3& wi, float& dist, float& pdf, Rng& g) {
+  const int w = sc.env_w, h = sc.env_h;
+  dist = INFINITY;
+  double sx, sy; rng_grid2(g, sx, sy);
+  int y = env_upper_bound(sc.env_marg, h, sy); if (y > h - 1) y = h - 1;
+  int x = env_upper_bound(sc.env_cond + (size_t)w * y, w, sx); if (x > w - 1) x = w - 1;
+  double phi = (double)x / w * 2.0 * RRT_PI, theta = (double)y / h * RRT_PI;
+  double st = sin(theta);
+  wi = D3(cos(phi - RRT_PI) * st, cos(theta), -sin(phi - RRT_PI) * st);
+  pdf = (float)(__ldg(sc.env_pdf + (size_t)w * y + x) * w * h / (2 * RRT_PI * RRT_PI * st));
+  return env_bilerp(sc, (double)x, (double)y);
+}

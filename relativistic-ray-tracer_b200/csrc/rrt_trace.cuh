@@ -29,6 +29,9 @@ struct DevScene {
   int32_t n_prims, n_mats, n_lights, root;
   float root_lo[3], root_hi[3];   // root box, rounded outward
   double ctr[3], rad;             // sphere around the root box (far-chord origin shift, boxctx_make)
+  // environment light (rrt_set_envmap): map [h][w][3] row 0 = top, and the reference's sampling tables
+  const float* env; const double* env_pdf; const double* env_cond; const double* env_marg;
+  int env_w, env_h;
   const float* wide;              // wide nodes (rrt_bvh.h): 8 * width floats each
   int32_t wroot;                  // child code of the wide root
   int width;                      // 2: `nodes`; 4 / 8: `wide`

@@ -185,6 +185,25 @@ def test_light_sample_L(api, scene):
     assert same(dist.astype(np.float64), ref[:, 6]) and same(pdf.astype(np.float64), ref[:, 7])
 
 
+def test_environment_light_matches_reference_vectors(api):
+    """EnvironmentLight::sample_L / sample_dir (golden vectors made by the reference's own class, tests/golden/kat_envmap.npz)"""
+    g = golden("kat_envmap")
+    c = make_ctx(api, str(g["scene"]))
+    c.set_envmap(g["env"])
+    inp, ref = g["inp"], g["out"]
+    rad, wi, dist, pdf = c.light_sample(int(g["light_index"]), inp[:, 0:3], inp[:, 3:5] / RAND_MAX)
+    # same table cell for every draw (integer work: exact); direction / pdf go through CUDA's sin / cos instead of glibc's
+    np.testing.assert_allclose(wi, ref[:, 3:6], rtol=0, atol=1e-15)
+    np.testing.assert_allclose(pdf, ref[:, 7], rtol=3e-7)
+    assert same(rad.astype(np.float64), ref[:, 0:3]) and np.isinf(dist).all()
+    got = c.env_lookup(g["dirs"]).astype(np.float64)
+    np.testing.assert_allclose(got, g["dir_out"], rtol=2e-5, atol=1e-6)       # acos / atan2 feed interpolation weights
+    assert (np.abs(got - g["dir_out"]) > 1e-6 * np.maximum(1, g["dir_out"])).mean() < 0.01
+    c.set_envmap(None)
+    with pytest.raises(api.RrtError):
+        c.env_lookup(g["dirs"][:1])
+
+
 def test_tonemap_matches_oracle(api, orc):
     rng = np.random.default_rng(5)
     hdr = np.concatenate([rng.uniform(0, 2, (4000, 3)), [[0, 0, 0], [1, 1, 1], [0.5, 10, 1e-6]]]).astype(np.float32)
