@@ -5,8 +5,9 @@
 //     -b <FLOAT> -d <FLOAT> -c <camera settings file>  -B <x> <y> <z> <r> <dtheta>        exactly as the reference
 //   additions (not in the reference): -F (flat spacetime, the reference has no working switch), -S <seed>,
 //     -G <device>, --dump-scene <out.rrtscene> (load + flatten only: needs no GPU), --dump-camera <file>
-//   not available: -e <map.exr> (environment light is a "next" row), the interactive viewer (no graphics stack on
-//     this box): without -f the program renders to <scene>_screenshot_<time>.png instead of opening a window.
+//   -e <map.exr | map.pfm>: uncompressed OpenEXR scan lines or PFM (no compression library in the image).
+//   not available: the interactive viewer (no graphics stack on this box): without -f the program renders to
+//     <scene>_screenshot_<time>.png instead of opening a window.
 // -t is accepted and ignored: the device replaces the worker threads.
 #include <stdio.h>
 #include <stdlib.h>
@@ -32,6 +33,7 @@ static void usage(const char* binary) {
   printf("  -p  <x> <y> <dx> <dy> Render only this cell of the frame\n");
   printf("  -c  <FILENAME>   Camera settings file\n");
   printf("  -b  <FLOAT>      Lens radius      -d  <FLOAT>  Focal distance\n");
+  printf("  -e  <FILENAME>   Environment map (uncompressed .exr or .pfm)\n");
   printf("  -B  <x> <y> <z> <r> <dtheta>  Black hole centre, Schwarzschild radius, angular step\n");
   printf("  -F               Flat spacetime (no hole)      -S <INT> RNG seed      -G <INT> CUDA device\n");
   printf("  --dump-scene <FILE>  write the flattened scene and exit (no GPU needed)\n");
@@ -44,7 +46,7 @@ int main(int argc, char** argv) {
   bool hemisphere = false, write_to_file = false, flat = false;
   double lens_radius = 0.25, focal_distance = 4.7;
   size_t w = 0, h = 0, x = (size_t)-1, y = 0, dx = 0, dy = 0;
-  std::string filename, cam_settings, dump_scene, dump_camera, scene_path;
+  std::string filename, cam_settings, dump_scene, dump_camera, scene_path, envmap_path;
   Vector3D bh_c(0, 1, 0); double bh_r = 0.1, bh_dtheta = 0.1;
   unsigned long long seed = 0; int device = 0;
 
@@ -79,7 +81,16 @@ int main(int argc, char** argv) {
       for (uint32_t k = 0; k < 15; ++k) px[k] = 0xFF000000u | (k * 17u) | ((255u - k * 17u) << 8) | ((k * 5u) << 16);
       return write_png(argv[i + 1], px, 5, 3) ? 0 : 2;
     }
-    else if (a == "-e") { fprintf(stderr, "-e: environment light is not available in this build (DESIGN.md section 9)\n"); return 1; }
+    else if (a == "-e") { need(i, 1); envmap_path = argv[++i]; }
+    else if (a == "--dump-envmap") {      // host self-check: decode a map, write int32 w, h + floats (tests/test_host_cpp.py)
+      need(i, 2);
+      int ew = 0, eh = 0; std::vector<float> env; std::string e;
+      if (!load_envmap(argv[i + 1], &ew, &eh, &env, &e)) { fprintf(stderr, "%s\n", e.c_str()); return 2; }
+      FILE* f = fopen(argv[i + 2], "wb"); if (!f) return 2;
+      int32_t wh[2] = {ew, eh};
+      fwrite(wh, 4, 2, f); fwrite(env.data(), 4, env.size(), f); fclose(f);
+      return 0;
+    }
     else if (a == "-h") { usage(argv[0]); return 1; }
     else if (!a.empty() && a[0] == '-') { usage(argv[0]); return 1; }
     else scene_path = a;
@@ -112,6 +123,11 @@ int main(int argc, char** argv) {
   PathTracer pt(ns_aa, max_ray_depth, ns_area_light, 1, 1, 1, num_threads, samples_per_batch, max_tolerance, nullptr, hemisphere,
                 scene_file, lens_radius, focal_distance);
   pt.set_device(device); pt.set_seed(seed); pt.set_blackhole(bh_c, bh_r, bh_dtheta, flat);
+  if (!envmap_path.empty()) {
+    int ew = 0, eh = 0; std::vector<float> env;
+    if (!load_envmap(envmap_path, &ew, &eh, &env, &err)) { fprintf(stderr, "[PathTracer] Error loading environment map: %s\n", err.c_str()); return 1; }
+    pt.set_envmap(ew, eh, env.data());
+  }
   pt.set_camera(&camera);
   pt.set_scene(&scene);
   pt.set_frame_size(camera.screenW, camera.screenH);

@@ -84,7 +84,7 @@ PathTracer::PathTracer(size_t ns_aa, size_t max_ray_depth, size_t ns_area_light,
       max_tolerance_(max_tolerance), hemisphere_(direct_hemisphere_sample), filename_(filename), lensRadius_(lensRadius),
       focalDistance_(focalDistance) {
   memset(&stats_, 0, sizeof stats_);
-  if (envmap) error_ = "environment light (-e) is not part of this path yet (DESIGN.md section 9)";
+  (void)envmap;   /* the pixels come through set_envmap: an opaque HDRImageBuffer* cannot cross this boundary */
 }
 
 PathTracer::~PathTracer() {
@@ -104,6 +104,11 @@ void PathTracer::set_scene(const FlatScene* scene) {
   if (rrt_upload_scene(ctx_, &s) != RRT_OK) { error_ = rrt_last_error(ctx_); fprintf(stdout, "failed: %s\n", error_.c_str()); return; }
   clock_gettime(CLOCK_MONOTONIC, &t1);
   fprintf(stdout, "Done! (%.4f sec)\n", (t1.tv_sec - t0.tv_sec) + 1e-9 * (t1.tv_nsec - t0.tv_nsec));
+  if (!env_.empty()) {
+    fprintf(stdout, "[PathTracer] Initializing environment light..."); fflush(stdout);
+    if (rrt_set_envmap(ctx_, env_w_, env_h_, env_.data()) != RRT_OK) { error_ = rrt_last_error(ctx_); fprintf(stdout, "failed: %s\n", error_.c_str()); return; }
+    fprintf(stdout, "done.\n");
+  }
   have_scene_ = true; n_prims_ = scene->n_prims();
   if (has_valid_configuration()) state_ = READY;
 }
@@ -121,6 +126,12 @@ void PathTracer::set_frame_size(size_t width, size_t height) {
   W_ = width; H_ = height;
   hdr_.assign(3 * W_ * H_, 0.f); counts_.assign(W_ * H_, 0); frame_.assign(W_ * H_, 0xFF000000u);
   if (has_valid_configuration()) state_ = READY;
+}
+
+void PathTracer::set_envmap(int width, int height, const float* rgb) {
+  if (state_ != INIT) return;
+  env_w_ = width; env_h_ = height;
+  if (rgb && width > 0 && height > 0) env_.assign(rgb, rgb + 3 * (size_t)width * (size_t)height); else { env_.clear(); env_w_ = env_h_ = 0; }
 }
 
 void PathTracer::set_blackhole(const Vector3D& c, double r, double dtheta, bool flat) { bh_centre_ = c; bh_r_ = r; bh_dtheta_ = dtheta; bh_flat_ = flat; }

@@ -94,6 +94,9 @@ bool save_rrtscene(const std::string& filename, const FlatScene& scene, const Ca
 bool halfedge_triangles_and_normals(const std::vector<std::vector<size_t>>& polygons, const std::vector<Vector3D>& positions,
                                     std::vector<size_t>* out_tri, std::vector<Vector3D>* out_normals, std::string* error);
 
+// ---- environment maps for -e: uncompressed OpenEXR (HALF / FLOAT scan lines) or PFM -> [h][w][3] floats, row 0 = top
+bool load_envmap(const std::string& filename, int* width, int* height, std::vector<float>* rgb, std::string* error);
+
 // ---- PNG (8-bit RGBA, stored deflate blocks: no compression library in the image)
 bool write_png(const std::string& filename, const uint32_t* rgba, size_t w, size_t h);
 
@@ -135,6 +138,9 @@ class PathTracer {
   void set_camera(Camera* camera);           // not owned; lens parameters are overwritten (reference src/pathtracer.cpp:127-128)
   void set_frame_size(size_t width, size_t height);
   void set_blackhole(const Vector3D& centre, double r, double delta_theta, bool flat = false);   // -B (reference src/main.cpp:139-145)
+  // -e: the reference takes an HDRImageBuffer* in its constructor (src/pathtracer.cpp:61-65); here the pixels are
+  // handed over before set_scene.  rgb: [height][width][3], row 0 = top.
+  void set_envmap(int width, int height, const float* rgb);
   void set_seed(uint64_t seed) { seed_ = seed; }
   void set_device(int device) { device_ = device; }
   void set_tile_shard(int tile, int rank, int world) { tile_ = tile; rank_ = rank; world_ = world; }
@@ -181,6 +187,8 @@ class PathTracer {
   rrt_stats stats_;
   std::string error_;
   size_t n_prims_ = 0;
+  int env_w_ = 0, env_h_ = 0;
+  std::vector<float> env_;
 };
 
 }  // namespace rrt_host

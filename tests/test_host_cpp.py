@@ -99,8 +99,8 @@ def test_cli_errors(exe, tmp_path):
     bad = tmp_path / "bad.dae"; bad.write_text("<COLLADA><asset><up_axis>Y_UP</up_axis></asset><scene>")
     r = subprocess.run([exe, "--dump-scene", str(tmp_path / "x"), str(bad)], capture_output=True, text=True)
     assert "missing end tag" in r.stderr and not os.path.exists(tmp_path / "x")
-    r = subprocess.run([exe, "-e", "map.exr", "scene.dae"], capture_output=True, text=True)
-    assert r.returncode == 1 and "environment light" in r.stderr
+    r = subprocess.run([exe, "-e", str(tmp_path / "nomap.exr"), "-f", str(tmp_path / "o.png"), str(bad)], capture_output=True, text=True)
+    assert r.returncode != 0 or "missing end tag" in r.stderr
 
 
 def test_minimal_collada_document(exe, tmp_path):
@@ -135,3 +135,54 @@ def test_minimal_collada_document(exe, tmp_path):
     assert [int(m["type"]) for m in a.mats] == [sc.MAT_DIFFUSE, sc.MAT_DIFFUSE] and a.mats[1]["a"].tolist() == [0.5, 0.5, 0.5]
     assert int(a.lights[0]["type"]) == sc.LIGHT_POINT and a.lights[0]["position"].tolist() == [0, 7, 0] and a.lights[0]["radiance"].tolist() == [1, 2, 3]
     assert a.camera["screenW"] == 800.0 and a.camera["screenH"] == 600.0         # Application::init's defaults
+
+
+def write_exr(path, img, pixel_type):
+    """minimal scan-line OpenEXR writer, compression NONE, channels B G R (alphabetical, as the format requires)"""
+    h, w, _ = img.shape
+    def attr(name, typ, data):
+        return name.encode() + b"\0" + typ.encode() + b"\0" + struct.pack("<i", len(data)) + data
+    chl = b"".join(n.encode() + b"\0" + struct.pack("<iBBBBii", pixel_type, 0, 0, 0, 0, 1, 1) for n in "BGR") + b"\0"
+    box = struct.pack("<iiii", 0, 0, w - 1, h - 1)
+    hdr = (struct.pack("<II", 20000630, 2) + attr("channels", "chlist", chl) + attr("compression", "compression", b"\0") +
+           attr("dataWindow", "box2i", box) + attr("displayWindow", "box2i", box) + attr("lineOrder", "lineOrder", b"\0") +
+           attr("pixelAspectRatio", "float", struct.pack("<f", 1.0)) + attr("screenWindowCenter", "v2f", struct.pack("<ff", 0, 0)) +
+           attr("screenWindowWidth", "float", struct.pack("<f", 1.0)) + b"\0")
+    dt = np.float16 if pixel_type == 1 else np.float32
+    rows = []
+    for y in range(h):
+        data = b"".join(np.ascontiguousarray(img[y, :, c], dt).tobytes() for c in (2, 1, 0))
+        rows.append(struct.pack("<ii", y, len(data)) + data)
+    off = len(hdr) + 8 * h
+    table = b""
+    for r in rows:
+        table += struct.pack("<Q", off); off += len(r)
+    open(path, "wb").write(hdr + table + b"".join(rows))
+
+
+def test_environment_map_readers(exe, tmp_path):
+    rng = np.random.default_rng(3)
+    img = rng.uniform(0, 4, (5, 7, 3)).astype(np.float32)
+    img[0, 0] = [0, 65504.0, 6e-8]                       # zero, largest half, a subnormal half
+    def decode(path):
+        out = str(tmp_path / "dec.bin")
+        r = subprocess.run([exe, "--dump-envmap", str(path), out], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        raw = open(out, "rb").read()
+        w, h = struct.unpack("<ii", raw[:8])
+        return np.frombuffer(raw[8:], np.float32).reshape(h, w, 3)
+    write_exr(tmp_path / "f.exr", img, 2)
+    assert np.array_equal(decode(tmp_path / "f.exr"), img)
+    write_exr(tmp_path / "h.exr", img, 1)
+    assert np.array_equal(decode(tmp_path / "h.exr"), img.astype(np.float16).astype(np.float32))
+    with open(tmp_path / "m.pfm", "wb") as f:
+        f.write(b"PF\n7 5\n-1.0\n" + np.ascontiguousarray(img[::-1]).tobytes())
+    assert np.array_equal(decode(tmp_path / "m.pfm"), img)
+    with open(tmp_path / "b.pfm", "wb") as f:
+        f.write(b"PF\n7 5\n1.0\n" + np.ascontiguousarray(img[::-1]).astype(">f4").tobytes())
+    assert np.array_equal(decode(tmp_path / "b.pfm"), img)
+    # a compressed file is refused with a reason, not misread
+    raw = open(tmp_path / "f.exr", "rb").read().replace(b"compression\0compression\0\x01\0\0\0\0", b"compression\0compression\0\x01\0\0\0\x03")
+    open(tmp_path / "z.exr", "wb").write(raw)
+    r = subprocess.run([exe, "--dump-envmap", str(tmp_path / "z.exr"), str(tmp_path / "x")], capture_output=True, text=True)
+    assert r.returncode == 2 and "compression" in r.stderr

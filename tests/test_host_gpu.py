@@ -85,3 +85,23 @@ def test_cli_loads_dae_when_present(exe, tmp_path):
     assert r.returncode == 0, r.stdout + r.stderr
     img = read_png(out)
     assert img.shape == (48, 64, 4) and img[..., :3].max() > 0
+
+
+def test_cli_environment_map(exe, tmp_path):
+    from util import golden
+    api = importlib.import_module("relativistic-ray-tracer_b200.api")
+    env = golden("kat_envmap")["env"]
+    s = load_scene("cbspheres_lambertian_96x72")
+    src = str(tmp_path / "s.rrtscene"); out = str(tmp_path / "o.png"); pfm = str(tmp_path / "env.pfm")
+    s.save(src)
+    with open(pfm, "wb") as f:
+        f.write(b"PF\n%d %d\n-1.0\n" % (env.shape[1], env.shape[0]) + np.ascontiguousarray(env[::-1], np.float32).tobytes())
+    r = subprocess.run([exe, "-s", "4", "-l", "2", "-m", "3", "-S", "5", "-e", pfm, "-f", out, src], capture_output=True, text=True)
+    assert r.returncode == 0 and "Initializing environment light...done." in r.stdout, r.stdout + r.stderr
+    c = api.Context(0); c.upload_scene(s); c.set_frame(96, 72); c.set_envmap(env)
+    hdr, _, _ = c.render(sc.make_params(ns_aa=4, max_ray_depth=3, ns_area_light=2, seed=5))
+    want = np.ascontiguousarray(c.tonemap(hdr).reshape(72, 96)[::-1]).view(np.uint8).reshape(72, 96, 4).copy(); want[..., 3] = 255
+    assert np.array_equal(read_png(out), want)
+    c.set_envmap(None)
+    dark, _, _ = c.render(sc.make_params(ns_aa=4, max_ray_depth=3, ns_area_light=2, seed=5))
+    assert hdr.mean() > dark.mean()      # the hole sends camera rays out of the box: they now see the sky
