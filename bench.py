@@ -369,6 +369,12 @@ def main():
     my_bytes = float(st_count["algorithmic_bytes"])
     my_trace_s = float(t[2]) / max(args.steps, 1)
     achieved = my_bytes / my_trace_s / 1e9 if my_trace_s > 0 else 0.0
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(args.workload)
+    except (OSError, ValueError):
+        pass
     line = {
         "metric": "Mpaths/s", "value": paths * args.steps / secs / 1e6, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -379,7 +385,8 @@ def main():
         "paths_per_step": paths, "geodesic_steps_per_step": steps_geo, "rays_per_step": rays,
         "e2e": {"value": paths * args.steps / e2e_s / 1e6, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic["dram_bytes"] if traffic else None,
+                     "traffic_of": (traffic["kernel"] + "; " + traffic["source"]) if traffic else None,
                      "kernel": "k_trace_closest + k_trace_shadow (geodesic advance + BVH intersect)", "peak_source": peak_src,
                      "algorithmic_bytes_per_step": my_bytes, "trace_ms_per_step": my_trace_s * 1e3,
                      "trace_launches_per_step": trace_launches / max(args.steps, 1),
