@@ -138,12 +138,12 @@ typedef struct rrt_stats {
   uint64_t paths;          /* est_radiance_global_illumination calls (= sum of sample counts) */
   uint64_t rays;           /* BVHAccel::intersect calls (camera + bounce + shadow) */
   uint64_t geodesic_steps; /* BlackHole::next_micro_ray calls (literal mode) or straight segments (flat) */
-  uint64_t node_visits;    /* 64-byte BVH node records fetched */
+  uint64_t node_visits;    /* BVH node records fetched: 64 bytes each (binary nodes) or 32 bytes per child slot (wide nodes: 256) */
   uint64_t tri_tests;      /* 80-byte triangle records tested */
   uint64_t sphere_tests;   /* sphere records tested */
   uint64_t kernel_launches;/* kernels of this library launched during the render */
   uint64_t trace_launches; /* of which trace kernels */
-  uint64_t algorithmic_bytes; /* 64*node_visits + 80*tri_tests + 32*sphere_tests + 160*rays */
+  uint64_t algorithmic_bytes; /* node record bytes*node_visits + 80*tri_tests + 32*sphere_tests + 160*rays */
 } rrt_stats;
 
 /* Result of one BVHAccel::intersect(ray, &isect) call. */

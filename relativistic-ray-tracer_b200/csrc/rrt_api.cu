@@ -313,6 +313,11 @@ static int compact(rrt_ctx* ctx, Keep keep, const uint32_t* in, uint32_t n, uint
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 /* trace-kernel dispatch: COUNT (instrumented) x variant (RRT_OPT_TRACE_KERNEL: 0 chord-lockstep, 1 vote-scheduled) */
+/* bytes of one node record as the running kernel fetches it: 64 (two child boxes) or 32 per child of a wide node */
+static uint64_t node_record_bytes(const rrt_ctx* ctx) {
+  if (ctx->opt[RRT_OPT_TRACE_KERNEL] == 1 || ctx->ds.width <= 2) return 64;
+  return 32ull * (uint64_t)ctx->ds.width;
+}
 /* kernel variant: 0 = lockstep over binary nodes, 1 = vote-scheduled (binary nodes), 4 / 8 = lockstep over wide nodes */
 static int trace_variant(const rrt_ctx* ctx) {
   if (ctx->opt[RRT_OPT_TRACE_KERNEL] == 1) return 1;
@@ -483,7 +488,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
     CK(cudaMemcpy(&hc, gcnt, sizeof hc, cudaMemcpyDeviceToHost));
     stats->rays = hc.rays; stats->geodesic_steps = hc.steps; stats->node_visits = hc.nodes; stats->tri_tests = hc.tris; stats->sphere_tests = hc.sph;
     stats->kernel_launches = launches; stats->trace_launches = trace_launches;
-    stats->algorithmic_bytes = 64 * hc.nodes + 80 * hc.tris + 32 * hc.sph + 160 * hc.rays;
+    stats->algorithmic_bytes = node_record_bytes(ctx) * hc.nodes + 80 * hc.tris + 32 * hc.sph + 160 * hc.rays;
     stats->paths = hc.paths; /* sum of sample counts */
   }
   return RRT_OK;
@@ -568,7 +573,7 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
     stats->seconds = stats->trace_seconds = ms * 1e-3;
     stats->rays = hc.rays; stats->geodesic_steps = hc.steps; stats->node_visits = hc.nodes; stats->tri_tests = hc.tris; stats->sphere_tests = hc.sph;
     stats->kernel_launches = stats->trace_launches = 1;
-    stats->algorithmic_bytes = 64 * hc.nodes + 80 * hc.tris + 32 * hc.sph + 160 * hc.rays;
+    stats->algorithmic_bytes = node_record_bytes(ctx) * hc.nodes + 80 * hc.tris + 32 * hc.sph + 160 * hc.rays;
   }
   return RRT_OK;
 }

@@ -107,7 +107,10 @@ __global__ void __launch_bounds__(256) k_generate(const __grid_constant__ DevCam
  * at_least_one_bounce_radiance / estimate_direct_lighting_* unrolled over the wavefront
  * (reference src/part1_code.cpp:15-123).  `it` = vertex index along the path (0 = camera hit); the reference's
  * recursion depth at this vertex is D - it. */
-__global__ void __launch_bounds__(RRT_BLOCK) k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+#ifndef RRT_SHADE_MINB
+#define RRT_SHADE_MINB 4   /* measured on C1: 3 / 4 / 5 / 6 blocks -> 4.87 / 4.43 / 4.69 / 4.75 ms per frame */
+#endif
+__global__ void __launch_bounds__(RRT_BLOCK, RRT_SHADE_MINB) k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                      const __grid_constant__ RenderK rk, const __grid_constant__ Queues q,
                                                      const uint32_t* __restrict__ act, int base_sample, int nb, int it) {
   const int cur = it & 1, nxt = cur ^ 1;
