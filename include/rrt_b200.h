@@ -166,7 +166,8 @@ enum {
   RRT_OPT_TRACE_KERNEL = 3, /* trace kernel variant, see DESIGN.md (0 = default) */
   RRT_OPT_LEAF_SIZE = 4,    /* primitives per leaf for topology 1 (1..7, default 2); takes effect at the next rrt_upload_scene */
   RRT_OPT_CLEARANCE_GRID = 5, /* cells along the longest axis of the empty-space grid (0 = off, the default); next rrt_upload_scene */
-  RRT_OPT_BVH_WIDTH = 6       /* children per node on the device: 2, 4, 8, or 0 (default) = 8 for scenes of <= 128 primitives, else 2; topology 0 and trace kernel 1 always use 2; next rrt_upload_scene */
+  RRT_OPT_BVH_WIDTH = 6,      /* children per node on the device: 2, 4, 8, or 0 (default) = 8 for scenes of <= 128 primitives, else 2; topology 0 and trace kernel 1 always use 2; next rrt_upload_scene */
+  RRT_OPT_SHADE_SPLIT = 7     /* direct lighting: 1 = its own kernel, one thread per light sample; 0 = inside k_shade's per-vertex loop; 2 (default) = 1 when the scene has a microfacet material, else 0 */
 };
 
 /* ---- lifecycle ---- */

@@ -37,6 +37,8 @@ struct rrt_ctx {
   DevScene ds; DevHole bh; DevCamera cam;
   rrt::FlatBvh bvh;
   int n_lights = 0, n_delta_lights = 0;
+  std::vector<rrt_light> host_lights;
+  bool has_microfacet = false;
   int W = 0, H = 0;
   int cell_x = 0, cell_y = 0, cell_w = 0, cell_h = 0;
   int tile = 32, rank = 0, world = 1;
@@ -99,6 +101,7 @@ int rrt_create(rrt_ctx** out, int device) {
   ctx->opt[RRT_OPT_CLEARANCE_GRID] = 0;   /* measured: no gain while chords of a warp are traversed in lockstep */
   ctx->opt[RRT_OPT_BVH_TOPOLOGY] = 1;
   ctx->opt[RRT_OPT_BVH_WIDTH] = 0;
+  ctx->opt[RRT_OPT_SHADE_SPLIT] = 2;
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaMallocHost((void**)&ctx->h_pinned, 4096)) != cudaSuccess) {
@@ -220,6 +223,9 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
     if (!(d.rad < 1e300)) { d.rad = 0.0; d.ctr[0] = d.ctr[1] = d.ctr[2] = 0.0; }
   }
   ctx->n_lights = (int)s->n_lights; ctx->n_delta_lights = 0;
+  ctx->host_lights.assign(s->lights, s->lights + s->n_lights);
+  ctx->has_microfacet = false;
+  for (uint32_t i = 0; i < s->n_mats; ++i) if (s->mats[i].type == RRT_MAT_MICROFACET) ctx->has_microfacet = true;
   for (uint32_t i = 0; i < s->n_lights; ++i) if (s->lights[i].is_delta) ctx->n_delta_lights++;
   ctx->have_scene = true;
   return RRT_OK;
@@ -358,6 +364,16 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   if (rk.hemi) rk.S = rk.total = n_lights_all * p->ns_area_light;
   else rk.S = rk.total = ctx->n_delta_lights + (n_lights_all - ctx->n_delta_lights) * p->ns_area_light;
   if (rk.D == 0) rk.S = 0;
+  /* 2 = choose: the per-sample kernel pays when evaluating the BSDF is expensive (microfacet: C3 34.2 -> 26.6 ms per
+   * 32 spp) and costs a little when it is not (diffuse C1: 4.43 -> 4.74 ms), DESIGN.md section 4.4 */
+  rk.split = ctx->opt[RRT_OPT_SHADE_SPLIT] == 2 ? (ctx->has_microfacet ? 1 : 0) : (ctx->opt[RRT_OPT_SHADE_SPLIT] != 0);
+  rk.direct_draws = 0;
+  if (rk.hemi) rk.direct_draws = 2 * rk.S;
+  else {
+    for (const rrt_light& l : ctx->host_lights)
+      if (l.type == RRT_LIGHT_AREA || l.type == RRT_LIGHT_HEMISPHERE) rk.direct_draws += 2 * (l.is_delta ? 1 : p->ns_area_light);
+    if (ctx->have_env) rk.direct_draws += 2 * p->ns_area_light;
+  }
   const int S = std::max(rk.S, 1);
   const int nb_max = std::min(rk.batch, rk.ns_aa);
   const int iters = std::max(rk.D, 1);
@@ -443,6 +459,10 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
         launch_closest(ctx, count, grid_trace, st, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt);
         if (stats) { CK(cudaEventRecord(e1, st)); trace_ev.push_back({e0, e1}); }
         k_shade<<<grid_small, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, rk, q, chunk, base_sample, nb, it);
+        if (rk.split && rk.D >= 1 && rk.S > 0) {
+          k_shade_direct<<<ctx->sm_count * 2 * RRT_DIRECT_MINB, 256, 0, st>>>(ctx->ds, rk, q, chunk, base_sample, nb, it);
+          launches++;
+        }
         launches += 2; trace_launches++;
         if (rk.D >= 1 && rk.S > 0) {
           if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, st)); }

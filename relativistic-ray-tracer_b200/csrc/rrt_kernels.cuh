@@ -19,6 +19,8 @@ struct RenderK {      // per-render constants (reference PathTracer members, src
   int S;              // light samples taken per shaded vertex (slots in the contribution table)
   int total;          // divisor of the direct estimate (reference src/part1_code.cpp:17,56)
   int cap;            // queue capacity = SoA stride
+  int direct_draws;   // uniforms one direct-lighting estimate consumes (fixed per scene: 2 per sample of an area / hemisphere / environment light)
+  int split;          // 1: direct lighting in k_shade_direct (one thread per light sample), k_shade does emission + bounce only
 };
 
 struct Queues {
@@ -161,7 +163,9 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_SHADE_MINB) k_shade(const __gri
             q.vflag[i] = 1;
             q.dbeta[i] = beta.r; q.dbeta[cap + i] = beta.g; q.dbeta[2 * cap + i] = beta.b;
             int k = 0;
-            if (rk.hemi) {
+            if (rk.split) {
+              g.n += (uint32_t)rk.direct_draws;   /* k_shade_direct takes these draws, one thread per sample */
+            } else if (rk.hemi) {
               /* estimate_direct_lighting_hemisphere (reference src/part1_code.cpp:15-31) */
               for (; k < rk.S; ++k) {
                 d3 w_in = hemisphere_sample(g);
@@ -240,6 +244,101 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_SHADE_MINB) k_shade(const __gri
         r[6 * cap + pos] = 0.0; r[7 * cap + pos] = INFINITY;
         q.slot[nxt][pos] = slot; q.rngn[nxt][pos] = en; q.flags[nxt][pos] = eflags;
         q.beta[nxt][pos] = ebeta.r; q.beta[nxt][cap + pos] = ebeta.g; q.beta[nxt][2 * cap + pos] = ebeta.b;
+      }
+    }
+  }
+}
+
+/* ---------------------------------------------------------------- direct lighting, one thread per (vertex, light sample).
+ * The same estimate k_shade makes in its light loop (estimate_direct_lighting_importance / _hemisphere, reference
+ * src/part1_code.cpp:15-57), spread over S times as many threads: a sample's uniforms sit at a fixed offset of the
+ * vertex's draw counter (every light class takes a fixed number of draws per sample and the RNG is counter based),
+ * so sample k needs nothing from samples 0..k-1.  Results are addressed by (vertex, sample) as before; the order in
+ * which shadow rays enter their queue changes, the image does not. */
+#ifndef RRT_DIRECT_MINB
+#define RRT_DIRECT_MINB 4   /* measured (C1 / C3 at 32 spp, ms per frame): 2 -> 5.22 / 27.7, 3 -> 4.82 / 27.0, 4 -> 4.74 / 26.6, 6 -> 4.92 / 26.7, 8 -> 5.89 / 27.7 */
+#endif
+__global__ void __launch_bounds__(256, RRT_DIRECT_MINB) k_shade_direct(const __grid_constant__ DevScene sc, const __grid_constant__ RenderK rk,
+                                                      const __grid_constant__ Queues q, const uint32_t* __restrict__ act, int base_sample, int nb, int it) {
+  const int cur = it & 1;
+  const size_t cap = (size_t)rk.cap;
+  const int count = q.ctl[it];
+  int* sh_count = q.ctl + q.ctl_stride + it;
+  const int S = rk.S;
+  const long long total = (long long)count * S;
+  const long long span = (total + 31) & ~31LL;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < span; t += (long long)gridDim.x * blockDim.x) {
+    bool emit = false;
+    d3 so = D3(0, 0, 0), wi_world = D3(0, 0, 0);
+    double dist_d = 0.0;
+    size_t ci = 0;
+    if (t < total) {
+      const int i = (int)(t / S), k = (int)(t - (long long)i * S);
+      const int prim = q.h_prim[i];
+      if (prim >= 0) {
+        const rrt_material m = sc.mats[sc.prim_mat[prim]];
+        if (rk.D == 1 || !mat_is_delta(m)) {
+          ci = (size_t)i * S + k;
+          const uint32_t slot = q.slot[cur][i];
+          const uint32_t pixel = act[slot / (uint32_t)nb];
+          const uint32_t n0 = q.rngn[cur][i];
+          const d3 hit_p = D3(q.h_geo[i], q.h_geo[cap + i], q.h_geo[2 * cap + i]);
+          const d3 wo_world = D3(q.h_geo[3 * cap + i], q.h_geo[4 * cap + i], q.h_geo[5 * cap + i]);
+          const d3 nrm = D3(q.h_geo[6 * cap + i], q.h_geo[7 * cap + i], q.h_geo[8 * cap + i]);
+          d3 o2w[3]; make_coord_space(o2w, nrm);
+          const d3 w_out = mat_tmul(o2w, wo_world);
+          if (rk.hemi) {
+            Rng g = rng_make(rk.seed, pixel, (uint32_t)(base_sample + slot % (uint32_t)nb), n0 + 2u * (uint32_t)k);
+            d3 w_in = hemisphere_sample(g);
+            wi_world = mat_mul(o2w, w_in);
+            f3 f = bsdf_f(m, w_out, w_in);
+            q.s_contrib[ci] = make_float4(f.r, f.g, f.b, (float)w_in.z);
+            q.s_res[ci] = -1;
+            dist_d = INFINITY; emit = true;
+          } else {
+            /* which light, which of its samples, and how many draws precede it */
+            const int n_all = sc.n_lights + (sc.env ? 1 : 0);
+            int li = 0, first = 0; uint32_t off = 0;
+            bool is_env = false; int ns = 1, draws = 0;
+            for (; li < n_all; ++li) {
+              is_env = li >= sc.n_lights;
+              const int ty = is_env ? -1 : sc.lights[li].type;
+              ns = (!is_env && sc.lights[li].is_delta) ? 1 : rk.ns_area_light;
+              draws = (is_env || ty == RRT_LIGHT_AREA || ty == RRT_LIGHT_HEMISPHERE) ? 2 : 0;
+              if (k < first + ns) break;
+              first += ns; off += (uint32_t)(ns * draws);
+            }
+            off += (uint32_t)((k - first) * draws);
+            Rng g = rng_make(rk.seed, pixel, (uint32_t)(base_sample + slot % (uint32_t)nb), n0 + off);
+            float dist, pdf;
+            f3 Li = is_env ? env_sample_L(sc, wi_world, dist, pdf, g) : light_sample_L(sc.lights[li], hit_p, wi_world, dist, pdf, g);
+            int verdict = -2;
+            if (is_env || sc.lights[li].type != RRT_LIGHT_NULL) {
+              d3 w_in = mat_tmul(o2w, wi_world);
+              if (!(w_in.z < 0)) {
+                f3 c = s_divf(s_mulf(s_mul(Li, bsdf_f(m, w_out, w_in)), (float)w_in.z), pdf);
+                q.s_contrib[ci] = make_float4(c.r, c.g, c.b, 0.f);
+                verdict = -1; dist_d = (double)dist; emit = true;
+              }
+            }
+            q.s_res[ci] = verdict;
+          }
+          so = vadd(hit_p, smul(RRT_EPS_D, wi_world));
+        }
+      }
+    }
+    const unsigned mask = __ballot_sync(0xffffffffu, emit);
+    if (mask) {
+      int base = 0;
+      if (lane_id() == 0) base = atomicAdd(sh_count, __popc(mask));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (emit) {
+        const int pos = base + __popc(mask & ((1u << lane_id()) - 1u));
+        const size_t cs = cap * (size_t)S;
+        q.sray[pos] = so.x; q.sray[cs + pos] = so.y; q.sray[2 * cs + pos] = so.z;
+        q.sray[3 * cs + pos] = wi_world.x; q.sray[4 * cs + pos] = wi_world.y; q.sray[5 * cs + pos] = wi_world.z;
+        q.sray[6 * cs + pos] = dist_d;
+        q.s_cidx[pos] = (uint32_t)ci;
       }
     }
   }

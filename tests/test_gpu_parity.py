@@ -220,6 +220,18 @@ def image_report(hdr, ref):
     return pix, rmse
 
 
+@pytest.mark.parametrize("name", ["flat_hemisphere", "flat_pointlight", "bh_envmap", "flat_microfacet", "bh_glass_mirror"])
+def test_render_is_identical_with_direct_lighting_inside_k_shade(api, name):
+    g = golden("render_" + name)
+    s = load_scene(str(g["scene"]))
+    out = []
+    for split in (1, 0):
+        c = api.Context(0); c.set_option(api.OPT_SHADE_SPLIT, split); c.upload_scene(s)
+        hdr, cnt, st = c.render(setup_from_golden(g, c))
+        out.append((hdr, cnt, st["rays"], st["geodesic_steps"]))
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1]) and out[0][2:] == out[1][2:]
+
+
 @pytest.mark.parametrize("name", RENDERS)
 def test_render_matches_reference_image(api, orc, name):
     """Same Philox stream as the golden image rendered by the reference's raytrace_pixel: images agree path by path.
@@ -272,6 +284,10 @@ def test_c2_full_size_properties(api):
     c0.upload_scene(s); c0.set_frame(480, 360)
     h0, _, st0 = c0.render(p)
     assert np.array_equal(hdr, h0) and st0["rays"] == st["rays"]
+    c.set_option(api.OPT_SHADE_SPLIT, 0)                                   # direct lighting inside k_shade instead of its own kernel
+    hs, _, sts = c.render(p)
+    c.set_option(api.OPT_SHADE_SPLIT, 1)
+    assert np.array_equal(hdr, hs) and sts["rays"] == st["rays"] and sts["kernel_launches"] < st["kernel_launches"]
     for width in (2, 4):                                                   # default is 8 children per node
         cw = api.Context(0); cw.set_option(api.OPT_BVH_WIDTH, width); cw.upload_scene(s); cw.set_frame(480, 360)
         hw, _, stw = cw.render(p)
