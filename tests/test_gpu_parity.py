@@ -284,10 +284,10 @@ def test_c2_full_size_properties(api):
     c0.upload_scene(s); c0.set_frame(480, 360)
     h0, _, st0 = c0.render(p)
     assert np.array_equal(hdr, h0) and st0["rays"] == st["rays"]
-    c.set_option(api.OPT_SHADE_SPLIT, 0)                                   # direct lighting inside k_shade instead of its own kernel
+    c.set_option(api.OPT_SHADE_SPLIT, 1)                                   # direct lighting as its own kernel instead of inside k_shade
     hs, _, sts = c.render(p)
-    c.set_option(api.OPT_SHADE_SPLIT, 1)
-    assert np.array_equal(hdr, hs) and sts["rays"] == st["rays"] and sts["kernel_launches"] < st["kernel_launches"]
+    c.set_option(api.OPT_SHADE_SPLIT, 2)
+    assert np.array_equal(hdr, hs) and sts["rays"] == st["rays"] and sts["kernel_launches"] > st["kernel_launches"]
     for width in (2, 4):                                                   # default is 8 children per node
         cw = api.Context(0); cw.set_option(api.OPT_BVH_WIDTH, width); cw.upload_scene(s); cw.set_frame(480, 360)
         hw, _, stw = cw.render(p)
