@@ -95,7 +95,10 @@ __device__ __forceinline__ void next_micro_ray(const DevHole& bh, d3& o, d3& d, 
 }
 
 /* Sphere::test + the range logic of Sphere::intersect (reference src/static_scene/sphere.cpp:10-53) for the horizon:
- * true when the chord [0, len] crosses the sphere of radius^2 r2 about c. */
+ * true when the chord [0, len] crosses the sphere of radius^2 r2 about c.
+ * (Measured and dropped: skipping the roots when |o - c| (1 - 1e-6) > len + 2 r, which holds for almost every chord
+ * and removes ~13 of a step's ~175 FP64 instructions, made C2 0.6 ms per frame SLOWER (37.7 vs 37.05 ms): this
+ * arithmetic is independent of the traversal set-up that follows and fills its latency gaps.  DESIGN.md section 6.) */
 __device__ __forceinline__ bool horizon_hit(const DevHole& bh, d3 o, d3 d, double len) {
   d3 tmp = vsub(o, D3(bh.cx, bh.cy, bh.cz));
   double b = 2 * vdot(tmp, d), c = vnorm2(tmp) - bh.r2, disc = b * b - 4 * c;
@@ -246,10 +249,69 @@ __device__ __forceinline__ bool leaf_record_test(const double2* __restrict__ rec
   return true;
 }
 
+/* Cooperative, deferred leaf tests for any-hit (shadow) chords.
+ * The exact primitive tests run on the FP64 pipe, which is what bounds this kernel (ncu: ~0.2 FP64 warp instructions
+ * per scheduler cycle, the most the pipe sustains), and a warp instruction costs the pipe the same whether 2 or 32 of
+ * its lanes are active.  Leaf boxes are hit by few lanes at a time (2.3 on average on C2), so "every lane tests its
+ * own leaf" wasted 90 % of each FP64 issue slot spent there: 36 % of the kernel's FP64 instructions.
+ * An any-hit query does not need its leaves tested in order, or at once.  So a lane that reaches a leaf only APPENDS
+ * (owner lane, record) pairs to a per-warp list in shared memory and keeps descending; when the list holds a warp's
+ * worth of pairs, or nobody has nodes left, the whole warp tests the list 32 pairs at a time, each lane fetching its
+ * pair's chord from the owner's registers by shuffle, and raises the owner's bit on an accept.  The arithmetic of
+ * each test is the one the owner would have done (same record, same chord, same bound), so verdicts are unchanged; the
+ * price is that an occluded chord may visit a few more nodes before it learns of its hit. */
+#ifndef RRT_COOP_FLUSH
+#define RRT_COOP_FLUSH 32                      /* test the list once it holds this many pairs */
+#endif
+#define RRT_COOP_CAP (RRT_COOP_FLUSH + 224)    /* a lane appends at most one leaf (<= 7 records) after the threshold is reached */
+struct CoopScratch {            /* one per warp, shared memory */
+  uint32_t list[RRT_COOP_CAP];  /* (owner lane << 27) | leaf record index */
+  int n;                        /* pairs in the list; 0 between traversals */
+  uint32_t hitmask;             /* bit per owner lane; 0 between traversals */
+  int pad[2];
+};
+__device__ __forceinline__ void coop_init(CoopScratch* cs) {
+  if ((threadIdx.x & 31) == 0) { cs->n = 0; cs->hitmask = 0u; }
+  __syncwarp();
+}
+/* any lane, divergent: queue the records of leaf code `cur`; true = the list is due for testing, stop descending */
+__device__ __forceinline__ bool coop_append(CoopScratch* cs, int cur) {
+  const uint32_t bits = (uint32_t)~cur, first = bits >> 3, count = bits & 7u;
+  const int pos = atomicAdd(&cs->n, (int)count);
+  const uint32_t tag = (uint32_t)(threadIdx.x & 31) << 27;
+  for (uint32_t k = 0; k < count; ++k) cs->list[pos + k] = tag | (first + k);
+  return pos + (int)count >= RRT_COOP_FLUSH;
+}
+/* all 32 lanes, converged, after a __syncwarp: test the n queued pairs; returns whether one of MY records accepted */
+template <bool COUNT>
+__device__ __forceinline__ bool coop_flush(const DevScene& sc, CoopScratch* cs, const Seg& s, int n, Counters& cnt) {
+  const int lane = threadIdx.x & 31;
+  for (int base = 0; base < n; base += 32) {
+    const int e = base + lane;
+    const uint32_t pr = e < n ? cs->list[e] : ((uint32_t)lane << 27);
+    const int owner = (int)(pr >> 27);
+    Seg s2;   /* the owner's chord, straight from its registers */
+    s2.o = D3(__shfl_sync(0xffffffffu, s.o.x, owner), __shfl_sync(0xffffffffu, s.o.y, owner), __shfl_sync(0xffffffffu, s.o.z, owner));
+    s2.d = D3(__shfl_sync(0xffffffffu, s.d.x, owner), __shfl_sync(0xffffffffu, s.d.y, owner), __shfl_sync(0xffffffffu, s.d.z, owner));
+    s2.tmin = __shfl_sync(0xffffffffu, s.tmin, owner); s2.tmax = __shfl_sync(0xffffffffu, s.tmax, owner);
+    if (e < n) {
+      Best b2; b2.t = s2.tmax; b2.rank = -1; b2.prim = -1; b2.kind = 0; b2.b1 = b2.b2 = 0.0;
+      if (leaf_record_test<COUNT>(sc.leaf + 5 * (size_t)(pr & 0x7ffffffu), s2, b2, cnt)) atomicOr(&cs->hitmask, 1u << owner);
+    }
+  }
+  __syncwarp();
+  const bool mine = ((*(volatile uint32_t*)&cs->hitmask) >> lane) & 1u;
+  __syncwarp();
+  if (lane == 0) { cs->n = 0; cs->hitmask = 0u; }
+  __syncwarp();
+  return mine;
+}
+
 /* BVHAccel::intersect_micro (reference src/bvh.cpp:115-138) as an iterative, near-child-first traversal with a
  * per-thread stack in shared memory.  ANY = shadow-ray form (stop at the first accepted primitive). */
-template <bool ANY, bool COUNT>
-__device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt, bool active) {
+template <bool ANY, bool COUNT, bool COOP = false>
+__device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt, bool active,
+                                         CoopScratch* cs = nullptr) {
   /* Called by ALL 32 lanes of the warp, converged; lanes without a chord pass active = false and idle through.
    * while-while: every lane first descends until it holds a leaf (or runs out of nodes), the warp re-converges, then
    * the lanes that hold a leaf test its records.  (Measured alternatives, C2 on B200, ms per frame: single if/else
@@ -267,22 +329,41 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best&
     tmaxf = boxctx_tmax(best.t, T);
     if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tl)) cur = sc.root;
   }
-  while (__any_sync(0xffffffffu, cur != DONE)) {
-    while (cur >= 0) {
-      const float4* nd = sc.nodes + 4 * (size_t)cur;
-      float4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2), q3 = __ldg(nd + 3);
-      if (COUNT) cnt.nodes++;
-      bool hl = box_hit(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, bc, tmaxf, tl);
-      bool hr = box_hit(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, bc, tmaxf, tr);
-      int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
-      if (hl && hr) {
-        if (tr < tl) { int t = cl; cl = cr; cr = t; }
-        stack[(sp++) * stride] = cr;
-        cur = cl;
-      } else if (hl) cur = cl;
-      else if (hr) cur = cr;
-      else cur = sp ? stack[(--sp) * stride] : DONE;
+  auto visit = [&]() {
+    const float4* nd = sc.nodes + 4 * (size_t)cur;
+    float4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2), q3 = __ldg(nd + 3);
+    if (COUNT) cnt.nodes++;
+    bool hl = box_hit(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, bc, tmaxf, tl);
+    bool hr = box_hit(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, bc, tmaxf, tr);
+    int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
+    if (hl && hr) {
+      if (tr < tl) { int t = cl; cl = cr; cr = t; }
+      stack[(sp++) * stride] = cr;
+      cur = cl;
+    } else if (hl) cur = cl;
+    else if (hr) cur = cr;
+    else cur = sp ? stack[(--sp) * stride] : DONE;
+  };
+  if (COOP) {
+    /* any-hit with deferred, warp-shared leaf tests (coop_* above) */
+    while (true) {
+      while (cur != DONE) {
+        if (cur >= 0) visit();
+        else {
+          const bool due = coop_append(cs, cur);
+          cur = sp ? stack[(--sp) * stride] : DONE;
+          if (due) break;
+        }
+      }
+      __syncwarp();
+      const int n = *(volatile int*)&cs->n;
+      if (n == 0) break;                       /* nothing queued => every lane ran out of nodes */
+      if (coop_flush<COUNT>(sc, cs, s, n, cnt)) { found = true; best.prim = 0; sp = 0; cur = DONE; }
     }
+    return found;
+  }
+  while (__any_sync(0xffffffffu, cur != DONE)) {
+    while (cur >= 0) visit();
     __syncwarp();
     if (cur != DONE) {
       uint32_t bits = (uint32_t)~cur;
@@ -309,8 +390,9 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best&
  * is what keeps the 32 lanes of a warp together.  Shadow rays (ANY) push every hit child and pop: order is irrelevant.
  * A visit can push up to W - 1 codes, so the stack bound is (W - 1) * depth + 1: the first RRT_STACK entries live in
  * shared memory as before, anything beyond (never observed) in a local-memory array; rrt_upload_scene checks the bound. */
-template <bool ANY, bool COUNT, int W>
-__device__ __forceinline__ bool traverse_wide(const DevScene& sc, const Seg& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt, bool active) {
+template <bool ANY, bool COUNT, int W, bool COOP = false>
+__device__ __forceinline__ bool traverse_wide(const DevScene& sc, const Seg& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt, bool active,
+                                              CoopScratch* cs = nullptr) {
   const int DONE = (int)0x80000000;   /* also the code of an unused child slot (kEmptyChild) */
   const float R = 9.5367431640625e-7f; /* 2^-20 */
   best.t = s.tmax; best.rank = -1; best.prim = -1; best.kind = 0; best.b1 = best.b2 = 0.0;
@@ -331,37 +413,56 @@ __device__ __forceinline__ bool traverse_wide(const DevScene& sc, const Seg& s, 
     if (bc.nz) { onz = 5 * W; ofz = 2 * W; }
     if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tl)) cur = sc.wroot;
   }
-  while (__any_sync(0xffffffffu, cur != DONE)) {
-    while (cur >= 0) {
-      const float* nd = sc.wide + (size_t)(8 * W) * (size_t)cur;
-      if (COUNT) cnt.nodes++;
-      int nearest = DONE;
-      float tbest = 0.f;
-      auto child = [&](float pnx, float pfx, float pny, float pfy, float pnz, float pfz, int code) {
-        float tn = fmaxf(fmaxf(__fmaf_rn(pnx, bc.ix, bc.nx_), __fmaf_rn(pny, bc.iy, bc.ny_)), __fmaf_rn(pnz, bc.iz, bc.nz_));
-        float tf = fminf(fminf(__fmaf_rn(pfx, bc.ix, bc.fx_), __fmaf_rn(pfy, bc.iy, bc.fy_)), __fmaf_rn(pfz, bc.iz, bc.fz_));
-        tn = __fmaf_rn(fabsf(tn), -R, tn);
-        tf = __fmaf_rn(fabsf(tf), R, tf);
-        if (tn <= tf && tn <= tmaxf && tf >= bc.tmin && code != DONE) {
-          if (ANY) push(code);
-          else if (nearest == DONE) { nearest = code; tbest = tn; }
-          else if (tn < tbest) { push(nearest); nearest = code; tbest = tn; }
-          else push(code);
-        }
-      };
-#pragma unroll
-      for (int g = 0; g < W / 4; ++g) {
-        const float4 a = __ldg((const float4*)(nd + onx) + g), b = __ldg((const float4*)(nd + ofx) + g);
-        const float4 c = __ldg((const float4*)(nd + ony) + g), d = __ldg((const float4*)(nd + ofy) + g);
-        const float4 e = __ldg((const float4*)(nd + onz) + g), f = __ldg((const float4*)(nd + ofz) + g);
-        const int4 k = __ldg((const int4*)(nd + 6 * W) + g);
-        child(a.x, b.x, c.x, d.x, e.x, f.x, k.x);
-        child(a.y, b.y, c.y, d.y, e.y, f.y, k.y);
-        child(a.z, b.z, c.z, d.z, e.z, f.z, k.z);
-        child(a.w, b.w, c.w, d.w, e.w, f.w, k.w);
+  auto visit = [&]() {
+    const float* nd = sc.wide + (size_t)(8 * W) * (size_t)cur;
+    if (COUNT) cnt.nodes++;
+    int nearest = DONE;
+    float tbest = 0.f;
+    auto child = [&](float pnx, float pfx, float pny, float pfy, float pnz, float pfz, int code) {
+      float tn = fmaxf(fmaxf(__fmaf_rn(pnx, bc.ix, bc.nx_), __fmaf_rn(pny, bc.iy, bc.ny_)), __fmaf_rn(pnz, bc.iz, bc.nz_));
+      float tf = fminf(fminf(__fmaf_rn(pfx, bc.ix, bc.fx_), __fmaf_rn(pfy, bc.iy, bc.fy_)), __fmaf_rn(pfz, bc.iz, bc.fz_));
+      tn = __fmaf_rn(fabsf(tn), -R, tn);
+      tf = __fmaf_rn(fabsf(tf), R, tf);
+      if (tn <= tf && tn <= tmaxf && tf >= bc.tmin && code != DONE) {
+        if (ANY) push(code);
+        else if (nearest == DONE) { nearest = code; tbest = tn; }
+        else if (tn < tbest) { push(nearest); nearest = code; tbest = tn; }
+        else push(code);
       }
-      cur = (!ANY && nearest != DONE) ? nearest : (sp ? pop() : DONE);
+    };
+#pragma unroll
+    for (int g = 0; g < W / 4; ++g) {
+      const float4 a = __ldg((const float4*)(nd + onx) + g), b = __ldg((const float4*)(nd + ofx) + g);
+      const float4 c = __ldg((const float4*)(nd + ony) + g), d = __ldg((const float4*)(nd + ofy) + g);
+      const float4 e = __ldg((const float4*)(nd + onz) + g), f = __ldg((const float4*)(nd + ofz) + g);
+      const int4 k = __ldg((const int4*)(nd + 6 * W) + g);
+      child(a.x, b.x, c.x, d.x, e.x, f.x, k.x);
+      child(a.y, b.y, c.y, d.y, e.y, f.y, k.y);
+      child(a.z, b.z, c.z, d.z, e.z, f.z, k.z);
+      child(a.w, b.w, c.w, d.w, e.w, f.w, k.w);
     }
+    cur = (!ANY && nearest != DONE) ? nearest : (sp ? pop() : DONE);
+  };
+  if (COOP) {
+    /* any-hit with deferred, warp-shared leaf tests (coop_* above) */
+    while (true) {
+      while (cur != DONE) {
+        if (cur >= 0) visit();
+        else {
+          const bool due = coop_append(cs, cur);
+          cur = sp ? pop() : DONE;
+          if (due) break;
+        }
+      }
+      __syncwarp();
+      const int n = *(volatile int*)&cs->n;
+      if (n == 0) break;                       /* nothing queued => every lane ran out of nodes */
+      if (coop_flush<COUNT>(sc, cs, s, n, cnt)) { found = true; best.prim = 0; sp = 0; cur = DONE; }
+    }
+    return found;
+  }
+  while (__any_sync(0xffffffffu, cur != DONE)) {
+    while (cur >= 0) visit();
     __syncwarp();
     if (cur != DONE) {
       uint32_t bits = (uint32_t)~cur;

@@ -18,6 +18,9 @@
 #ifndef RRT_MINB
 #define RRT_MINB 6     /* resident blocks per SM the trace kernels are compiled for */
 #endif
+#ifndef RRT_COOP_LEAVES
+#define RRT_COOP_LEAVES 0   /* 1 = any-hit leaf tests deferred and shared across the warp (rrt_trace.cuh coop_*): measured SLOWER, C2 41.4 vs 37.1 ms */
+#endif
 #ifndef RRT_MINB_WIDE
 #define RRT_MINB_WIDE 6   /* the same for the wide-node variants */
 #endif
@@ -104,7 +107,11 @@ __device__ __forceinline__ void wt_flush_counters(const Counters& c, Counters* g
 template <bool ANY, bool COUNT, int W, class IO>
 __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHole& bh, const IO& io, const int n, int* cursor, Counters* gcnt) {
   __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
+  __shared__ CoopScratch coop_mem[ANY ? RRT_BLOCK / 32 : 1];
   int* stack = stack_mem + threadIdx.x;
+  constexpr bool COOP = ANY && RRT_COOP_LEAVES;
+  CoopScratch* coop = &coop_mem[COOP ? threadIdx.x >> 5 : 0];
+  if (COOP) coop_init(coop);
   Counters cnt = {0, 0, 0, 0, 0, 0};
   const bool flat = bh.mode == RRT_MODE_FLAT;
   const unsigned lt_mask = (1u << wt_lane()) - 1u;
@@ -153,8 +160,8 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
     const bool want = has && h.status < 0 && !chord_is_clear(sc, s.o, s.tmax);
     const bool live = has && h.status < 0;
     bool found;                                                                            /* whole warp, converged */
-    if (W == 2) found = traverse<ANY, COUNT>(sc, s, best, stack, RRT_BLOCK, cnt, want);
-    else found = traverse_wide<ANY, COUNT, (W == 2 ? 4 : W)>(sc, s, best, stack, RRT_BLOCK, cnt, want);
+    if (W == 2) found = traverse<ANY, COUNT, COOP>(sc, s, best, stack, RRT_BLOCK, cnt, want, coop);
+    else found = traverse_wide<ANY, COUNT, (W == 2 ? 4 : W), COOP>(sc, s, best, stack, RRT_BLOCK, cnt, want, coop);
     if (live) {
       if (found) {
         h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
