@@ -397,6 +397,12 @@ def main():
                               if scene_bytes < 100e6 else "exceeds the 126 MB L2 together with the ray queues; DRAM-served"))},
         "clocks": clk,
     }
+    if steps_geo > rays:   # hole on: the geodesic step is FP64 and its pipe, not HBM, is what the trace kernel runs against
+        my_chords = float(st_count["geodesic_steps"])
+        ceil = 48.5e9      # next_micro_ray + horizon_hit alone, saturated (tools/ilp_probe.cu on a B200)
+        line["roofline"]["fp64_step"] = {"achieved": my_chords / my_trace_s / 1e9 if my_trace_s > 0 else 0.0, "peak": ceil / 1e9, "unit": "G chords/s",
+                                         "frac": (my_chords / my_trace_s / ceil) if my_trace_s > 0 else 0.0,
+                                         "peak_source": "measured: profiles/r01_i_fp64_step_probe.txt (174.5 FP64 warp instructions per chord)"}
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_sample(args.workload, 1)
     print(json.dumps(line))
