@@ -24,6 +24,7 @@
  *   BVHAccel::intersect(ray[,isect])       src/bvh.h:86-109, src/bvh.cpp:99-138 -> rrt_trace_rays
  *   BlackHole::next_micro_ray              src/static_scene/blackhole.cpp:17-40 -> rrt_geodesic
  *   Camera::generate_ray                   src/part1_code.cpp:182-187           -> rrt_generate_rays
+ *   Camera::generate_ray_for_thin_lens     src/camera.cpp:176-184               -> rrt_generate_rays_thin_lens
  *   BSDF::f / sample_f                     src/bsdf.cpp:33-171, src/part1_code.cpp:167-173 -> rrt_bsdf_sample, rrt_bsdf_eval
  *   SceneLight::sample_L                   src/static_scene/light.cpp:17-92     -> rrt_light_sample
  *   HDRImageBuffer::toColor                src/image.h:183-198,53-62            -> rrt_tonemap
@@ -37,7 +38,7 @@
 extern "C" {
 #endif
 
-#define RRT_ABI_VERSION 3
+#define RRT_ABI_VERSION 4
 
 /* error codes */
 #define RRT_OK 0
@@ -214,6 +215,9 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
 int rrt_geodesic(rrt_ctx* ctx, int64_t n, const double* o, const double* d, int nsteps, double* seg_out);
 /* Camera::generate_ray for n normalised sensor positions xy [n*2] -> o,d [n*3]. */
 int rrt_generate_rays(rrt_ctx* ctx, int64_t n, const double* xy, double* o, double* d);
+/* Camera::generate_ray_for_thin_lens (src/camera.cpp:176-184; what raytrace_pixel calls with useThinLens, -b / -d):
+ * lens [n*2] = (rndR, rndTheta) as the reference passes them (a [0,1) sample and a [0,2 pi) angle). */
+int rrt_generate_rays_thin_lens(rrt_ctx* ctx, int64_t n, const double* xy, const double* lens, double* o, double* d);
 /* BSDF::sample_f of material `mat` for n outgoing directions wo [n*3] with uniforms u [n*4] in [0,1)
  * (u0,u1 = 2-D sample, u2 = glass coin).  Outputs f [n*3] float, wi [n*3] double, pdf [n] float. */
 int rrt_bsdf_sample(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const double* u, float* f,

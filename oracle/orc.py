@@ -30,7 +30,7 @@ def lib():
         L.orc_create.restype = C.c_void_p
         L.orc_create.argtypes = [C.POINTER(_sc.Scene), C.POINTER(_sc.Camera)]
         for name in ("orc_destroy", "orc_set_camera", "orc_set_blackhole", "orc_set_frame", "orc_set_cell", "orc_set_tile_shard",
-                     "orc_bvh_info", "orc_geodesic", "orc_trace_rays", "orc_generate_rays", "orc_philox", "orc_tonemap", "orc_set_envmap"):
+                     "orc_bvh_info", "orc_geodesic", "orc_trace_rays", "orc_generate_rays", "orc_generate_rays_thin_lens", "orc_philox", "orc_tonemap", "orc_set_envmap"):
             getattr(L, name).restype = None
         _LIB = L
     return _LIB
@@ -109,6 +109,12 @@ class Oracle:
         xy = np.ascontiguousarray(xy, np.float64).reshape(-1, 2)
         o = np.zeros((xy.shape[0], 3)); d = np.zeros((xy.shape[0], 3))
         lib().orc_generate_rays(self.h, C.c_int64(xy.shape[0]), _p(xy), _p(o), _p(d))
+        return o, d
+
+    def generate_rays_thin_lens(self, xy, lens):
+        xy = np.ascontiguousarray(xy, np.float64).reshape(-1, 2); lens = np.ascontiguousarray(lens, np.float64).reshape(-1, 2)
+        o = np.zeros((xy.shape[0], 3)); d = np.zeros((xy.shape[0], 3))
+        lib().orc_generate_rays_thin_lens(self.h, C.c_int64(xy.shape[0]), _p(xy), _p(lens), _p(o), _p(d))
         return o, d
 
     def bsdf_sample(self, mat, wo, u):

@@ -66,6 +66,7 @@ struct RandState {
   std::vector<int> queue; size_t qpos = 0;
   uint64_t seed = 0; uint32_t pixel = 0, sample = 0, n = 0;
   uint64_t draws = 0;
+  int grid_calls_per_sample = 1; uint32_t grid_calls = 0;   // thin lens: the second gridSampler call of a sample is the lens sample
 };
 static thread_local RandState g_rs;
 
@@ -83,13 +84,14 @@ extern "C" int rand(void) {
   return (int)(w >> 1);
 }
 
-// grid sampler hook: PathTracer::raytrace_pixel calls gridSampler->get_sample() exactly once at the start
-// of every sample when ns_aa > 1 (src/part1_code.cpp:131-135, THIN_LENS 0): use it to switch streams.
+// grid sampler hook: PathTracer::raytrace_pixel calls gridSampler->get_sample() at the start of every sample when
+// ns_aa > 1 (src/part1_code.cpp:131-135) and once more for the lens when useThinLens (:137-139): the first call
+// of a sample switches streams.  (ns_aa == 1 with a lens: the only call is the lens sample, no switch.)
 struct StreamSwitchSampler : public Sampler2D {
   UniformGridSampler2D inner;
   Vector2D get_sample() const {
     RandState& s = g_rs;
-    s.sample += 1; s.n = 0;          // caller sets sample = (uint32_t)-1 before each pixel
+    if (s.grid_calls_per_sample > 0 && s.grid_calls++ % (uint32_t)s.grid_calls_per_sample == 0) { s.sample += 1; s.n = 0; }   // caller sets sample = (uint32_t)-1 before each pixel
     return inner.get_sample();
   }
 };
@@ -324,6 +326,22 @@ static int cmd_camrays(int argc, char** argv) {
   return 0;
 }
 
+// lensrays: in.bin = n x [x y rndR rndTheta]; out = n x [o3 d3 min_t max_t]  (Camera::generate_ray_for_thin_lens, src/camera.cpp:176-184)
+static int cmd_lensrays(int argc, char** argv) {
+  if (argc < 7) return 1;
+  Ctx c = load(argv[2], atoi(argv[3]), atoi(argv[4]));
+  std::vector<double> in = read_doubles(argv[5]);
+  size_t n = in.size() / 4;
+  std::vector<double> out(n * 8);
+  for (size_t i = 0; i < n; ++i) {
+    Ray r = c.app->camera.generate_ray_for_thin_lens(in[4 * i], in[4 * i + 1], in[4 * i + 2], in[4 * i + 3]);
+    double* o = &out[i * 8];
+    o[0] = r.o.x; o[1] = r.o.y; o[2] = r.o.z; o[3] = r.d.x; o[4] = r.d.y; o[5] = r.d.z; o[6] = r.min_t; o[7] = r.max_t;
+  }
+  write_doubles(argv[6], out);
+  return 0;
+}
+
 // bsdf: in = n x [wo3, wi3(for f), r0, r1, r2, r3] (r* = integer rand() values as doubles);
 // out = n x 12 = [f_eval3, fs3, wi3, pdf, draws, is_delta]
 static int cmd_bsdf(int argc, char** argv) {
@@ -415,7 +433,11 @@ static int cmd_render(int argc, char** argv) {
   cfg.pathtracer_samples_per_patch = atoi(argv[8]);
   cfg.pathtracer_max_tolerance = atof(argv[9]);
   uint64_t seed = strtoull(argv[10], nullptr, 10);
-  for (int i = 12; i < argc; ++i) if (!strcmp(argv[i], "hemi")) cfg.pathtracer_direct_hemisphere_sample = true;
+  bool lens = false;   // THIN_LENS is compiled out of raytrace_tile (src/pathtracer.h:6) but raytrace_pixel still takes the flag
+  for (int i = 12; i < argc; ++i) {
+    if (!strcmp(argv[i], "hemi")) cfg.pathtracer_direct_hemisphere_sample = true;
+    if (!strcmp(argv[i], "lens")) lens = true;
+  }
   Ctx c = load(argv[2], W, H, cfg);
   delete c.pt->gridSampler;
   c.pt->gridSampler = new StreamSwitchSampler();
@@ -431,7 +453,8 @@ static int cmd_render(int argc, char** argv) {
       s.mode = 1; s.seed = seed; s.pixel = (uint32_t)(x + y * W); s.n = 0; s.draws = 0;
       // ns_aa == 1: no jitter draw, the stream of sample 0 starts at the first light sample.
       s.sample = cfg.pathtracer_ns_aa == 1 ? 0u : (uint32_t)-1;
-      Spectrum sp = c.pt->raytrace_pixel(x, y, false);
+      s.grid_calls = 0; s.grid_calls_per_sample = cfg.pathtracer_ns_aa == 1 ? 0 : (lens ? 2 : 1);
+      Spectrum sp = c.pt->raytrace_pixel(x, y, lens);
       double* o = &out[((size_t)x + (size_t)y * W) * 4];
       o[0] = sp.r; o[1] = sp.g; o[2] = sp.b; o[3] = c.pt->sampleCountBuffer[x + y * W];
       draws += s.draws;
@@ -461,6 +484,7 @@ int main(int argc, char** argv) {
     else if (cmd == "trace") rc = cmd_trace(argc, argv);
     else if (cmd == "geodesic") rc = cmd_geodesic(argc, argv);
     else if (cmd == "camrays") rc = cmd_camrays(argc, argv);
+    else if (cmd == "lensrays") rc = cmd_lensrays(argc, argv);
     else if (cmd == "bsdf") rc = cmd_bsdf(argc, argv);
     else if (cmd == "light") rc = cmd_light(argc, argv);
     else if (cmd == "envdir") rc = cmd_envdir(argc, argv);
@@ -473,9 +497,10 @@ int main(int argc, char** argv) {
             "       ref_probe trace <dae> W H rays.bin out.bin [-B cx cy cz r dtheta]\n"
             "       ref_probe geodesic rays.bin nsteps out.bin [-B ...]\n"
             "       ref_probe camrays <dae> W H xy.bin out.bin\n"
+            "       ref_probe lensrays <dae> W H in.bin out.bin\n"
             "       ref_probe bsdf <dae> W H mat in.bin out.bin\n"
             "       ref_probe light <dae> W H light in.bin out.bin\n"
-            "       ref_probe render <dae> W H spp l m batch tol seed out.bin [hemi] [-B ...]\n"
+            "       ref_probe render <dae> W H spp l m batch tol seed out.bin [hemi] [lens] [-B ...]\n"
             "       ref_probe order\n");
   return rc;
 }

@@ -871,6 +871,14 @@ void orc_generate_rays(const orc_ctx* c, int64_t n, const double* xy, double* o,
   }
 }
 
+/* Camera::generate_ray_for_thin_lens (reference src/camera.cpp:176-184); lens [n*2] = (rndR, rndTheta) */
+void orc_generate_rays_thin_lens(const orc_ctx* c, int64_t n, const double* xy, const double* lens, double* o, double* d) {
+  for (int64_t i = 0; i < n; ++i) {
+    ray_t r = generate_ray_thin_lens(&c->cam, xy[2 * i], xy[2 * i + 1], lens[2 * i], lens[2 * i + 1]);
+    o[3 * i] = r.o.x; o[3 * i + 1] = r.o.y; o[3 * i + 2] = r.o.z; d[3 * i] = r.d.x; d[3 * i + 1] = r.d.y; d[3 * i + 2] = r.d.z;
+  }
+}
+
 /* u [n*4]: the draws the reference would take from rand()/RAND_MAX, in draw order */
 int orc_bsdf_sample(const orc_ctx* c, int mat, int64_t n, const double* wo, const double* u, float* f, double* wi, float* pdf) {
   if (mat < 0 || mat >= (int)c->n_mats) return RRT_E_ARG;

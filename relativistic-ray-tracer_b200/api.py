@@ -27,7 +27,7 @@ OPT_BVH_TOPOLOGY, OPT_COUNTERS, OPT_WORK_BYTES, OPT_TRACE_KERNEL, OPT_LEAF_SIZE,
 
 EXPORTS = ["rrt_abi_version", "rrt_device_count", "rrt_create", "rrt_destroy", "rrt_last_error", "rrt_set_option", "rrt_upload_scene",
            "rrt_set_camera", "rrt_set_blackhole", "rrt_set_frame", "rrt_set_cell", "rrt_set_tile_shard", "rrt_render", "rrt_render_device",
-           "rrt_trace_rays", "rrt_geodesic", "rrt_generate_rays", "rrt_bsdf_sample", "rrt_bsdf_eval", "rrt_light_sample", "rrt_philox",
+           "rrt_trace_rays", "rrt_geodesic", "rrt_generate_rays", "rrt_generate_rays_thin_lens", "rrt_bsdf_sample", "rrt_bsdf_eval", "rrt_light_sample", "rrt_philox",
            "rrt_tonemap", "rrt_bvh_info", "rrt_bvh_build_host", "rrt_chords_per_ray", "rrt_set_envmap", "rrt_env_lookup"]
 
 
@@ -61,6 +61,7 @@ def lib():
                                      C.POINTER(_sc.Stats)]
         L.rrt_geodesic.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.rrt_generate_rays.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.rrt_generate_rays_thin_lens.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rrt_bsdf_sample.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rrt_bsdf_eval.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rrt_light_sample.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -187,6 +188,13 @@ class Context:
         xy = np.ascontiguousarray(xy, np.float64).reshape(-1, 2)
         o = np.zeros((xy.shape[0], 3)); d = np.zeros((xy.shape[0], 3))
         self._ck(lib().rrt_generate_rays(self.h, xy.shape[0], _p(xy), _p(o), _p(d)))
+        return o, d
+
+    def generate_rays_thin_lens(self, xy, lens):
+        """Camera::generate_ray_for_thin_lens; lens [n, 2] = (rndR, rndTheta)"""
+        xy = np.ascontiguousarray(xy, np.float64).reshape(-1, 2); lens = np.ascontiguousarray(lens, np.float64).reshape(-1, 2)
+        o = np.zeros((xy.shape[0], 3)); d = np.zeros((xy.shape[0], 3))
+        self._ck(lib().rrt_generate_rays_thin_lens(self.h, xy.shape[0], _p(xy), _p(lens), _p(o), _p(d)))
         return o, d
 
     def bsdf_sample(self, mat, wo, u):

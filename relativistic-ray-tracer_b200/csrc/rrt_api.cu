@@ -631,6 +631,23 @@ int rrt_generate_rays(rrt_ctx* ctx, int64_t n, const double* xy, double* o, doub
   return RRT_OK;
 }
 
+int rrt_generate_rays_thin_lens(rrt_ctx* ctx, int64_t n, const double* xy, const double* lens, double* o, double* d) {
+  if (!ctx || n < 0 || (n && (!xy || !lens || !o || !d))) return RRT_E_ARG;
+  if (!ctx->have_cam) FAIL(RRT_E_STATE, "rrt_generate_rays_thin_lens: no camera");
+  if (n == 0) return RRT_OK;
+  int rc = hook_begin(ctx, 32 * (size_t)n + 1024, 48 * (size_t)n + 1024);
+  if (rc) return rc;
+  size_t io = 0, oo = 0;
+  double* d_xy = (double*)hook_in(ctx, io, xy, 16 * (size_t)n); double* d_lens = (double*)hook_in(ctx, io, lens, 16 * (size_t)n);
+  double* d_o = (double*)hook_out(ctx, oo, 24 * (size_t)n); double* d_d = (double*)hook_out(ctx, oo, 24 * (size_t)n);
+  k_hook_camera_lens<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->cam, n, d_xy, d_lens, d_o, d_d);
+  CK(cudaMemcpyAsync(o, d_o, 24 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(d, d_d, 24 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
+  return RRT_OK;
+}
+
 static int bsdf_hook(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const double* wi_in, const double* u, float* f, double* wi, float* pdf) {
   if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_bsdf: no scene");
   if (mat < 0 || mat >= ctx->ds.n_mats) FAIL(RRT_E_ARG, "rrt_bsdf: material index out of range");

@@ -523,6 +523,14 @@ __global__ void k_hook_camera(const __grid_constant__ DevCamera cam, long long n
   }
 }
 
+__global__ void k_hook_camera_lens(const __grid_constant__ DevCamera cam, long long n, const double* __restrict__ xy, const double* __restrict__ lens,
+                                   double* __restrict__ o, double* __restrict__ d) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    d3 ro, rd; generate_ray_thin_lens(cam, xy[2 * i], xy[2 * i + 1], lens[2 * i], lens[2 * i + 1], ro, rd);
+    o[3 * i] = ro.x; o[3 * i + 1] = ro.y; o[3 * i + 2] = ro.z; d[3 * i] = rd.x; d[3 * i + 1] = rd.y; d[3 * i + 2] = rd.z;
+  }
+}
+
 __global__ void k_hook_bsdf(const rrt_material* __restrict__ mats, int mat, long long n, const double* __restrict__ wo, const double* __restrict__ wi_in,
                             const double* __restrict__ u, float* __restrict__ f, double* __restrict__ wi, float* __restrict__ pdf) {
   const rrt_material m = mats[mat];

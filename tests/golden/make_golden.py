@@ -250,7 +250,23 @@ def kat_envmap(scene, seed):
     print("kat_envmap", scene)
 
 
-def make_kat():
+def kat_thin_lens(scene, seed):
+    """Camera::generate_ray_for_thin_lens for seeded (x, y, rndR, rndTheta); lens parameters are the AppConfig defaults the fixture carries"""
+    dae, w, h, _ = SCENES[scene]
+    rng = np.random.default_rng(seed)
+    n = 2048
+    inp = np.stack([rng.uniform(0, 1, n), rng.uniform(0, 1, n), rng.uniform(0, 1, n), rng.uniform(0, 2 * np.pi, n)], 1)
+    inp[0] = [0.5, 0.5, 0.0, 0.0]; inp[1] = [0.0, 1.0, 1.0, 2 * np.pi]; inp[2] = [1.0, 0.0, 1.0, np.pi]
+    probe("bh", "lensrays", os.path.join(DAE, dae), w, h, wr("lens_in.bin", inp), tmpf("lens_out.bin"), env=scene_env(scene))
+    np.savez_compressed(os.path.join(HERE, "kat_thin_lens.npz"), scene=scene, inp=inp, out=rd("lens_out.bin", 8))
+    print("kat_thin_lens", scene)
+
+
+def make_kat(only=None):
+    if only and "thin_lens" in only:
+        kat_thin_lens("cbspheres_lambertian_480x360", 23)
+        return
+    kat_thin_lens("cbspheres_lambertian_480x360", 23)
     kat_geodesic()
     kat_trace("cbspheres_lambertian_480x360", 96, 72, 2000, 1, bh_alt=(0.2, 0.8, -0.1, 0.05, 0.2))
     kat_trace("cbgems_480x360", 64, 48, 1000, 2)
@@ -285,6 +301,9 @@ RENDERS = {  # name -> (scene, mode, spp, l, m, batch, tol, seed, extra args)
     "flat_envmap": ("cbspheres_lambertian_96x72", "flat", 8, 2, 4, 32, 0.05, 18, ["env"]),
     "bh_envmap": ("cbspheres_lambertian_96x72", "bh", 4, 2, 3, 32, 0.05, 19, ["env"]),
     "bh_envmap_gems": ("cbgems_96x72", "bh", 4, 1, 5, 32, 0.05, 20, ["env"]),
+    # thin lens (-b / -d): raytrace_pixel(x, y, useThinLens = true), which the reference's THIN_LENS switch compiles out of its tile loop
+    "flat_thin_lens": ("cbspheres_lambertian_96x72", "flat", 8, 2, 4, 32, 0.05, 21, ["lens"]),
+    "bh_thin_lens": ("cbspheres_lambertian_96x72", "bh", 4, 1, 3, 32, 0.05, 22, ["lens"]),
 }
 
 
@@ -304,7 +323,7 @@ def make_render(only=None):
         np.savez_compressed(os.path.join(HERE, "render_%s.npz" % name), hdr=img[..., :3].astype(np.float32),
                             counts=img[..., 3].astype(np.int32), scene=scene, mode=mode,
                             params=np.array([spp, l, m, batch, tol, seed], np.float64),
-                            hemi=np.array("hemi" in extra), envmap=np.array("env" in extra), bh=np.array([x for x in extra if not isinstance(x, str)], np.float64),
+                            hemi=np.array("hemi" in extra), envmap=np.array("env" in extra), lens=np.array("lens" in extra), bh=np.array([x for x in extra if not isinstance(x, str)], np.float64),
                             draws=tail[2])
         print("render", name, "mean radiance %.5f  paths %d" % (img[..., :3].mean(), img[..., 3].sum()))
 
@@ -314,6 +333,6 @@ if __name__ == "__main__":
     if "scenes" in what:
         make_scenes()
     if "kat" in what:
-        make_kat()
+        make_kat([w for w in what if w == "thin_lens"])
     if "render" in what:
         make_render([w for w in what if w in RENDERS] or None)

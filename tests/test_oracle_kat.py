@@ -121,3 +121,10 @@ def test_environment_light_sample_L_and_sample_dir():
     assert np.isinf(dist).all() and np.isinf(ref[:, 6]).all() and same(pdf.astype(np.float64), ref[:, 7])
     assert (ref[:, 8] == 2).all() and (ref[:, 9] == 0).all()      # two draws per sample, not a delta light
     assert same(o.env_lookup(g["dirs"]).astype(np.float64), g["dir_out"])
+
+
+def test_thin_lens_rays_match_reference():
+    """Camera::generate_ray_for_thin_lens (-b / -d; the reference compiles its call out with THIN_LENS 0 but ships the function)"""
+    g = golden("kat_thin_lens")
+    o, d = orc.Oracle(load_scene(str(g["scene"]))).generate_rays_thin_lens(g["inp"][:, :2], g["inp"][:, 2:])
+    assert np.array_equal(o, g["out"][:, :3]) and np.array_equal(d, g["out"][:, 3:6])

@@ -9,7 +9,8 @@ from oracle import orc
 
 RENDERS = ["c1_flat_lambertian", "c2_bh_lambertian", "bh_glass_mirror", "flat_glass_mirror", "flat_microfacet", "bh_microfacet",
            "flat_gems", "flat_bunny_microfacet", "bh_bunny_microfacet", "flat_adaptive", "bh_adaptive", "flat_depth0",
-           "flat_depth1", "bh_depth1_spp1", "flat_pointlight", "flat_hemisphere", "bh_alt_hole", "flat_envmap", "bh_envmap", "bh_envmap_gems"]
+           "flat_depth1", "bh_depth1_spp1", "flat_pointlight", "flat_hemisphere", "bh_alt_hole", "flat_envmap", "bh_envmap", "bh_envmap_gems",
+           "flat_thin_lens", "bh_thin_lens"]
 
 
 def setup_from_golden(g, obj):
@@ -26,7 +27,7 @@ def setup_from_golden(g, obj):
         obj.set_envmap(golden("kat_envmap")["env"])          # the synthetic map the reference rendered with (-e)
     spp, l, m, batch, tol, seed = g["params"]
     return sc.make_params(ns_aa=spp, max_ray_depth=m, ns_area_light=l, samples_per_batch=batch, max_tolerance=tol,
-                          direct_hemisphere_sample=bool(g["hemi"]), seed=int(seed))
+                          direct_hemisphere_sample=bool(g["hemi"]), thin_lens=("lens" in g.files and bool(g["lens"])), seed=int(seed))
 
 
 @pytest.mark.parametrize("name", RENDERS)
