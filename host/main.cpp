@@ -36,6 +36,8 @@ static void usage(const char* binary) {
   printf("  -e  <FILENAME>   Environment map (uncompressed .exr or .pfm)\n");
   printf("  -B  <x> <y> <z> <r> <dtheta>  Black hole centre, Schwarzschild radius, angular step\n");
   printf("  -F               Flat spacetime (no hole)      -S <INT> RNG seed      -G <INT> CUDA device\n");
+  printf("  --progress <PREFIX> [--progress-every <INT>]  write <PREFIX>_<samples>.png after every n-th adaptive batch\n");
+  printf("  --thin-lens      sample the lens (-b, -d) for every camera ray\n");
   printf("  --dump-scene <FILE>  write the flattened scene and exit (no GPU needed)\n");
   printf("  -h               Print this help message\n\n");
 }
@@ -49,6 +51,7 @@ int main(int argc, char** argv) {
   std::string filename, cam_settings, dump_scene, dump_camera, scene_path, envmap_path;
   Vector3D bh_c(0, 1, 0); double bh_r = 0.1, bh_dtheta = 0.1;
   unsigned long long seed = 0; int device = 0;
+  std::string progress_prefix; int progress_every = 1; bool thin_lens = false;
 
   auto need = [&](int i, int k) { if (i + k >= argc) { usage(argv[0]); exit(1); } };
   for (int i = 1; i < argc; ++i) {
@@ -73,6 +76,9 @@ int main(int argc, char** argv) {
     else if (a == "-F") flat = true;
     else if (a == "-S") { need(i, 1); seed = strtoull(argv[++i], nullptr, 10); }
     else if (a == "-G") { need(i, 1); device = atoi(argv[++i]); }
+    else if (a == "--progress") { need(i, 1); progress_prefix = argv[++i]; }
+    else if (a == "--progress-every") { need(i, 1); progress_every = atoi(argv[++i]); }
+    else if (a == "--thin-lens") thin_lens = true;
     else if (a == "--dump-scene") { need(i, 1); dump_scene = argv[++i]; }
     else if (a == "--dump-camera") { need(i, 1); dump_camera = argv[++i]; }
     else if (a == "--write-test-png") {   // host self-check used by tests/test_host_cpp.py: a 5x3 gradient through write_png
@@ -128,6 +134,7 @@ int main(int argc, char** argv) {
     if (!load_envmap(envmap_path, &ew, &eh, &env, &err)) { fprintf(stderr, "[PathTracer] Error loading environment map: %s\n", err.c_str()); return 1; }
     pt.set_envmap(ew, eh, env.data());
   }
+  pt.set_progress_snapshots(progress_prefix, progress_every); pt.use_thin_lens = thin_lens;
   pt.set_camera(&camera);
   pt.set_scene(&scene);
   pt.set_frame_size(camera.screenW, camera.screenH);

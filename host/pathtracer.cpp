@@ -155,23 +155,51 @@ void PathTracer::worker() {
   rrt_params p; memset(&p, 0, sizeof p);
   p.ns_aa = (int32_t)ns_aa_; p.max_ray_depth = (int32_t)max_ray_depth_; p.ns_area_light = (int32_t)ns_area_light_;
   p.samples_per_batch = (int32_t)samples_per_batch_; p.max_tolerance = max_tolerance_; p.direct_hemisphere_sample = hemisphere_ ? 1 : 0;
-  p.thin_lens = 0; p.seed = seed_;
+  p.thin_lens = use_thin_lens ? 1 : 0; p.seed = seed_;
+  snap_calls_ = 0; snaps_written_ = 0;
+  if (rrt_set_progress(ctx_, &PathTracer::progress_trampoline, this) != RRT_OK) return finish("rrt_set_progress");
   if (rrt_render(ctx_, &p, hdr_.data(), counts_.data(), &stats_) != RRT_OK) return finish("rrt_render");
   if (rrt_tonemap(ctx_, (int64_t)(W_ * H_), hdr_.data(), frame_.data()) != RRT_OK) return finish("rrt_tonemap");
   finish(nullptr);
+}
+
+int PathTracer::progress_trampoline(void* self, int32_t done, int32_t total, int64_t active) {
+  return static_cast<PathTracer*>(self)->on_progress(done, total, active);
+}
+
+// runs on the render thread between adaptive batches
+int PathTracer::on_progress(int32_t done, int32_t total, int64_t active) {
+  if (stop_requested_.load()) return 1;
+  if (!snap_prefix_.empty() && ++snap_calls_ % snap_every_ == 0) {
+    std::vector<float> hdr(W_ * H_ * 3);
+    std::vector<uint32_t> rgba(W_ * H_), out(W_ * H_);
+    if (rrt_snapshot(ctx_, hdr.data(), nullptr) == RRT_OK && rrt_tonemap(ctx_, (int64_t)(W_ * H_), hdr.data(), rgba.data()) == RRT_OK) {
+      for (size_t i = 0; i < H_; ++i)
+        for (size_t j = 0; j < W_; ++j) out[i * W_ + j] = rgba[(H_ - i - 1) * W_ + j] | 0xFF000000u;
+      char name[64]; snprintf(name, sizeof name, "_%06d.png", (int)done);
+      if (write_png(snap_prefix_ + name, out.data(), W_, H_)) {
+        ++snaps_written_;
+        fprintf(stderr, "[PathTracer] %d / %d samples, %lld pixels still sampling: %s%s\n", (int)done, (int)total, (long long)active, snap_prefix_.c_str(), name);
+      }
+    }
+  }
+  return 0;
 }
 
 void PathTracer::start_raytracing() {
   if (state_ != READY) return;
   if (thread_.joinable()) thread_.join();
   error_.clear();
+  stop_requested_.store(false);
   state_ = RENDERING;
   fprintf(stdout, "[PathTracer] Rendering... "); fflush(stdout);
   thread_ = std::thread(&PathTracer::worker, this);
 }
 
 void PathTracer::stop() {
+  stop_requested_.store(true);
   if (thread_.joinable()) thread_.join();
+  stop_requested_.store(false);
   std::lock_guard<std::mutex> lk(m_done_);
   if (state_ == RENDERING || state_ == DONE) state_ = READY;
 }

@@ -13,6 +13,7 @@
 
 #include <stdint.h>
 
+#include <atomic>
 #include <condition_variable>
 #include <mutex>
 #include <string>
@@ -145,7 +146,13 @@ class PathTracer {
   void set_device(int device) { device_ = device; }
   void set_tile_shard(int tile, int rank, int world) { tile_ = tile; rank_ = rank; world_ = world; }
   void start_raytracing();                   // asynchronous: returns at once, state becomes DONE when the frame is ready
-  void stop();                               // waits for a running render and returns to READY
+  void stop();                               // abandons a running render after its current adaptive batch (reference: continueRaytracing
+                                             // = false, src/pathtracer.cpp:180-200) and returns to READY; the partial frame stays readable
+  // Progressive output (stands in for the frame the viewer shows while RENDERING): after every `every`-th
+  // adaptive batch the running estimate is tone-mapped and written to <prefix>_<samples>.png.  Empty prefix = off.
+  void set_progress_snapshots(const std::string& prefix, int every = 1) { snap_prefix_ = prefix; snap_every_ = every > 0 ? every : 1; }
+  int snapshots_written() const { return snaps_written_; }
+  bool use_thin_lens = false;                // raytrace_pixel(x, y, useThinLens): the reference compiles it out (THIN_LENS 0, src/pathtracer.h:6)
   void clear();
   bool is_done();
   State get_state();
@@ -163,6 +170,10 @@ class PathTracer {
  private:
   bool has_valid_configuration() const;
   void worker();
+  static int progress_trampoline(void* self, int32_t done, int32_t total, int64_t active);
+  int on_progress(int32_t done, int32_t total, int64_t active);
+  std::atomic<bool> stop_requested_{false};
+  std::string snap_prefix_; int snap_every_ = 1, snap_calls_ = 0, snaps_written_ = 0;
   rrt_ctx* ctx_ = nullptr;
   int device_ = 0, tile_ = 16, rank_ = 0, world_ = 1;
   bool have_scene_ = false;

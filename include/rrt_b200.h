@@ -28,6 +28,7 @@
  *   BSDF::f / sample_f                     src/bsdf.cpp:33-171, src/part1_code.cpp:167-173 -> rrt_bsdf_sample, rrt_bsdf_eval
  *   SceneLight::sample_L                   src/static_scene/light.cpp:17-92     -> rrt_light_sample
  *   HDRImageBuffer::toColor                src/image.h:183-198,53-62            -> rrt_tonemap
+ *   update_screen (RENDERING) / stop       src/pathtracer.cpp:156-200           -> rrt_set_progress, rrt_snapshot
  */
 #ifndef RRT_B200_H
 #define RRT_B200_H
@@ -235,6 +236,19 @@ int rrt_env_lookup(rrt_ctx* ctx, int64_t n, const double* dir, float* radiance);
 int rrt_philox(rrt_ctx* ctx, uint64_t seed, int64_t n, const uint32_t* counters, uint32_t* out);
 /* toColor: [n*3] float HDR -> [n] RGBA8 (alpha 0xFF), on the device. */
 int rrt_tonemap(rrt_ctx* ctx, int64_t n, const float* hdr_rgb, uint32_t* rgba);
+
+/* ---- progressive output ----
+ * Stands in for what the viewer shows while the reference is in its RENDERING state (the frame buffer fills tile by
+ * tile, src/pathtracer.cpp:156-178) and for PathTracer::stop() (:180-200, `continueRaytracing = false`).
+ * fn runs on the thread that called rrt_render[_device], after every adaptive batch (samples_per_batch samples of every
+ * still-active pixel) except the last; samples_done counts samples per still-active pixel.  Inside fn, rrt_snapshot
+ * copies the running estimate (sum / n per pixel, 0 where n == 0) and the per-pixel sample counts to the host.  A
+ * non-zero return abandons the remaining batches: rrt_render then returns RRT_OK with the estimate reached so far.
+ * fn == NULL removes the callback.  Without a callback the render makes no extra synchronisation. */
+typedef int (*rrt_progress_fn)(void* user, int32_t samples_done, int32_t samples_total, int64_t active_pixels);
+int rrt_set_progress(rrt_ctx* ctx, rrt_progress_fn fn, void* user);
+/* only valid inside an rrt_progress_fn call; either pointer may be NULL.  hdr_rgb [W*H*3], sample_counts [W*H]. */
+int rrt_snapshot(rrt_ctx* ctx, float* hdr_rgb, int32_t* sample_counts);
 
 /* ---- introspection ---- */
 /* BVH facts after rrt_upload_scene: nodes, leaves, depth; dfs_rank [n_prims] (may be NULL) receives, for

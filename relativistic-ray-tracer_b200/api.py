@@ -27,8 +27,11 @@ OPT_BVH_TOPOLOGY, OPT_COUNTERS, OPT_WORK_BYTES, OPT_TRACE_KERNEL, OPT_LEAF_SIZE,
 
 EXPORTS = ["rrt_abi_version", "rrt_device_count", "rrt_create", "rrt_destroy", "rrt_last_error", "rrt_set_option", "rrt_upload_scene",
            "rrt_set_camera", "rrt_set_blackhole", "rrt_set_frame", "rrt_set_cell", "rrt_set_tile_shard", "rrt_render", "rrt_render_device",
-           "rrt_trace_rays", "rrt_geodesic", "rrt_generate_rays", "rrt_generate_rays_thin_lens", "rrt_bsdf_sample", "rrt_bsdf_eval", "rrt_light_sample", "rrt_philox",
+           "rrt_trace_rays", "rrt_geodesic", "rrt_generate_rays", "rrt_generate_rays_thin_lens", "rrt_set_progress", "rrt_snapshot", "rrt_bsdf_sample", "rrt_bsdf_eval", "rrt_light_sample", "rrt_philox",
            "rrt_tonemap", "rrt_bvh_info", "rrt_bvh_build_host", "rrt_chords_per_ray", "rrt_set_envmap", "rrt_env_lookup"]
+
+
+PROGRESS_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.c_int32, C.c_int64)
 
 
 class RrtError(RuntimeError):
@@ -61,6 +64,8 @@ def lib():
                                      C.POINTER(_sc.Stats)]
         L.rrt_geodesic.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.rrt_generate_rays.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.rrt_set_progress.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.rrt_snapshot.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.rrt_generate_rays_thin_lens.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rrt_bsdf_sample.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rrt_bsdf_eval.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -136,6 +141,28 @@ class Context:
 
     def set_cell(self, x, y, w, h):
         self._ck(lib().rrt_set_cell(self.h, int(x), int(y), int(w), int(h)))
+
+    def set_progress(self, fn):
+        """fn(samples_done, samples_total, active_pixels) -> truthy to stop; called between adaptive batches on the
+        rendering thread, may call self.snapshot().  None removes it."""
+        if fn is None:
+            self._progress = None
+            self._ck(lib().rrt_set_progress(self.h, None, None))
+            return
+        def tramp(_user, done, total, active):
+            try:
+                return 1 if fn(int(done), int(total), int(active)) else 0
+            except Exception:          # an exception cannot cross the C frame: stop the render instead
+                import traceback; traceback.print_exc()
+                return 1
+        self._progress = PROGRESS_FN(tramp)
+        self._ck(lib().rrt_set_progress(self.h, C.cast(self._progress, C.c_void_p), None))
+
+    def snapshot(self):
+        """running estimate (hdr [H, W, 3] float32, counts [H, W] int32); only inside a progress callback"""
+        hdr = np.zeros((self.H, self.W, 3), np.float32); cnt = np.zeros((self.H, self.W), np.int32)
+        self._ck(lib().rrt_snapshot(self.h, _p(hdr), _p(cnt)))
+        return hdr, cnt
 
     def set_tile_shard(self, tile, rank, world):
         self._ck(lib().rrt_set_tile_shard(self.h, int(tile), int(rank), int(world)))

@@ -41,6 +41,9 @@ struct rrt_ctx {
   bool has_microfacet = false;
   int W = 0, H = 0;
   int cell_x = 0, cell_y = 0, cell_w = 0, cell_h = 0;
+  // progressive output: callback between adaptive batches; snap_* are valid while it runs
+  rrt_progress_fn progress_fn = nullptr; void* progress_user = nullptr;
+  bool in_progress_cb = false; PixelAcc snap_px; size_t snap_npix = 0;
   int tile = 32, rank = 0, world = 1;
   int64_t opt[16];
   // device memory
@@ -259,6 +262,27 @@ int rrt_set_frame(rrt_ctx* ctx, int w, int h) {
 int rrt_set_cell(rrt_ctx* ctx, int x, int y, int w, int h) {
   if (!ctx) return RRT_E_ARG;
   ctx->cell_x = x; ctx->cell_y = y; ctx->cell_w = w; ctx->cell_h = h;
+  return RRT_OK;
+}
+
+int rrt_set_progress(rrt_ctx* ctx, rrt_progress_fn fn, void* user) {
+  if (!ctx) return RRT_E_ARG;
+  if (ctx->in_progress_cb) FAIL(RRT_E_STATE, "rrt_set_progress: called from inside the callback");
+  ctx->progress_fn = fn; ctx->progress_user = user;
+  return RRT_OK;
+}
+
+int rrt_snapshot(rrt_ctx* ctx, float* hdr_rgb, int32_t* sample_counts) {
+  if (!ctx) return RRT_E_ARG;
+  if (!ctx->in_progress_cb) FAIL(RRT_E_STATE, "rrt_snapshot: only valid inside an rrt_progress_fn call");
+  const size_t npix = ctx->snap_npix;
+  CK(cudaSetDevice(ctx->device));
+  CK(ctx->d_out_rgb.ensure(12 * npix)); CK(ctx->d_out_cnt.ensure(4 * npix));
+  k_finalize<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(ctx->snap_px, npix, ctx->d_out_rgb.as<float>(), ctx->d_out_cnt.as<int>(), nullptr, nullptr);
+  if (hdr_rgb) CK(cudaMemcpyAsync(hdr_rgb, ctx->d_out_rgb.p, 12 * npix, cudaMemcpyDeviceToHost, ctx->stream));
+  if (sample_counts) CK(cudaMemcpyAsync(sample_counts, ctx->d_out_cnt.p, 4 * npix, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaGetLastError());
   return RRT_OK;
 }
 
@@ -490,6 +514,13 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
       if (rc) return rc;
       launches += 3;
       a ^= 1; n_act = n_next;
+      if (ctx->progress_fn && n_act > 0) {   /* progressive output / stop(): include/rrt_b200.h */
+        CK(cudaStreamSynchronize(st));
+        ctx->snap_px = px; ctx->snap_npix = npix; ctx->in_progress_cb = true;
+        const int stop = ctx->progress_fn(ctx->progress_user, base_sample, rk.ns_aa, (int64_t)n_act);
+        ctx->in_progress_cb = false;
+        if (stop) break;
+      }
     }
   }
   k_finalize<<<grid_small, 256, 0, st>>>(px, npix, d_rgb, d_counts, d_rgbn, gcnt);

@@ -420,7 +420,7 @@ __global__ void __launch_bounds__(256) k_finalize(const __grid_constant__ PixelA
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) paths += __shfl_xor_sync(0xffffffffu, paths, o);
-  if (lane_id() == 0 && paths) atomicAdd(&gcnt->paths, paths);
+  if (gcnt && lane_id() == 0 && paths) atomicAdd(&gcnt->paths, paths);   /* gcnt == nullptr: rrt_snapshot */
 }
 
 /* ---------------------------------------------------------------- stable compaction (ballot + prefix), three passes:

@@ -414,3 +414,37 @@ def test_thin_lens_rays_match_reference(api):
     o, d = c.generate_rays_thin_lens(g["inp"][:, :2], g["inp"][:, 2:])
     np.testing.assert_allclose(o, g["out"][:, :3], rtol=0, atol=3e-16)
     np.testing.assert_allclose(d, g["out"][:, 3:6], rtol=0, atol=4e-16)
+
+
+def test_progress_callback_snapshots_and_stop(api):
+    """rrt_set_progress / rrt_snapshot: called between adaptive batches; snapshots are the running estimate; a render
+    with a callback equals one without; a truthy return abandons the remaining batches and leaves the partial estimate."""
+    s = load_scene("cbspheres_lambertian_96x72")
+    c = api.Context(0); c.upload_scene(s); c.set_frame(96, 72)
+    p = sc.make_params(ns_aa=32, max_ray_depth=3, ns_area_light=1, samples_per_batch=8, max_tolerance=0.0, seed=3)   # tol 0: only black pixels stop early
+    ref_hdr, ref_cnt, _ = c.render(p)
+    seen = []
+    def cb(done, total, active):
+        hdr, cnt = c.snapshot()
+        seen.append((done, total, active, hdr, cnt))
+        return False
+    c.set_progress(cb)
+    hdr, cnt, st = c.render(p)
+    c.set_progress(None)
+    assert np.array_equal(hdr, ref_hdr) and np.array_equal(cnt, ref_cnt)
+    assert [x[0] for x in seen] == [8, 16, 24] and all(x[1] == 32 for x in seen)
+    for done, _, active, shdr, scnt in seen:
+        assert scnt.max() == done and set(np.unique(scnt)) <= {8, done} and int((scnt == done).sum()) >= active > 0
+        assert np.isfinite(shdr).all() and shdr.max() > 0
+    # the 24-sample snapshot of a pixel that went all the way is the mean of its first 24 samples: close to, not equal to, the final mean
+    full = seen[-1][4] == 24
+    assert np.abs(seen[-1][3][full] - ref_hdr[full]).mean() < 0.05
+    with pytest.raises(api.RrtError):
+        c.snapshot()                                  # outside a callback
+    # stop after the second batch
+    calls = []
+    c.set_progress(lambda done, total, active: calls.append(done) or done >= 16)
+    hdr2, cnt2, st2 = c.render(p)
+    c.set_progress(None)
+    assert calls == [8, 16] and cnt2.max() == 16 and st2["paths"] == int(cnt2.sum())
+    assert np.array_equal(cnt2, seen[1][4]) and np.array_equal(hdr2, seen[1][3])

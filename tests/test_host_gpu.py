@@ -105,3 +105,29 @@ def test_cli_environment_map(exe, tmp_path):
     c.set_envmap(None)
     dark, _, _ = c.render(sc.make_params(ns_aa=4, max_ray_depth=3, ns_area_light=2, seed=5))
     assert hdr.mean() > dark.mean()      # the hole sends camera rays out of the box: they now see the sky
+
+
+def test_cli_progress_snapshots_and_thin_lens(exe, tmp_path):
+    """--progress writes one PNG per adaptive batch (the stand-in for the viewer's RENDERING frame); the last snapshot before the
+    final batch differs from the final image, the final image equals the binding's; --thin-lens equals thin_lens=True."""
+    api = importlib.import_module("relativistic-ray-tracer_b200.api")
+    s = load_scene("cbspheres_lambertian_96x72")
+    src = str(tmp_path / "s.rrtscene"); out = str(tmp_path / "o.png"); pre = str(tmp_path / "snap")
+    s.save(src)
+    r = subprocess.run([exe, "-s", "24", "-l", "1", "-m", "2", "-a", "8", "0", "-F", "--thin-lens", "--progress", pre, "-f", out, src], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    snaps = sorted(f for f in os.listdir(tmp_path) if f.startswith("snap_"))
+    assert snaps == ["snap_000008.png", "snap_000016.png"]
+    c = api.Context(0); c.upload_scene(s); c.set_frame(96, 72); c.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_FLAT)
+    p = sc.make_params(ns_aa=24, max_ray_depth=2, ns_area_light=1, samples_per_batch=8, max_tolerance=0.0, seed=0, thin_lens=True)
+    shots = []
+    c.set_progress(lambda d, t, a: shots.append(c.snapshot()[0]) and False)
+    hdr, _, _ = c.render(p)
+    c.set_progress(None)
+    def png_of(h):
+        w = np.ascontiguousarray(c.tonemap(h).reshape(72, 96)[::-1]).view(np.uint8).reshape(72, 96, 4).copy(); w[..., 3] = 255
+        return w
+    assert np.array_equal(read_png(out), png_of(hdr))
+    for f, h in zip(snaps, shots):
+        assert np.array_equal(read_png(str(tmp_path / f)), png_of(h))
+    assert not np.array_equal(read_png(str(tmp_path / snaps[-1])), read_png(out))
