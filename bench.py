@@ -240,6 +240,8 @@ def main():
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--grid", type=int, default=0)
     ap.add_argument("--width", type=int, default=0, choices=[0, 2, 4, 8], help="BVH node width (0 = library default: 8 for small scenes, else 2)")
+    ap.add_argument("--stepper", default="fp64", choices=["fp64", "fp32"],
+                    help="geodesic stepper: fp64 = bit-identical to the reference (default, the headline); fp32 = RRT_OPT_STEPPER 1, within 1e-4")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -271,6 +273,7 @@ def main():
     ctx.set_option(api.OPT_TRACE_KERNEL, args.variant)
     ctx.set_option(api.OPT_CLEARANCE_GRID, args.grid)
     ctx.set_option(api.OPT_BVH_WIDTH, args.width)
+    ctx.set_option(api.OPT_STEPPER, 1 if args.stepper == "fp32" else 0)
     ctx.upload_scene(s)
     ctx.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
     ctx.set_frame(W, H)
@@ -379,7 +382,7 @@ def main():
         "metric": "Mpaths/s", "value": paths * args.steps / secs / 1e6, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": desc, "frame": [W, H], "spp": spp_job, "ns_area_light": l, "max_ray_depth": m, "samples_per_batch": batch,
-                   "parallelism": "tile%d" % world, "bvh_topology": args.topology, "bvh_leaf": args.leaf, "trace_variant": args.variant, "clearance_grid": args.grid, "bvh_width": args.width, "l2": "flushed between timed iterations (256 MiB write)",
+                   "parallelism": "tile%d" % world, "bvh_topology": args.topology, "bvh_leaf": args.leaf, "trace_variant": args.variant, "clearance_grid": args.grid, "bvh_width": args.width, "stepper": args.stepper, "l2": "flushed between timed iterations (256 MiB write)",
                    "scaling_rule": "frame fixed, spp = %d x n_gpus, 16x16 interleaved tiles, one NCCL reduce per frame" % spp},
         "geodesic_steps_per_s": steps_geo * args.steps / secs, "rays_per_s": rays * args.steps / secs,
         "paths_per_step": paths, "geodesic_steps_per_step": steps_geo, "rays_per_step": rays,
@@ -397,7 +400,7 @@ def main():
                               if scene_bytes < 100e6 else "exceeds the 126 MB L2 together with the ray queues; DRAM-served"))},
         "clocks": clk,
     }
-    if steps_geo > rays:   # hole on: the geodesic step is FP64 and its pipe, not HBM, is what the trace kernel runs against
+    if steps_geo > rays and args.stepper == "fp64":   # hole on: the geodesic step is FP64 and its pipe, not HBM, is what the trace kernel runs against
         my_chords = float(st_count["geodesic_steps"])
         ceil = 48.5e9      # next_micro_ray + horizon_hit alone, saturated (tools/ilp_probe.cu on a B200)
         line["roofline"]["fp64_step"] = {"achieved": my_chords / my_trace_s / 1e9 if my_trace_s > 0 else 0.0, "peak": ceil / 1e9, "unit": "G chords/s",

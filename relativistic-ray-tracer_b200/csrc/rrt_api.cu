@@ -72,6 +72,14 @@ static int chords_for(double dtheta) {
   return j;
 }
 
+/* FP32 copies of the hole's constants for fast_step (rrt_trace.cuh), rounded once from the doubles */
+static void hole_fp32_constants(DevHole& b) {
+  const double h = b.h;
+  b.f_cx = (float)b.cx; b.f_cy = (float)b.cy; b.f_cz = (float)b.cz; b.f_r2 = (float)b.r2; b.f_r15 = (float)(1.5 * b.r);
+  b.f_h = (float)h; b.f_h2 = (float)(h / 2); b.f_h24 = (float)(h * h / 4); b.f_h26 = (float)(h * h / 6);
+  b.f_ch = (float)b.cos_h; b.f_sh = (float)b.sin_h; b.f_k = (float)(2.0 * sin(h / 2) * sin(h / 2));
+  b.f_cot = (float)(b.cos_h / b.sin_h); b.f_tan2 = (float)tan(h / 2);
+}
 extern "C" {
 
 int rrt_abi_version(void) { return RRT_ABI_VERSION; }
@@ -115,6 +123,7 @@ int rrt_create(rrt_ctx** out, int device) {
   /* global_black_hole(nullptr, Vector3D(0, 1, 0), 0.1, 0.1)  (reference src/static_scene/blackhole.cpp:5) */
   ctx->bh.cx = 0; ctx->bh.cy = 1; ctx->bh.cz = 0; ctx->bh.r = 0.1; ctx->bh.r2 = 0.1 * 0.1; ctx->bh.h = 0.1;
   ctx->bh.cos_h = cos(0.1); ctx->bh.sin_h = sin(0.1); ctx->bh.mode = RRT_MODE_LITERAL; ctx->bh.nchords = chords_for(0.1);
+  hole_fp32_constants(ctx->bh);
   *out = ctx;
   return RRT_OK;
 }
@@ -249,6 +258,7 @@ int rrt_set_blackhole(rrt_ctx* ctx, const double c[3], double r, double dtheta, 
   ctx->bh.cx = c[0]; ctx->bh.cy = c[1]; ctx->bh.cz = c[2]; ctx->bh.r = r; ctx->bh.r2 = r * r; ctx->bh.h = dtheta;
   ctx->bh.cos_h = cos(dtheta); ctx->bh.sin_h = sin(dtheta);  /* host libm, as the reference evaluates them (src/static_scene/blackhole.cpp:34-35) */
   ctx->bh.mode = mode; ctx->bh.nchords = chords_for(dtheta);
+  hole_fp32_constants(ctx->bh);
   return RRT_OK;
 }
 
@@ -355,21 +365,33 @@ static int trace_variant(const rrt_ctx* ctx) {
 }
 #define RRT_VARIANT_SWITCH(v, CALL) \
   switch (v) { case 1: { CALL(1); break; } case 4: { CALL(4); break; } case 8: { CALL(8); break; } default: { CALL(0); break; } }
+/* RRT_OPT_STEPPER = 1: the FP32 stepper, for the lockstep kernels over binary and 8-wide nodes, hole on */
+static bool fast_stepper(const rrt_ctx* ctx) {
+  return ctx->opt[RRT_OPT_STEPPER] == 1 && ctx->bh.mode != RRT_MODE_FLAT && ctx->opt[RRT_OPT_TRACE_KERNEL] != 1 && ctx->ds.width != 4;
+}
+#define RRT_STEP_SWITCH(ctx, v, CALL, CALLF) \
+  if (fast_stepper(ctx)) { if ((v) == 8) { CALLF(8); } else { CALLF(0); } } else RRT_VARIANT_SWITCH(v, CALL)
 
 static void launch_closest(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, const double* ray, size_t cap, const int* cnt_ptr, int* cursor, int* h_prim,
                            double* h_geo, Counters* gc) {
 #define RRT_CALL(V) if (count) k_trace_closest<true, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc); \
                     else k_trace_closest<false, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc)
-  RRT_VARIANT_SWITCH(trace_variant(ctx), RRT_CALL)
+#define RRT_CALLF(V) if (count) k_trace_closest<true, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc); \
+                    else k_trace_closest<false, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc)
+  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF)
 #undef RRT_CALL
+#undef RRT_CALLF
 }
 template <bool ANY>
 static void launch_shadow(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, const double* ray, size_t cap, const int* cnt_ptr, int* cursor,
                           const uint32_t* cidx, int* res, Counters* gc) {
 #define RRT_CALL(V) if (count) k_trace_shadow<ANY, true, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc); \
                     else k_trace_shadow<ANY, false, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc)
-  RRT_VARIANT_SWITCH(trace_variant(ctx), RRT_CALL)
+#define RRT_CALLF(V) if (count) k_trace_shadow<ANY, true, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc); \
+                    else k_trace_shadow<ANY, false, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc)
+  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF)
 #undef RRT_CALL
+#undef RRT_CALLF
 }
 
 static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_counts, float4* d_rgbn, cudaStream_t user_stream, rrt_stats* stats) {
@@ -612,8 +634,11 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
   int grid = (int)std::min<int64_t>((n + RRT_BLOCK - 1) / RRT_BLOCK, (int64_t)ctx->sm_count * 4);
 #define RRT_CALL(V) if (any_hit) k_hook_trace<true, V><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc); \
                     else k_hook_trace<false, V><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc)
-  RRT_VARIANT_SWITCH(trace_variant(ctx), RRT_CALL)
+#define RRT_CALLF(V) if (any_hit) k_hook_trace<true, V, 1><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc); \
+                    else k_hook_trace<false, V, 1><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc)
+  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF)
 #undef RRT_CALL
+#undef RRT_CALLF
   CK(cudaEventRecord(e1, ctx->stream));
   CK(cudaMemcpyAsync(out, d_out, sizeof(rrt_hit) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
@@ -638,7 +663,8 @@ int rrt_geodesic(rrt_ctx* ctx, int64_t n, const double* o, const double* d, int 
   size_t io = 0, oo = 0;
   double* d_o = (double*)hook_in(ctx, io, o, 24 * (size_t)n); double* d_d = (double*)hook_in(ctx, io, d, 24 * (size_t)n);
   double* d_s = (double*)hook_out(ctx, oo, ob);
-  k_hook_geodesic<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->bh, n, d_o, d_d, nsteps, d_s);
+  if (ctx->opt[RRT_OPT_STEPPER] == 1) k_hook_geodesic_fp32<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->bh, n, d_o, d_d, nsteps, d_s);
+  else k_hook_geodesic<<<grid_for(n, 128), 128, 0, ctx->stream>>>(ctx->bh, n, d_o, d_d, nsteps, d_s);
   CK(cudaMemcpyAsync(seg_out, d_s, ob, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   CK(cudaGetLastError());

@@ -516,6 +516,22 @@ __global__ void k_hook_geodesic(const __grid_constant__ DevHole bh, long long n,
   }
 }
 
+/* the same hook through the FP32 stepper (RRT_OPT_STEPPER = 1) */
+__global__ void k_hook_geodesic_fp32(const __grid_constant__ DevHole bh, long long n, const double* __restrict__ o, const double* __restrict__ d, int nsteps,
+                                     double* __restrict__ seg) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    d3 ro = D3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), rd = D3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+    FastRay fr; fast_init(bh, ro, rd, fr);
+    for (int j = 0; j < nsteps; ++j) {
+      float ox, oy, oz, dx, dy, dz, len;
+      const bool captured = fast_step(bh, fr, ox, oy, oz, dx, dy, dz, len);
+      double* s = seg + ((size_t)i * nsteps + j) * 8;
+      s[0] = ox; s[1] = oy; s[2] = oz; s[3] = dx; s[4] = dy; s[5] = dz; s[6] = len;
+      s[7] = captured ? 1.0 : 0.0;
+    }
+  }
+}
+
 __global__ void k_hook_camera(const __grid_constant__ DevCamera cam, long long n, const double* __restrict__ xy, double* __restrict__ o, double* __restrict__ d) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     d3 ro, rd; generate_ray(cam, xy[2 * i], xy[2 * i + 1], ro, rd);

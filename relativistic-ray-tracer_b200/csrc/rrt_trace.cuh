@@ -44,6 +44,9 @@ struct DevScene {
 struct DevHole {            // global_black_hole (reference src/static_scene/blackhole.cpp:5) + per-frame constants
   double cx, cy, cz, r, r2, h, cos_h, sin_h;
   int32_t mode, nchords;
+  // FP32 stepper (RRT_OPT_STEPPER = 1, fast_step below): the same constants rounded once on the host
+  float f_cx, f_cy, f_cz, f_r2, f_r15 /* 1.5 r */, f_h, f_h2 /* h/2 */, f_h24 /* h^2/4 */, f_h26 /* h^2/6 */;
+  float f_ch, f_sh, f_k /* 1 - cos h */, f_cot /* cos h / sin h */, f_tan2 /* tan(h/2) */;
 };
 
 struct Counters { unsigned long long rays, steps, nodes, tris, sph, paths; };
@@ -106,6 +109,91 @@ __device__ __forceinline__ bool horizon_hit(const DevHole& bh, d3 o, d3 d, doubl
   double sq = sqrt(disc);
   double t1 = (-b - sq) / 2, t2 = (-b + sq) / 2;
   return (0.0 <= t1 && t1 <= len) || (0.0 <= t2 && t2 <= len);
+}
+
+/* ---------------------------------------------------------------- FP32 state-carrying stepper (RRT_OPT_STEPPER = 1)
+ * The reference re-derives the orbital frame and u' = du/dphi from the previous chord every step
+ * (src/static_scene/blackhole.cpp:20-29).  Written out in the orbital plane that recurrence is EXACTLY
+ *     G    = h u' + (f1 + f2 + f3) h^2 / 6          f1..f3 as in the reference, f(u) = -u + 1.5 r u^2
+ *     u+   = u + G                                   (signed: u+ <= 0 is a ray that left; the reference carries on)
+ *     x^'  = sign(u+) (cos h x^ + sin h y^)           new radial unit vector   (p' = c + x^' / |u+|)
+ *     y^'  = -sin h x^ + cos h y^                     new tangential unit vector: the chord's tangential part at p'
+ *                                                     is sin h / u > 0 along it whatever the sign of u+
+ *     u''  = (u+ cos h - u) / sin h = G cot h - u tan(h/2)     what -u dx/dy of the NEW chord evaluates to
+ *     u    = |u+|
+ * (derivation: DESIGN.md section 6.2; with u+ < 0 the point lands on the far side of the hole, the frame changes
+ * handedness and the ray falls into the reference's two-point cycle, reproduced here because images depend on it).
+ * So a ray is (x^, y^, u, u') — the conserved orbital plane and the scalar state — in 8 registers; nothing is
+ * re-derived from positions, no division or square root touches the carried state, and the chord is formed from
+ * small terms:  q = p' - p = x^ A + y^ B,  A = -(u (1 - cos h) + G) / (u u+),  B = sin h / u+.
+ * Per chord: ~70 FP32 instructions + 3 MUFU instead of ~175 FP64 instructions.  Accuracy against the reference's
+ * doubles (tests/test_gpu_parity.py::test_fp32_stepper_*): chord end points and directions ~1e-6 relative after 63
+ * chords — well inside BASELINE.json's 1e-4 — but NOT bit-identical, so primitive ids can differ for rays that graze
+ * an edge; that is why this is an option and the FP64 stepper is the default. */
+struct FastRay { float xx, xy, xz, yx, yy, yz, u, up; };
+
+__device__ __forceinline__ float fast_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float fast_rsqrt(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
+/* first chord: the reference's own derivation from (o, d) with len = 0 (src/static_scene/blackhole.cpp:18-29), once per
+ * ray.  In double because near-radial rays cancel in d - dx x^, but without double divisions or square roots: the few
+ * lanes of a warp that are being refilled execute this alone (ncu: ~3 active threads per instruction), so its length is
+ * paid in full.  1/sqrt(.) = FP32 MUFU seed (rel. 2^-22) + one Newton step in double (rel. < 1e-13). */
+__device__ __forceinline__ double fast_rsqrt_d(double a) {
+  const double y = (double)fast_rsqrt((float)a);
+  return y * (1.5 - 0.5 * a * y * y);
+}
+__device__ __forceinline__ void fast_init(const DevHole& bh, const d3& o, const d3& d, FastRay& fr) {
+  d3 x = vsub(o, D3(bh.cx, bh.cy, bh.cz));
+  const double u = fast_rsqrt_d(vnorm2(x));
+  x = D3(x.x * u, x.y * u, x.z * u);
+  const double dx = vdot(d, x);
+  const d3 y = vsub(d, smul(dx, x));
+  const double rdy = fast_rsqrt_d(vnorm2(y));
+  fr.xx = (float)x.x; fr.xy = (float)x.y; fr.xz = (float)x.z;
+  fr.yx = (float)(y.x * rdy); fr.yy = (float)(y.y * rdy); fr.yz = (float)(y.z * rdy);
+  fr.u = (float)u; fr.up = (float)(-u * dx * rdy);
+}
+
+/* one chord: returns origin, unit direction and length of the chord from the current point to the next one, whether
+ * it crosses the horizon (Sphere::intersect on the hole, src/static_scene/sphere.cpp:10-53, in plane coordinates:
+ * distance of the chord's line from the centre = rho |B| / len, foot at t = -rho A / len), and advances the state */
+__device__ __forceinline__ bool fast_step(const DevHole& bh, FastRay& fr, float& ox, float& oy, float& oz, float& dx, float& dy, float& dz, float& len) {
+  const float u = fr.u, up = fr.up;
+  const float rho = fast_rcp(u);
+  ox = __fmaf_rn(rho, fr.xx, bh.f_cx); oy = __fmaf_rn(rho, fr.xy, bh.f_cy); oz = __fmaf_rn(rho, fr.xz, bh.f_cz);
+  const float f1 = __fmaf_rn(bh.f_r15 * u, u, -u);
+  const float v2 = __fmaf_rn(up, bh.f_h2, u);
+  const float f2 = __fmaf_rn(bh.f_r15 * v2, v2, -v2);
+  const float v3 = __fmaf_rn(f1, bh.f_h24, v2);
+  const float f3 = __fmaf_rn(bh.f_r15 * v3, v3, -v3);
+  const float G = __fmaf_rn(up, bh.f_h, (f1 + f2 + f3) * bh.f_h26);
+  const float un = u + G;
+  const float rhon = fast_rcp(un);
+  const float A = -__fmaf_rn(u, bh.f_k, G) * rho * rhon;
+  const float B = bh.f_sh * rhon;
+  const float qx = __fmaf_rn(A, fr.xx, B * fr.yx), qy = __fmaf_rn(A, fr.xy, B * fr.yy), qz = __fmaf_rn(A, fr.xz, B * fr.yz);
+  const float l2 = __fmaf_rn(qx, qx, __fmaf_rn(qy, qy, qz * qz));
+  const float rl = fast_rsqrt(l2);
+  len = l2 * rl;
+  dx = qx * rl; dy = qy * rl; dz = qz * rl;
+  /* horizon */
+  const float perp = rho * B * rl;
+  const float disc = __fmaf_rn(-perp, perp, bh.f_r2);
+  bool captured = false;
+  if (disc >= 0.f) {
+    const float sq = sqrtf(disc), tc = -rho * A * rl;
+    const float t1 = tc - sq, t2 = tc + sq;
+    captured = (0.f <= t1 && t1 <= len) || (0.f <= t2 && t2 <= len);
+  }
+  /* frame and scalar state */
+  const float sg = un < 0.f ? -1.f : 1.f;
+  const float ex = __fmaf_rn(bh.f_ch, fr.xx, bh.f_sh * fr.yx), ey = __fmaf_rn(bh.f_ch, fr.xy, bh.f_sh * fr.yy), ez = __fmaf_rn(bh.f_ch, fr.xz, bh.f_sh * fr.yz);
+  fr.yx = __fmaf_rn(bh.f_ch, fr.yx, -bh.f_sh * fr.xx); fr.yy = __fmaf_rn(bh.f_ch, fr.yy, -bh.f_sh * fr.xy); fr.yz = __fmaf_rn(bh.f_ch, fr.yz, -bh.f_sh * fr.xz);
+  fr.xx = sg * ex; fr.xy = sg * ey; fr.xz = sg * ez;
+  fr.up = __fmaf_rn(G, bh.f_cot, -u * bh.f_tan2);
+  fr.u = fabsf(un);
+  return captured;
 }
 
 /* Conservative FP32 version of BBox::intersect (reference src/bbox.cpp:10-25).  The reference evaluates
@@ -184,6 +272,52 @@ __device__ __forceinline__ bool box_hit(float lox, float loy, float loz, float h
   return tn <= tf && tn <= tmaxf && tf >= c.tmin;
 }
 
+/* Chord as the FP32 stepper produces it (RRT_OPT_STEPPER = 1): float origin, unit direction (to 1e-7) and length, plus
+ * e = (exact origin) - (float origin): non-zero only for a ray's first chord, which must leave from the caller's own
+ * double origin (rays start ON surfaces, hit_p + 1e-11 w_in, reference src/part1_code.cpp:45,88: an origin rounded to
+ * float lands behind the surface half the time).  The traversals below are generic over Seg / SegF through these adapters:
+ * box tests read the floats directly (no double -> float conversions), the exact leaf tests get doubles on demand. */
+struct SegF { float ox, oy, oz, dx, dy, dz, tmax, ex, ey, ez; };
+__device__ __forceinline__ const Seg& seg_exact(const Seg& s) { return s; }
+__device__ __forceinline__ Seg seg_exact(const SegF& s) {
+  Seg r;
+  r.o = D3((double)s.ox + (double)s.ex, (double)s.oy + (double)s.ey, (double)s.oz + (double)s.ez);
+  r.d = D3((double)s.dx, (double)s.dy, (double)s.dz); r.tmin = 0.0; r.tmax = (double)s.tmax;
+  return r;
+}
+__device__ __forceinline__ double seg_tmax(const Seg& s) { return s.tmax; }
+__device__ __forceinline__ double seg_tmax(const SegF& s) { return (double)s.tmax; }
+/* box context + float upper end of the range; returns whether the far-chord origin shift is in effect */
+__device__ __forceinline__ bool seg_boxctx(const DevScene& sc, const Seg& s, BoxCtx& bc, float& tmaxf) {
+  const double T = boxctx_make(sc, s.o, s.d, s.tmin, bc);
+  tmaxf = boxctx_tmax(s.tmax, T);
+  return T != 0.0;
+}
+__device__ __forceinline__ void boxctx_axis_f(float of, float df, float slack, float& inv, float& cn, float& cf, bool& neg) {
+  if (fabsf(df) < 1e-30f) df = copysignf(0.f, df);
+  inv = __frcp_rn(df);
+  float c = of * inv;
+  float a = __fmaf_rn(2.3841858e-7f, fabsf(of), slack) * fabsf(inv);   /* same bound as boxctx_axis; here o_f and d_f ARE the chord */
+  cn = -c - a; cf = -c + a;
+  neg = __float_as_int(df) < 0;
+}
+__device__ __forceinline__ bool seg_boxctx(const DevScene& sc, const SegF& s, BoxCtx& bc, float& tmaxf) {
+  const float m = fmaxf(fmaxf(fabsf(s.ox), fabsf(s.oy)), fabsf(s.oz));
+  if (m > RRT_FAR_ORIGIN && m < 1e30f) {   /* far chord: rare, take the double path */
+    const Seg e = seg_exact(s);
+    const double T = boxctx_make(sc, e.o, e.d, 0.0, bc);
+    tmaxf = boxctx_tmax(e.tmax, T);
+    return T != 0.0;
+  }
+  const float slack = fmaxf(fmaxf(fabsf(s.ex), fabsf(s.ey)), fabsf(s.ez));   /* |exact origin - float origin| */
+  bc.tmin = 0.f;
+  boxctx_axis_f(s.ox, s.dx, slack, bc.ix, bc.nx_, bc.fx_, bc.nx);
+  boxctx_axis_f(s.oy, s.dy, slack, bc.iy, bc.ny_, bc.fy_, bc.ny);
+  boxctx_axis_f(s.oz, s.dz, slack, bc.iz, bc.nz_, bc.fz_, bc.nz);
+  tmaxf = s.tmax;
+  return false;
+}
+
 /* True when x * (1 / det) is certainly a negative, non-zero number: opposite signs and both magnitudes far enough
  * from the ends of the exponent range that the product can neither underflow to (-)0 nor involve inf/NaN.  Used to
  * reject a triangle before the division; anything this test does not cover takes the literal path below. */
@@ -207,7 +341,7 @@ __device__ __forceinline__ bool chord_is_clear(const DevScene& sc, const d3& p, 
 
 /* Triangle::intersect and Sphere::intersect on one 80-byte leaf record.  Accepts when the reference would and the
  * hit is at least as close as the best so far (ties: higher depth-first rank wins). */
-template <bool COUNT>
+template <bool COUNT, bool UNITD = true>
 __device__ __forceinline__ bool leaf_record_test(const double2* __restrict__ rec, const Seg& s, Best& best, Counters& cnt) {
   double2 a0 = __ldg(rec + 0), a1 = __ldg(rec + 1), a2 = __ldg(rec + 2), a3 = __ldg(rec + 3), a4 = __ldg(rec + 4);
   unsigned long long tag = (unsigned long long)__double_as_longlong(a4.y);
@@ -236,10 +370,19 @@ __device__ __forceinline__ bool leaf_record_test(const double2* __restrict__ rec
   } else {
     if (COUNT) cnt.sph++;
     d3 tmp = vsub(s.o, D3(a0.x, a0.y, a1.x));
-    double b = 2 * vdot(tmp, s.d), c = vnorm2(tmp) - a1.y, disc = b * b - 4 * c;
-    if (disc < 0) return false;
-    double sq = sqrt(disc);
-    double t1 = (-b - sq) / 2, t2 = (-b + sq) / 2;
+    double b = 2 * vdot(tmp, s.d), c = vnorm2(tmp) - a1.y, t1, t2;
+    if (UNITD) {   /* the reference's form: a = 1 assumed (src/static_scene/sphere.cpp:10-20) */
+      double disc = b * b - 4 * c;
+      if (disc < 0) return false;
+      double sq = sqrt(disc);
+      t1 = (-b - sq) / 2; t2 = (-b + sq) / 2;
+    } else {       /* FP32 stepper: |d| = 1 +- 1e-7, and a root taken with a = 1 would leave the hit point ~1e-8 off the sphere —
+                      inside it half the time, where the next ray (origin + 1e-11 w_in) starts by hitting the sphere from within */
+      double a = vnorm2(s.d), disc = b * b - 4 * a * c;
+      if (disc < 0) return false;
+      double sq = sqrt(disc), ia = 0.5 / a;
+      t1 = (-b - sq) * ia; t2 = (-b + sq) * ia;
+    }
     if (s.tmin <= t1 && t1 <= best.t) t = t1;
     else if (s.tmin <= t2 && t2 <= best.t) t = t2;
     else return false;
@@ -309,24 +452,22 @@ __device__ __forceinline__ bool coop_flush(const DevScene& sc, CoopScratch* cs, 
 
 /* BVHAccel::intersect_micro (reference src/bvh.cpp:115-138) as an iterative, near-child-first traversal with a
  * per-thread stack in shared memory.  ANY = shadow-ray form (stop at the first accepted primitive). */
-template <bool ANY, bool COUNT, bool COOP = false>
-__device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt, bool active,
+template <bool ANY, bool COUNT, bool COOP = false, bool UNITD = true, class SEG = Seg>
+__device__ __forceinline__ bool traverse(const DevScene& sc, const SEG& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt, bool active,
                                          CoopScratch* cs = nullptr) {
   /* Called by ALL 32 lanes of the warp, converged; lanes without a chord pass active = false and idle through.
    * while-while: every lane first descends until it holds a leaf (or runs out of nodes), the warp re-converges, then
    * the lanes that hold a leaf test its records.  (Measured alternatives, C2 on B200, ms per frame: single if/else
    * loop 40.3; this form 38.2-38.9; remembering the leaves and testing them after the whole descent 41.3.) */
   const int DONE = (int)0x80000000;   /* not a valid leaf code: n_prims < 2^28 */
-  best.t = s.tmax; best.rank = -1; best.prim = -1; best.kind = 0; best.b1 = best.b2 = 0.0;
+  best.t = seg_tmax(s); best.rank = -1; best.prim = -1; best.kind = 0; best.b1 = best.b2 = 0.0;
   BoxCtx bc;
   float tmaxf = 0.f, tl, tr;
   bool found = false;
   int cur = DONE, sp = 0;
   bool shifted = false;               /* far chord: box parameters count from o + T d, see boxctx_make */
   if (active) {
-    const double T = boxctx_make(sc, s.o, s.d, s.tmin, bc);
-    shifted = T != 0.0;
-    tmaxf = boxctx_tmax(best.t, T);
+    shifted = seg_boxctx(sc, s, bc, tmaxf);
     if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tl)) cur = sc.root;
   }
   auto visit = [&]() {
@@ -344,7 +485,7 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best&
     else if (hr) cur = cr;
     else cur = sp ? stack[(--sp) * stride] : DONE;
   };
-  if (COOP) {
+  if constexpr (COOP) {
     /* any-hit with deferred, warp-shared leaf tests (coop_* above) */
     while (true) {
       while (cur != DONE) {
@@ -370,7 +511,7 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best&
       uint32_t first = bits >> 3, count = bits & 7u;
       cur = DONE;
       for (uint32_t k = 0; k < count; ++k) {
-        if (leaf_record_test<COUNT>(sc.leaf + 5 * (size_t)(first + k), s, best, cnt)) {
+        if (leaf_record_test<COUNT, UNITD>(sc.leaf + 5 * (size_t)(first + k), seg_exact(s), best, cnt)) {
           found = true;
           if (ANY) { sp = 0; break; }
           if (!shifted) tmaxf = __double2float_ru(best.t);   /* shifted chords keep the chord-long range: rare, and conservative */
@@ -390,12 +531,12 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const Seg& s, Best&
  * is what keeps the 32 lanes of a warp together.  Shadow rays (ANY) push every hit child and pop: order is irrelevant.
  * A visit can push up to W - 1 codes, so the stack bound is (W - 1) * depth + 1: the first RRT_STACK entries live in
  * shared memory as before, anything beyond (never observed) in a local-memory array; rrt_upload_scene checks the bound. */
-template <bool ANY, bool COUNT, int W, bool COOP = false>
-__device__ __forceinline__ bool traverse_wide(const DevScene& sc, const Seg& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt, bool active,
+template <bool ANY, bool COUNT, int W, bool COOP = false, bool UNITD = true, class SEG = Seg>
+__device__ __forceinline__ bool traverse_wide(const DevScene& sc, const SEG& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt, bool active,
                                               CoopScratch* cs = nullptr) {
   const int DONE = (int)0x80000000;   /* also the code of an unused child slot (kEmptyChild) */
   const float R = 9.5367431640625e-7f; /* 2^-20 */
-  best.t = s.tmax; best.rank = -1; best.prim = -1; best.kind = 0; best.b1 = best.b2 = 0.0;
+  best.t = seg_tmax(s); best.rank = -1; best.prim = -1; best.kind = 0; best.b1 = best.b2 = 0.0;
   BoxCtx bc;
   float tmaxf = 0.f, tl;
   bool found = false, shifted = false;
@@ -405,9 +546,7 @@ __device__ __forceinline__ bool traverse_wide(const DevScene& sc, const Seg& s, 
   auto pop = [&]() -> int { --sp; return sp < RRT_STACK ? stack[sp * stride] : spill[min(sp - RRT_STACK, RRT_SPILL - 1)]; };
   int onx = 0, ony = W, onz = 2 * W, ofx = 3 * W, ofy = 4 * W, ofz = 5 * W;   /* float offsets of the near / far plane arrays */
   if (active) {
-    const double T = boxctx_make(sc, s.o, s.d, s.tmin, bc);
-    shifted = T != 0.0;
-    tmaxf = boxctx_tmax(best.t, T);
+    shifted = seg_boxctx(sc, s, bc, tmaxf);
     if (bc.nx) { onx = 3 * W; ofx = 0; }
     if (bc.ny) { ony = 4 * W; ofy = W; }
     if (bc.nz) { onz = 5 * W; ofz = 2 * W; }
@@ -443,7 +582,7 @@ __device__ __forceinline__ bool traverse_wide(const DevScene& sc, const Seg& s, 
     }
     cur = (!ANY && nearest != DONE) ? nearest : (sp ? pop() : DONE);
   };
-  if (COOP) {
+  if constexpr (COOP) {
     /* any-hit with deferred, warp-shared leaf tests (coop_* above) */
     while (true) {
       while (cur != DONE) {
@@ -469,7 +608,7 @@ __device__ __forceinline__ bool traverse_wide(const DevScene& sc, const Seg& s, 
       uint32_t first = bits >> 3, count = bits & 7u;
       cur = DONE;
       for (uint32_t k = 0; k < count; ++k) {
-        if (leaf_record_test<COUNT>(sc.leaf + 5 * (size_t)(first + k), s, best, cnt)) {
+        if (leaf_record_test<COUNT, UNITD>(sc.leaf + 5 * (size_t)(first + k), seg_exact(s), best, cnt)) {
           found = true;
           if (ANY) { sp = 0; break; }
           if (!shifted) tmaxf = __double2float_ru(best.t);

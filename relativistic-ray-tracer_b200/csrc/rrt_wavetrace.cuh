@@ -104,7 +104,7 @@ __device__ __forceinline__ void wt_flush_counters(const Counters& c, Counters* g
 }
 
 /* ---------------------------------------------------------------- variant 0 (default): chord-lockstep loop */
-template <bool ANY, bool COUNT, int W, class IO>
+template <bool ANY, bool COUNT, int W, int STEP, class IO>
 __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHole& bh, const IO& io, const int n, int* cursor, Counters* gcnt) {
   __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
   __shared__ CoopScratch coop_mem[ANY ? RRT_BLOCK / 32 : 1];
@@ -113,12 +113,14 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
   CoopScratch* coop = &coop_mem[COOP ? threadIdx.x >> 5 : 0];
   if (COOP) coop_init(coop);
   Counters cnt = {0, 0, 0, 0, 0, 0};
-  const bool flat = bh.mode == RRT_MODE_FLAT;
+  const bool flat = STEP == 0 && bh.mode == RRT_MODE_FLAT;   /* the host only picks STEP = 1 with the hole on */
   const unsigned lt_mask = (1u << wt_lane()) - 1u;
   int pool_next = 0, pool_end = 0;   /* warp-uniform */
   bool more = true;                  /* warp-uniform: the global queue may still have entries */
   bool has = false;
   int idx = 0, j = 0;
+  FastRay fr; fr.xx = fr.xy = fr.xz = fr.yx = fr.yy = fr.yz = fr.u = fr.up = 0.f;
+  float e0x = 0.f, e0y = 0.f, e0z = 0.f;   /* STEP 1: (double origin) - (float origin of the first chord) */
   d3 o = D3(0, 0, 0), d = D3(0, 0, 0);
   double len = 0.0, tmin = 0.0, tmax = 0.0;
   while (true) {
@@ -139,6 +141,12 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
         idx = pool_next + rank;
         io.load(idx, o, d, tmin, tmax);
         has = true; j = 0; len = 0.0;
+        if (STEP == 1) {
+          fast_init(bh, o, d, fr);
+          const float rho = fast_rcp(fr.u);   /* the float origin fast_step is about to form, to the bit */
+          e0x = (float)(o.x - (double)__fmaf_rn(rho, fr.xx, bh.f_cx)); e0y = (float)(o.y - (double)__fmaf_rn(rho, fr.xy, bh.f_cy));
+          e0z = (float)(o.z - (double)__fmaf_rn(rho, fr.xz, bh.f_cz));
+        }
         if (COUNT) cnt.rays++;
       }
       pool_next += min(__popc(need), avail);
@@ -147,28 +155,51 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
     if (!__any_sync(0xffffffffu, has)) break;
     /* ---- one chord for every lane that holds a ray */
     Hit h; h.status = -1;
-    Seg s; s.o = o; s.d = d; s.tmin = tmin; s.tmax = tmax;
     Best best;
-    if (has) {
-      if (!flat) {
-        next_micro_ray(bh, o, d, len);
-        s.o = o; s.d = d; s.tmin = 0.0; s.tmax = len;
-        if (horizon_hit(bh, o, d, len)) { h.status = 2; h.prim = -1; h.chord = j; h.steps = j + 1; h.t = 0.0; }
+    bool found;
+    if constexpr (STEP == 1) {
+      SegF sf; sf.ox = sf.oy = sf.oz = sf.dx = sf.dy = sf.dz = sf.tmax = sf.ex = sf.ey = sf.ez = 0.f;
+      if (has) {
+        const bool captured = fast_step(bh, fr, sf.ox, sf.oy, sf.oz, sf.dx, sf.dy, sf.dz, sf.tmax);
+        sf.ex = e0x; sf.ey = e0y; sf.ez = e0z; e0x = e0y = e0z = 0.f;   /* first chord: leaves from the caller's double origin */
+        if (captured) { h.status = 2; h.prim = -1; h.chord = j; h.steps = j + 1; h.t = 0.0; }
+        if (COUNT) cnt.steps++;
       }
-      if (COUNT) cnt.steps++;
-    }
-    const bool want = has && h.status < 0 && !chord_is_clear(sc, s.o, s.tmax);
-    const bool live = has && h.status < 0;
-    bool found;                                                                            /* whole warp, converged */
-    if (W == 2) found = traverse<ANY, COUNT, COOP>(sc, s, best, stack, RRT_BLOCK, cnt, want, coop);
-    else found = traverse_wide<ANY, COUNT, (W == 2 ? 4 : W), COOP>(sc, s, best, stack, RRT_BLOCK, cnt, want, coop);
-    if (live) {
-      if (found) {
-        h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
-        if (IO::GEO) fill_geo(sc, s, best, h);
-      } else {
-        ++j;
-        if (flat || j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = flat ? 0 : j - 1; h.steps = flat ? 1 : j; h.t = 0.0; }
+      const bool live = has && h.status < 0;
+      if (W == 2) found = traverse<ANY, COUNT, false, false>(sc, sf, best, stack, RRT_BLOCK, cnt, live, coop);
+      else found = traverse_wide<ANY, COUNT, (W == 2 ? 4 : W), false, false>(sc, sf, best, stack, RRT_BLOCK, cnt, live, coop);
+      if (live) {
+        if (found) {
+          h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
+          if (IO::GEO) fill_geo(sc, seg_exact(sf), best, h);
+        } else {
+          ++j;
+          if (j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = j - 1; h.steps = j; h.t = 0.0; }
+        }
+      }
+    } else {
+      Seg s; s.o = o; s.d = d; s.tmin = tmin; s.tmax = tmax;
+      if (has) {
+        if (!flat) {
+          next_micro_ray(bh, o, d, len);
+          s.o = o; s.d = d; s.tmin = 0.0; s.tmax = len;
+          if (horizon_hit(bh, o, d, len)) { h.status = 2; h.prim = -1; h.chord = j; h.steps = j + 1; h.t = 0.0; }
+        }
+        if (COUNT) cnt.steps++;
+      }
+      const bool want = has && h.status < 0 && !chord_is_clear(sc, s.o, s.tmax);
+      const bool live = has && h.status < 0;
+      /* whole warp, converged */
+      if (W == 2) found = traverse<ANY, COUNT, COOP>(sc, s, best, stack, RRT_BLOCK, cnt, want, coop);
+      else found = traverse_wide<ANY, COUNT, (W == 2 ? 4 : W), COOP>(sc, s, best, stack, RRT_BLOCK, cnt, want, coop);
+      if (live) {
+        if (found) {
+          h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
+          if (IO::GEO) fill_geo(sc, s, best, h);
+        } else {
+          ++j;
+          if (flat || j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = flat ? 0 : j - 1; h.steps = flat ? 1 : j; h.t = 0.0; }
+        }
       }
     }
     if (has && h.status >= 0) { io.store(idx, h); has = false; }
@@ -318,31 +349,31 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
 }
 
 /* extension rays: closest hit */
-template <bool COUNT, int V>
+template <bool COUNT, int V, int STEP = 0>
 __global__ void __launch_bounds__(RRT_BLOCK, (V >= 4 ? RRT_MINB_WIDE : RRT_MINB)) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                 const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
                                                                 int* cursor, int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt) {
   ClosestIO io; io.ray = ray; io.cap = cap; io.h_prim = h_prim; io.h_geo = h_geo;
   if (V == 1) trace_sched<false, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
-  else trace_persistent<false, COUNT, (V == 0 ? 2 : V)>(sc, bh, io, *count_ptr, cursor, gcnt);
+  else trace_persistent<false, COUNT, (V == 0 ? 2 : V), STEP>(sc, bh, io, *count_ptr, cursor, gcnt);
 }
 
 /* shadow rays: BVHAccel::intersect(ray) (any hit), or closest hit when the hemisphere estimator needs the emitter */
-template <bool ANY, bool COUNT, int V>
+template <bool ANY, bool COUNT, int V, int STEP = 0>
 __global__ void __launch_bounds__(RRT_BLOCK, (V >= 4 ? RRT_MINB_WIDE : RRT_MINB)) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
                                                                int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt) {
   ShadowIO io; io.ray = ray; io.cap = cap; io.cidx = cidx; io.res = res;
   if (V == 1) trace_sched<ANY, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
-  else trace_persistent<ANY, COUNT, (V == 0 ? 2 : V)>(sc, bh, io, *count_ptr, cursor, gcnt);
+  else trace_persistent<ANY, COUNT, (V == 0 ? 2 : V), STEP>(sc, bh, io, *count_ptr, cursor, gcnt);
 }
 
 /* parity hook: the same loop on caller-supplied rays */
-template <bool ANY, int V>
+template <bool ANY, int V, int STEP = 0>
 __global__ void __launch_bounds__(RRT_BLOCK, (V >= 4 ? RRT_MINB_WIDE : RRT_MINB)) k_hook_trace(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, int n,
                                                             const double* __restrict__ o, const double* __restrict__ d, const double* __restrict__ tmin,
                                                             const double* __restrict__ tmax, rrt_hit* __restrict__ out, int* cursor, Counters* gcnt) {
   HookIO<ANY> io; io.o = o; io.d = d; io.tmin = tmin; io.tmax = tmax; io.out = out;
   if (V == 1) trace_sched<ANY, true>(sc, bh, io, n, cursor, gcnt);
-  else trace_persistent<ANY, true, (V == 0 ? 2 : V)>(sc, bh, io, n, cursor, gcnt);
+  else trace_persistent<ANY, true, (V == 0 ? 2 : V), STEP>(sc, bh, io, n, cursor, gcnt);
 }

@@ -448,3 +448,80 @@ def test_progress_callback_snapshots_and_stop(api):
     c.set_progress(None)
     assert calls == [8, 16] and cnt2.max() == 16 and st2["paths"] == int(cnt2.sum())
     assert np.array_equal(cnt2, seen[1][4]) and np.array_equal(hdr2, seen[1][3])
+
+
+# ---------------------------------------------------------------- FP32 stepper (RRT_OPT_STEPPER = 1, opt-in)
+def _chord_errors(ref, got, c):
+    end_r = ref[..., 0:3] + ref[..., 3:6] * ref[..., 6:7]; end_g = got[..., 0:3] + got[..., 3:6] * got[..., 6:7]
+    with np.errstate(all="ignore"):
+        perr = np.linalg.norm(end_r - end_g, axis=-1) / np.linalg.norm(end_r - c, axis=-1)
+        derr = np.linalg.norm(ref[..., 3:6] - got[..., 3:6], axis=-1)
+    captured_before = np.cumsum(ref[..., 7] > 0, axis=1) - (ref[..., 7] > 0) > 0
+    return perr, derr, np.isfinite(perr) & np.isfinite(derr) & ~captured_before
+
+
+@pytest.mark.parametrize("tag", ["default", "alt"])
+def test_fp32_stepper_chords_within_tolerance(api, tag):
+    """BASELINE.json: geodesic end points and directions within 1e-4 relative at the same step size.  Against the chords of
+    the reference's own BlackHole::next_micro_ray (golden): directions always (< 1e-5), end points for 99 % of the chords
+    (median ~1e-6); the remainder are far points of escaped rays, see tests/test_plane_recurrence.py."""
+    g = golden("kat_geodesic")
+    c = make_ctx(api, "cbempty_480x360")
+    bh = g["bh_" + tag]
+    c.set_blackhole(bh[:3], bh[3], bh[4], sc.MODE_LITERAL)
+    c.set_option(api.OPT_STEPPER, 1)
+    ref = g["seg_" + tag]
+    got = c.geodesic(g["o"], g["d"], ref.shape[1])
+    perr, derr, ok = _chord_errors(ref, got, bh[:3])
+    assert ok.sum() > 0.5 * ok.size
+    assert np.median(perr[ok]) < 2e-6 and np.percentile(perr[ok], 99) < 1e-4 and perr[ok].max() < 1e-3
+    assert np.median(derr[ok]) < 1e-6 and derr[ok].max() < 1e-5
+    assert np.array_equal((ref[..., 7] > 0)[ok], (got[..., 7] > 0)[ok])          # horizon verdicts
+    c.set_option(api.OPT_STEPPER, 0)
+    assert same(c.geodesic(g["o"], g["d"], ref.shape[1]), ref)                   # and the default is still bit-exact
+
+
+@pytest.mark.parametrize("scene", ["cbspheres_lambertian_480x360", "cbbunny_microfacet_480x360", "cbgems_480x360"])
+@pytest.mark.parametrize("width", [0, 2])
+def test_fp32_stepper_hits_agree_with_reference(api, scene, width):
+    """The reference's own hit records (camera, shadow-style and bounce rays, hole on) through the FP32 stepper: hit / miss
+    and primitive id agree for all but rays that graze an edge (< 0.2 %); where they agree the hit point is within 1e-5
+    (99 %; beyond 1e-4 for < 0.1 %)."""
+    g = golden("kat_trace_" + scene)
+    c = api.Context(0)
+    c.set_option(api.OPT_STEPPER, 1); c.set_option(api.OPT_BVH_WIDTH, width)
+    c.upload_scene(load_scene(scene))
+    rays = g["rays_bh"]; ref = hits_from_probe(g["hit_bh"])
+    got, st = c.trace_rays(rays[:, 0:3], rays[:, 3:6], rays[:, 6], rays[:, 7])
+    hit = got["status"] == 1
+    assert (hit != ref["hit"]).mean() < 2e-3
+    both = hit & ref["hit"]
+    same_prim = got["prim"][both] == ref["prim"][both]
+    assert (~same_prim).mean() < 2e-3
+    d = np.linalg.norm(got["hit_p"][both][same_prim] - ref["hit_p"][both][same_prim], axis=-1)
+    assert np.percentile(d, 99) < 1e-5 and (d > 1e-4).mean() < 1e-3   # the odd ray meets the same primitive on another chord
+    anyh, _ = c.trace_rays(rays[:, 0:3], rays[:, 3:6], rays[:, 6], rays[:, 7], any_hit=True)
+    assert ((anyh["status"] == 1) != ref["any"]).mean() < 2e-3
+    assert st["rays"] == len(rays)
+
+
+@pytest.mark.parametrize("scene", ["cbspheres_lambertian_96x72", "cbspheres_96x72", "cbbunny_microfacet_96x72"])
+def test_fp32_stepper_image_within_one_percent_rmse(api, scene):
+    """BASELINE.json: converged images within 1 % RMSE of mean radiance.  Same seed, same Philox streams, 1024 spp without
+    the adaptive stop: the FP32-stepper image against the bit-exact one (which the golden renders pin to the reference)."""
+    s = load_scene(scene)
+    p = sc.make_params(ns_aa=1024, max_ray_depth=5, ns_area_light=4, seed=11, samples_per_batch=1025)
+    out = []
+    for stepper in (0, 1):
+        c = api.Context(0); c.set_option(api.OPT_STEPPER, stepper); c.upload_scene(s); c.set_frame(96, 72)
+        hdr, cnt, st = c.render(p)
+        out.append((hdr, st))
+        c.close()
+    (a, sa), (b, sb) = out
+    mean = float(a.mean())
+    assert np.sqrt(np.mean((a - b) ** 2)) <= 0.01 * mean
+    assert abs(float(b.mean()) - mean) <= 2e-3 * mean
+    assert abs(sb["rays"] - sa["rays"]) <= 1e-3 * sa["rays"] and abs(sb["geodesic_steps"] - sa["geodesic_steps"]) <= 2e-3 * sa["geodesic_steps"]
+    c = api.Context(0); c.set_option(api.OPT_STEPPER, 1); c.upload_scene(s); c.set_frame(96, 72)
+    hdr2, _, _ = c.render(p)
+    assert np.array_equal(hdr2, b)                                               # the FP32 path is deterministic too
