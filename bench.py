@@ -242,6 +242,7 @@ def main():
     ap.add_argument("--width", type=int, default=0, choices=[0, 2, 4, 8], help="BVH node width (0 = library default: 8 for small scenes, else 2)")
     ap.add_argument("--stepper", default="fp64", choices=["fp64", "fp32"],
                     help="geodesic stepper: fp64 = bit-identical to the reference (default, the headline); fp32 = RRT_OPT_STEPPER 1, within 1e-4")
+    ap.add_argument("--builder", default="host", choices=["host", "device"], help="BVH construction: host (binned SAH, default) or device (RRT_OPT_BVH_BUILDER 1: LBVH)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -274,6 +275,7 @@ def main():
     ctx.set_option(api.OPT_CLEARANCE_GRID, args.grid)
     ctx.set_option(api.OPT_BVH_WIDTH, args.width)
     ctx.set_option(api.OPT_STEPPER, 1 if args.stepper == "fp32" else 0)
+    ctx.set_option(api.OPT_BVH_BUILDER, 1 if args.builder == "device" else 0)
     ctx.upload_scene(s)
     ctx.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
     ctx.set_frame(W, H)
@@ -382,7 +384,7 @@ def main():
         "metric": "Mpaths/s", "value": paths * args.steps / secs / 1e6, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": desc, "frame": [W, H], "spp": spp_job, "ns_area_light": l, "max_ray_depth": m, "samples_per_batch": batch,
-                   "parallelism": "tile%d" % world, "bvh_topology": args.topology, "bvh_leaf": args.leaf, "trace_variant": args.variant, "clearance_grid": args.grid, "bvh_width": args.width, "stepper": args.stepper, "l2": "flushed between timed iterations (256 MiB write)",
+                   "parallelism": "tile%d" % world, "bvh_topology": args.topology, "bvh_leaf": args.leaf, "trace_variant": args.variant, "clearance_grid": args.grid, "bvh_width": args.width, "stepper": args.stepper, "bvh_builder": args.builder, "l2": "flushed between timed iterations (256 MiB write)",
                    "scaling_rule": "frame fixed, spp = %d x n_gpus, 16x16 interleaved tiles, one NCCL reduce per frame" % spp},
         "geodesic_steps_per_s": steps_geo * args.steps / secs, "rays_per_s": rays * args.steps / secs,
         "paths_per_step": paths, "geodesic_steps_per_step": steps_geo, "rays_per_step": rays,

@@ -170,9 +170,13 @@ enum {
   RRT_OPT_CLEARANCE_GRID = 5, /* cells along the longest axis of the empty-space grid (0 = off, the default); next rrt_upload_scene */
   RRT_OPT_BVH_WIDTH = 6,      /* children per node on the device: 2, 4, 8, or 0 (default) = 8 for scenes of <= 128 primitives, else 2; topology 0 and trace kernel 1 always use 2; next rrt_upload_scene */
   RRT_OPT_SHADE_SPLIT = 7,    /* direct lighting: 1 = its own kernel, one thread per light sample; 0 = inside k_shade's per-vertex loop; 2 (default) = 1 when the scene has a microfacet material, else 0 */
-  RRT_OPT_STEPPER = 8         /* geodesic stepper with the hole on: 0 (default) = the reference's recurrence in IEEE double, bit-identical chords;
+  RRT_OPT_STEPPER = 8,        /* geodesic stepper with the hole on: 0 (default) = the reference's recurrence in IEEE double, bit-identical chords;
                                  1 = the same recurrence carried as (orbital frame, u, u') in FP32 registers (BASELINE.json north_star item 3):
                                  chords within ~1e-6 of the reference's (bound asserted: 1e-4), NOT bit-identical; trace kernel 0 only */
+  RRT_OPT_BVH_BUILDER = 9     /* 0 (default) = host build (reference tree shape or binned SAH, threaded); 1 = on the device: the reference's depth-first
+                                 ranks by level-synchronous stable partition + an LBVH for the traversal (scenes of >= 64 primitives, binary nodes;
+                                 falls back to the host build if the tree comes out deeper than the traversal stack); same images, faster upload,
+                                 slower traversal; next rrt_upload_scene */
 };
 
 /* ---- lifecycle ---- */

@@ -11,6 +11,7 @@
 
 #include "rrt_bvh.h"
 #include "rrt_kernels.cuh"
+#include "rrt_bvh_device.cuh"
 
 static thread_local std::string g_create_error;
 
@@ -49,7 +50,7 @@ struct rrt_ctx {
   // device memory
   DevBuf d_env, d_env_pdf, d_env_cond, d_env_marg;
   bool have_env = false;
-  DevBuf d_grid, d_nodes, d_wide, d_leaf, d_nrm, d_kind, d_index, d_pmat, d_sph, d_mats, d_lights;
+  DevBuf d_tripos, d_build, d_grid, d_nodes, d_wide, d_leaf, d_nrm, d_kind, d_index, d_pmat, d_sph, d_mats, d_lights;
   DevBuf d_work, d_px, d_act, d_blk, d_cnt, d_out_rgb, d_out_cnt, d_out_rgbn, d_hook_in, d_hook_out;
   std::vector<cudaEvent_t> events;
   size_t events_used = 0;
@@ -132,7 +133,7 @@ void rrt_destroy(rrt_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->d_env, &ctx->d_env_pdf, &ctx->d_env_cond, &ctx->d_env_marg, &ctx->d_grid, &ctx->d_nodes, &ctx->d_wide, &ctx->d_leaf, &ctx->d_nrm, &ctx->d_kind, &ctx->d_index, &ctx->d_pmat, &ctx->d_sph, &ctx->d_mats, &ctx->d_lights,
+  DevBuf* bufs[] = {&ctx->d_env, &ctx->d_env_pdf, &ctx->d_env_cond, &ctx->d_env_marg, &ctx->d_grid, &ctx->d_nodes, &ctx->d_tripos, &ctx->d_build, &ctx->d_wide, &ctx->d_leaf, &ctx->d_nrm, &ctx->d_kind, &ctx->d_index, &ctx->d_pmat, &ctx->d_sph, &ctx->d_mats, &ctx->d_lights,
                     &ctx->d_work, &ctx->d_px, &ctx->d_act, &ctx->d_blk, &ctx->d_cnt, &ctx->d_out_rgb, &ctx->d_out_cnt, &ctx->d_out_rgbn,
                     &ctx->d_hook_in, &ctx->d_hook_out};
   for (DevBuf* b : bufs) b->release();
@@ -170,6 +171,116 @@ static int flat_depth(const rrt::FlatBvh& b) {
   return depth;
 }
 
+
+/* ---------------------------------------------------------------- device BVH build (RRT_OPT_BVH_BUILDER = 1, rrt_bvh_device.cuh)
+ * Needs d_kind / d_index / d_sph uploaded.  Fills d_nodes and d_leaf on the device and the host-side summary in ctx->bvh
+ * (root box, counts, reference-tree statistics, depth-first ranks for rrt_bvh_info).  *built = false: the tree came out
+ * deeper than the traversal stack (or the scene is tiny) and the caller falls back to the host builder. */
+static int build_bvh_on_device(rrt_ctx* ctx, const rrt_scene* s, bool* built) {
+  using namespace rrtdev;
+  *built = false;
+  const uint32_t n = s->n_prims;
+  if (n < 64) return RRT_OK;
+  cudaStream_t st = ctx->stream;
+  int rc;
+  if ((rc = upload(ctx, ctx->d_tripos, s->tri_pos, 72 * (size_t)s->n_tris))) return rc;
+  /* scratch layout */
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+  const size_t o_plo = take(24 * (size_t)n), o_phi = take(24 * (size_t)n), o_cen = take(24 * (size_t)n);
+  const size_t o_ord[2] = {take(4 * (size_t)n), take(4 * (size_t)n)}, o_ss[2] = {take(4 * (size_t)n), take(4 * (size_t)n)}, o_se[2] = {take(4 * (size_t)n), take(4 * (size_t)n)};
+  const size_t o_isl = take(4 * ((size_t)n + 1)), o_pre = take(4 * ((size_t)n + 1)), o_seg = take(48 * (size_t)n), o_rank = take(4 * (size_t)n);
+  const size_t o_key[2] = {take(8 * (size_t)n), take(8 * (size_t)n)}, o_val[2] = {take(4 * (size_t)n), take(4 * (size_t)n)};
+  const size_t o_child = take(8 * (size_t)n), o_pint = take(4 * (size_t)n), o_pleaf = take(4 * (size_t)n), o_vis = take(4 * (size_t)n), o_dep = take(4 * (size_t)n);
+  const size_t o_lbox = take(24 * (size_t)n), o_nbox = take(24 * (size_t)n), o_flags = take(256);
+  size_t scan_bytes = 0, sort_bytes = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)n + 1, st);
+  cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 63, st);
+  const size_t o_tmp = take(std::max(scan_bytes, sort_bytes) + 256);
+  CK(ctx->d_build.ensure(off));
+  char* base = (char*)ctx->d_build.p;
+  double* plo = (double*)(base + o_plo); double* phi = (double*)(base + o_phi); double* cen = (double*)(base + o_cen);
+  uint32_t* ord[2] = {(uint32_t*)(base + o_ord[0]), (uint32_t*)(base + o_ord[1])};
+  uint32_t* ss[2] = {(uint32_t*)(base + o_ss[0]), (uint32_t*)(base + o_ss[1])};
+  uint32_t* se[2] = {(uint32_t*)(base + o_se[0]), (uint32_t*)(base + o_se[1])};
+  uint32_t* isl = (uint32_t*)(base + o_isl); uint32_t* pre = (uint32_t*)(base + o_pre);
+  unsigned long long* segbox = (unsigned long long*)(base + o_seg);
+  uint32_t* rank = (uint32_t*)(base + o_rank);
+  unsigned long long* key[2] = {(unsigned long long*)(base + o_key[0]), (unsigned long long*)(base + o_key[1])};
+  uint32_t* val[2] = {(uint32_t*)(base + o_val[0]), (uint32_t*)(base + o_val[1])};
+  int* child = (int*)(base + o_child); int* pint = (int*)(base + o_pint); int* pleaf = (int*)(base + o_pleaf); int* vis = (int*)(base + o_vis); int* dep = (int*)(base + o_dep);
+  float* lbox = (float*)(base + o_lbox); float* nbox = (float*)(base + o_nbox);
+  int* flags = (int*)(base + o_flags);   /* [0] any segment left to split, [1] reference nodes, [2] reference leaves */
+  void* tmp = base + o_tmp; size_t tmp_bytes = std::max(scan_bytes, sort_bytes) + 256;
+  const int B = 256; const int G = (int)((n + B - 1) / B), G1 = (int)((n + 1 + B - 1) / B);
+
+  k_prim_bounds<<<G, B, 0, st>>>(n, ctx->d_kind.as<uint8_t>(), ctx->d_index.as<uint32_t>(), ctx->d_tripos.as<double>(), ctx->d_sph.as<double>(), plo, phi, cen);
+  /* 1. the reference's depth-first order */
+  k_ref_init<<<G, B, 0, st>>>(n, ord[0], ss[0], se[0]);
+  CK(cudaMemsetAsync(flags, 0, 256, st));
+  int cur = 0, levels = 0;
+  Box6 sb;
+  int* h_flags = (int*)ctx->h_pinned;
+  for (;; ++levels) {
+    if (levels > 1 << 16) FAIL(RRT_E_ARG, "rrt_upload_scene: device BVH build did not terminate");
+    k_ref_reset<<<G, B, 0, st>>>(n, ss[cur], se[cur], segbox);
+    k_ref_accum<<<G, B, 0, st>>>(n, ord[cur], ss[cur], se[cur], plo, phi, segbox);
+    if (levels == 0) {   /* the root box = the scene box (doubles, exact) */
+      unsigned long long h[6];
+      for (int k = 0; k < 6; ++k) CK(cudaMemcpyAsync(&h[k], segbox + (size_t)k * n, 8, cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+      for (int k = 0; k < 3; ++k) {
+        unsigned long long e0 = h[k], e1 = h[3 + k];
+        unsigned long long b0 = (e0 >> 63) ? (e0 & 0x7fffffffffffffffull) : ~e0, b1 = (e1 >> 63) ? (e1 & 0x7fffffffffffffffull) : ~e1;
+        memcpy(&sb.lo[k], &b0, 8); memcpy(&sb.hi[k], &b1, 8);
+      }
+      if (n <= 4) break;
+    }
+    k_ref_flag<<<G1, B, 0, st>>>(n, ord[cur], ss[cur], se[cur], segbox, cen, isl);
+    size_t tb = tmp_bytes;
+    cub::DeviceScan::ExclusiveSum(tmp, tb, isl, pre, (int)n + 1, st);
+    CK(cudaMemsetAsync(flags, 0, 4, st));
+    k_ref_scatter<<<G, B, 0, st>>>(n, ord[cur], ss[cur], se[cur], isl, pre, ord[cur ^ 1], ss[cur ^ 1], se[cur ^ 1], flags, flags + 1);
+    cur ^= 1;
+    CK(cudaMemcpyAsync(h_flags, flags, 12, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (!h_flags[0]) { ++levels; break; }
+  }
+  k_ref_rank<<<G, B, 0, st>>>(n, ord[cur], rank);
+  /* 2. LBVH */
+  k_morton<<<G, B, 0, st>>>(n, sb, plo, phi, cen, key[0], val[0]);
+  {
+    size_t tb = tmp_bytes;
+    cub::DeviceRadixSort::SortPairs(tmp, tb, key[0], key[1], val[0], val[1], (int)n, 0, 63, st);
+  }
+  CK(cudaMemsetAsync(vis, 0, 4 * (size_t)n, st));
+  k_lbvh_topology<<<G, B, 0, st>>>((int)n, key[1], child, pint, pleaf);
+  k_lbvh_refit<<<G, B, 0, st>>>((int)n, val[1], plo, phi, child, pint, pleaf, lbox, nbox, dep, vis);
+  CK(cudaMemcpyAsync(h_flags + 4, dep, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  CK(cudaGetLastError());
+  const int depth = h_flags[4];
+  if (depth >= RRT_STACK) return RRT_OK;   /* too deep for the shared-memory stack: host builder */
+  CK(ctx->d_nodes.ensure(64 * (size_t)(n - 1)));
+  CK(ctx->d_leaf.ensure(80 * (size_t)n));
+  k_lbvh_emit<<<G, B, 0, st>>>((int)n, child, lbox, nbox, ctx->d_nodes.as<float4>());
+  k_leaf_records<<<G, B, 0, st>>>(n, val[1], ctx->d_kind.as<uint8_t>(), ctx->d_index.as<uint32_t>(), ctx->d_tripos.as<double>(), ctx->d_sph.as<double>(), rank,
+                                  ctx->d_leaf.as<double>());
+  rrt::FlatBvh& b = ctx->bvh;
+  b = rrt::FlatBvh();
+  b.dfs_rank.resize(n);
+  CK(cudaMemcpyAsync(b.dfs_rank.data(), rank, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  CK(cudaGetLastError());
+  b.prim_mat.resize(n);
+  for (uint32_t p = 0; p < n; ++p) b.prim_mat[p] = s->prim_kind[p] == 0 ? s->tri_mat[s->prim_index[p]] : s->sph_mat[s->prim_index[p]];
+  b.root = 0; b.n_nodes = (int)n - 1; b.width = 2; b.device_depth = depth; b.device_built = true;
+  for (int k = 0; k < 3; ++k) { b.root_lo[k] = sb.lo[k]; b.root_hi[k] = sb.hi[k]; }
+  b.ref_nodes = 1 + h_flags[1]; b.ref_leaves = n <= 4 ? 1 : h_flags[2]; b.ref_depth = n <= 4 ? 0 : levels;
+  *built = true;
+  return RRT_OK;
+}
+
 extern "C" {
 int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   if (!ctx || !s) return RRT_E_ARG;
@@ -190,26 +301,32 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
    * triangles: 110.8 vs 116.2 ms; C3 trace time 16.0 vs 18.1 ms).  Measured on B200, DESIGN.md section 4.2. */
   if (width == 0) width = s->n_prims <= 128 ? 8 : 2;
   if (ctx->opt[RRT_OPT_TRACE_KERNEL] == 1 || ctx->opt[RRT_OPT_BVH_TOPOLOGY] == 0) width = 2;   /* A/B variants keep the binary nodes */
-  rrt::build_bvh(s, (int)ctx->opt[RRT_OPT_BVH_TOPOLOGY], (int)ctx->opt[RRT_OPT_LEAF_SIZE], &ctx->bvh, width);
-  if (ctx->bvh.width > 2 && ctx->bvh.width * ctx->bvh.wide_depth + 1 > RRT_STACK + RRT_SPILL) {
-    /* cannot happen below 2^28 primitives with the depth budget of the builder; keep the binary nodes if it ever does */
-    rrt::build_bvh(s, (int)ctx->opt[RRT_OPT_BVH_TOPOLOGY], (int)ctx->opt[RRT_OPT_LEAF_SIZE], &ctx->bvh, 2);
+  int rc;
+  CK(cudaStreamSynchronize(ctx->stream));
+  if ((rc = upload(ctx, ctx->d_kind, s->prim_kind, s->n_prims))) return rc;
+  if ((rc = upload(ctx, ctx->d_index, s->prim_index, 4 * (size_t)s->n_prims))) return rc;
+  if ((rc = upload(ctx, ctx->d_sph, s->sph, 32 * (size_t)s->n_spheres))) return rc;
+  bool on_device = false;
+  if (ctx->opt[RRT_OPT_BVH_BUILDER] == 1 && ctx->opt[RRT_OPT_TRACE_KERNEL] != 1 && (rc = build_bvh_on_device(ctx, s, &on_device))) return rc;
+  if (!on_device) {
+    rrt::build_bvh(s, (int)ctx->opt[RRT_OPT_BVH_TOPOLOGY], (int)ctx->opt[RRT_OPT_LEAF_SIZE], &ctx->bvh, width);
+    if (ctx->bvh.width > 2 && ctx->bvh.width * ctx->bvh.wide_depth + 1 > RRT_STACK + RRT_SPILL) {
+      /* cannot happen below 2^28 primitives with the depth budget of the builder; keep the binary nodes if it ever does */
+      rrt::build_bvh(s, (int)ctx->opt[RRT_OPT_BVH_TOPOLOGY], (int)ctx->opt[RRT_OPT_LEAF_SIZE], &ctx->bvh, 2);
+    }
   }
   rrt::build_clearance_grid(s, (int)ctx->opt[RRT_OPT_CLEARANCE_GRID], &ctx->bvh);
   const rrt::FlatBvh& b = ctx->bvh;
-  const int tree_depth = flat_depth(b);   /* bounds the traversal stack */
-  if (tree_depth >= RRT_STACK) FAIL(RRT_E_ARG, "rrt_upload_scene: BVH deeper than the traversal stack; set RRT_OPT_BVH_TOPOLOGY = 1");
-  CK(cudaStreamSynchronize(ctx->stream));
-  int rc;
-  if ((rc = upload(ctx, ctx->d_nodes, b.nodes.data(), b.nodes.size() * 4))) return rc;
-  if ((rc = upload(ctx, ctx->d_wide, b.wide.data(), b.wide.size() * 4))) return rc;
-  if ((rc = upload(ctx, ctx->d_leaf, b.leaf.data(), b.leaf.size() * 8))) return rc;
+  if (!on_device) {
+    const int tree_depth = flat_depth(b);   /* bounds the traversal stack */
+    if (tree_depth >= RRT_STACK) FAIL(RRT_E_ARG, "rrt_upload_scene: BVH deeper than the traversal stack; set RRT_OPT_BVH_TOPOLOGY = 1");
+    if ((rc = upload(ctx, ctx->d_nodes, b.nodes.data(), b.nodes.size() * 4))) return rc;
+    if ((rc = upload(ctx, ctx->d_wide, b.wide.data(), b.wide.size() * 4))) return rc;
+    if ((rc = upload(ctx, ctx->d_leaf, b.leaf.data(), b.leaf.size() * 8))) return rc;
+  }
   if ((rc = upload(ctx, ctx->d_grid, b.clearance.data(), b.clearance.size() * 4))) return rc;
   if ((rc = upload(ctx, ctx->d_nrm, s->tri_nrm, 72 * (size_t)s->n_tris))) return rc;
-  if ((rc = upload(ctx, ctx->d_kind, s->prim_kind, s->n_prims))) return rc;
-  if ((rc = upload(ctx, ctx->d_index, s->prim_index, 4 * (size_t)s->n_prims))) return rc;
   if ((rc = upload(ctx, ctx->d_pmat, b.prim_mat.data(), 4 * (size_t)s->n_prims))) return rc;
-  if ((rc = upload(ctx, ctx->d_sph, s->sph, 32 * (size_t)s->n_spheres))) return rc;
   if ((rc = upload(ctx, ctx->d_mats, s->mats, sizeof(rrt_material) * (size_t)s->n_mats))) return rc;
   if ((rc = upload(ctx, ctx->d_lights, s->lights, sizeof(rrt_light) * (size_t)s->n_lights))) return rc;
   CK(cudaStreamSynchronize(ctx->stream));

@@ -43,6 +43,8 @@ struct FlatBvh {
   int grid_n[3] = {0, 0, 0};
   double grid_lo[3] = {0, 0, 0}, grid_inv_h[3] = {0, 0, 0};
   int ref_nodes = 0, ref_leaves = 0, ref_depth = 0; // shape of the reference tree (nodes incl. leaves)
+  bool device_built = false;      // built by rrt_bvh_device.cuh: nodes / leaf live only on the device
+  int device_depth = 0;           // its interior levels
 };
 
 static const int32_t kEmptyChild = (int32_t)0x80000000;   // not a valid leaf code: n_prims < 2^28

@@ -525,3 +525,58 @@ def test_fp32_stepper_image_within_one_percent_rmse(api, scene):
     c = api.Context(0); c.set_option(api.OPT_STEPPER, 1); c.upload_scene(s); c.set_frame(96, 72)
     hdr2, _, _ = c.render(p)
     assert np.array_equal(hdr2, b)                                               # the FP32 path is deterministic too
+
+
+# ---------------------------------------------------------------- BVH built on the device (RRT_OPT_BVH_BUILDER = 1, opt-in)
+def _device_built(api, s):
+    c = api.Context(0); c.set_option(api.OPT_BVH_BUILDER, 1); c.upload_scene(s)
+    return c
+
+
+@pytest.mark.parametrize("scene", ["cbbunny_microfacet_480x360", "cbgems_480x360", "synth"])
+def test_device_bvh_build_reproduces_reference_order(api, scene):
+    """construct_bvh's depth-first primitive order (reference src/bvh.cpp:49-96), computed on the device by level-synchronous
+    stable partition, equals the host restatement's — ranks, node / leaf counts and depth, integer for integer."""
+    if scene == "synth":
+        synth = importlib.import_module("relativistic-ray-tracer_b200.synth")
+        s = synth.c5_scene(load_scene("cbspheres_lambertian_96x72"), 96, 97)
+    else:
+        s = load_scene(scene)
+    host = api.bvh_build_host(s, 0)
+    dev = _device_built(api, s).bvh_info()
+    assert np.array_equal(dev["dfs_rank"], host["dfs_rank"])
+    assert sorted(dev["dfs_rank"].tolist()) == list(range(s.n_prims))
+    assert (dev["n_nodes"], dev["n_leaves"], dev["depth"]) == (host["n_nodes"], host["n_leaves"], host["depth"])
+
+
+@pytest.mark.parametrize("scene", ["cbbunny_microfacet_480x360", "cbgems_480x360"])
+@pytest.mark.parametrize("mode", ["flat", "bh"])
+def test_device_bvh_build_hits_match_reference(api, scene, mode):
+    """The LBVH walks to the same hits: the reference's own records, bit for bit, as for the host-built trees."""
+    g = golden("kat_trace_" + scene)
+    c = _device_built(api, load_scene(scene))
+    if mode == "flat":
+        c.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_FLAT)
+    rays = g["rays_" + mode]; ref = hits_from_probe(g["hit_" + mode])
+    got, st = c.trace_rays(rays[:, 0:3], rays[:, 3:6], rays[:, 6], rays[:, 7])
+    assert np.array_equal(got["status"] == 1, ref["hit"])
+    h = ref["hit"]
+    assert np.array_equal(got["prim"][h], ref["prim"][h])
+    assert same(got["hit_p"][h], ref["hit_p"][h]) and same(got["w_out"][h], ref["w_out"][h]) and same(got["n"][h], ref["n"][h])
+    anyh, _ = c.trace_rays(rays[:, 0:3], rays[:, 3:6], rays[:, 6], rays[:, 7], any_hit=True)
+    assert np.array_equal(anyh["status"] == 1, ref["any"])
+
+
+def test_device_bvh_build_renders_the_same_image(api):
+    synth = importlib.import_module("relativistic-ray-tracer_b200.synth")
+    s = synth.c5_scene(load_scene("cbspheres_lambertian_96x72"), 96, 97)
+    p = sc.make_params(ns_aa=4, max_ray_depth=4, ns_area_light=2, seed=2)
+    imgs = []
+    for builder in (0, 1):
+        c = api.Context(0); c.set_option(api.OPT_BVH_BUILDER, builder); c.upload_scene(s); c.set_frame(96, 72)
+        hdr, cnt, st = c.render(p)
+        imgs.append((hdr, cnt, st["rays"], st["geodesic_steps"]))
+    assert np.array_equal(imgs[0][0], imgs[1][0]) and np.array_equal(imgs[0][1], imgs[1][1]) and imgs[0][2:] == imgs[1][2:]
+    small = api.Context(0); small.set_option(api.OPT_BVH_BUILDER, 1); small.upload_scene(load_scene("cbspheres_lambertian_96x72"))   # 14 primitives: host path
+    small.set_frame(96, 72)
+    assert np.isfinite(small.render(p)[0]).all()
