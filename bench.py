@@ -242,7 +242,7 @@ def main():
     ap.add_argument("--width", type=int, default=0, choices=[0, 2, 4, 8], help="BVH node width (0 = library default: 8 for small scenes, else 2)")
     ap.add_argument("--stepper", default="fp64", choices=["fp64", "fp32"],
                     help="geodesic stepper: fp64 = bit-identical to the reference (default, the headline); fp32 = RRT_OPT_STEPPER 1, within 1e-4")
-    ap.add_argument("--builder", default="host", choices=["host", "device"], help="BVH construction: host (binned SAH, default) or device (RRT_OPT_BVH_BUILDER 1: LBVH)")
+    ap.add_argument("--builder", default="auto", choices=["auto", "host", "device"], help="BVH construction (RRT_OPT_BVH_BUILDER): auto = device LBVH for >= 4096 primitives, else host binned SAH")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -275,7 +275,7 @@ def main():
     ctx.set_option(api.OPT_CLEARANCE_GRID, args.grid)
     ctx.set_option(api.OPT_BVH_WIDTH, args.width)
     ctx.set_option(api.OPT_STEPPER, 1 if args.stepper == "fp32" else 0)
-    ctx.set_option(api.OPT_BVH_BUILDER, 1 if args.builder == "device" else 0)
+    ctx.set_option(api.OPT_BVH_BUILDER, {"auto": 0, "device": 1, "host": 2}[args.builder])
     ctx.upload_scene(s)
     ctx.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
     ctx.set_frame(W, H)

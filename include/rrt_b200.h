@@ -173,10 +173,11 @@ enum {
   RRT_OPT_STEPPER = 8,        /* geodesic stepper with the hole on: 0 (default) = the reference's recurrence in IEEE double, bit-identical chords;
                                  1 = the same recurrence carried as (orbital frame, u, u') in FP32 registers (BASELINE.json north_star item 3):
                                  chords within ~1e-6 of the reference's (bound asserted: 1e-4), NOT bit-identical; trace kernel 0 only */
-  RRT_OPT_BVH_BUILDER = 9     /* 0 (default) = host build (reference tree shape or binned SAH, threaded); 1 = on the device: the reference's depth-first
-                                 ranks by level-synchronous stable partition + an LBVH for the traversal (scenes of >= 64 primitives, binary nodes;
-                                 falls back to the host build if the tree comes out deeper than the traversal stack); same images, faster upload,
-                                 slower traversal; next rrt_upload_scene */
+  RRT_OPT_BVH_BUILDER = 9     /* where the BVH is built.  1 = on the device: the reference's depth-first ranks by level-synchronous stable partition
+                                 + an LBVH for the traversal (scenes of >= 64 primitives, binary nodes; falls back to the host if the tree comes
+                                 out deeper than the traversal stack); 2 = on the host (reference tree shape or binned SAH, threaded);
+                                 0 (default) = device for scenes of >= 4096 primitives unless a host-tree option (topology, leaf size, width) is set.
+                                 Same images either way; next rrt_upload_scene */
 };
 
 /* ---- lifecycle ---- */

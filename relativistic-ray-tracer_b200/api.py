@@ -24,7 +24,7 @@ LIB_PATH = os.environ.get("RRT_B200_LIB") or os.path.join(_HERE, "csrc", "librrt
 _LIB = None
 
 OPT_BVH_TOPOLOGY, OPT_COUNTERS, OPT_WORK_BYTES, OPT_TRACE_KERNEL, OPT_LEAF_SIZE, OPT_CLEARANCE_GRID, OPT_BVH_WIDTH, OPT_SHADE_SPLIT = 0, 1, 2, 3, 4, 5, 6, 7
-OPT_BVH_BUILDER = 9  # 0 = host build (default), 1 = device build (reference ranks + LBVH)
+OPT_BVH_BUILDER = 9  # 0 = auto (device for >= 4096 primitives), 1 = device (reference ranks + LBVH), 2 = host
 OPT_STEPPER = 8   # 0 = FP64 bit-exact stepper (default), 1 = FP32 state-carrying stepper (include/rrt_b200.h)
 
 EXPORTS = ["rrt_abi_version", "rrt_device_count", "rrt_create", "rrt_destroy", "rrt_last_error", "rrt_set_option", "rrt_upload_scene",

@@ -307,7 +307,13 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   if ((rc = upload(ctx, ctx->d_index, s->prim_index, 4 * (size_t)s->n_prims))) return rc;
   if ((rc = upload(ctx, ctx->d_sph, s->sph, 32 * (size_t)s->n_spheres))) return rc;
   bool on_device = false;
-  if (ctx->opt[RRT_OPT_BVH_BUILDER] == 1 && ctx->opt[RRT_OPT_TRACE_KERNEL] != 1 && (rc = build_bvh_on_device(ctx, s, &on_device))) return rc;
+  /* 0 = auto: on the device for scenes of >= 4096 primitives when no host-tree option (shape, leaf size, node width, A/B kernel)
+   * is set: measured on B200, the LBVH is walked 0.5-3 % slower than the host's binned-SAH tree and is ready ~100x sooner
+   * (C5, 1 M triangles: e2e 32.9 -> 339.7 Mpaths/s at 4 spp); 1 = device whenever possible; 2 = host */
+  const int64_t builder = ctx->opt[RRT_OPT_BVH_BUILDER];
+  const bool host_opts = ctx->opt[RRT_OPT_BVH_TOPOLOGY] != 1 || ctx->opt[RRT_OPT_LEAF_SIZE] != 2 || ctx->opt[RRT_OPT_BVH_WIDTH] != 0;
+  const bool want_device = ctx->opt[RRT_OPT_TRACE_KERNEL] != 1 && (builder == 1 || (builder == 0 && !host_opts && s->n_prims >= 4096));
+  if (want_device && (rc = build_bvh_on_device(ctx, s, &on_device))) return rc;
   if (!on_device) {
     rrt::build_bvh(s, (int)ctx->opt[RRT_OPT_BVH_TOPOLOGY], (int)ctx->opt[RRT_OPT_LEAF_SIZE], &ctx->bvh, width);
     if (ctx->bvh.width > 2 && ctx->bvh.width * ctx->bvh.wide_depth + 1 > RRT_STACK + RRT_SPILL) {

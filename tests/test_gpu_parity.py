@@ -572,7 +572,7 @@ def test_device_bvh_build_renders_the_same_image(api):
     s = synth.c5_scene(load_scene("cbspheres_lambertian_96x72"), 96, 97)
     p = sc.make_params(ns_aa=4, max_ray_depth=4, ns_area_light=2, seed=2)
     imgs = []
-    for builder in (0, 1):
+    for builder in (2, 1):
         c = api.Context(0); c.set_option(api.OPT_BVH_BUILDER, builder); c.upload_scene(s); c.set_frame(96, 72)
         hdr, cnt, st = c.render(p)
         imgs.append((hdr, cnt, st["rays"], st["geodesic_steps"]))
