@@ -21,6 +21,10 @@
 #ifndef RRT_COOP_LEAVES
 #define RRT_COOP_LEAVES 0   /* 1 = any-hit leaf tests deferred and shared across the warp (rrt_trace.cuh coop_*): measured SLOWER, C2 41.4 vs 37.1 ms */
 #endif
+#ifndef RRT_MINB_FP32
+#define RRT_MINB_FP32 5   /* resident blocks per SM for the FP32-stepper variants (STEP = 1): 4 / 5 / 6 / 7 / 8 measured, see DESIGN.md 6.2 */
+#endif
+#define RRT_MINBLOCKS(V, STEP) ((STEP) == 1 ? RRT_MINB_FP32 : (V) >= 4 ? RRT_MINB_WIDE : RRT_MINB)
 #ifndef RRT_MINB_WIDE
 #define RRT_MINB_WIDE 6   /* the same for the wide-node variants */
 #endif
@@ -350,7 +354,7 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
 
 /* extension rays: closest hit */
 template <bool COUNT, int V, int STEP = 0>
-__global__ void __launch_bounds__(RRT_BLOCK, (V >= 4 ? RRT_MINB_WIDE : RRT_MINB)) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINBLOCKS(V, STEP)) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                 const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
                                                                 int* cursor, int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt) {
   ClosestIO io; io.ray = ray; io.cap = cap; io.h_prim = h_prim; io.h_geo = h_geo;
@@ -360,7 +364,7 @@ __global__ void __launch_bounds__(RRT_BLOCK, (V >= 4 ? RRT_MINB_WIDE : RRT_MINB)
 
 /* shadow rays: BVHAccel::intersect(ray) (any hit), or closest hit when the hemisphere estimator needs the emitter */
 template <bool ANY, bool COUNT, int V, int STEP = 0>
-__global__ void __launch_bounds__(RRT_BLOCK, (V >= 4 ? RRT_MINB_WIDE : RRT_MINB)) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINBLOCKS(V, STEP)) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
                                                                int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt) {
   ShadowIO io; io.ray = ray; io.cap = cap; io.cidx = cidx; io.res = res;
@@ -370,7 +374,7 @@ __global__ void __launch_bounds__(RRT_BLOCK, (V >= 4 ? RRT_MINB_WIDE : RRT_MINB)
 
 /* parity hook: the same loop on caller-supplied rays */
 template <bool ANY, int V, int STEP = 0>
-__global__ void __launch_bounds__(RRT_BLOCK, (V >= 4 ? RRT_MINB_WIDE : RRT_MINB)) k_hook_trace(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, int n,
+__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINBLOCKS(V, STEP)) k_hook_trace(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, int n,
                                                             const double* __restrict__ o, const double* __restrict__ d, const double* __restrict__ tmin,
                                                             const double* __restrict__ tmax, rrt_hit* __restrict__ out, int* cursor, Counters* gcnt) {
   HookIO<ANY> io; io.o = o; io.d = d; io.tmin = tmin; io.tmax = tmax; io.out = out;
