@@ -38,6 +38,8 @@ static void usage(const char* binary) {
   printf("  -F               Flat spacetime (no hole)      -S <INT> RNG seed      -G <INT> CUDA device\n");
   printf("  --progress <PREFIX> [--progress-every <INT>]  write <PREFIX>_<samples>.png after every n-th adaptive batch\n");
   printf("  --thin-lens      sample the lens (-b, -d) for every camera ray\n");
+  printf("  --stepper <fp64|fp32>   geodesic stepper: fp64 = bit-identical to the reference (default), fp32 = within 1e-4, faster\n");
+  printf("  --bvh-builder <auto|host|device>   where the BVH is built (default auto: device for >= 4096 primitives)\n");
   printf("  --dump-scene <FILE>  write the flattened scene and exit (no GPU needed)\n");
   printf("  -h               Print this help message\n\n");
 }
@@ -51,7 +53,7 @@ int main(int argc, char** argv) {
   std::string filename, cam_settings, dump_scene, dump_camera, scene_path, envmap_path;
   Vector3D bh_c(0, 1, 0); double bh_r = 0.1, bh_dtheta = 0.1;
   unsigned long long seed = 0; int device = 0;
-  std::string progress_prefix; int progress_every = 1; bool thin_lens = false;
+  std::string progress_prefix; int progress_every = 1; bool thin_lens = false; bool stepper_fp32 = false; int bvh_builder = 0;
 
   auto need = [&](int i, int k) { if (i + k >= argc) { usage(argv[0]); exit(1); } };
   for (int i = 1; i < argc; ++i) {
@@ -79,6 +81,8 @@ int main(int argc, char** argv) {
     else if (a == "--progress") { need(i, 1); progress_prefix = argv[++i]; }
     else if (a == "--progress-every") { need(i, 1); progress_every = atoi(argv[++i]); }
     else if (a == "--thin-lens") thin_lens = true;
+    else if (a == "--stepper") { need(i, 1); std::string v = argv[++i]; if (v != "fp64" && v != "fp32") { usage(argv[0]); return 1; } stepper_fp32 = v == "fp32"; }
+    else if (a == "--bvh-builder") { need(i, 1); std::string v = argv[++i]; bvh_builder = v == "device" ? 1 : v == "host" ? 2 : v == "auto" ? 0 : -1; if (bvh_builder < 0) { usage(argv[0]); return 1; } }
     else if (a == "--dump-scene") { need(i, 1); dump_scene = argv[++i]; }
     else if (a == "--dump-camera") { need(i, 1); dump_camera = argv[++i]; }
     else if (a == "--write-test-png") {   // host self-check used by tests/test_host_cpp.py: a 5x3 gradient through write_png
@@ -129,6 +133,7 @@ int main(int argc, char** argv) {
   PathTracer pt(ns_aa, max_ray_depth, ns_area_light, 1, 1, 1, num_threads, samples_per_batch, max_tolerance, nullptr, hemisphere,
                 scene_file, lens_radius, focal_distance);
   pt.set_device(device); pt.set_seed(seed); pt.set_blackhole(bh_c, bh_r, bh_dtheta, flat);
+  pt.set_option(RRT_OPT_STEPPER, stepper_fp32 ? 1 : 0); pt.set_option(RRT_OPT_BVH_BUILDER, bvh_builder);
   if (!envmap_path.empty()) {
     int ew = 0, eh = 0; std::vector<float> env;
     if (!load_envmap(envmap_path, &ew, &eh, &env, &err)) { fprintf(stderr, "[PathTracer] Error loading environment map: %s\n", err.c_str()); return 1; }

@@ -97,6 +97,7 @@ bool PathTracer::has_valid_configuration() const { return have_scene_ && camera_
 void PathTracer::set_scene(const FlatScene* scene) {
   if (state_ != INIT) return;
   if (!ctx_ && rrt_create(&ctx_, device_) != RRT_OK) { error_ = rrt_last_error(nullptr); ctx_ = nullptr; return; }
+  for (const auto& o : options_) if (rrt_set_option(ctx_, o.first, o.second) != RRT_OK) { error_ = rrt_last_error(ctx_); return; }
   fprintf(stdout, "[PathTracer] Collecting primitives... Done! (%.4f sec)\n", 0.0);
   fprintf(stdout, "[PathTracer] Building BVH from %lu primitives... ", (unsigned long)scene->n_prims()); fflush(stdout);
   struct timespec t0, t1; clock_gettime(CLOCK_MONOTONIC, &t0);

@@ -18,6 +18,7 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <utility>
 #include <vector>
 
 #include "../include/rrt_b200.h"
@@ -143,6 +144,8 @@ class PathTracer {
   // handed over before set_scene.  rgb: [height][width][3], row 0 = top.
   void set_envmap(int width, int height, const float* rgb);
   void set_seed(uint64_t seed) { seed_ = seed; }
+  // rrt_set_option pass-through (RRT_OPT_*: stepper, BVH builder, A/B variants); applied before the next set_scene
+  void set_option(int option, int64_t value) { options_.push_back({option, value}); }
   void set_device(int device) { device_ = device; }
   void set_tile_shard(int tile, int rank, int world) { tile_ = tile; rank_ = rank; world_ = world; }
   void start_raytracing();                   // asynchronous: returns at once, state becomes DONE when the frame is ready
@@ -185,6 +188,7 @@ class PathTracer {
   std::string filename_;
   double lensRadius_, focalDistance_;
   uint64_t seed_ = 0;
+  std::vector<std::pair<int, int64_t>> options_;
   Vector3D bh_centre_ = Vector3D(0, 1, 0);
   double bh_r_ = 0.1, bh_dtheta_ = 0.1;
   bool bh_flat_ = false;

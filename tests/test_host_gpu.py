@@ -131,3 +131,23 @@ def test_cli_progress_snapshots_and_thin_lens(exe, tmp_path):
     for f, h in zip(snaps, shots):
         assert np.array_equal(read_png(str(tmp_path / f)), png_of(h))
     assert not np.array_equal(read_png(str(tmp_path / snaps[-1])), read_png(out))
+
+
+def test_cli_stepper_and_bvh_builder_flags(exe, tmp_path):
+    """--stepper fp32 equals the binding with RRT_OPT_STEPPER = 1; --bvh-builder host / device write byte-identical PNGs."""
+    api = importlib.import_module("relativistic-ray-tracer_b200.api")
+    s = load_scene("cbbunny_microfacet_96x72")
+    src = str(tmp_path / "s.rrtscene")
+    s.save(src)
+    outs = {}
+    for name, flags in (("fp32", ["--stepper", "fp32"]), ("host", ["--bvh-builder", "host"]), ("device", ["--bvh-builder", "device"]), ("auto", [])):
+        outs[name] = str(tmp_path / (name + ".png"))
+        r = subprocess.run([exe, "-s", "4", "-l", "2", "-m", "3", "-S", "5", "-f", outs[name]] + flags + [src], capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
+    assert np.array_equal(read_png(outs["host"]), read_png(outs["device"])) and np.array_equal(read_png(outs["host"]), read_png(outs["auto"]))
+    c = api.Context(0); c.set_option(api.OPT_STEPPER, 1); c.upload_scene(s); c.set_frame(96, 72)
+    hdr, _, _ = c.render(sc.make_params(ns_aa=4, max_ray_depth=3, ns_area_light=2, seed=5))
+    w = np.ascontiguousarray(c.tonemap(hdr).reshape(72, 96)[::-1]).view(np.uint8).reshape(72, 96, 4).copy(); w[..., 3] = 255
+    assert np.array_equal(read_png(outs["fp32"]), w)
+    r = subprocess.run([exe, "--stepper", "fp16", src], capture_output=True, text=True)
+    assert r.returncode != 0
