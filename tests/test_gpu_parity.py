@@ -580,3 +580,64 @@ def test_device_bvh_build_renders_the_same_image(api):
     small = api.Context(0); small.set_option(api.OPT_BVH_BUILDER, 1); small.upload_scene(load_scene("cbspheres_lambertian_96x72"))   # 14 primitives: host path
     small.set_frame(96, 72)
     assert np.isfinite(small.render(p)[0]).all()
+
+
+def _soup_scene(base, tri_pos, spheres=None):
+    """walls of `base` + a triangle soup (flat normals) [+ spheres]"""
+    tri_pos = np.asarray(tri_pos, np.float64).reshape(-1, 9)
+    n = np.cross(tri_pos[:, 3:6] - tri_pos[:, 0:3], tri_pos[:, 6:9] - tri_pos[:, 0:3])
+    ln = np.linalg.norm(n, axis=1, keepdims=True); ln[ln == 0] = 1.0
+    nrm = np.tile(n / ln, 3)
+    nb, ns = base.tri_pos.shape[0], 0 if spheres is None else len(spheres)
+    nt = nb + len(tri_pos)
+    kind = np.concatenate([np.zeros(nt, np.uint8), np.ones(ns, np.uint8)])
+    index = np.concatenate([np.arange(nt, dtype=np.uint32), np.arange(ns, dtype=np.uint32)])
+    return sc.SceneData(kind, index, np.concatenate([base.tri_pos, tri_pos]), np.concatenate([base.tri_nrm, nrm]),
+                        np.concatenate([base.tri_mat, np.zeros(len(tri_pos), np.int32)]),
+                        np.zeros((0, 4)) if spheres is None else np.asarray(spheres, np.float64), np.zeros(ns, np.int32), base.mats, base.lights, base.camera)
+
+
+@pytest.mark.parametrize("case", ["identical", "coplanar_grid", "clustered_with_spheres", "just_above_threshold", "nested_deep"])
+def test_device_bvh_build_degenerate_inputs(api, case):
+    """Inputs that push the builder's corner cases — every centroid equal (index halving at every level of the reference
+    tree, Morton keys distinguished by the primitive id alone), thousands of coplanar triangles, two tight clusters far
+    apart plus spheres, 64 primitives — give the host's ranks and the host-built tree's hits, bit for bit."""
+    base = load_scene("cbspheres_lambertian_96x72")
+    rng = np.random.default_rng(7)
+    spheres = None
+    if case == "identical":
+        tri = np.tile(np.array([[-0.2, 0.3, 0.0, 0.2, 0.3, 0.0, 0.0, 0.6, 0.1]]), (5000, 1))
+    elif case == "coplanar_grid":
+        g = np.stack(np.meshgrid(np.arange(70), np.arange(70)), -1).reshape(-1, 2) / 70.0 - 0.5
+        a = np.concatenate([g, np.full((len(g), 1), 0.0)], 1)[:, [0, 2, 1]] + [0, 0.4, 0]
+        tri = np.concatenate([a, a + [1 / 70.0, 0, 0], a + [0, 0, 1 / 70.0]], 1)
+    elif case == "clustered_with_spheres":
+        c = np.concatenate([rng.normal([-0.6, 0.3, -0.5], 1e-3, (3000, 3)), rng.normal([0.6, 1.2, 0.5], 1e-3, (3000, 3))])
+        tri = np.concatenate([c, c + rng.normal(0, 2e-3, c.shape), c + rng.normal(0, 2e-3, c.shape)], 1)
+        spheres = np.concatenate([rng.uniform([-0.8, 0.1, -0.8], [0.8, 1.3, 0.8], (40, 3)), rng.uniform(0.01, 0.05, (40, 1))], 1)
+    elif case == "nested_deep":
+        # clusters nested toward one corner of the scene box, then 6000 identical triangles in the innermost Morton cell: an LBVH of
+        # ~30 + 13 levels, deeper than the 40-entry traversal stack => the builder must hand the scene to the host path
+        corner = np.array([-0.999, 0.001, -0.999])
+        c = np.concatenate([corner + 1.9 * 2.0 ** -k * np.ones((1, 3)) for k in range(1, 31)] + [np.tile(corner + 1e-9, (6000, 1))])
+        tri = np.concatenate([c, c + [1e-4, 0, 0], c + [0, 1e-4, 0]], 1)
+    else:
+        c = rng.uniform([-0.8, 0.1, -0.8], [0.8, 1.3, 0.8], (64 - base.tri_pos.shape[0], 3))
+        tri = np.concatenate([c, c + rng.normal(0, 0.05, c.shape), c + rng.normal(0, 0.05, c.shape)], 1)
+    s = _soup_scene(base, tri, spheres)
+    host = api.bvh_build_host(s, 0)
+    dev = api.Context(0); dev.set_option(api.OPT_BVH_BUILDER, 1); dev.upload_scene(s)
+    ref = api.Context(0); ref.set_option(api.OPT_BVH_BUILDER, 2); ref.upload_scene(s)
+    info = dev.bvh_info()
+    assert np.array_equal(info["dfs_rank"], host["dfs_rank"])
+    assert (info["n_nodes"], info["n_leaves"], info["depth"]) == (host["n_nodes"], host["n_leaves"], host["depth"])
+    ro, rd = dev.generate_rays(rng.uniform(0, 1, (20000, 2)))
+    for mode in (sc.MODE_LITERAL, sc.MODE_FLAT):
+        dev.set_blackhole((0, 1, 0), 0.1, 0.1, mode); ref.set_blackhole((0, 1, 0), 0.1, 0.1, mode)
+        a, _ = dev.trace_rays(ro, rd); b, _ = ref.trace_rays(ro, rd)
+        for f in ("status", "prim", "chord", "steps"):
+            assert np.array_equal(a[f], b[f]), (case, f)
+        assert same(a["t"], b["t"]) and same(a["hit_p"], b["hit_p"]) and same(a["n"], b["n"])
+        aa, _ = dev.trace_rays(ro, rd, any_hit=True); bb, _ = ref.trace_rays(ro, rd, any_hit=True)
+        assert np.array_equal(aa["status"], bb["status"])
+    assert case == "nested_deep" or (a["prim"] >= base.tri_pos.shape[0]).sum() > 50          # the soup is actually hit
