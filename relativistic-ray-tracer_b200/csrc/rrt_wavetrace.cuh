@@ -353,8 +353,14 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
 }
 
 /* extension rays: closest hit */
+#ifdef RRT_MINB_CLOSEST_N      /* A/B: resident blocks for the closest-hit kernel alone */
+#define RRT_MINB_CLOSEST(V, STEP) RRT_MINB_CLOSEST_N
+#else   /* wide closest-hit kernel: 5 blocks at 96 registers (fewer spills around Best / fill_geo): C2 37.08 -> 36.51 ms, C1 4.47 -> 4.42;
+           the binary one stays at 6 (5: bunny 1080p 103.8 -> 104.8, C5 68.6 -> 70.4) */
+#define RRT_MINB_CLOSEST(V, STEP) (((V) >= 4 && (STEP) == 0) ? 5 : RRT_MINBLOCKS(V, STEP))
+#endif
 template <bool COUNT, int V, int STEP = 0>
-__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINBLOCKS(V, STEP)) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
+__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB_CLOSEST(V, STEP)) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                 const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
                                                                 int* cursor, int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt) {
   ClosestIO io; io.ray = ray; io.cap = cap; io.h_prim = h_prim; io.h_geo = h_geo;
