@@ -164,11 +164,22 @@ def run_reference_binary(wl, spp, threads):
     fixture, dae, W, H, _, l, m, mode, _ = WORKLOADS[wl]
     exe = os.path.join(ROOT, "oracle", "_ref", "ref_bh" if mode == "bh" else "ref_flat")
     scene = os.path.join(ROOT, "oracle", "_ref", "dae", dae or "-")
-    if dae is None or not (os.path.exists(exe) and os.path.exists(scene)):
+    template = os.path.join(ROOT, "oracle", "_ref", "dae", "CBspheres_lambertian.dae")
+    synthetic = fixture == "synth:c5" and os.path.exists(template)
+    if not os.path.exists(exe) or not (synthetic or (dae is not None and os.path.exists(scene))):
         return None
     with tempfile.TemporaryDirectory() as td:
         out = os.path.join(td, "o.png")
-        cmd = [exe, "-t", str(threads), "-s", str(spp), "-l", str(l), "-m", str(m), "-r", str(W), str(H), "-f", out, scene]
+        cell = []
+        if synthetic:
+            # the procedural scene as a COLLADA file the reference's own loader reads (synth.write_c5_dae: vertices as float32),
+            # and a bounded sample: the centre cell of the frame, 1/16 of its area (it holds the mesh: heavier than the average pixel)
+            synth = importlib.import_module("relativistic-ray-tracer_b200.synth")
+            scene = os.path.join(td, "c5.dae")
+            synth.write_c5_dae(scene, open(template).read())
+            cw, ch = W // 4, H // 4
+            cell = ["-p", str((W - cw) // 2), str((H - ch) // 2), str(cw), str(ch)]
+        cmd = [exe, "-t", str(threads), "-s", str(spp), "-l", str(l), "-m", str(m), "-r", str(W), str(H)] + cell + ["-f", out, scene]
         t0 = time.perf_counter()
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         wall = time.perf_counter() - t0
@@ -176,7 +187,8 @@ def run_reference_binary(wl, spp, threads):
     ms = re.findall(r"100%! \(([0-9.]+)s\)", txt)          # reference src/pathtracer.cpp:636
     rays = re.findall(r"BVH traced (\d+) rays", txt)       # reference src/pathtracer.cpp:637
     secs = float(ms[-1]) if ms else wall
-    return W * H * spp, secs, int(rays[-1]) if rays else 0
+    npx = (W // 4) * (H // 4) if synthetic else W * H
+    return npx * spp, secs, int(rays[-1]) if rays else 0
 
 
 def run_oracle_port(wl, spp):
@@ -197,8 +209,9 @@ def cpu_sample(wl, spp=1):
     res = run_reference_binary(wl, spp, cores)
     if res is not None:
         paths, secs, rays = res
+        what = "centre cell (1/16 of the frame) of the same scene exported as .dae," if WORKLOADS[wl][0] == "synth:c5" else "same frame"
         return {"value": paths / secs / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "reference",
-                "sample": "reference binary (oracle/_ref) -t %d, same frame at -s %d: %d paths in %.2f s, %d rays" % (cores, spp, paths, secs, rays)}
+                "sample": "reference binary (oracle/_ref) -t %d, %s at -s %d: %d paths in %.2f s, %d rays" % (cores, what, spp, paths, secs, rays)}
     paths, secs, rays = run_oracle_port(wl, spp)
     return {"value": paths / secs / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
             "sample": "oracle port (OpenMP, %d threads), same frame at %d spp: %d paths in %.2f s, %d rays" % (cores, spp, paths, secs, rays)}
@@ -399,7 +412,7 @@ def main():
                      "scene_bytes": scene_bytes,
                      "note": ("BVH nodes + leaf records = %.1f MB: %s" % (scene_bytes / 1e6,
                               "L1/L2 resident, the kernel is instruction-issue bound (FP64 + FP32 pipes), the fraction counts cache-served bytes; see DESIGN.md section 6"
-                              if scene_bytes < 100e6 else "exceeds the 126 MB L2 together with the ray queues; DRAM-served"))},
+                              if scene_bytes < 100e6 else "close to the 126 MB L2, yet served by it (ncu, profiles/traffic.json: L2 hit rate 95 %, 0.35 GB of DRAM traffic in the longest launch); the kernel is issue- / FP64-bound, see DESIGN.md section 6"))},
         "clocks": clk,
     }
     if steps_geo > rays and args.stepper == "fp64":   # hole on: the geodesic step is FP64 and its pipe, not HBM, is what the trace kernel runs against

@@ -87,3 +87,46 @@ def c5_scene(base, n_u=708, n_v=709, seed=184):
     """about one million triangles (nodes + FP64 leaf records > the 126 MB L2)"""
     v, f = displaced_sphere(n_u, n_v, seed=seed)
     return cornell_box_with_mesh(base, v, f)
+
+
+# ---------------------------------------------------------------- COLLADA export (SURVEY.md 8d: "written as a .dae so both sides load the same file")
+def _fmt(a):
+    return " ".join(repr(float(x)) for x in np.asarray(a).ravel())
+
+
+def write_cornell_dae(path, template_text, verts, faces, to_file_axes=None):
+    """Writes a COLLADA file the reference's loader (src/collada/collada.cpp) and host/dae_loader.cpp both accept: the Cornell
+    box of `template_text` (the text of CBspheres_lambertian.dae) with its two spheres replaced by one triangle mesh bound to
+    the `lambertian` material.  Vertex positions are written as float32 (the loaders parse floats), so the scene that comes
+    back is `verts.astype(float32)`, not `verts`.  `to_file_axes(v)` maps world positions to what must stand in the file so
+    that the loaders' node transform + up-axis handling return them (default: the Z_UP convention of the bundled scenes)."""
+    import re
+    v = np.asarray(verts, np.float64)
+    if to_file_axes is None:
+        to_file_axes = lambda w: np.stack([-w[:, 0], w[:, 2], w[:, 1]], axis=1)      # Z_UP file as the loaders read it: world = (-x, z, y)_file
+    vf = to_file_axes(v).astype(np.float32)
+    f = np.asarray(faces, np.int64)
+    t = re.sub(r'\s*<node id="Sphere[12]".*?</node>', "", template_text, flags=re.S)
+    geo = ('    <geometry id="bump-mesh" name="bump">\n      <mesh>\n        <source id="bump-mesh-positions">\n'
+           '          <float_array id="bump-mesh-positions-array" count="%d">%s</float_array>\n'
+           '          <technique_common>\n            <accessor source="#bump-mesh-positions-array" count="%d" stride="3">\n'
+           '              <param name="X" type="float"/>\n              <param name="Y" type="float"/>\n              <param name="Z" type="float"/>\n'
+           '            </accessor>\n          </technique_common>\n        </source>\n'
+           '        <vertices id="bump-mesh-vertices">\n          <input semantic="POSITION" source="#bump-mesh-positions"/>\n        </vertices>\n'
+           '        <polylist material="lambertian" count="%d">\n          <input semantic="VERTEX" source="#bump-mesh-vertices" offset="0"/>\n'
+           '          <vcount>%s</vcount>\n          <p>%s</p>\n        </polylist>\n      </mesh>\n    </geometry>\n'
+           % (vf.size, " ".join(repr(float(x)) for x in vf.ravel()), len(vf), len(f), "3 " * len(f), " ".join(str(int(i)) for i in f.ravel())))
+    node = ('      <node id="bump" name="bump" type="NODE">\n        <matrix sid="transform">1 0 0 0 0 1 0 0 0 0 1 0 0 0 0 1</matrix>\n'
+            '        <instance_geometry url="#bump-mesh">\n          <bind_material>\n            <technique_common>\n'
+            '              <instance_material symbol="lambertian" target="#lambertian"/>\n            </technique_common>\n'
+            '          </bind_material>\n        </instance_geometry>\n      </node>\n')
+    t = t.replace("  </library_geometries>", geo + "  </library_geometries>", 1)
+    t = t.replace("    </visual_scene>", node + "    </visual_scene>", 1)
+    with open(path, "w") as fh:
+        fh.write(t)
+    return vf
+
+
+def write_c5_dae(path, template_text, n_u=708, n_v=709, seed=184):
+    v, f = displaced_sphere(n_u, n_v, seed=seed)
+    return write_cornell_dae(path, template_text, v, f), f

@@ -63,7 +63,18 @@ SCENES = {  # name -> (dae, W, H, screenDist scale)
     "cbgems_96x72": ("CBgems.dae", 96, 72, 0.2),
     "cbempty_96x72": ("CBempty.dae", 96, 72, 0.2),
     "cbbunny_microfacet_96x72": ("CBbunny_microfacet_cu.dae", 96, 72, 0.2),
+    # C5's generator at 4,608 triangles, exported as COLLADA (synth.write_c5_dae) and loaded by the reference's own loader
+    "cbsynth_480x360": ("_generated_CBsynth_mesh.dae", 480, 360, None),
+    "cbsynth_96x72": ("_generated_CBsynth_mesh.dae", 96, 72, 0.2),
 }
+SYNTH_MESH = (48, 49)   # n_u, n_v of the exported mesh
+
+
+def ensure_generated_dae():
+    sys.path.insert(0, ROOT)
+    import importlib
+    synth = importlib.import_module("relativistic-ray-tracer_b200.synth")
+    synth.write_c5_dae(os.path.join(DAE, "_generated_CBsynth_mesh.dae"), open(os.path.join(DAE, "CBspheres_lambertian.dae")).read(), *SYNTH_MESH)
 
 
 def scene_env(name):
@@ -71,11 +82,14 @@ def scene_env(name):
     return {"RRT_PROBE_SCREENDIST_SCALE": str(k)} if k else {}
 
 
-def make_scenes():
+def make_scenes(only=None):
     sys.path.insert(0, ROOT)
     import importlib
     sc = importlib.import_module("relativistic-ray-tracer_b200.scene")
+    ensure_generated_dae()
     for name, (dae, w, h, _) in SCENES.items():
+        if only and name not in only:
+            continue
         out = tmpf(name + ".rrtscene")
         probe("bh", "scene", os.path.join(DAE, dae), w, h, out, env=scene_env(name))
         s = sc.SceneData.load(out)
@@ -304,10 +318,14 @@ RENDERS = {  # name -> (scene, mode, spp, l, m, batch, tol, seed, extra args)
     # thin lens (-b / -d): raytrace_pixel(x, y, useThinLens = true), which the reference's THIN_LENS switch compiles out of its tile loop
     "flat_thin_lens": ("cbspheres_lambertian_96x72", "flat", 8, 2, 4, 32, 0.05, 21, ["lens"]),
     "bh_thin_lens": ("cbspheres_lambertian_96x72", "bh", 4, 1, 3, 32, 0.05, 22, ["lens"]),
+    # the procedural mesh (C5's generator), through the reference's loader and raytrace_pixel
+    "flat_synth_mesh": ("cbsynth_96x72", "flat", 8, 2, 4, 32, 0.05, 23, []),
+    "bh_synth_mesh": ("cbsynth_96x72", "bh", 4, 2, 4, 32, 0.05, 24, []),
 }
 
 
 def make_render(only=None):
+    ensure_generated_dae()
     for name, (scene, mode, spp, l, m, batch, tol, seed, extra) in RENDERS.items():
         if only and name not in only:
             continue
@@ -331,7 +349,7 @@ def make_render(only=None):
 if __name__ == "__main__":
     what = sys.argv[1:] or ["scenes", "kat", "render"]
     if "scenes" in what:
-        make_scenes()
+        make_scenes([w for w in what if w in SCENES] or None)
     if "kat" in what:
         make_kat([w for w in what if w == "thin_lens"])
     if "render" in what:

@@ -186,3 +186,38 @@ def test_environment_map_readers(exe, tmp_path):
     open(tmp_path / "z.exr", "wb").write(raw)
     r = subprocess.run([exe, "--dump-envmap", str(tmp_path / "z.exr"), str(tmp_path / "x")], capture_output=True, text=True)
     assert r.returncode == 2 and "compression" in r.stderr
+
+
+def test_procedural_scene_as_collada_loads_like_the_reference(exe, tmp_path):
+    """synth.write_c5_dae (C5 "written as a .dae so both sides load the same file"), at 18 k triangles: the C++ loader
+    returns the intended geometry — float32 vertices, the reference's (c, a, b) vertex order — and, where the reference's own
+    loader is present (oracle/_ref/ref_probe), the same positions, area-weighted vertex normals, materials, light and camera
+    bit for bit.  (At the full 1,002,540 triangles: equal as well; 3.9 s here against the reference loader's 10.9 s.)"""
+    template = os.path.join(DAE, "CBspheres_lambertian.dae")
+    if not os.path.exists(template):
+        pytest.skip("reference .dae files not present (oracle/build_ref.sh copies them)")
+    synth = importlib.import_module("relativistic-ray-tracer_b200.synth")
+    src = str(tmp_path / "c5.dae"); out = str(tmp_path / "ours.rrtscene")
+    vf, faces = synth.write_c5_dae(src, open(template).read(), 96, 97)
+    r = subprocess.run([exe, "--dump-scene", out, "-r", "480", "360", src], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    a = sc.SceneData.load(out)
+    walls = load_scene("cbspheres_lambertian_480x360")
+    nb = walls.tri_pos.shape[0]
+    assert a.n_prims == nb + len(faces) and a.sph.shape[0] == 0
+    assert np.array_equal(a.tri_pos[:nb], walls.tri_pos) and a.lights.tobytes() == walls.lights.tobytes()
+    v, f2 = synth.displaced_sphere(96, 97)
+    assert np.array_equal(f2, faces)
+    want = v.astype(np.float32).astype(np.float64)[faces][:, [2, 0, 1]].reshape(-1, 9)
+    assert np.array_equal(a.tri_pos[nb:], want)
+    mesh_nrm = a.tri_nrm[nb:].reshape(-1, 3)
+    assert np.allclose(np.linalg.norm(mesh_nrm, axis=1), 1.0, atol=1e-12)
+    probe = os.path.join(ROOT, "oracle", "_ref", "ref_probe")
+    if os.path.exists(probe):
+        ref_out = str(tmp_path / "ref.rrtscene")
+        r = subprocess.run([probe, "scene", src, "480", "360", ref_out], capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
+        b = sc.SceneData.load(ref_out)
+        for fld in ("prim_kind", "prim_index", "tri_pos", "tri_nrm", "tri_mat"):
+            assert np.array_equal(getattr(a, fld), getattr(b, fld)), fld
+        assert a.mats.tobytes() == b.mats.tobytes() and a.lights.tobytes() == b.lights.tobytes() and a.camera == b.camera
