@@ -192,7 +192,7 @@ def test_procedural_scene_as_collada_loads_like_the_reference(exe, tmp_path):
     """synth.write_c5_dae (C5 "written as a .dae so both sides load the same file"), at 18 k triangles: the C++ loader
     returns the intended geometry — float32 vertices, the reference's (c, a, b) vertex order — and, where the reference's own
     loader is present (oracle/_ref/ref_probe), the same positions, area-weighted vertex normals, materials, light and camera
-    bit for bit.  (At the full 1,002,540 triangles: equal as well; 3.9 s here against the reference loader's 10.9 s.)"""
+    bit for bit.  (At the full 1,002,540 triangles: equal as well; 1.3 s here against the reference loader's 10.9 s.)"""
     template = os.path.join(DAE, "CBspheres_lambertian.dae")
     if not os.path.exists(template):
         pytest.skip("reference .dae files not present (oracle/build_ref.sh copies them)")
