@@ -122,7 +122,7 @@ class ClockSampler:
             try:
                 sm = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
                 r = get_reasons(self.handle)
-                self.rows.append([str(sm), str(mx), "0"] + ["Active" if r & b else "Not Active" for b, _ in bits])
+                self.rows.append([str(sm), str(mx), "0"] + ["Active" if r & b else "Not Active" for b, _ in bits] + [time.perf_counter()])
             except Exception:
                 pass
             self._stop.wait(0.01)
@@ -131,7 +131,9 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append([x.strip() for x in line.split(",")])
 
-    def stop(self):
+    def stop(self, window=None):
+        """window = (t0, t1) in time.perf_counter(): only the samples taken inside it count (NVML path; the sampler is started early
+        so that NVML's first-call latency is not inside the timed region); fewer than 3 inside -> every sample, and the result says so."""
         if self.nvml:
             self._stop.set()
             self.t.join(timeout=2)
@@ -145,7 +147,11 @@ class ClockSampler:
                 self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        rows, scope = self.rows, "timed region"
+        if window and self.nvml:
+            inside = [r for r in rows if isinstance(r[-1], float) and window[0] <= r[-1] <= window[1]]
+            rows, scope = (inside, "timed region") if len(inside) >= 3 else (rows, "whole run (warm-up + timed region)")
+        for r in rows:
             try:
                 sm.append(float(r[0])); mx.append(float(r[1]))
             except (ValueError, IndexError):
@@ -155,7 +161,7 @@ class ClockSampler:
                     reasons.add(nm)
         sm_load = sorted(sm)[len(sm) // 2:] if sm else []  # upper half = samples taken under load
         return {"sm_mhz": float(np.median(sm_load)) if sm_load else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self.nvml else "nvidia-smi"}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self.nvml else "nvidia-smi", "scope": scope}
 
 
 # ------------------------------------------------------------------------------------------------ CPU arms
@@ -306,6 +312,9 @@ def main():
         shard.assemble(frame)
         return st
 
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()          # early: NVML's first calls are slow; only samples inside the timed window are reported
     for _ in range(args.warmup):
         step_device()
     # ---- instrumented pass (counters on) for the algorithmic-byte and work figures; deterministic, so it describes
@@ -314,14 +323,12 @@ def main():
     ctx.set_option(api.OPT_COUNTERS, 0)
     step_device()
 
-    clocks = ClockSampler(local)
-    if rank == 0:
-        clocks.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     trace_s, render_s, launches, trace_launches = 0.0, 0.0, 0, 0
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    t_win0 = time.perf_counter()
     for k in range(args.steps):
         flush.zero_()                    # L2 flush between timed iterations (outside the events)
         torch.cuda.synchronize()
@@ -333,7 +340,7 @@ def main():
         dist.barrier()
     torch.cuda.synchronize()
     total_ms = sum(a.elapsed_time(b) for a, b in ev)
-    clk = clocks.stop() if rank == 0 else None
+    clk = clocks.stop((t_win0, time.perf_counter())) if rank == 0 else None
 
     # ---- e2e: public host-buffer API; scene upload (pinned host arrays -> HBM, BVH build) + render + frame read-back
     hdr = np.empty((H, W, 3), np.float32); cnt = np.empty((H, W), np.int32)
