@@ -200,7 +200,8 @@ __device__ __forceinline__ bool fast_step(const DevHole& bh, FastRay& fr, float&
  * t = (plane - o) / d in double for the six planes; here one chord-constant context holds o and 1/d rounded to float
  * and every plane parameter is widened by a rigorous bound on what those roundings can do, so that every box the
  * reference accepts is accepted here (the reverse need not hold: the exact primitive tests decide the hit):
- *   o_f = fl(o), i_f = fl(1 / fl(d)); the per-plane formula and its error bound are with boxctx_axis below.
+ *   o_f = fl(o), i_f ~ 1 / fl(d) (correctly rounded, or within 1 ulp: RRT_BOX_APPROX_RCP); the per-plane formula and its error bound
+ *   are with boxctx_axis below.
  * Direction components below 1e-30 are flushed to a signed zero (i_f = +-inf; the constants become inf or NaN), which
  * removes the float-denormal case from the analysis; NaN parameters are dropped by fminf/fmaxf, which only ever
  * widens the interval.  Node boxes are already rounded outward from the reference's doubles on the host.
@@ -208,7 +209,7 @@ __device__ __forceinline__ bool fast_step(const DevHole& bh, FastRay& fr, float&
 #ifndef RRT_BOX_APPROX_RCP
 #define RRT_BOX_APPROX_RCP 1   /* 1 = MUFU.RCP alone (rcp.approx.ftz, <= 1 ulp = 2u) for the box context's three reciprocals instead of the
                                   correctly rounded __frcp_rn.  i_f multiplies BOTH terms of t_f = b i_f - o_f i_f, so its error is a common
-                                  relative factor of every plane parameter of the axis: the relative bound below grows from 3u to 5u of the
+                                  relative factor of every plane parameter of the axis: the relative bound below grows from 3u to 4u of the
                                   16u (2^-20) the test grants; the absolute term A is untouched.  Measured on B200 (0 -> 1): C2 36.52 ->
                                   35.54 ms, bunny 1080p 103.9 -> 100.6, C5 68.6 -> 66.4, C1 4.40 -> 4.36; results unchanged (parity suite). */
 #endif
@@ -227,12 +228,14 @@ struct BoxCtx {
 /* Plane parameter in one FFMA: t_f = fl(b * i_f - c), c = fl(o_f * i_f).  Against the exact t = (b - o) / d:
  *   |t - t_f| <= |t_f| * 3u  +  (|o - o_f| |1/d| + |c - o_f i_f|) (1 + 3u)  <=  |t_f| * 3u + 2u |o_f| |i_f| (1 + ...)
  * (u = 2^-24), widened to |t_f| * 2^-20 + A with A = 2^-22 |o_f| |i_f|: 2x slack on the absolute term, 5x on the
- * relative one.  `slack` is an extra bound on |o - o_true| (far chords, below); it enters A as slack |i_f|. */
+ * relative one.  With i_f from MUFU.RCP alone (RRT_BOX_APPROX_RCP: |i_f d_f - 1| <= 2u instead of u) the factor common to
+ * b i_f and o_f i_f is off by one more u: relative term 4u (+ second order) of the 16u granted, absolute term as before.
+ * `slack` is an extra bound on |o - o_true| (far chords, below); it enters A as slack |i_f|. */
 __device__ __forceinline__ void boxctx_axis(double o, double d, float slack, float& inv, float& cn, float& cf, bool& neg) {
   float df = (float)d;
   if (fabsf(df) < 1e-30f) df = copysignf(0.f, df);
   float of = (float)o;
-  inv = RRT_BOX_RCP(df);   /* correctly rounded, like 1.0f / df, without the division's slow path */
+  inv = RRT_BOX_RCP(df);
   float c = of * inv;
   float a = __fmaf_rn(2.3841858e-7f, fabsf(of), slack) * fabsf(inv);
   cn = -c - a; cf = -c + a;
