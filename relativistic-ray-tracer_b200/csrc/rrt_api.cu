@@ -492,8 +492,11 @@ static int trace_variant(const rrt_ctx* ctx) {
 static bool fast_stepper(const rrt_ctx* ctx) {
   return ctx->opt[RRT_OPT_STEPPER] == 1 && ctx->bh.mode != RRT_MODE_FLAT && ctx->opt[RRT_OPT_TRACE_KERNEL] != 1 && ctx->ds.width != 4;
 }
-#define RRT_STEP_SWITCH(ctx, v, CALL, CALLF) \
-  if (fast_stepper(ctx)) { if ((v) == 8) { CALLF(8); } else { CALLF(0); } } else RRT_VARIANT_SWITCH(v, CALL)
+/* third template argument of the lockstep kernels: 0 = hole on / FP64 stepper, 1 = hole on / FP32 stepper, 2 = flat spacetime */
+#define RRT_STEP_SWITCH(ctx, v, CALL, CALLF, CALLX) \
+  if (fast_stepper(ctx)) { if ((v) == 8) { CALLF(8); } else { CALLF(0); } } \
+  else if ((ctx)->bh.mode == RRT_MODE_FLAT && (v) != 1) { if ((v) == 8) { CALLX(8); } else if ((v) == 4) { CALLX(4); } else { CALLX(0); } } \
+  else RRT_VARIANT_SWITCH(v, CALL)
 
 static void launch_closest(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, const double* ray, size_t cap, const int* cnt_ptr, int* cursor, int* h_prim,
                            double* h_geo, Counters* gc) {
@@ -501,9 +504,12 @@ static void launch_closest(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, 
                     else k_trace_closest<false, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc)
 #define RRT_CALLF(V) if (count) k_trace_closest<true, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc); \
                     else k_trace_closest<false, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc)
-  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF)
+#define RRT_CALLX(V) if (count) k_trace_closest<true, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc); \
+                    else k_trace_closest<false, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc)
+  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF, RRT_CALLX)
 #undef RRT_CALL
 #undef RRT_CALLF
+#undef RRT_CALLX
 }
 template <bool ANY>
 static void launch_shadow(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, const double* ray, size_t cap, const int* cnt_ptr, int* cursor,
@@ -512,9 +518,12 @@ static void launch_shadow(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, c
                     else k_trace_shadow<ANY, false, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc)
 #define RRT_CALLF(V) if (count) k_trace_shadow<ANY, true, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc); \
                     else k_trace_shadow<ANY, false, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc)
-  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF)
+#define RRT_CALLX(V) if (count) k_trace_shadow<ANY, true, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc); \
+                    else k_trace_shadow<ANY, false, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc)
+  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF, RRT_CALLX)
 #undef RRT_CALL
 #undef RRT_CALLF
+#undef RRT_CALLX
 }
 
 static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_counts, float4* d_rgbn, cudaStream_t user_stream, rrt_stats* stats) {
@@ -759,9 +768,12 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
                     else k_hook_trace<false, V><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc)
 #define RRT_CALLF(V) if (any_hit) k_hook_trace<true, V, 1><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc); \
                     else k_hook_trace<false, V, 1><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc)
-  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF)
+#define RRT_CALLX(V) if (any_hit) k_hook_trace<true, V, 2><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc); \
+                    else k_hook_trace<false, V, 2><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc)
+  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF, RRT_CALLX)
 #undef RRT_CALL
 #undef RRT_CALLF
+#undef RRT_CALLX
   CK(cudaEventRecord(e1, ctx->stream));
   CK(cudaMemcpyAsync(out, d_out, sizeof(rrt_hit) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));

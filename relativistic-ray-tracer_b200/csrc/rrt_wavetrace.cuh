@@ -117,7 +117,8 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
   CoopScratch* coop = &coop_mem[COOP ? threadIdx.x >> 5 : 0];
   if (COOP) coop_init(coop);
   Counters cnt = {0, 0, 0, 0, 0, 0};
-  const bool flat = STEP == 0 && bh.mode == RRT_MODE_FLAT;   /* the host only picks STEP = 1 with the hole on */
+  constexpr bool flat = STEP == 2;   /* STEP: 0 = hole on, FP64 stepper; 1 = hole on, FP32 stepper; 2 = flat spacetime (the host dispatches on the mode:
+                                        a compile-time switch keeps the flat path's tmin / tmax and the hole path's chord state out of each other's registers) */
   const unsigned lt_mask = (1u << wt_lane()) - 1u;
   int pool_next = 0, pool_end = 0;   /* warp-uniform */
   bool more = true;                  /* warp-uniform: the global queue may still have entries */
@@ -357,7 +358,7 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
 #define RRT_MINB_CLOSEST(V, STEP) RRT_MINB_CLOSEST_N
 #else   /* wide closest-hit kernel: 5 blocks at 96 registers (fewer spills around Best / fill_geo): C2 37.08 -> 36.51 ms, C1 4.47 -> 4.42;
            the binary one stays at 6 (5: bunny 1080p 103.8 -> 104.8, C5 68.6 -> 70.4) */
-#define RRT_MINB_CLOSEST(V, STEP) (((V) >= 4 && (STEP) == 0) ? 5 : RRT_MINBLOCKS(V, STEP))
+#define RRT_MINB_CLOSEST(V, STEP) (((V) >= 4 && (STEP) != 1) ? 5 : RRT_MINBLOCKS(V, STEP))
 #endif
 template <bool COUNT, int V, int STEP = 0>
 __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB_CLOSEST(V, STEP)) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
