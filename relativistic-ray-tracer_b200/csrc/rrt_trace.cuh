@@ -206,6 +206,11 @@ __device__ __forceinline__ bool fast_step(const DevHole& bh, FastRay& fr, float&
  * removes the float-denormal case from the analysis; NaN parameters are dropped by fminf/fmaxf, which only ever
  * widens the interval.  Node boxes are already rounded outward from the reference's doubles on the host.
  * Requires tmin >= 0 (true for chords and for every ray the estimator makes). */
+#ifndef RRT_WIDE_RECOMPUTE_OFFSETS
+#define RRT_WIDE_RECOMPUTE_OFFSETS 1   /* wide-node plane-array offsets from the three sign flags at every visit instead of six live registers: the kernels sit at
+                                          their register cap, and what this frees comes out of the spills (closest-hit 256 -> 64 B, shadow 148 -> 134 B).
+                                          B200, 0 -> 1: C2 35.38 -> 34.53 ms, C1 4.31 -> 4.25, C2 with the FP32 stepper 32.76 -> 30.91 */
+#endif
 #ifndef RRT_BOX_APPROX_RCP
 #define RRT_BOX_APPROX_RCP 1   /* 1 = MUFU.RCP alone (rcp.approx.ftz, <= 1 ulp = 2u) for the box context's three reciprocals instead of the
                                   correctly rounded __frcp_rn.  i_f multiplies BOTH terms of t_f = b i_f - o_f i_f, so its error is a common
@@ -586,9 +591,15 @@ __device__ __forceinline__ bool traverse_wide(const DevScene& sc, const SEG& s, 
     };
 #pragma unroll
     for (int g = 0; g < W / 4; ++g) {
+#if RRT_WIDE_RECOMPUTE_OFFSETS
+      const float4 a = __ldg((const float4*)(nd + (bc.nx ? 3 * W : 0)) + g), b = __ldg((const float4*)(nd + (bc.nx ? 0 : 3 * W)) + g);
+      const float4 c = __ldg((const float4*)(nd + (bc.ny ? 4 * W : W)) + g), d = __ldg((const float4*)(nd + (bc.ny ? W : 4 * W)) + g);
+      const float4 e = __ldg((const float4*)(nd + (bc.nz ? 5 * W : 2 * W)) + g), f = __ldg((const float4*)(nd + (bc.nz ? 2 * W : 5 * W)) + g);
+#else
       const float4 a = __ldg((const float4*)(nd + onx) + g), b = __ldg((const float4*)(nd + ofx) + g);
       const float4 c = __ldg((const float4*)(nd + ony) + g), d = __ldg((const float4*)(nd + ofy) + g);
       const float4 e = __ldg((const float4*)(nd + onz) + g), f = __ldg((const float4*)(nd + ofz) + g);
+#endif
       const int4 k = __ldg((const int4*)(nd + 6 * W) + g);
       child(a.x, b.x, c.x, d.x, e.x, f.x, k.x);
       child(a.y, b.y, c.y, d.y, e.y, f.y, k.y);
