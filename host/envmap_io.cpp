@@ -1,14 +1,17 @@
 // envmap_io.cpp — environment maps for -e (reference src/main.cpp:42-79 reads them through tinyexr).
-// Two containers, both uncompressed, since the image has no compression library:
-//   * OpenEXR scanline files with compression NONE and HALF or FLOAT channels R, G, B (anything else in the header is
-//     reported, not guessed at);
+// Two containers:
+//   * OpenEXR scanline files with compression NONE, RLE, ZIPS or ZIP (zlib) and HALF / FLOAT / UINT channels R, G, B; the wavelet
+//     and lossy codecs (PIZ, PXR24, B44, DWA) and tiled / deep / multi-part files are reported, not guessed at;
 //   * PFM ("PF", little- or big-endian, bottom row first).
 // Output: [h][w][3] floats, row 0 = top, the layout rrt_set_envmap takes.
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <map>
+
+#include <zlib.h>
 
 #include "rrt_host.h"
 
@@ -69,6 +72,32 @@ bool load_pfm(const std::vector<uint8_t>& b, int* w, int* h, std::vector<float>*
   return true;
 }
 
+// OpenEXR's byte shuffling behind RLE / ZIPS / ZIP (ImfZip.cpp, ImfRle.cpp): the block is split into even and odd bytes, then
+// delta-coded; decoding undoes the delta (t[i] += t[i-1] - 128) and re-interleaves the two halves.
+void exr_unpredict_and_interleave(std::vector<uint8_t>& t, std::vector<uint8_t>* out) {
+  for (size_t i = 1; i < t.size(); ++i) t[i] = (uint8_t)(t[i - 1] + t[i] - 128);
+  out->resize(t.size());
+  const size_t half = (t.size() + 1) / 2;
+  for (size_t i = 0, a = 0, b = half; i < t.size(); ++i) (*out)[i] = (i & 1) ? t[b++] : t[a++];
+}
+bool exr_rle_decode(const uint8_t* in, size_t n, size_t expect, std::vector<uint8_t>* out) {
+  out->clear(); out->reserve(expect);
+  size_t i = 0;
+  while (i < n) {
+    const int8_t c = (int8_t)in[i++];
+    if (c < 0) {
+      const size_t k = (size_t)(-(int)c);
+      if (i + k > n || out->size() + k > expect) return false;
+      out->insert(out->end(), in + i, in + i + k); i += k;
+    } else {
+      const size_t k = (size_t)c + 1;
+      if (i >= n || out->size() + k > expect) return false;
+      out->insert(out->end(), k, in[i++]);
+    }
+  }
+  return out->size() == expect;
+}
+
 struct Channel { std::string name; int type; };   // 0 uint, 1 half, 2 float
 
 bool load_exr(const std::vector<uint8_t>& b, int* w, int* h, std::vector<float>* rgb, std::string* err) {
@@ -104,7 +133,12 @@ bool load_exr(const std::vector<uint8_t>& b, int* w, int* h, std::vector<float>*
     else if (name == "dataWindow") memcpy(dw, v, 16);
     pos += (size_t)size;
   }
-  if (compression != 0) { *err = "compressed OpenEXR files cannot be read here (no compression library): store the map with compression NONE, or as .pfm"; return false; }
+  if (compression < 0 || compression > 3) {
+    static const char* names[] = {"NONE", "RLE", "ZIPS", "ZIP", "PIZ", "PXR24", "B44", "B44A", "DWAA", "DWAB"};
+    *err = std::string("OpenEXR compression ") + (compression >= 0 && compression < 10 ? names[compression] : "(unknown)") +
+           " is not supported (NONE, RLE, ZIPS and ZIP are): re-save the map with one of those, or as .pfm";
+    return false;
+  }
   *w = dw[2] - dw[0] + 1; *h = dw[3] - dw[1] + 1;
   if (*w <= 0 || *h <= 0 || chans.empty()) { *err = "OpenEXR header without channels / data window"; return false; }
   std::map<std::string, int> slot = {{"R", 0}, {"G", 1}, {"B", 2}};
@@ -113,23 +147,43 @@ bool load_exr(const std::vector<uint8_t>& b, int* w, int* h, std::vector<float>*
     if (c.type < 0 || c.type > 2) { *err = "unknown OpenEXR pixel type"; return false; }
     row_bytes += (size_t)*w * (c.type == 1 ? 2 : 4);
   }
-  if (pos + 8 * (size_t)*h > b.size()) { *err = "truncated OpenEXR offset table"; return false; }
+  const int lines_per_chunk = compression == 3 ? 16 : 1;
+  const int n_chunks = (*h + lines_per_chunk - 1) / lines_per_chunk;
+  if (pos + 8 * (size_t)n_chunks > b.size()) { *err = "truncated OpenEXR offset table"; return false; }
   rgb->assign((size_t)*w * *h * 3, 0.f);
-  for (int line = 0; line < *h; ++line) {
-    uint64_t off; memcpy(&off, b.data() + pos + 8 * (size_t)line, 8);
-    if (off + 8 + row_bytes > b.size()) { *err = "truncated OpenEXR scan line"; return false; }
-    int32_t y; memcpy(&y, b.data() + off, 4);
-    int row = y - dw[1];
-    if (row < 0 || row >= *h) { *err = "OpenEXR scan line outside the data window"; return false; }
+  std::vector<uint8_t> tmp, block;
+  for (int chunk = 0; chunk < n_chunks; ++chunk) {
+    uint64_t off; memcpy(&off, b.data() + pos + 8 * (size_t)chunk, 8);
+    if (off + 8 > b.size()) { *err = "truncated OpenEXR chunk"; return false; }
+    int32_t y, size; memcpy(&y, b.data() + off, 4); memcpy(&size, b.data() + off + 4, 4);
+    const int row0 = y - dw[1];
+    if (row0 < 0 || row0 >= *h) { *err = "OpenEXR scan line outside the data window"; return false; }
+    const int lines = std::min(lines_per_chunk, *h - row0);
+    const size_t expect = row_bytes * (size_t)lines;
+    if (size < 0 || off + 8 + (size_t)size > b.size()) { *err = "truncated OpenEXR chunk"; return false; }
     const uint8_t* q = b.data() + off + 8;
-    for (const Channel& c : chans) {    // channels are stored in the header's (alphabetical) order
-      auto it = slot.find(c.name);
-      for (int x = 0; x < *w; ++x) {
-        float f;
-        if (c.type == 1) { uint16_t hv; memcpy(&hv, q, 2); q += 2; f = half_to_float(hv); }
-        else if (c.type == 2) { memcpy(&f, q, 4); q += 4; }
-        else { uint32_t u; memcpy(&u, q, 4); q += 4; f = (float)u; }
-        if (it != slot.end()) (*rgb)[((size_t)row * *w + x) * 3 + it->second] = f;
+    if (compression != 0 && (size_t)size < expect) {      // a chunk that did not shrink is stored raw
+      if (compression == 1) {
+        if (!exr_rle_decode(q, (size_t)size, expect, &tmp)) { *err = "corrupt RLE data in OpenEXR chunk"; return false; }
+      } else {
+        tmp.resize(expect);
+        uLongf got = (uLongf)expect;
+        if (uncompress(tmp.data(), &got, q, (uLong)size) != Z_OK || got != expect) { *err = "corrupt zlib data in OpenEXR chunk"; return false; }
+      }
+      exr_unpredict_and_interleave(tmp, &block);
+      q = block.data();
+    } else if ((size_t)size != expect) { *err = "OpenEXR chunk of unexpected size"; return false; }
+    for (int l = 0; l < lines; ++l) {
+      const int row = row0 + l;
+      for (const Channel& c : chans) {    // per scan line, channels in the header's (alphabetical) order
+        auto it = slot.find(c.name);
+        for (int x = 0; x < *w; ++x) {
+          float f;
+          if (c.type == 1) { uint16_t hv; memcpy(&hv, q, 2); q += 2; f = half_to_float(hv); }
+          else if (c.type == 2) { memcpy(&f, q, 4); q += 4; }
+          else { uint32_t u; memcpy(&u, q, 4); q += 4; f = (float)u; }
+          if (it != slot.end()) (*rgb)[((size_t)row * *w + x) * 3 + it->second] = f;
+        }
       }
     }
   }

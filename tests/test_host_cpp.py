@@ -137,27 +137,57 @@ def test_minimal_collada_document(exe, tmp_path):
     assert a.camera["screenW"] == 800.0 and a.camera["screenH"] == 600.0         # Application::init's defaults
 
 
-def write_exr(path, img, pixel_type):
-    """minimal scan-line OpenEXR writer, compression NONE, channels B G R (alphabetical, as the format requires)"""
+def _exr_shuffle(raw):
+    """OpenEXR's pre-compression byte shuffling (even bytes, then odd bytes, then delta coding), ImfZip.cpp / ImfRle.cpp"""
+    a = np.frombuffer(raw, np.uint8)
+    t = np.concatenate([a[0::2], a[1::2]]).astype(np.int32)
+    d = t.copy()
+    d[1:] = (t[1:] - t[:-1] + 128 + 256) % 256
+    return d.astype(np.uint8).tobytes()
+
+
+def _exr_rle(raw):
+    out, i, n = bytearray(), 0, len(raw)
+    while i < n:
+        j = i
+        while j + 1 < n and raw[j + 1] == raw[i] and j - i < 127:
+            j += 1
+        if j - i >= 2:                                   # a run of 3..128 equal bytes
+            out += bytes([j - i, raw[i]]); i = j + 1
+        else:                                            # literals up to the next run of 3
+            k = i
+            while k < n and k - i < 127 and not (k + 2 < n and raw[k] == raw[k + 1] == raw[k + 2]):
+                k += 1
+            out += bytes([(256 - (k - i)) & 0xFF]) + raw[i:k]; i = k
+    return bytes(out)
+
+
+def write_exr(path, img, pixel_type, compression=0):
+    """minimal scan-line OpenEXR writer; compression 0 NONE, 1 RLE, 2 ZIPS, 3 ZIP; channels B G R (alphabetical, as the format requires)"""
     h, w, _ = img.shape
     def attr(name, typ, data):
         return name.encode() + b"\0" + typ.encode() + b"\0" + struct.pack("<i", len(data)) + data
     chl = b"".join(n.encode() + b"\0" + struct.pack("<iBBBBii", pixel_type, 0, 0, 0, 0, 1, 1) for n in "BGR") + b"\0"
     box = struct.pack("<iiii", 0, 0, w - 1, h - 1)
-    hdr = (struct.pack("<II", 20000630, 2) + attr("channels", "chlist", chl) + attr("compression", "compression", b"\0") +
+    hdr = (struct.pack("<II", 20000630, 2) + attr("channels", "chlist", chl) + attr("compression", "compression", bytes([compression])) +
            attr("dataWindow", "box2i", box) + attr("displayWindow", "box2i", box) + attr("lineOrder", "lineOrder", b"\0") +
            attr("pixelAspectRatio", "float", struct.pack("<f", 1.0)) + attr("screenWindowCenter", "v2f", struct.pack("<ff", 0, 0)) +
            attr("screenWindowWidth", "float", struct.pack("<f", 1.0)) + b"\0")
     dt = np.float16 if pixel_type == 1 else np.float32
-    rows = []
-    for y in range(h):
-        data = b"".join(np.ascontiguousarray(img[y, :, c], dt).tobytes() for c in (2, 1, 0))
-        rows.append(struct.pack("<ii", y, len(data)) + data)
-    off = len(hdr) + 8 * h
+    per = 16 if compression == 3 else 1
+    chunks = []
+    for y0 in range(0, h, per):
+        data = b"".join(np.ascontiguousarray(img[y, :, c], dt).tobytes() for y in range(y0, min(y0 + per, h)) for c in (2, 1, 0))
+        if compression:
+            packed = _exr_rle(_exr_shuffle(data)) if compression == 1 else zlib.compress(_exr_shuffle(data))
+            if len(packed) < len(data):                  # the format stores a chunk raw when compression does not shrink it
+                data = packed
+        chunks.append(struct.pack("<ii", y0, len(data)) + data)
+    off = len(hdr) + 8 * len(chunks)
     table = b""
-    for r in rows:
+    for r in chunks:
         table += struct.pack("<Q", off); off += len(r)
-    open(path, "wb").write(hdr + table + b"".join(rows))
+    open(path, "wb").write(hdr + table + b"".join(chunks))
 
 
 def test_environment_map_readers(exe, tmp_path):
@@ -181,11 +211,27 @@ def test_environment_map_readers(exe, tmp_path):
     with open(tmp_path / "b.pfm", "wb") as f:
         f.write(b"PF\n7 5\n1.0\n" + np.ascontiguousarray(img[::-1]).astype(">f4").tobytes())
     assert np.array_equal(decode(tmp_path / "b.pfm"), img)
-    # a compressed file is refused with a reason, not misread
-    raw = open(tmp_path / "f.exr", "rb").read().replace(b"compression\0compression\0\x01\0\0\0\0", b"compression\0compression\0\x01\0\0\0\x03")
+    # RLE / ZIPS / ZIP chunks (zlib): a smooth 40 x 33 map so that chunks do shrink, plus the noisy one whose chunks are stored raw
+    yy, xx = np.mgrid[0:33, 0:40]
+    smooth = np.stack([np.floor(xx / 8) * 0.25, np.floor(yy / 4) * 0.5, np.ones_like(xx) * 2.0], -1).astype(np.float32)
+    for comp in (1, 2, 3):
+        for pt in (1, 2):
+            write_exr(tmp_path / "c.exr", smooth, pt, comp)
+            if pt == 2:
+                assert os.path.getsize(tmp_path / "c.exr") < 0.8 * smooth.nbytes     # the writer did compress
+            assert np.array_equal(decode(tmp_path / "c.exr"), smooth.astype(np.float16).astype(np.float32) if pt == 1 else smooth), (comp, pt)
+        write_exr(tmp_path / "n.exr", img, 2, comp)
+        assert np.array_equal(decode(tmp_path / "n.exr"), img)
+    # corrupt zlib data and the codecs that are not implemented are refused with a reason, not misread
+    write_exr(tmp_path / "c.exr", smooth, 2, 3)
+    raw = bytearray(open(tmp_path / "c.exr", "rb").read()); raw[-20] ^= 0xFF
+    open(tmp_path / "bad.exr", "wb").write(bytes(raw))
+    r = subprocess.run([exe, "--dump-envmap", str(tmp_path / "bad.exr"), str(tmp_path / "x")], capture_output=True, text=True)
+    assert r.returncode == 2 and "zlib" in r.stderr
+    raw = open(tmp_path / "f.exr", "rb").read().replace(b"compression\0compression\0\x01\0\0\0\0", b"compression\0compression\0\x01\0\0\0\x04")
     open(tmp_path / "z.exr", "wb").write(raw)
     r = subprocess.run([exe, "--dump-envmap", str(tmp_path / "z.exr"), str(tmp_path / "x")], capture_output=True, text=True)
-    assert r.returncode == 2 and "compression" in r.stderr
+    assert r.returncode == 2 and "PIZ" in r.stderr
 
 
 def test_procedural_scene_as_collada_loads_like_the_reference(exe, tmp_path):
