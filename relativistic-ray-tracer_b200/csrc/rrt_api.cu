@@ -221,30 +221,44 @@ static int build_bvh_on_device(rrt_ctx* ctx, const rrt_scene* s, bool* built) {
   int cur = 0, levels = 0;
   Box6 sb;
   int* h_flags = (int*)ctx->h_pinned;
-  for (;; ++levels) {
-    if (levels > 1 << 16) FAIL(RRT_E_ARG, "rrt_upload_scene: device BVH build did not terminate");
-    k_ref_reset<<<G, B, 0, st>>>(n, ss[cur], se[cur], segbox);
-    k_ref_accum<<<G, B, 0, st>>>(n, ord[cur], ss[cur], se[cur], plo, phi, segbox);
-    if (levels == 0) {   /* the root box = the scene box (doubles, exact) */
-      unsigned long long h[6];
-      for (int k = 0; k < 6; ++k) CK(cudaMemcpyAsync(&h[k], segbox + (size_t)k * n, 8, cudaMemcpyDeviceToHost, st));
-      CK(cudaStreamSynchronize(st));
-      for (int k = 0; k < 3; ++k) {
-        unsigned long long e0 = h[k], e1 = h[3 + k];
-        unsigned long long b0 = (e0 >> 63) ? (e0 & 0x7fffffffffffffffull) : ~e0, b1 = (e1 >> 63) ? (e1 & 0x7fffffffffffffffull) : ~e1;
-        memcpy(&sb.lo[k], &b0, 8); memcpy(&sb.hi[k], &b1, 8);
-      }
-      if (n <= 4) break;
-    }
-    k_ref_flag<<<G1, B, 0, st>>>(n, ord[cur], ss[cur], se[cur], segbox, cen, isl);
-    size_t tb = tmp_bytes;
-    cub::DeviceScan::ExclusiveSum(tmp, tb, isl, pre, (int)n + 1, st);
-    CK(cudaMemsetAsync(flags, 0, 4, st));
-    k_ref_scatter<<<G, B, 0, st>>>(n, ord[cur], ss[cur], se[cur], isl, pre, ord[cur ^ 1], ss[cur ^ 1], se[cur ^ 1], flags, flags + 1);
-    cur ^= 1;
-    CK(cudaMemcpyAsync(h_flags, flags, 12, cudaMemcpyDeviceToHost, st));
+  /* the root box = the scene box (doubles, exact): first half of level 0, read back once */
+  k_ref_reset<<<G, B, 0, st>>>(n, ss[cur], se[cur], segbox);
+  k_ref_accum<<<G, B, 0, st>>>(n, ord[cur], ss[cur], se[cur], plo, phi, segbox);
+  {
+    unsigned long long h[6];
+    for (int k = 0; k < 6; ++k) CK(cudaMemcpyAsync(&h[k], segbox + (size_t)k * n, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    if (!h_flags[0]) { ++levels; break; }
+    for (int k = 0; k < 3; ++k) {
+      unsigned long long e0 = h[k], e1 = h[3 + k];
+      unsigned long long b0 = (e0 >> 63) ? (e0 & 0x7fffffffffffffffull) : ~e0, b1 = (e1 >> 63) ? (e1 & 0x7fffffffffffffffull) : ~e1;
+      memcpy(&sb.lo[k], &b0, 8); memcpy(&sb.hi[k], &b1, 8);
+    }
+  }
+  /* levels run in groups of 8 without a host round trip (C5's reference tree is 194 levels deep); a level with nothing left to
+   * split is a no-op that copies the order through, and each level leaves its own "new segments to split" flag behind */
+  const int GROUP = 8;
+  bool first = true;
+  for (bool done = false; !done;) {
+    if (levels > 1 << 16) FAIL(RRT_E_ARG, "rrt_upload_scene: device BVH build did not terminate");
+    CK(cudaMemsetAsync(flags + 8, 0, 4 * GROUP, st));
+    for (int g = 0; g < GROUP; ++g) {
+      if (!first) {
+        k_ref_reset<<<G, B, 0, st>>>(n, ss[cur], se[cur], segbox);
+        k_ref_accum<<<G, B, 0, st>>>(n, ord[cur], ss[cur], se[cur], plo, phi, segbox);
+      }
+      first = false;
+      k_ref_flag<<<G1, B, 0, st>>>(n, ord[cur], ss[cur], se[cur], segbox, cen, isl);
+      size_t tb = tmp_bytes;
+      cub::DeviceScan::ExclusiveSum(tmp, tb, isl, pre, (int)n + 1, st);
+      k_ref_scatter<<<G, B, 0, st>>>(n, ord[cur], ss[cur], se[cur], isl, pre, ord[cur ^ 1], ss[cur ^ 1], se[cur ^ 1], flags + 8 + g, flags + 1);
+      cur ^= 1;
+    }
+    CK(cudaMemcpyAsync(h_flags, flags, 4 * (8 + GROUP), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    for (int g = 0; g < GROUP; ++g) {
+      ++levels;
+      if (!h_flags[8 + g]) { done = true; break; }
+    }
   }
   k_ref_rank<<<G, B, 0, st>>>(n, ord[cur], rank);
   /* 2. LBVH */
