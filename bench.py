@@ -418,7 +418,7 @@ def main():
                      "trace_share_of_step": trace_s / (render_s if render_s > 0 else 1.0),
                      "scene_bytes": scene_bytes,
                      "note": ("BVH nodes + leaf records = %.1f MB: %s" % (scene_bytes / 1e6,
-                              "L1/L2 resident, the kernel is instruction-issue bound (FP64 + FP32 pipes), the fraction counts cache-served bytes; see DESIGN.md section 6"
+                              "L1/L2 resident: the algorithmic bytes are served by the caches (compare `traffic`, the DRAM bytes of the same launch), so this fraction is not a DRAM utilisation and can exceed 1; the kernel is instruction-issue bound (ncu: 74 % of issue slots), see DESIGN.md section 6 and the fp64_step view"
                               if scene_bytes < 100e6 else "close to the 126 MB L2, yet served by it (ncu, profiles/traffic.json: L2 hit rate 95 %, 0.35 GB of DRAM traffic in the longest launch); the kernel is issue- / FP64-bound, see DESIGN.md section 6"))},
         "clocks": clk,
     }

@@ -230,6 +230,20 @@ struct BoxCtx {
   float tmin;
   bool nx, ny, nz;           /* direction component negative: the near plane is the box maximum */
 };
+#ifndef RRT_BOX_SIGN_FROM_INV
+#define RRT_BOX_SIGN_FROM_INV 1   /* "direction component negative" read off the sign bit of i_f (the sign of d_f, -0 -> -inf included; a NaN axis is dropped by
+                                     fminf / fmaxf whichever way it is read) instead of three flags kept live: wide shadow kernel spill stores 134 -> 4 B.
+                                     B200, 0 -> 1: C2 34.50 -> 33.54 ms, C1 4.20 -> 4.12, bunny 1080p 100.1 -> 98.2, C5 66.0 -> 64.6 */
+#endif
+#if RRT_BOX_SIGN_FROM_INV
+#define RRT_NEGX(c) (__float_as_int((c).ix) < 0)
+#define RRT_NEGY(c) (__float_as_int((c).iy) < 0)
+#define RRT_NEGZ(c) (__float_as_int((c).iz) < 0)
+#else
+#define RRT_NEGX(c) ((c).nx)
+#define RRT_NEGY(c) ((c).ny)
+#define RRT_NEGZ(c) ((c).nz)
+#endif
 /* Plane parameter in one FFMA: t_f = fl(b * i_f - c), c = fl(o_f * i_f).  Against the exact t = (b - o) / d:
  *   |t - t_f| <= |t_f| * 3u  +  (|o - o_f| |1/d| + |c - o_f i_f|) (1 + 3u)  <=  |t_f| * 3u + 2u |o_f| |i_f| (1 + ...)
  * (u = 2^-24), widened to |t_f| * 2^-20 + A with A = 2^-22 |o_f| |i_f|: 2x slack on the absolute term, 5x on the
@@ -282,9 +296,9 @@ __device__ __forceinline__ float boxctx_tmax(double tmax, double T) {
 __device__ __forceinline__ bool box_hit(float lox, float loy, float loz, float hix, float hiy, float hiz, const BoxCtx& c, float tmaxf,
                                         float& tnear) {
   const float R = 9.5367431640625e-7f; /* 2^-20 */
-  float tnx = __fmaf_rn(c.nx ? hix : lox, c.ix, c.nx_), tfx = __fmaf_rn(c.nx ? lox : hix, c.ix, c.fx_);
-  float tny = __fmaf_rn(c.ny ? hiy : loy, c.iy, c.ny_), tfy = __fmaf_rn(c.ny ? loy : hiy, c.iy, c.fy_);
-  float tnz = __fmaf_rn(c.nz ? hiz : loz, c.iz, c.nz_), tfz = __fmaf_rn(c.nz ? loz : hiz, c.iz, c.fz_);
+  float tnx = __fmaf_rn(RRT_NEGX(c) ? hix : lox, c.ix, c.nx_), tfx = __fmaf_rn(RRT_NEGX(c) ? lox : hix, c.ix, c.fx_);
+  float tny = __fmaf_rn(RRT_NEGY(c) ? hiy : loy, c.iy, c.ny_), tfy = __fmaf_rn(RRT_NEGY(c) ? loy : hiy, c.iy, c.fy_);
+  float tnz = __fmaf_rn(RRT_NEGZ(c) ? hiz : loz, c.iz, c.nz_), tfz = __fmaf_rn(RRT_NEGZ(c) ? loz : hiz, c.iz, c.fz_);
   float tn = fmaxf(fmaxf(tnx, tny), tnz), tf = fminf(fminf(tfx, tfy), tfz);
   tn = __fmaf_rn(fabsf(tn), -R, tn);
   tf = __fmaf_rn(fabsf(tf), R, tf);
@@ -592,9 +606,9 @@ __device__ __forceinline__ bool traverse_wide(const DevScene& sc, const SEG& s, 
 #pragma unroll
     for (int g = 0; g < W / 4; ++g) {
 #if RRT_WIDE_RECOMPUTE_OFFSETS
-      const float4 a = __ldg((const float4*)(nd + (bc.nx ? 3 * W : 0)) + g), b = __ldg((const float4*)(nd + (bc.nx ? 0 : 3 * W)) + g);
-      const float4 c = __ldg((const float4*)(nd + (bc.ny ? 4 * W : W)) + g), d = __ldg((const float4*)(nd + (bc.ny ? W : 4 * W)) + g);
-      const float4 e = __ldg((const float4*)(nd + (bc.nz ? 5 * W : 2 * W)) + g), f = __ldg((const float4*)(nd + (bc.nz ? 2 * W : 5 * W)) + g);
+      const float4 a = __ldg((const float4*)(nd + (RRT_NEGX(bc) ? 3 * W : 0)) + g), b = __ldg((const float4*)(nd + (RRT_NEGX(bc) ? 0 : 3 * W)) + g);
+      const float4 c = __ldg((const float4*)(nd + (RRT_NEGY(bc) ? 4 * W : W)) + g), d = __ldg((const float4*)(nd + (RRT_NEGY(bc) ? W : 4 * W)) + g);
+      const float4 e = __ldg((const float4*)(nd + (RRT_NEGZ(bc) ? 5 * W : 2 * W)) + g), f = __ldg((const float4*)(nd + (RRT_NEGZ(bc) ? 2 * W : 5 * W)) + g);
 #else
       const float4 a = __ldg((const float4*)(nd + onx) + g), b = __ldg((const float4*)(nd + ofx) + g);
       const float4 c = __ldg((const float4*)(nd + ony) + g), d = __ldg((const float4*)(nd + ofy) + g);
