@@ -350,6 +350,12 @@ def main():
               s.mats.nbytes + s.lights.nbytes + 18 * 8 + 48)
     d2h = int(hdr.nbytes + cnt.nbytes)
     host_frame = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()
+    # the scene's geometry arrays are page-locked in place (cudaHostRegister), as the contract asks of a step's inputs
+    pinned = []
+    rt = torch.cuda.cudart()
+    for a in (s.tri_pos, s.tri_nrm, s.prim_index, s.prim_kind, s.tri_mat, s.sph):
+        if a.nbytes >= 4096 and int(rt.cudaHostRegister(a.ctypes.data, a.nbytes, 0)) == 0:
+            pinned.append(a)
 
     def step_e2e():
         ctx.upload_scene(s)
@@ -371,6 +377,8 @@ def main():
         dist.barrier()
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
+    for a in pinned:
+        rt.cudaHostUnregister(a.ctypes.data)
 
     t = torch.tensor([total_ms, e2e_s, trace_s, float(st_count["paths"]), float(st_count["geodesic_steps"]), float(st_count["rays"]),
                       float(st_count["algorithmic_bytes"])], dtype=torch.float64, device="cuda")
