@@ -219,6 +219,18 @@ int rrt_render_device(rrt_ctx* ctx, const rrt_params* p, void* d_rgbn, void* d_c
  * gives BVHAccel::intersect(ray) (shadow-ray form): only status is meaningful. */
 int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, const double* min_t,
                    const double* max_t, int any_hit, rrt_hit* out, rrt_stats* stats);
+/* rrt_trace_rays without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same kernel, same arguments and results as rrt_trace_rays (no rrt_stats); o, d, min_t, max_t and out may be
+ * host or device pointers.  All device scratch — staged rays, hit records, the work cursor, the counters — lives in one
+ * file-scope `static __device__` array of 4 KiB + RRT_STATIC_MAX_RAYS * 160 B (10 MiB) that every GPU loading the
+ * library holds until exit; the call makes no cudaMalloc / cudaFree / allocating library call (the scene must have
+ * been uploaded before, which does allocate).  n > RRT_STATIC_MAX_RAYS fails with RRT_E_ARG and a message naming the
+ * limit.  Every call (from any context on that GPU) shares the array and finds the previous call's contents in it;
+ * the call clears what must start at zero, but calls that overlap on one GPU RACE: serialise them. */
+#define RRT_STATIC_MAX_RAYS 65536
+int rrt_trace_rays_static(rrt_ctx* ctx, int64_t n, const double* o, const double* d, const double* min_t,
+                          const double* max_t, int any_hit, rrt_hit* out);
 /* First nsteps chords of each ray: seg_out [n*nsteps*8] = origin xyz, unit direction xyz, length, and 1.0 when the
  * chord crosses the horizon (the reference's capture test, src/bvh.cpp:107), else 0.0. */
 int rrt_geodesic(rrt_ctx* ctx, int64_t n, const double* o, const double* d, int nsteps, double* seg_out);

@@ -30,7 +30,8 @@ OPT_STEPPER = 8   # 0 = FP64 bit-exact stepper (default), 1 = FP32 state-carryin
 EXPORTS = ["rrt_abi_version", "rrt_device_count", "rrt_create", "rrt_destroy", "rrt_last_error", "rrt_set_option", "rrt_upload_scene",
            "rrt_set_camera", "rrt_set_blackhole", "rrt_set_frame", "rrt_set_cell", "rrt_set_tile_shard", "rrt_render", "rrt_render_device",
            "rrt_trace_rays", "rrt_geodesic", "rrt_generate_rays", "rrt_generate_rays_thin_lens", "rrt_set_progress", "rrt_snapshot", "rrt_bsdf_sample", "rrt_bsdf_eval", "rrt_light_sample", "rrt_philox",
-           "rrt_tonemap", "rrt_bvh_info", "rrt_bvh_build_host", "rrt_chords_per_ray", "rrt_set_envmap", "rrt_env_lookup"]
+           "rrt_tonemap", "rrt_bvh_info", "rrt_bvh_build_host", "rrt_chords_per_ray", "rrt_set_envmap", "rrt_env_lookup", "rrt_trace_rays_static"]
+STATIC_MAX_RAYS = 65536  # RRT_STATIC_MAX_RAYS
 
 
 PROGRESS_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.c_int32, C.c_int64)
@@ -64,6 +65,7 @@ def lib():
         L.rrt_render_device.argtypes = [C.c_void_p, C.POINTER(_sc.Params), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(_sc.Stats)]
         L.rrt_trace_rays.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
                                      C.POINTER(_sc.Stats)]
+        L.rrt_trace_rays_static.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.rrt_geodesic.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.rrt_generate_rays.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rrt_set_progress.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
@@ -206,6 +208,16 @@ class Context:
         st = _sc.Stats()
         self._ck(lib().rrt_trace_rays(self.h, n, _p(o), _p(d), _p(mn), _p(mx), int(bool(any_hit)), _p(out), C.byref(st)))
         return out, st.as_dict()
+
+    def trace_rays_static(self, o, d, min_t=None, max_t=None, any_hit=False):
+        """rrt_trace_rays_static: the same kernel with all device scratch in the library's static array (no allocation in the call)."""
+        o = np.ascontiguousarray(o, np.float64).reshape(-1, 3); d = np.ascontiguousarray(d, np.float64).reshape(-1, 3)
+        n = o.shape[0]
+        mn = None if min_t is None else np.ascontiguousarray(min_t, np.float64)
+        mx = None if max_t is None else np.ascontiguousarray(max_t, np.float64)
+        out = np.zeros(n, _sc.HIT_DTYPE)
+        self._ck(lib().rrt_trace_rays_static(self.h, n, _p(o), _p(d), _p(mn), _p(mx), int(bool(any_hit)), _p(out)))
+        return out
 
     def geodesic(self, o, d, nsteps):
         o = np.ascontiguousarray(o, np.float64).reshape(-1, 3); d = np.ascontiguousarray(d, np.float64).reshape(-1, 3)

@@ -996,3 +996,71 @@ int rrt_tonemap(rrt_ctx* ctx, int64_t n, const float* hdr_rgb, uint32_t* rgba) {
 }
 
 }  // extern "C"
+
+/* ---------------------------------------------------------------- rrt_trace_rays_static: the parity hook's trace kernel without any allocation.
+ * No counterpart in the reference; added for callers that cannot call cudaMalloc.
+ * All device scratch of the call (staged rays, hit records, the work cursor, the counters) lives in ONE file-scope array
+ * that every GPU loading the library holds until exit.  Layout (offsets in bytes, n_max = RRT_STATIC_MAX_RAYS):
+ *   [0, 256)  work cursor (int, must start at 0)     [256, 512)  Counters (must start at 0)     [4096 ...)  o, d, min_t, max_t, hits
+ * In HOST code the name g_static_scratch is only a stand-in for the symbol, not a device address: the address the kernel
+ * gets comes from cudaGetSymbolAddress, asked once per device with that device current. */
+#define RRT_STATIC_SCRATCH_BYTES (4096 + (size_t)RRT_STATIC_MAX_RAYS * (24 + 24 + 8 + 8 + sizeof(rrt_hit)))
+static __device__ __align__(256) unsigned char g_static_scratch[RRT_STATIC_SCRATCH_BYTES];
+
+#include <mutex>
+static std::mutex g_static_mu;
+static unsigned char* g_static_ptr[64];   /* per device, filled on first use */
+
+static int static_scratch_for(rrt_ctx* ctx, unsigned char** out) {
+  if (ctx->device < 0 || ctx->device >= 64) FAIL(RRT_E_ARG, "rrt_trace_rays_static: device index beyond 63");
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  CK(cudaSetDevice(ctx->device));
+  if (!g_static_ptr[ctx->device]) {
+    void* p = nullptr;
+    CK(cudaGetSymbolAddress(&p, g_static_scratch));
+    if (!p) FAIL(RRT_E_CUDA, "rrt_trace_rays_static: cudaGetSymbolAddress returned a null address");
+    g_static_ptr[ctx->device] = (unsigned char*)p;
+  }
+  *out = g_static_ptr[ctx->device];
+  return RRT_OK;
+}
+
+extern "C" int rrt_trace_rays_static(rrt_ctx* ctx, int64_t n, const double* o, const double* d, const double* min_t, const double* max_t, int any_hit,
+                                     rrt_hit* out) {
+  if (!ctx || n < 0 || (n && (!o || !d || !out))) return RRT_E_ARG;
+  if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_trace_rays_static: no scene");
+  if (n > RRT_STATIC_MAX_RAYS) {
+    char b[160]; snprintf(b, sizeof b, "rrt_trace_rays_static: %lld rays exceed the static scratch limit of %d rays per call", (long long)n, RRT_STATIC_MAX_RAYS);
+    FAIL(RRT_E_ARG, b);
+  }
+  if (n == 0) return RRT_OK;
+  unsigned char* base = nullptr;
+  int rc = static_scratch_for(ctx, &base);
+  if (rc) return rc;
+  const size_t N = (size_t)RRT_STATIC_MAX_RAYS;
+  int* d_cursor = (int*)base; Counters* gc = (Counters*)(base + 256);
+  double* d_o = (double*)(base + 4096); double* d_d = d_o + 3 * N; double* d_mn = d_d + 3 * N; double* d_mx = d_mn + N;
+  rrt_hit* d_out = (rrt_hit*)(d_mx + N);
+  cudaStream_t st = ctx->stream;
+  /* every call shares the array and finds the last call's contents in it: the cursor and the counters must start at zero */
+  CK(cudaMemsetAsync(base, 0, 512, st));
+  CK(cudaMemcpyAsync(d_o, o, 24 * (size_t)n, cudaMemcpyDefault, st)); CK(cudaMemcpyAsync(d_d, d, 24 * (size_t)n, cudaMemcpyDefault, st));
+  if (min_t) CK(cudaMemcpyAsync(d_mn, min_t, 8 * (size_t)n, cudaMemcpyDefault, st));
+  if (max_t) CK(cudaMemcpyAsync(d_mx, max_t, 8 * (size_t)n, cudaMemcpyDefault, st));
+  const double* k_mn = min_t ? d_mn : nullptr; const double* k_mx = max_t ? d_mx : nullptr;
+  int grid = (int)std::min<int64_t>((n + RRT_BLOCK - 1) / RRT_BLOCK, (int64_t)ctx->sm_count * 4);
+#define RRT_CALL(V) if (any_hit) k_hook_trace<true, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc); \
+                    else k_hook_trace<false, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc)
+#define RRT_CALLF(V) if (any_hit) k_hook_trace<true, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc); \
+                    else k_hook_trace<false, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc)
+#define RRT_CALLX(V) if (any_hit) k_hook_trace<true, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc); \
+                    else k_hook_trace<false, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc)
+  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF, RRT_CALLX)
+#undef RRT_CALL
+#undef RRT_CALLF
+#undef RRT_CALLX
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out, d_out, sizeof(rrt_hit) * (size_t)n, cudaMemcpyDefault, st));
+  CK(cudaStreamSynchronize(st));
+  return RRT_OK;
+}
