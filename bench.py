@@ -262,6 +262,7 @@ def main():
     ap.add_argument("--stepper", default="fp64", choices=["fp64", "fp32"],
                     help="geodesic stepper: fp64 = bit-identical to the reference (default, the headline); fp32 = RRT_OPT_STEPPER 1, within 1e-4")
     ap.add_argument("--builder", default="auto", choices=["auto", "host", "device"], help="BVH construction (RRT_OPT_BVH_BUILDER): auto = device LBVH for >= 4096 primitives, else host binned SAH")
+    ap.add_argument("--batch", type=int, default=0, help="override samples_per_batch (the reference's -a batch; default rule: shard.weak_scaling_params)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -302,6 +303,8 @@ def main():
     # spp <= 32 keeps the reference's default adaptive batch (32) from ever triggering; above it the batch is the job's
     # spp so that every rank traces exactly W*H*spp/N paths (stated in config)
     spp_job, batch = shard.weak_scaling_params(spp, world)
+    if args.batch:
+        batch = args.batch
     params = sc.make_params(ns_aa=spp_job, max_ray_depth=m, ns_area_light=l, samples_per_batch=batch, seed=1)
 
     frame = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
