@@ -2,19 +2,24 @@
 """bench.py — headline benchmark of the hot path (per-pixel Monte Carlo radiance estimation with Schwarzschild ray
 bending) on B200.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c5|bunny_bh]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c4|c2|c1|c3|c5|bunny_bh|bunny_box]
+                    [--scaling strong|weak]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 
-One step = one full render of the workload.  Default workload = BASELINE.json configs[1] ("C2"):
-CBspheres_lambertian.dae 480x360, -s 16 -l 4 -m 5, black hole on (the reference's default hole).  The scene is the
-committed flattened copy of that .dae (tests/golden/*.rrtscene, written by the reference's own COLLADA loader).
-At N GPUs the frame is tile-sharded (16x16 interleaved tiles), every rank renders 16*N samples per pixel of its
-tiles (per-GPU work fixed => "scaling": "weak") and the per-rank float4 frames are combined with ONE NCCL reduce.
+One step = one full render of the workload.  Default workload = BASELINE.json configs[3] ("C4"), the configuration the
+north_star's target is stated on: 1920x1080, -s 1024 -l 4 -m 5, black hole on, the reference's default adaptive sampling
+(batch 32, tolerance 0.05, src/application.h:56-57).  CBdragon.dae is not in the reference tree
+(/root/reference/.MISSING_LARGE_BLOBS), so the scene is the largest bundled Cornell-box scene,
+CBbunny_microfacet_cu.dae ("CBdragon substitute"), as the committed flattened copy the reference's own COLLADA loader wrote.
+At N GPUs the SAME frame at the SAME spp is tile-sharded (16x16 interleaved tiles; "scaling": "strong") and the per-rank
+float4 frames are combined with ONE NCCL reduce; --scaling weak keeps round 1's rule (spp x N).
 
-Prints ONE JSON line (rank 0).  `value` = Mpaths/s with everything resident in HBM; `e2e` = the same through the
-public host-buffer API (scene upload + render + frame read-back inside the timed region).
+Prints ONE JSON line (rank 0).  `value` = Mpaths/s with everything resident in HBM (path = one traced camera sample, i.e. the
+sum of the per-pixel sample counts after adaptive stopping); `e2e` = the same through the public host-buffer API (scene
+upload + BVH build + render + frame read-back inside the timed region).  `roofline` is the FP64 pipe's: the trace kernel
+(geodesic advance + BVH intersect, ~90 % of a step) is bound by FP64 instruction issue, its scene data is L1/L2 resident.
 --impl reference times the reference's own CPU path tracer (oracle/_ref/ref_bh, built from /root/reference by
-oracle/build_ref.sh; falls back to the OpenMP oracle port when that binary is absent) on the host cores.
+oracle/build_ref.sh) on the host cores, on a bounded sample of the same workload (see cpu_sample).
 """
 import argparse
 import importlib
@@ -41,8 +46,14 @@ WORKLOADS = {
            "C1: CBspheres_lambertian.dae 480x360 -s 16 -l 4 -m 5, flat spacetime"),
     "c3": ("cbbunny_microfacet_480x360", "CBbunny_microfacet_cu.dae", 1280, 720, 256, 4, 5, "flat",
            "C3: CBbunny_microfacet_cu.dae 1280x720 -s 256 -l 4 -m 5, flat spacetime"),
+    "c4": ("cbbunny_microfacet_480x360", "CBbunny_microfacet_cu.dae", 1920, 1080, 1024, 4, 5, "bh",
+           "C4 (CBdragon substitute: CBdragon.dae is not in the reference tree): CBbunny_microfacet_cu.dae 1920x1080 -s 1024 -l 4 -m 5, "
+           "Schwarzschild hole on (0,1,0) r=0.1 dtheta=0.1, adaptive sampling at the reference's defaults (batch 32, tolerance 0.05)"),
     "bunny_bh": ("cbbunny_microfacet_480x360", "CBbunny_microfacet_cu.dae", 1920, 1080, 16, 4, 5, "bh",
                  "C4 substitute (CBdragon.dae is not in the reference tree): CBbunny_microfacet_cu.dae 1920x1080 -s 16 -l 4 -m 5, hole on"),
+    "bunny_box": ("cbbunny_microfacet_480x360", "CBbunny_microfacet_cu.dae", 480, 360, 64, 4, 5, "bh",
+                  "CBbunny_microfacet_cu.dae 480x360 -s 64 -l 4 -m 5, hole on: the in-box pixels of the 1080p frame (the box covers the same "
+                  "460x345 pixels at every -r, SURVEY App. C)"),
     "c5": ("synth:c5", None, 3840, 2160, 4, 4, 5, "bh",
            "C5 at reduced spp: procedural Cornell box + displaced UV sphere, 1,002,540 triangles (synth.py, seed 184), 3840x2160 -s 4 "
            "(the config names 4096 spp) -l 4 -m 5, hole on; BVH nodes + FP64 leaf records = 115 MB"),
@@ -165,8 +176,21 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ CPU arms
-def run_reference_binary(wl, spp, threads):
-    """One run of the UNMODIFIED reference CPU path tracer (oracle/_ref/ref_bh or ref_flat).  Returns (paths, seconds, rays)."""
+# Workloads whose spp exceeds the adaptive batch: the reference's adaptive rule (src/part1_code.cpp:147-159) stops a pixel at the
+# first batch boundary where 1.96 sigma / sqrt(n) <= tol * mu, so the frame's paths are far from W*H*spp and fall in two classes with
+# very different costs.  Class A = pixels outside the central 480x360 cell: at every -r the Cornell box covers the same central
+# pixels (the reference fixes screenDist at 800x600, SURVEY finding 0.1-4), outside it every camera ray escapes, mu = sigma = 0, and
+# the pixel stops after exactly one batch of one-ray paths.  Class B = the central cell: the in-box pixels, ~15 rays per path.
+# ADAPTIVE[wl] = paths of the whole frame and of class B, measured by the GPU arm (deterministic: seed 1; the GPU arm re-measures
+# them every run and says so in config.class_mix if they moved) — the CPU arms need them to weight their two per-class rates.
+ADAPTIVE = {
+    "c4": {"batch": 32, "tol": 0.05, "cell": (720, 360, 480, 360), "paths_total": 222926816, "paths_cell": 162101216},
+}
+
+
+def run_reference_binary(wl, spp, threads, cell=None):
+    """One run of the UNMODIFIED reference CPU path tracer (oracle/_ref/ref_bh or ref_flat), optionally on a -p cell
+    (reference src/main.cpp:99-105).  Returns (paths, seconds, rays) or None when the binary / scene is not there."""
     fixture, dae, W, H, _, l, m, mode, _ = WORKLOADS[wl]
     exe = os.path.join(ROOT, "oracle", "_ref", "ref_bh" if mode == "bh" else "ref_flat")
     scene = os.path.join(ROOT, "oracle", "_ref", "dae", dae or "-")
@@ -176,16 +200,14 @@ def run_reference_binary(wl, spp, threads):
         return None
     with tempfile.TemporaryDirectory() as td:
         out = os.path.join(td, "o.png")
-        cell = []
         if synthetic:
-            # the procedural scene as a COLLADA file the reference's own loader reads (synth.write_c5_dae: vertices as float32),
-            # and a bounded sample: the centre cell of the frame, 1/16 of its area (it holds the mesh: heavier than the average pixel)
+            # the procedural scene as a COLLADA file the reference's own loader reads (synth.write_c5_dae: vertices as float32)
             synth = importlib.import_module("relativistic-ray-tracer_b200.synth")
             scene = os.path.join(td, "c5.dae")
             synth.write_c5_dae(scene, open(template).read())
-            cw, ch = W // 4, H // 4
-            cell = ["-p", str((W - cw) // 2), str((H - ch) // 2), str(cw), str(ch)]
-        cmd = [exe, "-t", str(threads), "-s", str(spp), "-l", str(l), "-m", str(m), "-r", str(W), str(H)] + cell + ["-f", out, scene]
+        cellarg = ["-p"] + [str(v) for v in cell] if cell else []
+        # -a <spp+1> 0: no adaptive stop inside a CPU sample (it only acts above 32 spp anyway)
+        cmd = [exe, "-t", str(threads), "-s", str(spp), "-l", str(l), "-m", str(m), "-r", str(W), str(H)] + cellarg + ["-f", out, scene]
         t0 = time.perf_counter()
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         wall = time.perf_counter() - t0
@@ -193,7 +215,7 @@ def run_reference_binary(wl, spp, threads):
     ms = re.findall(r"100%! \(([0-9.]+)s\)", txt)          # reference src/pathtracer.cpp:636
     rays = re.findall(r"BVH traced (\d+) rays", txt)       # reference src/pathtracer.cpp:637
     secs = float(ms[-1]) if ms else wall
-    npx = (W // 4) * (H // 4) if synthetic else W * H
+    npx = cell[2] * cell[3] if cell else W * H
     return npx * spp, secs, int(rays[-1]) if rays else 0
 
 
@@ -210,17 +232,71 @@ def run_oracle_port(wl, spp):
     return int(cnt.sum()), time.perf_counter() - t0, st["rays"]
 
 
-def cpu_sample(wl, spp=1):
+_T1_CACHE = {}
+
+
+def t1_versus_tn(wl, cores):
+    """-t 1 beside -t <cores> (the reference's shared rand() lock, src/random_util.h:11-13, can make one thread the
+    faster arm), once per process, on a small cell of the in-box region.  Returns (rate_t1, rate_tn, cell) in Mpaths/s or None."""
+    if wl in _T1_CACHE:
+        return _T1_CACHE[wl]
+    fixture, dae, W, H = WORKLOADS[wl][:4]
+    cw, ch = 96, 72
+    cell = ((W - cw) // 2 - 2 * cw, (H - ch) // 2, cw, ch)     # left of the hole's image: walls, floor and mesh, no captured pixels
+    if cell[0] < 0:
+        cell = (max((W - cw) // 2, 0), max((H - ch) // 2, 0), min(cw, W), min(ch, H))
+    a = run_reference_binary(wl, 1, 1, cell)
+    b = run_reference_binary(wl, 1, cores, cell) if a else None
+    _T1_CACHE[wl] = (a[0] / a[1] / 1e6, b[0] / b[1] / 1e6, cell) if a and b else None
+    return _T1_CACHE[wl]
+
+
+def cpu_sample(wl, spp=1, with_t1=True):
+    """Bounded CPU sample of the workload on the host cores, as paths/s of the whole workload.
+    * workloads without adaptive stopping (spp <= 32): every path costs the same on average -> the same frame at `spp` samples
+      (C5: a strided set of 4 x 4 cells, 1/16 of the frame's area spread over the whole frame).
+    * adaptive workloads (ADAPTIVE above): per-class rates r_A, r_B from the LEFT HALF of each class's cell at 1 spp (the scene is
+      mirror-symmetric up to the mesh), combined with the workload's own class mix: rate = (P_A + P_B) / (P_A / r_A + P_B / r_B).
+    The thread count is the faster of -t 1 and -t <cores> measured on a small cell (both rates are in `sample`)."""
     cores = os.cpu_count() or 1
-    res = run_reference_binary(wl, spp, cores)
-    if res is not None:
-        paths, secs, rays = res
-        what = "centre cell (1/16 of the frame) of the same scene exported as .dae," if WORKLOADS[wl][0] == "synth:c5" else "same frame"
-        return {"value": paths / secs / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "reference",
-                "sample": "reference binary (oracle/_ref) -t %d, %s at -s %d: %d paths in %.2f s, %d rays" % (cores, what, spp, paths, secs, rays)}
-    paths, secs, rays = run_oracle_port(wl, spp)
-    return {"value": paths / secs / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
-            "sample": "oracle port (OpenMP, %d threads), same frame at %d spp: %d paths in %.2f s, %d rays" % (cores, spp, paths, secs, rays)}
+    fixture, dae, W, H = WORKLOADS[wl][:4]
+    mode = WORKLOADS[wl][7]
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_bh" if mode == "bh" else "ref_flat")
+    have_scene = os.path.exists(os.path.join(ROOT, "oracle", "_ref", "dae", dae or "CBspheres_lambertian.dae"))
+    if not (os.path.exists(exe) and have_scene):
+        paths, secs, rays = run_oracle_port(wl, spp)
+        return {"value": paths / secs / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
+                "sample": "oracle port (OpenMP, %d threads), same frame at %d spp: %d paths in %.2f s, %d rays" % (cores, spp, paths, secs, rays)}
+    t1 = t1_versus_tn(wl, cores) if with_t1 else None
+    threads = 1 if (t1 and t1[0] > t1[1]) else cores
+    t1_txt = ("; -t 1 vs -t %d on cell %s at 1 spp: %.5f vs %.5f Mpaths/s -> -t %d used" % (cores, list(t1[2]), t1[0], t1[1], threads)) if t1 else ""
+    ad = ADAPTIVE.get(wl)
+    if ad and ad.get("paths_cell"):
+        cx, cy, cw, ch = ad["cell"]
+        pB = ad["paths_cell"]; pA = ad["paths_total"] - pB
+        b = run_reference_binary(wl, 1, threads, (cx, cy, cw // 2, ch))             # class B: left half of the central cell
+        a = run_reference_binary(wl, 1, threads, (0, cy, cw // 2, ch))              # class A: same size, frame's left edge
+        rA, rB = a[0] / a[1], b[0] / b[1]
+        v = (pA + pB) / (pA / rA + pB / rB) / 1e6
+        return {"value": v, "unit": "Mpaths/s", "cores": threads, "kind": "reference", "seconds": a[1] + b[1],
+                "sample": "reference binary (oracle/_ref) -t %d at 1 spp on two %dx%d cells of the same frame: in-box class (left half of the central "
+                          "480x360 cell) %d paths / %d rays in %.2f s, background class (frame's left edge) %d paths in %.2f s; weighted by the workload's "
+                          "class mix %d : %d paths%s" % (threads, cw // 2, ch, b[0], b[2], b[1], a[0], a[1], pB, pA, t1_txt)}
+    if fixture == "synth:c5":
+        # 16 cells of 1/256 of the frame each, on a 4 x 4 lattice over the whole frame (centre cell alone holds the mesh and is heavier
+        # than the average pixel: ADVICE r01)
+        cw, ch = W // 16, H // 16
+        paths = rays = 0; secs = 0.0
+        for j in range(4):
+            for i in range(4):
+                r = run_reference_binary(wl, spp, threads, ((2 * i + 1) * W // 8 - cw // 2, (2 * j + 1) * H // 8 - ch // 2, cw, ch))
+                paths += r[0]; secs += r[1]; rays += r[2]
+        what = "16 cells of %dx%d on a 4x4 lattice over the frame (1/16 of its area), scene exported as .dae," % (cw, ch)
+    else:
+        paths, secs, rays = run_reference_binary(wl, spp, threads)
+        what = "same frame"
+    return {"value": paths / secs / 1e6, "unit": "Mpaths/s", "cores": threads, "kind": "reference", "seconds": secs,
+            "sample": "reference binary (oracle/_ref) -t %d, %s at -s %d: %d paths in %.2f s, %d rays%s" % (threads, what, spp, paths, secs, rays, t1_txt)}
 
 
 def reference_arm(args):
@@ -228,20 +304,19 @@ def reference_arm(args):
     if rank != 0:
         return
     wl = args.workload
-    times, paths = [], 0
+    vals, secs = [], []
     last = None
     for i in range(args.warmup + args.steps):
         last = cpu_sample(wl, 1)
-        m = re.search(r"(\d+) paths in ([0-9.]+) s", last["sample"])
         if i >= args.warmup:
-            paths += int(m.group(1)); times.append(float(m.group(2)))
-    total = sum(times)
-    v = paths / total / 1e6
+            vals.append(last["value"]); secs.append(last.get("seconds", 0.0))
+    # every step is the same sample: the run's rate is the harmonic mean of the steps' rates (total paths / total time)
+    v = len(vals) / sum(1.0 / x for x in vals)
     last["value"] = v
     print(json.dumps({"impl": "reference", "metric": "Mpaths/s", "value": v, "unit": "Mpaths/s", "n_gpus": args.gpus, "steps": args.steps,
-                      "warmup": args.warmup, "ms_per_step": 1e3 * total / max(args.steps, 1), "higher_is_better": True, "scaling": "weak",
+                      "warmup": args.warmup, "ms_per_step": 1e3 * sum(secs) / max(args.steps, 1), "higher_is_better": True, "scaling": args.scaling,
                       "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                      "config": {"workload": WORKLOADS[wl][8], "sample": "each step = the same frame at 1 spp on the host cores"},
+                      "config": {"workload": WORKLOADS[wl][8], "sample": "each step = one bounded CPU sample of the workload on the host cores (cpu_baseline.sample)"},
                       "cpu_baseline": last, "e2e": {"value": v, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
@@ -249,10 +324,11 @@ def reference_arm(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"], help="N > 1: strong = same frame and spp for every N (default); weak = spp x N")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel")
     ap.add_argument("--topology", type=int, default=1)
     ap.add_argument("--leaf", type=int, default=2)
@@ -286,7 +362,20 @@ def main():
     fixture, _, W, H, spp, l, m, mode, desc = WORKLOADS[args.workload]
     if args.spp:
         spp = args.spp
-    spp_job = spp * world                       # weak scaling: per-GPU paths fixed
+    ad = ADAPTIVE.get(args.workload) if not args.spp else None
+    if args.scaling == "weak":
+        # round 1's rule: frame fixed, spp x N, one batch = the whole job (no adaptive stop) above 32 spp
+        spp_job, batch = shard.weak_scaling_params(spp, world)
+        rule = "weak: frame fixed, spp = %d x n_gpus, 16x16 interleaved tiles, one NCCL reduce per frame" % spp
+    else:
+        # strong: the SAME frame at the SAME spp and batch for every N (the reference hands a fixed frame's tiles to N workers,
+        # src/pathtracer.cpp:243-255).  Adaptive workloads keep the reference's default batch; the others keep the whole job in one
+        # batch above 32 spp so that every pixel takes exactly spp samples.
+        spp_job = spp
+        batch = ad["batch"] if ad else (32 if spp <= 32 else spp)
+        rule = "strong: same frame, spp and batch for every N; 16x16 interleaved tiles, one NCCL reduce per frame"
+    if args.batch:
+        batch = args.batch
     s = workload_scene(args.workload)
     ctx = api.Context(local)
     ctx.set_option(api.OPT_BVH_TOPOLOGY, args.topology)
@@ -300,18 +389,15 @@ def main():
     ctx.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
     ctx.set_frame(W, H)
     ctx.set_tile_shard(shard.DEFAULT_TILE, rank, world)
-    # spp <= 32 keeps the reference's default adaptive batch (32) from ever triggering; above it the batch is the job's
-    # spp so that every rank traces exactly W*H*spp/N paths (stated in config)
-    spp_job, batch = shard.weak_scaling_params(spp, world)
-    if args.batch:
-        batch = args.batch
-    params = sc.make_params(ns_aa=spp_job, max_ray_depth=m, ns_area_light=l, samples_per_batch=batch, seed=1)
+    params = sc.make_params(ns_aa=spp_job, max_ray_depth=m, ns_area_light=l, samples_per_batch=batch,
+                            max_tolerance=ad["tol"] if ad else 0.05, seed=1)
 
     frame = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    counts = torch.zeros((H, W), dtype=torch.int32, device="cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
-    def step_device():
-        st = ctx.render_device(params, frame.data_ptr(), 0, 0, want_stats=True)
+    def step_device(want_counts=False):
+        st = ctx.render_device(params, frame.data_ptr(), counts.data_ptr() if want_counts else 0, 0, want_stats=True)
         shard.assemble(frame)
         return st
 
@@ -320,9 +406,13 @@ def main():
         clocks.start()          # early: NVML's first calls are slow; only samples inside the timed window are reported
     for _ in range(args.warmup):
         step_device()
-    # ---- instrumented pass (counters on) for the algorithmic-byte and work figures; deterministic, so it describes
-    # the timed passes exactly.  Timed passes run with counters off.
-    st_count = step_device()
+    # ---- instrumented pass (counters on) for the work figures; deterministic, so it describes the timed passes exactly.
+    # Timed passes run with counters off.
+    st_count = step_device(want_counts=True)
+    cell_paths = 0.0
+    if ad:
+        cx, cy, cw, ch = ad["cell"]
+        cell_paths = float(counts[cy:cy + ch, cx:cx + cw].sum().item())
     ctx.set_option(api.OPT_COUNTERS, 0)
     step_device()
 
@@ -384,61 +474,90 @@ def main():
         rt.cudaHostUnregister(a.ctypes.data)
 
     t = torch.tensor([total_ms, e2e_s, trace_s, float(st_count["paths"]), float(st_count["geodesic_steps"]), float(st_count["rays"]),
-                      float(st_count["algorithmic_bytes"])], dtype=torch.float64, device="cuda")
+                      float(st_count["algorithmic_bytes"]), float(st_count["tri_tests"]), float(st_count["sphere_tests"]), float(st_count["node_visits"]),
+                      cell_paths, render_s], dtype=torch.float64, device="cuda")
+    rank_ms = [render_s * 1e3 / max(args.steps, 1)]
     if world > 1:
         mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        total_ms, e2e_s, trace_s = float(mx[0]), float(mx[1]), float(mx[2])
-        paths, steps_geo, rays, alg_bytes = float(sm[3]), float(sm[4]), float(sm[5]), float(sm[6])
+        allr = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allr, t)
+        rank_ms = [float(x[11]) * 1e3 / max(args.steps, 1) for x in allr]
+        total_ms, e2e_s = float(mx[0]), float(mx[1])
+        trace_sum_s = float(sm[2])
+        paths, steps_geo, rays, alg_bytes, tris, sphs, nodes, cell_paths = [float(x) for x in sm[3:11]]
     else:
-        paths, steps_geo, rays, alg_bytes = [float(x) for x in t[3:7]]
+        trace_sum_s = trace_s
+        paths, steps_geo, rays, alg_bytes, tris, sphs, nodes, cell_paths = [float(x) for x in t[3:11]]
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
     secs = total_ms * 1e-3
-    peak, peak_src = peaks()
+    hbm_peak, hbm_src = peaks()
     binfo = api.bvh_build_host(s, args.topology) if s.n_prims <= 200000 else None
     scene_bytes = (64 * binfo["flat_nodes"] + 80 * binfo["leaf_records"]) if binfo else 64 * (s.n_prims // 2) + 80 * s.n_prims
-    # roofline of the dominant kernel (trace: geodesic-advance + BVH intersect): rank-0 algorithmic bytes / rank-0 trace time
-    my_bytes = float(st_count["algorithmic_bytes"])
-    my_trace_s = float(t[2]) / max(args.steps, 1)
-    achieved = my_bytes / my_trace_s / 1e9 if my_trace_s > 0 else 0.0
+    # ---- roofline of the dominant kernel (trace: geodesic advance + BVH intersect), job-wide: algorithmic work of all ranks over the
+    # summed trace time of all ranks per step (= one GPU's rate; at N = 1 simply rank 0's)
+    trace_s_per_step = trace_sum_s / max(args.steps, 1) / world
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             traffic = json.load(f).get(args.workload)
     except (OSError, ValueError):
         pass
+    alg_gbs = alg_bytes / world / trace_s_per_step / 1e9 if trace_s_per_step > 0 else 0.0
+    algorithmic = {"bytes_per_step": alg_bytes, "rate": alg_gbs, "unit": "GB/s", "served_by": "L1/L2",
+                   "hbm_peak": hbm_peak, "hbm_peak_source": hbm_src, "scene_bytes": scene_bytes,
+                   "note": "SURVEY 8(d) bytes (64 B per node record, 80 B per triangle test, 32 B per sphere test, 160 B per ray): served by the caches "
+                           "(scene = %.1f MB against a 126 MB L2; DRAM traffic of the longest launch in `traffic`), NOT a DRAM utilisation" % (scene_bytes / 1e6)}
+    hole = steps_geo > rays
+    if hole and args.stepper == "fp64":
+        # FP64 instructions the path needs, per unit (thread instructions; /32 = warp instructions at full lanes):
+        #   chord = next_micro_ray + horizon_hit = 174.5 (ncu on tools/ilp_probe.cu, profiles/r01_i_fp64_step_probe.txt)
+        #   triangle test = 61, sphere test = 36 (Moller-Trumbore / quadratic run to completion; counted from the source: upper bounds,
+        #   most tests leave at the first sign test) -- 2-6 % of the total
+        fp64_warp_instr = (174.5 * steps_geo + 61.0 * tris + 36.0 * sphs) / 32.0
+        peak = 578.7     # G FP64 warp-instr/s: plain independent DADD / DMUL stream on this part (DFMA: 533.2); tools/fp64_peak_probe.cu
+        ach = fp64_warp_instr / world / trace_s_per_step / 1e9 if trace_s_per_step > 0 else 0.0
+        roof = {"bound": "fp64_pipe", "achieved": ach, "peak": peak, "unit": "G FP64 warp-instr/s", "frac": ach / peak,
+                "traffic": traffic["dram_bytes"] if traffic else None,
+                "peak_source": "measured on B200: profiles/r02_a_fp64_peak_probe.txt (DADD / DMUL 578.7, DFMA 533.2 G warp-instr/s = 1.99 / 1.83 per clk per SM at 1965 MHz)",
+                "per_unit": {"chord": 174.5, "triangle_test": 61, "sphere_test": 36},
+                "stepper_alone": {"achieved": steps_geo / world / trace_s_per_step / 1e9 if trace_s_per_step > 0 else 0.0, "peak": 48.5, "unit": "G chords/s",
+                                  "note": "next_micro_ray + horizon_hit alone, from registers, saturate at 48.5 G chords/s = 46 % of the pipe's plain-stream peak "
+                                          "(tools/ilp_probe.cu): the reachable ceiling of this instruction mix (6 divisions + 4 square roots per chord)"}}
+    else:
+        roof = {"bound": "hbm", "achieved": alg_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": alg_gbs / hbm_peak,
+                "traffic": traffic["dram_bytes"] if traffic else None, "peak_source": hbm_src,
+                "note": "flat spacetime / FP32 stepper: no FP64 stepping; the bytes are the SURVEY 8(d) algorithmic bytes, served by L1/L2 (see `algorithmic`)"}
+    roof.update({"traffic_of": (traffic["kernel"] + "; " + traffic["source"]) if traffic else None,
+                 "kernel": "k_trace_closest + k_trace_shadow (geodesic advance + BVH intersect)",
+                 "trace_ms_per_step": trace_s_per_step * 1e3, "trace_launches_per_step": trace_launches / max(args.steps, 1),
+                 "trace_share_of_step": trace_s / (render_s if render_s > 0 else 1.0), "algorithmic": algorithmic})
+    cfg = {"workload": desc, "frame": [W, H], "spp": spp_job, "ns_area_light": l, "max_ray_depth": m, "samples_per_batch": batch,
+           "max_tolerance": ad["tol"] if ad else 0.05, "adaptive_stop": bool(ad) or spp_job > batch,
+           "parallelism": "tile%d" % world, "bvh_topology": args.topology, "bvh_leaf": args.leaf, "trace_variant": args.variant, "clearance_grid": args.grid,
+           "bvh_width": args.width, "stepper": args.stepper, "bvh_builder": args.builder, "l2": "flushed between timed iterations (256 MiB write)",
+           "scaling_rule": rule}
+    if ad:
+        cfg["class_mix"] = {"cell": list(ad["cell"]), "paths_cell": cell_paths, "paths_total": paths,
+                            "matches_table": bool(ad.get("paths_cell") == cell_paths and ad.get("paths_total") == paths)}
+        ad = dict(ad, paths_cell=int(cell_paths), paths_total=int(paths))
+        ADAPTIVE[args.workload] = ad
     line = {
         "metric": "Mpaths/s", "value": paths * args.steps / secs / 1e6, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": desc, "frame": [W, H], "spp": spp_job, "ns_area_light": l, "max_ray_depth": m, "samples_per_batch": batch,
-                   "parallelism": "tile%d" % world, "bvh_topology": args.topology, "bvh_leaf": args.leaf, "trace_variant": args.variant, "clearance_grid": args.grid, "bvh_width": args.width, "stepper": args.stepper, "bvh_builder": args.builder, "l2": "flushed between timed iterations (256 MiB write)",
-                   "scaling_rule": "frame fixed, spp = %d x n_gpus, 16x16 interleaved tiles, one NCCL reduce per frame" % spp},
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": cfg,
         "geodesic_steps_per_s": steps_geo * args.steps / secs, "rays_per_s": rays * args.steps / secs,
-        "paths_per_step": paths, "geodesic_steps_per_step": steps_geo, "rays_per_step": rays,
+        "paths_per_step": paths, "geodesic_steps_per_step": steps_geo, "rays_per_step": rays, "node_visits_per_step": nodes,
+        "rank_render_ms": {"min": min(rank_ms), "max": max(rank_ms), "all": [round(x, 3) for x in rank_ms]},
         "e2e": {"value": paths * args.steps / e2e_s / 1e6, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic["dram_bytes"] if traffic else None,
-                     "traffic_of": (traffic["kernel"] + "; " + traffic["source"]) if traffic else None,
-                     "kernel": "k_trace_closest + k_trace_shadow (geodesic advance + BVH intersect)", "peak_source": peak_src,
-                     "algorithmic_bytes_per_step": my_bytes, "trace_ms_per_step": my_trace_s * 1e3,
-                     "trace_launches_per_step": trace_launches / max(args.steps, 1),
-                     "trace_share_of_step": trace_s / (render_s if render_s > 0 else 1.0),
-                     "scene_bytes": scene_bytes,
-                     "note": ("BVH nodes + leaf records = %.1f MB: %s" % (scene_bytes / 1e6,
-                              "L1/L2 resident: the algorithmic bytes are served by the caches (compare `traffic`, the DRAM bytes of the same launch), so this fraction is not a DRAM utilisation and can exceed 1; the kernel is instruction-issue bound (ncu: 74 % of issue slots), see DESIGN.md section 6 and the fp64_step view"
-                              if scene_bytes < 100e6 else "close to the 126 MB L2, yet served by it (ncu, profiles/traffic.json: L2 hit rate 95 %, 0.35 GB of DRAM traffic in the longest launch); the kernel is issue- / FP64-bound, see DESIGN.md section 6"))},
+        "roofline": roof,
         "clocks": clk,
     }
-    if steps_geo > rays and args.stepper == "fp64":   # hole on: the geodesic step is FP64 and its pipe, not HBM, is what the trace kernel runs against
-        my_chords = float(st_count["geodesic_steps"])
-        ceil = 48.5e9      # next_micro_ray + horizon_hit alone, saturated (tools/ilp_probe.cu on a B200)
-        line["roofline"]["fp64_step"] = {"achieved": my_chords / my_trace_s / 1e9 if my_trace_s > 0 else 0.0, "peak": ceil / 1e9, "unit": "G chords/s",
-                                         "frac": (my_chords / my_trace_s / ceil) if my_trace_s > 0 else 0.0,
-                                         "peak_source": "measured: profiles/r01_i_fp64_step_probe.txt (174.5 FP64 warp instructions per chord)"}
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_sample(args.workload, 1)
     print(json.dumps(line))

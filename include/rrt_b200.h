@@ -165,10 +165,11 @@ enum {
   RRT_OPT_BVH_TOPOLOGY = 0, /* 0 = the reference's midpoint-split tree shape, 1 = binned SAH (default); takes effect at the next rrt_upload_scene */
   RRT_OPT_COUNTERS = 1,     /* 1 (default) = trace kernels count rays / chords / node visits / primitive tests for rrt_stats */
   RRT_OPT_WORK_BYTES = 2,   /* upper bound for the wavefront work buffers in bytes (default 12 GiB) */
-  RRT_OPT_TRACE_KERNEL = 3, /* trace kernel variant, see DESIGN.md (0 = default) */
+  RRT_OPT_TRACE_KERNEL = 3, /* trace kernel variant: 0 = chord-lockstep loop (default).  A/B builds of the library only (make EXTRA=-DRRT_AB=1; otherwise
+                               RRT_E_ARG): 1 = vote-scheduled state machine, 2 = decoupled stepping, both measured slower */
   RRT_OPT_LEAF_SIZE = 4,    /* primitives per leaf for topology 1 (1..7, default 2); takes effect at the next rrt_upload_scene */
   RRT_OPT_CLEARANCE_GRID = 5, /* cells along the longest axis of the empty-space grid (0 = off, the default); next rrt_upload_scene */
-  RRT_OPT_BVH_WIDTH = 6,      /* children per node on the device: 2, 4, 8, or 0 (default) = 8 for scenes of <= 128 primitives, else 2; topology 0 and trace kernel 1 always use 2; next rrt_upload_scene */
+  RRT_OPT_BVH_WIDTH = 6,      /* children per node on the device: 2, 8 (4 in A/B builds only), or 0 (default) = 8 for scenes of <= 128 primitives, else 2; topology 0 and trace kernel 1 always use 2; next rrt_upload_scene */
   RRT_OPT_SHADE_SPLIT = 7,    /* direct lighting: 1 = its own kernel, one thread per light sample; 0 = inside k_shade's per-vertex loop; 2 (default) = 1 when the scene has a microfacet material, else 0 */
   RRT_OPT_STEPPER = 8,        /* geodesic stepper with the hole on: 0 (default) = the reference's recurrence in IEEE double, bit-identical chords;
                                  1 = the same recurrence carried as (orbital frame, u, u') in FP32 registers (BASELINE.json north_star item 3):

@@ -145,7 +145,11 @@ void rrt_destroy(rrt_ctx* ctx) {
 
 int rrt_set_option(rrt_ctx* ctx, int option, int64_t value) {
   if (!ctx) return RRT_E_ARG;
-  if (option < 0 || option >= 16) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
+  if (option < 0 || option > RRT_OPT_BVH_BUILDER) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
+#if !RRT_AB
+  if ((option == RRT_OPT_TRACE_KERNEL && value != 0) || (option == RRT_OPT_BVH_WIDTH && value == 4))
+    FAIL(RRT_E_ARG, "rrt_set_option: this variant is compiled only into A/B builds (make EXTRA=-DRRT_AB=1)");
+#endif
   ctx->opt[option] = value;
   return RRT_OK;
 }
@@ -489,55 +493,115 @@ static int compact(rrt_ctx* ctx, Keep keep, const uint32_t* in, uint32_t n, uint
 
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
-/* trace-kernel dispatch: COUNT (instrumented) x variant (RRT_OPT_TRACE_KERNEL: 0 chord-lockstep, 1 vote-scheduled) */
-/* bytes of one node record as the running kernel fetches it: 64 (two child boxes) or 32 per child of a wide node */
+/* ---- trace-kernel selection.  Template arguments of the kernels in rrt_wavetrace.cuh:
+ *   V    = node form / scheduler: 0 lockstep-or-decoupled over binary nodes, 8 over 8-wide nodes; A/B builds (-DRRT_AB=1) add 1 = vote-scheduled
+ *          state machine (binary nodes) and 4 = 4-wide nodes, both measured slower
+ *   STEP = 0 hole on, FP64 stepper, chord-lockstep loop (the default); 1 hole on, FP32 stepper (RRT_OPT_STEPPER = 1); 2 flat spacetime;
+ *          A/B builds add 3 = hole on, FP64 stepper, decoupled stepping (RRT_OPT_TRACE_KERNEL = 2), measured slower (rrt_wavetrace.cuh)
+ * bytes of one node record as the running kernel fetches it: 64 (two child boxes) or 32 per child of a wide node */
+#ifndef RRT_AB
+#define RRT_AB 0
+#endif
 static uint64_t node_record_bytes(const rrt_ctx* ctx) {
   if (ctx->opt[RRT_OPT_TRACE_KERNEL] == 1 || ctx->ds.width <= 2) return 64;
   return 32ull * (uint64_t)ctx->ds.width;
 }
-/* kernel variant: 0 = lockstep over binary nodes, 1 = vote-scheduled (binary nodes), 4 / 8 = lockstep over wide nodes */
 static int trace_variant(const rrt_ctx* ctx) {
   if (ctx->opt[RRT_OPT_TRACE_KERNEL] == 1) return 1;
   return ctx->ds.width == 8 ? 8 : ctx->ds.width == 4 ? 4 : 0;
 }
-#define RRT_VARIANT_SWITCH(v, CALL) \
-  switch (v) { case 1: { CALL(1); break; } case 4: { CALL(4); break; } case 8: { CALL(8); break; } default: { CALL(0); break; } }
 /* RRT_OPT_STEPPER = 1: the FP32 stepper, for the lockstep kernels over binary and 8-wide nodes, hole on */
 static bool fast_stepper(const rrt_ctx* ctx) {
   return ctx->opt[RRT_OPT_STEPPER] == 1 && ctx->bh.mode != RRT_MODE_FLAT && ctx->opt[RRT_OPT_TRACE_KERNEL] != 1 && ctx->ds.width != 4;
 }
-/* third template argument of the lockstep kernels: 0 = hole on / FP64 stepper, 1 = hole on / FP32 stepper, 2 = flat spacetime */
-#define RRT_STEP_SWITCH(ctx, v, CALL, CALLF, CALLX) \
-  if (fast_stepper(ctx)) { if ((v) == 8) { CALLF(8); } else { CALLF(0); } } \
-  else if ((ctx)->bh.mode == RRT_MODE_FLAT && (v) != 1) { if ((v) == 8) { CALLX(8); } else if ((v) == 4) { CALLX(4); } else { CALLX(0); } } \
-  else RRT_VARIANT_SWITCH(v, CALL)
+static int trace_step_mode(const rrt_ctx* ctx) {
+  if (ctx->bh.mode == RRT_MODE_FLAT) return 2;
+  if (fast_stepper(ctx)) return 1;
+  return (RRT_AB && ctx->opt[RRT_OPT_TRACE_KERNEL] == 2) ? 3 : 0;
+}
+typedef void (*closest_fn)(const DevScene, const DevHole, const double*, size_t, const int*, int*, int*, double*, Counters*);
+typedef void (*shadow_fn)(const DevScene, const DevHole, const double*, size_t, const int*, int*, const uint32_t*, int*, Counters*);
+typedef void (*hook_fn)(const DevScene, const DevHole, int, const double*, const double*, const double*, const double*, rrt_hit*, int*, Counters*);
+
+template <bool COUNT, int V> static closest_fn closest_of_step(int step) {
+  switch (step) {
+    case 1: if constexpr (V != 4) return k_trace_closest<COUNT, V, 1>; else return k_trace_closest<COUNT, V, 0>;
+    case 2: return k_trace_closest<COUNT, V, 2>;
+#if RRT_AB
+    case 3: return k_trace_closest<COUNT, V, 3>;
+#endif
+    default: return k_trace_closest<COUNT, V, 0>;
+  }
+}
+template <bool COUNT> static closest_fn closest_kernel(int v, int step) {
+  switch (v) {
+#if RRT_AB
+    case 1: return k_trace_closest<COUNT, 1, 0>;
+    case 4: return closest_of_step<COUNT, 4>(step);
+#endif
+    case 8: return closest_of_step<COUNT, 8>(step);
+    default: return closest_of_step<COUNT, 0>(step);
+  }
+}
+template <bool ANY, bool COUNT, int V> static shadow_fn shadow_of_step(int step) {
+  switch (step) {
+    case 1: if constexpr (V != 4) return k_trace_shadow<ANY, COUNT, V, 1>; else return k_trace_shadow<ANY, COUNT, V, 0>;
+    case 2: return k_trace_shadow<ANY, COUNT, V, 2>;
+#if RRT_AB
+    case 3: return k_trace_shadow<ANY, COUNT, V, 3>;
+#endif
+    default: return k_trace_shadow<ANY, COUNT, V, 0>;
+  }
+}
+template <bool ANY, bool COUNT> static shadow_fn shadow_kernel(int v, int step) {
+  switch (v) {
+#if RRT_AB
+    case 1: return k_trace_shadow<ANY, COUNT, 1, 0>;
+    case 4: return shadow_of_step<ANY, COUNT, 4>(step);
+#endif
+    case 8: return shadow_of_step<ANY, COUNT, 8>(step);
+    default: return shadow_of_step<ANY, COUNT, 0>(step);
+  }
+}
+template <bool ANY, int V> static hook_fn hook_of_step(int step) {
+  switch (step) {
+    case 1: if constexpr (V != 4) return k_hook_trace<ANY, V, 1>; else return k_hook_trace<ANY, V, 0>;
+    case 2: return k_hook_trace<ANY, V, 2>;
+#if RRT_AB
+    case 3: return k_hook_trace<ANY, V, 3>;
+#endif
+    default: return k_hook_trace<ANY, V, 0>;
+  }
+}
+template <bool ANY> static hook_fn hook_kernel(int v, int step) {
+  switch (v) {
+#if RRT_AB
+    case 1: return k_hook_trace<ANY, 1, 0>;
+    case 4: return hook_of_step<ANY, 4>(step);
+#endif
+    case 8: return hook_of_step<ANY, 8>(step);
+    default: return hook_of_step<ANY, 0>(step);
+  }
+}
 
 static void launch_closest(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, const double* ray, size_t cap, const int* cnt_ptr, int* cursor, int* h_prim,
                            double* h_geo, Counters* gc) {
-#define RRT_CALL(V) if (count) k_trace_closest<true, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc); \
-                    else k_trace_closest<false, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc)
-#define RRT_CALLF(V) if (count) k_trace_closest<true, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc); \
-                    else k_trace_closest<false, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc)
-#define RRT_CALLX(V) if (count) k_trace_closest<true, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc); \
-                    else k_trace_closest<false, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc)
-  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF, RRT_CALLX)
-#undef RRT_CALL
-#undef RRT_CALLF
-#undef RRT_CALLX
+  const int v = trace_variant(ctx), step = trace_step_mode(ctx);
+  closest_fn fn = count ? closest_kernel<true>(v, step) : closest_kernel<false>(v, step);
+  fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc);
 }
 template <bool ANY>
 static void launch_shadow(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, const double* ray, size_t cap, const int* cnt_ptr, int* cursor,
                           const uint32_t* cidx, int* res, Counters* gc) {
-#define RRT_CALL(V) if (count) k_trace_shadow<ANY, true, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc); \
-                    else k_trace_shadow<ANY, false, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc)
-#define RRT_CALLF(V) if (count) k_trace_shadow<ANY, true, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc); \
-                    else k_trace_shadow<ANY, false, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc)
-#define RRT_CALLX(V) if (count) k_trace_shadow<ANY, true, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc); \
-                    else k_trace_shadow<ANY, false, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc)
-  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF, RRT_CALLX)
-#undef RRT_CALL
-#undef RRT_CALLF
-#undef RRT_CALLX
+  const int v = trace_variant(ctx), step = trace_step_mode(ctx);
+  shadow_fn fn = count ? shadow_kernel<ANY, true>(v, step) : shadow_kernel<ANY, false>(v, step);
+  fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc);
+}
+static void launch_hook(rrt_ctx* ctx, bool any_hit, int grid, cudaStream_t st, int n, const double* d_o, const double* d_d, const double* d_mn, const double* d_mx,
+                        rrt_hit* d_out, int* d_cursor, Counters* gc) {
+  const int v = trace_variant(ctx), step = trace_step_mode(ctx);
+  hook_fn fn = any_hit ? hook_kernel<true>(v, step) : hook_kernel<false>(v, step);
+  fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc);
 }
 
 static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_counts, float4* d_rgbn, cudaStream_t user_stream, rrt_stats* stats) {
@@ -778,16 +842,7 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
   cudaEvent_t e0, e1; ctx->events_used = 0; e0 = next_event(ctx); e1 = next_event(ctx);
   CK(cudaEventRecord(e0, ctx->stream));
   int grid = (int)std::min<int64_t>((n + RRT_BLOCK - 1) / RRT_BLOCK, (int64_t)ctx->sm_count * 4);
-#define RRT_CALL(V) if (any_hit) k_hook_trace<true, V><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc); \
-                    else k_hook_trace<false, V><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc)
-#define RRT_CALLF(V) if (any_hit) k_hook_trace<true, V, 1><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc); \
-                    else k_hook_trace<false, V, 1><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc)
-#define RRT_CALLX(V) if (any_hit) k_hook_trace<true, V, 2><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc); \
-                    else k_hook_trace<false, V, 2><<<grid, RRT_BLOCK, 0, ctx->stream>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc)
-  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF, RRT_CALLX)
-#undef RRT_CALL
-#undef RRT_CALLF
-#undef RRT_CALLX
+  launch_hook(ctx, any_hit != 0, grid, ctx->stream, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc);
   CK(cudaEventRecord(e1, ctx->stream));
   CK(cudaMemcpyAsync(out, d_out, sizeof(rrt_hit) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
@@ -1049,16 +1104,7 @@ extern "C" int rrt_trace_rays_static(rrt_ctx* ctx, int64_t n, const double* o, c
   if (max_t) CK(cudaMemcpyAsync(d_mx, max_t, 8 * (size_t)n, cudaMemcpyDefault, st));
   const double* k_mn = min_t ? d_mn : nullptr; const double* k_mx = max_t ? d_mx : nullptr;
   int grid = (int)std::min<int64_t>((n + RRT_BLOCK - 1) / RRT_BLOCK, (int64_t)ctx->sm_count * 4);
-#define RRT_CALL(V) if (any_hit) k_hook_trace<true, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc); \
-                    else k_hook_trace<false, V><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc)
-#define RRT_CALLF(V) if (any_hit) k_hook_trace<true, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc); \
-                    else k_hook_trace<false, V, 1><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc)
-#define RRT_CALLX(V) if (any_hit) k_hook_trace<true, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc); \
-                    else k_hook_trace<false, V, 2><<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc)
-  RRT_STEP_SWITCH(ctx, trace_variant(ctx), RRT_CALL, RRT_CALLF, RRT_CALLX)
-#undef RRT_CALL
-#undef RRT_CALLF
-#undef RRT_CALLX
+  launch_hook(ctx, any_hit != 0, grid, st, (int)n, d_o, d_d, k_mn, k_mx, d_out, d_cursor, gc);
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(out, d_out, sizeof(rrt_hit) * (size_t)n, cudaMemcpyDefault, st));
   CK(cudaStreamSynchronize(st));

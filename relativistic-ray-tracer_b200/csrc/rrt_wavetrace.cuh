@@ -11,6 +11,9 @@
 #pragma once
 #include "rrt_trace.cuh"
 
+#ifndef RRT_AB
+#define RRT_AB 0   /* 1 = also compile the measured-slower A/B variants: the vote-scheduled loop (V = 1) and 4-wide nodes (make EXTRA=-DRRT_AB=1) */
+#endif
 #ifndef RRT_BLOCK
 #define RRT_BLOCK 128
 #endif
@@ -213,6 +216,113 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
   if (COUNT) wt_flush_counters(cnt, gcnt);
 }
 
+#if RRT_AB
+/* ---------------------------------------------------------------- STEP = 3: decoupled stepping (hole on, FP64 stepper; RRT_OPT_TRACE_KERNEL = 2, A/B builds).
+ * MEASURED SLOWER than the lockstep loop on B200 (round 2, profiles/r02_a_ab_decoupled.jsonl; ms per frame, lockstep -> decoupled -> decoupled + 128-cell grid):
+ *   bunny 480x360 64 spp 211.2 -> 217.8 -> 221.8 (node visits 20.2 G -> 20.2 G -> 9.0 G), C2 33.4 -> 35.3 -> 42.3, bunny 1080p 16 spp 97.6 -> 103.2 -> 106.5,
+ *   C5 63.3 -> 68.5.  Halving the node visits buys nothing: a warp's traversal lasts as long as its longest lane, and the chords that
+ *   still need the BVH are the long ones; the clear tests cost FP64-pipe slots (6 FP64 ops + 4 conversions per chord) the stepper needs.
+ * The lockstep loop above pays one BVH traversal per loop trip as long as ANY lane's chord needs one, and the whole warp
+ * waits for it.  Most chords need none: a chord that starts outside the scene box and is shorter than its distance to
+ * the box (chord_outside_root: the escaped rays of a wide frame, 92 % of a 1080p frame's camera rays), or one that is
+ * shorter than the clearance of the grid cell it starts in (chord_is_clear: open space inside the box), provably meets
+ * no primitive, so BVHAccel::intersect_micro would return false for it (reference src/bvh.cpp:107-110 only ever looks at
+ * primitives the chord reaches).  Here a lane whose chord is provably clear simply steps on; a lane whose chord does need
+ * the BVH parks it (`pend`), and the warp votes each trip: STEP while at least RRT_S_THRESH lanes can still step (or
+ * nobody is parked), otherwise TRAVERSE the parked chords — with most lanes taking part instead of a few.  Arithmetic of
+ * every chord, horizon test and primitive test is untouched and chords are visited in order, so results are bit-identical
+ * to the lockstep loop (test_bvh_intersect_matches_reference / test_far_origin_chords_match_oracle run it in A/B builds). */
+#ifndef RRT_S_THRESH
+#define RRT_S_THRESH 8
+#endif
+/* FP32, conservative: true when every point within `len` of p is outside the (outward-rounded) root box.  |p - fl(p)| <=
+ * sqrt(3) 2^-24 max|p_i| < 1.04e-7 m enters the reach L; the float evaluation of the box distance is good to a few 2^-24
+ * relative, covered by the 1e-5 margins.  NaN / inf anywhere compares false: the chord takes the traversal path. */
+__device__ __forceinline__ bool chord_outside_root(const DevScene& sc, const d3& p, double len) {
+  const float px = (float)p.x, py = (float)p.y, pz = (float)p.z;
+  const float m = fmaxf(fmaxf(fabsf(px), fabsf(py)), fabsf(pz));
+  const float ex = fmaxf(fmaxf(sc.root_lo[0] - px, px - sc.root_hi[0]), 0.f);
+  const float ey = fmaxf(fmaxf(sc.root_lo[1] - py, py - sc.root_hi[1]), 0.f);
+  const float ez = fmaxf(fmaxf(sc.root_lo[2] - pz, pz - sc.root_hi[2]), 0.f);
+  const float d2 = ex * ex + ey * ey + ez * ez;
+  const float L = __double2float_ru(len) * 1.00001f + m * 2.4e-7f;
+  return d2 * 0.99999f > L * L;
+}
+
+template <bool ANY, bool COUNT, int W, class IO>
+__device__ __forceinline__ void trace_decoupled(const DevScene& sc, const DevHole& bh, const IO& io, const int n, int* cursor, Counters* gcnt) {
+  __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
+  int* stack = stack_mem + threadIdx.x;
+  Counters cnt = {0, 0, 0, 0, 0, 0};
+  const unsigned lt_mask = (1u << wt_lane()) - 1u;
+  int pool_next = 0, pool_end = 0;   /* warp-uniform */
+  bool more = true;                  /* warp-uniform */
+  bool has = false, pend = false;    /* pend: the current chord (o, d, len) waits for its BVH traversal */
+  int idx = 0, j = 0;
+  d3 o = D3(0, 0, 0), d = D3(0, 0, 0);
+  double len = 0.0;
+  while (true) {
+    unsigned need = __ballot_sync(0xffffffffu, !has);
+    while (need) {
+      if (pool_next >= pool_end) {
+        if (!more) break;
+        int base = 0;
+        if (wt_lane() == 0) base = atomicAdd(cursor, RRT_POOL);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) { more = false; break; }
+        pool_next = base; pool_end = min(base + RRT_POOL, n);
+      }
+      const int avail = pool_end - pool_next;
+      const int rank = __popc(need & lt_mask);
+      if (!has && rank < avail) {
+        double tmin_unused, tmax_unused;   /* the bender discards the caller's range (reference src/bvh.cpp:104) */
+        idx = pool_next + rank;
+        io.load(idx, o, d, tmin_unused, tmax_unused);
+        has = true; pend = false; j = 0; len = 0.0;
+        if (COUNT) cnt.rays++;
+      }
+      pool_next += min(__popc(need), avail);
+      need = __ballot_sync(0xffffffffu, !has);
+    }
+    const unsigned m_has = __ballot_sync(0xffffffffu, has);
+    if (!m_has) break;
+    const unsigned m_step = __ballot_sync(0xffffffffu, has && !pend);
+    Hit h; h.status = -1;
+    if (__popc(m_step) >= RRT_S_THRESH || m_step == m_has) {
+      /* ---- STEP: one chord for every lane that is not parked */
+      if (has && !pend) {
+        next_micro_ray(bh, o, d, len);
+        if (COUNT) cnt.steps++;
+        if (horizon_hit(bh, o, d, len)) { h.status = 2; h.prim = -1; h.chord = j; h.steps = j + 1; h.t = 0.0; }
+        else if (chord_is_clear(sc, o, len) || chord_outside_root(sc, o, len)) {
+          ++j;
+          if (j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = j - 1; h.steps = j; h.t = 0.0; }
+        } else pend = true;
+      }
+    } else {
+      /* ---- TRAVERSE: the parked chords, whole warp converged */
+      Seg s; s.o = o; s.d = d; s.tmin = 0.0; s.tmax = len;
+      Best best;
+      bool found;
+      if (W == 2) found = traverse<ANY, COUNT, false>(sc, s, best, stack, RRT_BLOCK, cnt, pend, nullptr);
+      else found = traverse_wide<ANY, COUNT, (W == 2 ? 4 : W), false>(sc, s, best, stack, RRT_BLOCK, cnt, pend, nullptr);
+      if (pend) {
+        pend = false;
+        if (found) {
+          h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
+          if (IO::GEO) fill_geo(sc, s, best, h);
+        } else {
+          ++j;
+          if (j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = j - 1; h.steps = j; h.t = 0.0; }
+        }
+      }
+    }
+    if (has && h.status >= 0) { io.store(idx, h); has = false; }
+    __syncwarp();
+  }
+  if (COUNT) wt_flush_counters(cnt, gcnt);
+}
+
 /* ---------------------------------------------------------------- variant 1: vote-scheduled state machine (measured
  * SLOWER than variant 0 on C2, 62.9 vs 48.2 ms per frame: kept for A/B).
  * The lockstep loop above still loses lanes INSIDE a chord: traversals have different lengths and lanes that reach a
@@ -353,6 +463,8 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
   if (COUNT) wt_flush_counters(cnt, gcnt);
 }
 
+#endif  /* RRT_AB */
+
 /* extension rays: closest hit */
 #ifdef RRT_MINB_CLOSEST_N      /* A/B: resident blocks for the closest-hit kernel alone */
 #define RRT_MINB_CLOSEST(V, STEP) RRT_MINB_CLOSEST_N
@@ -365,8 +477,12 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB_CLOSEST(V, STEP)) k_trace_
                                                                 const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
                                                                 int* cursor, int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt) {
   ClosestIO io; io.ray = ray; io.cap = cap; io.h_prim = h_prim; io.h_geo = h_geo;
-  if (V == 1) trace_sched<false, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
-  else trace_persistent<false, COUNT, (V == 0 ? 2 : V), STEP>(sc, bh, io, *count_ptr, cursor, gcnt);
+#if RRT_AB
+  if constexpr (V == 1) trace_sched<false, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
+  else if constexpr (STEP == 3) trace_decoupled<false, COUNT, (V == 0 ? 2 : V)>(sc, bh, io, *count_ptr, cursor, gcnt);
+  else
+#endif
+  trace_persistent<false, COUNT, (V == 0 ? 2 : V), STEP>(sc, bh, io, *count_ptr, cursor, gcnt);
 }
 
 /* shadow rays: BVHAccel::intersect(ray) (any hit), or closest hit when the hemisphere estimator needs the emitter */
@@ -375,8 +491,12 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINBLOCKS(V, STEP)) k_trace_sha
                                                                const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
                                                                int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt) {
   ShadowIO io; io.ray = ray; io.cap = cap; io.cidx = cidx; io.res = res;
-  if (V == 1) trace_sched<ANY, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
-  else trace_persistent<ANY, COUNT, (V == 0 ? 2 : V), STEP>(sc, bh, io, *count_ptr, cursor, gcnt);
+#if RRT_AB
+  if constexpr (V == 1) trace_sched<ANY, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
+  else if constexpr (STEP == 3) trace_decoupled<ANY, COUNT, (V == 0 ? 2 : V)>(sc, bh, io, *count_ptr, cursor, gcnt);
+  else
+#endif
+  trace_persistent<ANY, COUNT, (V == 0 ? 2 : V), STEP>(sc, bh, io, *count_ptr, cursor, gcnt);
 }
 
 /* parity hook: the same loop on caller-supplied rays */
@@ -385,6 +505,10 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINBLOCKS(V, STEP)) k_hook_trac
                                                             const double* __restrict__ o, const double* __restrict__ d, const double* __restrict__ tmin,
                                                             const double* __restrict__ tmax, rrt_hit* __restrict__ out, int* cursor, Counters* gcnt) {
   HookIO<ANY> io; io.o = o; io.d = d; io.tmin = tmin; io.tmax = tmax; io.out = out;
-  if (V == 1) trace_sched<ANY, true>(sc, bh, io, n, cursor, gcnt);
-  else trace_persistent<ANY, true, (V == 0 ? 2 : V), STEP>(sc, bh, io, n, cursor, gcnt);
+#if RRT_AB
+  if constexpr (V == 1) trace_sched<ANY, true>(sc, bh, io, n, cursor, gcnt);
+  else if constexpr (STEP == 3) trace_decoupled<ANY, true, (V == 0 ? 2 : V)>(sc, bh, io, n, cursor, gcnt);
+  else
+#endif
+  trace_persistent<ANY, true, (V == 0 ? 2 : V), STEP>(sc, bh, io, n, cursor, gcnt);
 }
