@@ -11,7 +11,7 @@ north_star's target is stated on: 1920x1080, -s 1024 -l 4 -m 5, black hole on, t
 (batch 32, tolerance 0.05, src/application.h:56-57).  CBdragon.dae is not in the reference tree
 (/root/reference/.MISSING_LARGE_BLOBS), so the scene is the largest bundled Cornell-box scene,
 CBbunny_microfacet_cu.dae ("CBdragon substitute"), as the committed flattened copy the reference's own COLLADA loader wrote.
-At N GPUs the SAME frame at the SAME spp is tile-sharded (16x16 interleaved tiles; "scaling": "strong") and the per-rank
+At N GPUs the SAME frame at the SAME spp is tile-sharded (8x8 interleaved tiles; "scaling": "strong") and the per-rank
 float4 frames are combined with ONE NCCL reduce; --scaling weak keeps round 1's rule (spp x N).
 
 Prints ONE JSON line (rank 0).  `value` = Mpaths/s with everything resident in HBM (path = one traced camera sample, i.e. the
@@ -339,6 +339,7 @@ def main():
                     help="geodesic stepper: fp64 = bit-identical to the reference (default, the headline); fp32 = RRT_OPT_STEPPER 1, within 1e-4")
     ap.add_argument("--builder", default="auto", choices=["auto", "host", "device"], help="BVH construction (RRT_OPT_BVH_BUILDER): auto = device LBVH for >= 4096 primitives, else host binned SAH")
     ap.add_argument("--batch", type=int, default=0, help="override samples_per_batch (the reference's -a batch; default rule: shard.weak_scaling_params)")
+    ap.add_argument("--streams", type=int, default=0, help="RRT_OPT_STREAMS override (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -366,14 +367,14 @@ def main():
     if args.scaling == "weak":
         # round 1's rule: frame fixed, spp x N, one batch = the whole job (no adaptive stop) above 32 spp
         spp_job, batch = shard.weak_scaling_params(spp, world)
-        rule = "weak: frame fixed, spp = %d x n_gpus, 16x16 interleaved tiles, one NCCL reduce per frame" % spp
+        rule = "weak: frame fixed, spp = %d x n_gpus, 8x8 interleaved tiles, one NCCL reduce per frame" % spp
     else:
         # strong: the SAME frame at the SAME spp and batch for every N (the reference hands a fixed frame's tiles to N workers,
         # src/pathtracer.cpp:243-255).  Adaptive workloads keep the reference's default batch; the others keep the whole job in one
         # batch above 32 spp so that every pixel takes exactly spp samples.
         spp_job = spp
         batch = ad["batch"] if ad else (32 if spp <= 32 else spp)
-        rule = "strong: same frame, spp and batch for every N; 16x16 interleaved tiles, one NCCL reduce per frame"
+        rule = "strong: same frame, spp and batch for every N; 8x8 interleaved tiles, one NCCL reduce per frame"
     if args.batch:
         batch = args.batch
     s = workload_scene(args.workload)
@@ -385,6 +386,8 @@ def main():
     ctx.set_option(api.OPT_BVH_WIDTH, args.width)
     ctx.set_option(api.OPT_STEPPER, 1 if args.stepper == "fp32" else 0)
     ctx.set_option(api.OPT_BVH_BUILDER, {"auto": 0, "device": 1, "host": 2}[args.builder])
+    if args.streams:
+        ctx.set_option(api.OPT_STREAMS, args.streams)
     ctx.upload_scene(s)
     ctx.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
     ctx.set_frame(W, H)

@@ -174,6 +174,8 @@ enum {
   RRT_OPT_STEPPER = 8,        /* geodesic stepper with the hole on: 0 (default) = the reference's recurrence in IEEE double, bit-identical chords;
                                  1 = the same recurrence carried as (orbital frame, u, u') in FP32 registers (BASELINE.json north_star item 3):
                                  chords within ~1e-6 of the reference's (bound asserted: 1e-4), NOT bit-identical; trace kernel 0 only */
+  RRT_OPT_STREAMS = 10,       /* CUDA streams the wavefront chunks of one adaptive round are dealt over (1..4, default 2): a trace launch ends ragged
+                                 (rays need 1..63 chords) and another stream's kernels fill the idle SMs; bit-identical results for any value */
   RRT_OPT_BVH_BUILDER = 9     /* where the BVH is built.  1 = on the device: the reference's depth-first ranks by level-synchronous stable partition
                                  + an LBVH for the traversal (scenes of >= 64 primitives, binary nodes; falls back to the host if the tree comes
                                  out deeper than the traversal stack); 2 = on the host (reference tree shape or binned SAH, threaded);
@@ -202,7 +204,8 @@ int rrt_set_cell(rrt_ctx* ctx, int x, int y, int w, int h);
  * hole) return the map's radiance along their own, unbent direction.  rgb == NULL removes it.  Survives
  * rrt_upload_scene.  Maps with an all-black row are not usable (the reference divides by that row's marginal). */
 int rrt_set_envmap(rrt_ctx* ctx, int width, int height, const float* rgb);
-/* interleaved tile ownership for multi-GPU: tile (tx,ty) belongs to rank (tx + ty*ntx) % world */
+/* interleaved tile ownership for multi-GPU: tile (tx, ty) belongs to rank (tx + ty * s) % world, s = the smallest integer >= round(sqrt(world))
+ * coprime with world (8 -> 3, 4 -> 3, 2 -> 1): every run of `world` tiles along a row or a column holds every rank once */
 int rrt_set_tile_shard(rrt_ctx* ctx, int tile_size, int rank, int world);
 
 /* ---- the hot path ---- */

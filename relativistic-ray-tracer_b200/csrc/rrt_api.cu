@@ -32,6 +32,8 @@ struct DevBuf {
 struct rrt_ctx {
   int device = 0, sm_count = 148;
   cudaStream_t stream = nullptr;
+  cudaStream_t aux[3] = {nullptr, nullptr, nullptr};   /* wavefront chunks of one round are dealt over stream + aux[0 .. n-2] (RRT_OPT_STREAMS) */
+  cudaEvent_t ev_fork = nullptr, ev_join[3] = {nullptr, nullptr, nullptr};
   std::string err;
   // configuration
   bool have_scene = false, have_cam = false;
@@ -114,6 +116,7 @@ int rrt_create(rrt_ctx** out, int device) {
   ctx->opt[RRT_OPT_BVH_TOPOLOGY] = 1;
   ctx->opt[RRT_OPT_BVH_WIDTH] = 0;
   ctx->opt[RRT_OPT_SHADE_SPLIT] = 2;
+  ctx->opt[RRT_OPT_STREAMS] = 2;
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaMallocHost((void**)&ctx->h_pinned, 4096)) != cudaSuccess) {
@@ -139,13 +142,15 @@ void rrt_destroy(rrt_ctx* ctx) {
   for (DevBuf* b : bufs) b->release();
   for (cudaEvent_t ev : ctx->events) cudaEventDestroy(ev);
   if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+  for (int k = 0; k < 3; ++k) { if (ctx->aux[k]) cudaStreamDestroy(ctx->aux[k]); if (ctx->ev_join[k]) cudaEventDestroy(ctx->ev_join[k]); }
+  if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
 
 int rrt_set_option(rrt_ctx* ctx, int option, int64_t value) {
   if (!ctx) return RRT_E_ARG;
-  if (option < 0 || option > RRT_OPT_BVH_BUILDER) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
+  if (option < 0 || option > RRT_OPT_STREAMS) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
 #if !RRT_AB
   if ((option == RRT_OPT_TRACE_KERNEL && value != 0) || (option == RRT_OPT_BVH_WIDTH && value == 4))
     FAIL(RRT_E_ARG, "rrt_set_option: this variant is compiled only into A/B builds (make EXTRA=-DRRT_AB=1)");
@@ -638,32 +643,48 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   const size_t per_path = 2 * (8 * 8 + 4 + 4 + 4 + 12) + 4 + 72 + 12 + 1 + 12 + (size_t)S * (56 + 4 + 4 + 16);
   size_t want = p->max_paths_in_flight > 0 ? (size_t)p->max_paths_in_flight : (size_t)4 << 20;
   size_t budget = (size_t)(ctx->opt[RRT_OPT_WORK_BYTES] > 0 ? ctx->opt[RRT_OPT_WORK_BYTES] : (int64_t)12 << 30);
-  want = std::min(want, std::max<size_t>(budget / per_path, 1024));
+  want = std::min(want, std::max<size_t>(budget / per_path / (size_t)std::min<int64_t>(std::max<int64_t>(ctx->opt[RRT_OPT_STREAMS], 1), 4), 1024));
   size_t pix_per_chunk = std::max<size_t>(want / nb_max, 1);
   pix_per_chunk = std::min(pix_per_chunk, npix);
   const size_t cap = pix_per_chunk * nb_max, capS = cap * S;
   if (capS >= ((size_t)1 << 31)) FAIL(RRT_E_ARG, "rrt_render: max_paths_in_flight x light samples exceeds 2^31");
   rk.cap = (int)cap;
 
-  Queues q; memset(&q, 0, sizeof q);
+  /* Wavefront chunks of one adaptive round are independent (disjoint pixels, slot-addressed results), so they are dealt round-robin over
+   * NS streams, each with its own queues: a trace launch ends ragged — rays need 1 to 63 chords, and the last ones keep a few lanes alive —
+   * and the other stream's kernels fill the SMs that tail leaves idle.  Matters most where launches are small: strong scaling (C4 on 8 GPUs:
+   * 20 k pixels per rank and round).  RRT_OPT_STREAMS (1..4, default 2); results are bit-identical for any value. */
+  const int NS = (int)std::min<int64_t>(std::max<int64_t>(ctx->opt[RRT_OPT_STREAMS], 1), 4);
+  cudaStream_t streams[4] = {st, nullptr, nullptr, nullptr};
+  for (int k = 1; k < NS; ++k) {
+    if (!ctx->aux[k - 1]) { CK(cudaStreamCreateWithFlags(&ctx->aux[k - 1], cudaStreamNonBlocking)); CK(cudaEventCreateWithFlags(&ctx->ev_join[k - 1], cudaEventDisableTiming)); }
+    streams[k] = ctx->aux[k - 1];
+  }
+  if (!ctx->ev_fork) CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+  Queues qs[4]; memset(qs, 0, sizeof qs);
   size_t off = 0;
   auto carve = [&](size_t bytes) { size_t o = off; off += align_up(bytes); return o; };
   size_t o_ray[2], o_slot[2], o_rngn[2], o_flags[2], o_beta[2];
   for (int b = 0; b < 2; ++b) { o_ray[b] = carve(64 * cap); o_slot[b] = carve(4 * cap); o_rngn[b] = carve(4 * cap); o_flags[b] = carve(4 * cap); o_beta[b] = carve(12 * cap); }
   size_t o_hprim = carve(4 * cap), o_hgeo = carve(72 * cap), o_dbeta = carve(12 * cap), o_vflag = carve(cap), o_sray = carve(56 * capS),
          o_scidx = carve(4 * capS), o_sres = carve(4 * capS), o_scon = carve(16 * capS), o_L = carve(12 * cap);
-  q.ctl_stride = iters + 2;
-  size_t o_ctl = carve(4 * 4 * (size_t)q.ctl_stride);
-  CK(ctx->d_work.ensure(off));
-  char* wb = ctx->d_work.as<char>();
-  for (int b = 0; b < 2; ++b) {
-    q.ray[b] = (double*)(wb + o_ray[b]); q.slot[b] = (uint32_t*)(wb + o_slot[b]); q.rngn[b] = (uint32_t*)(wb + o_rngn[b]);
-    q.flags[b] = (uint32_t*)(wb + o_flags[b]); q.beta[b] = (float*)(wb + o_beta[b]);
+  const int ctl_stride = iters + 2;
+  size_t o_ctl = carve(4 * 4 * (size_t)ctl_stride);
+  const size_t per_stream = off;
+  CK(ctx->d_work.ensure(per_stream * NS));
+  for (int k = 0; k < NS; ++k) {
+    Queues& q = qs[k];
+    char* wb = ctx->d_work.as<char>() + per_stream * k;
+    q.ctl_stride = ctl_stride;
+    for (int b = 0; b < 2; ++b) {
+      q.ray[b] = (double*)(wb + o_ray[b]); q.slot[b] = (uint32_t*)(wb + o_slot[b]); q.rngn[b] = (uint32_t*)(wb + o_rngn[b]);
+      q.flags[b] = (uint32_t*)(wb + o_flags[b]); q.beta[b] = (float*)(wb + o_beta[b]);
+    }
+    q.h_prim = (int*)(wb + o_hprim); q.h_geo = (double*)(wb + o_hgeo); q.dbeta = (float*)(wb + o_dbeta); q.vflag = (uint8_t*)(wb + o_vflag);
+    q.sray = (double*)(wb + o_sray); q.s_cidx = (uint32_t*)(wb + o_scidx); q.s_res = (int*)(wb + o_sres); q.s_contrib = (float4*)(wb + o_scon);
+    q.Lsample = (float*)(wb + o_L); q.ctl = (int*)(wb + o_ctl);
   }
-  q.h_prim = (int*)(wb + o_hprim); q.h_geo = (double*)(wb + o_hgeo); q.dbeta = (float*)(wb + o_dbeta); q.vflag = (uint8_t*)(wb + o_vflag);
-  q.sray = (double*)(wb + o_sray); q.s_cidx = (uint32_t*)(wb + o_scidx); q.s_res = (int*)(wb + o_sres); q.s_contrib = (float4*)(wb + o_scon);
-  q.Lsample = (float*)(wb + o_L); q.ctl = (int*)(wb + o_ctl);
-  const size_t ctl_bytes = 4 * 4 * (size_t)q.ctl_stride;
+  const size_t ctl_bytes = 4 * 4 * (size_t)ctl_stride;
 
   /* ---- per-pixel accumulators and the active list */
   PixelAcc px;
@@ -687,7 +708,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   CK(cudaEventRecord(ev_begin, st));
 
   KeepOwned own;
-  own.W = ctx->W; own.tile = ctx->tile; own.ntx = (ctx->W + ctx->tile - 1) / ctx->tile; own.rank = ctx->rank; own.world = ctx->world;
+  own.W = ctx->W; own.tile = ctx->tile; own.ntx = rrt_shard_stride(ctx->world); own.rank = ctx->rank; own.world = ctx->world;
   own.x0 = 0; own.y0 = 0; own.x1 = ctx->W; own.y1 = ctx->H;
   if (ctx->cell_w > 0) {
     own.x0 = std::max(ctx->cell_x, 0); own.y0 = std::max(ctx->cell_y, 0);
@@ -702,41 +723,58 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   int a = 0;
   for (int base_sample = 0; base_sample < rk.ns_aa && n_act > 0;) {
     const int nb = std::min(rk.batch, rk.ns_aa - base_sample);
-    for (size_t c0 = 0; c0 < n_act; c0 += pix_per_chunk) {
-      const int npx = (int)std::min(pix_per_chunk, (size_t)n_act - c0);
+    /* chunks of this round: as few as the buffers allow, but a multiple of NS of equal size once every chunk still fills the machine */
+    size_t nchunks = (n_act + pix_per_chunk - 1) / pix_per_chunk;
+    const int ns_round = (NS > 1 && (size_t)n_act * nb >= (size_t)NS * 65536) ? NS : 1;
+    nchunks = (nchunks + ns_round - 1) / ns_round * ns_round;
+    const size_t chunk_px = ((size_t)n_act + nchunks - 1) / nchunks;
+    if (ns_round > 1) {
+      CK(cudaEventRecord(ctx->ev_fork, st));
+      for (int k = 1; k < ns_round; ++k) CK(cudaStreamWaitEvent(streams[k], ctx->ev_fork, 0));
+    }
+    size_t ci = 0;
+    for (size_t c0 = 0; c0 < n_act; c0 += chunk_px, ++ci) {
+      const int npx = (int)std::min(chunk_px, (size_t)n_act - c0);
       const uint32_t* chunk = act[a] + c0;
-      CK(cudaMemsetAsync(q.ctl, 0, ctl_bytes, st));
-      k_generate<<<grid_small, 256, 0, st>>>(ctx->cam, rk, q, chunk, npx, base_sample, nb);
+      const int si = (int)(ci % ns_round);
+      cudaStream_t cs = streams[si];
+      const Queues& q = qs[si];
+      CK(cudaMemsetAsync(q.ctl, 0, ctl_bytes, cs));
+      k_generate<<<grid_small, 256, 0, cs>>>(ctx->cam, rk, q, chunk, npx, base_sample, nb);
       launches++;
       for (int it = 0; it < iters; ++it) {
         const int cur = it & 1;
         cudaEvent_t e0 = nullptr, e1 = nullptr;
-        if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, st)); }
-        launch_closest(ctx, count, grid_trace, st, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt);
-        if (stats) { CK(cudaEventRecord(e1, st)); trace_ev.push_back({e0, e1}); }
-        k_shade<<<grid_small, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, rk, q, chunk, base_sample, nb, it);
+        if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, cs)); }
+        launch_closest(ctx, count, grid_trace, cs, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt);
+        if (stats) { CK(cudaEventRecord(e1, cs)); trace_ev.push_back({e0, e1}); }
+        k_shade<<<grid_small, RRT_BLOCK, 0, cs>>>(ctx->ds, ctx->bh, rk, q, chunk, base_sample, nb, it);
         if (rk.split && rk.D >= 1 && rk.S > 0) {
-          k_shade_direct<<<ctx->sm_count * 2 * RRT_DIRECT_MINB, 256, 0, st>>>(ctx->ds, rk, q, chunk, base_sample, nb, it);
+          k_shade_direct<<<ctx->sm_count * 2 * RRT_DIRECT_MINB, 256, 0, cs>>>(ctx->ds, rk, q, chunk, base_sample, nb, it);
           launches++;
         }
         launches += 2; trace_launches++;
         if (rk.D >= 1 && rk.S > 0) {
-          if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, st)); }
+          if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, cs)); }
           int* scount = q.ctl + q.ctl_stride + it; int* scursor = q.ctl + 3 * q.ctl_stride + it;
-          if (rk.hemi) launch_shadow<false>(ctx, count, grid_trace, st, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
-          else launch_shadow<true>(ctx, count, grid_trace, st, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
-          if (stats) { CK(cudaEventRecord(e1, st)); trace_ev.push_back({e0, e1}); }
-          k_accumulate<<<grid_small, 256, 0, st>>>(ctx->ds, rk, q, it);
+          if (rk.hemi) launch_shadow<false>(ctx, count, grid_trace, cs, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
+          else launch_shadow<true>(ctx, count, grid_trace, cs, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
+          if (stats) { CK(cudaEventRecord(e1, cs)); trace_ev.push_back({e0, e1}); }
+          k_accumulate<<<grid_small, 256, 0, cs>>>(ctx->ds, rk, q, it);
           launches += 2; trace_launches++;
         }
-        if (it + 1 < iters && (it & 3) == 3) {  /* long depth budgets: stop once every path has died */
-          CK(cudaMemcpyAsync(ctx->h_pinned, q.ctl + it + 1, 4, cudaMemcpyDeviceToHost, st));
-          CK(cudaStreamSynchronize(st));
+        if (iters > 8 && it + 1 < iters && (it & 3) == 3) {  /* long depth budgets (-m 100): stop once every path has died */
+          CK(cudaMemcpyAsync(ctx->h_pinned, q.ctl + it + 1, 4, cudaMemcpyDeviceToHost, cs));
+          CK(cudaStreamSynchronize(cs));
           if (ctx->h_pinned[0] == 0) break;
         }
       }
-      k_resolve<<<grid_small, 256, 0, st>>>(rk, q, px, chunk, npx, nb);
+      k_resolve<<<grid_small, 256, 0, cs>>>(rk, q, px, chunk, npx, nb);
       launches++;
+    }
+    for (int k = 1; k < ns_round; ++k) {   /* join: the round's compaction and the next round read what every stream wrote */
+      CK(cudaEventRecord(ctx->ev_join[k - 1], streams[k]));
+      CK(cudaStreamWaitEvent(st, ctx->ev_join[k - 1], 0));
     }
     base_sample += nb;
     if (base_sample < rk.ns_aa) {
@@ -764,8 +802,22 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
     memset(stats, 0, sizeof *stats);
     float ms = 0; CK(cudaEventElapsedTime(&ms, ev_begin, ev_end));
     stats->seconds = ms * 1e-3;
-    double tms = 0;
-    for (auto& pr : trace_ev) { float t = 0; CK(cudaEventElapsedTime(&t, pr.first, pr.second)); tms += t; }
+    /* time during which at least one trace kernel was running: the launches of different streams overlap, so their durations are
+     * merged as intervals on the device clock (relative to the render's first event) instead of summed */
+    std::vector<std::pair<float, float>> iv;
+    iv.reserve(trace_ev.size());
+    for (auto& pr : trace_ev) {
+      float t0 = 0, t1 = 0;
+      CK(cudaEventElapsedTime(&t0, ev_begin, pr.first)); CK(cudaEventElapsedTime(&t1, ev_begin, pr.second));
+      iv.push_back({t0, t1});
+    }
+    std::sort(iv.begin(), iv.end());
+    double tms = 0; float lo = 0, hi = -1;
+    for (auto& x : iv) {
+      if (hi < lo || x.first > hi) { if (hi >= lo) tms += hi - lo; lo = x.first; hi = x.second; }
+      else hi = std::max(hi, x.second);
+    }
+    if (hi >= lo) tms += hi - lo;
     stats->trace_seconds = tms * 1e-3;
     Counters hc;
     CK(cudaMemcpy(&hc, gcnt, sizeof hc, cudaMemcpyDeviceToHost));

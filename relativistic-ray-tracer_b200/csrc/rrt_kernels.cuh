@@ -426,8 +426,21 @@ __global__ void __launch_bounds__(256) k_finalize(const __grid_constant__ PixelA
 /* ---------------------------------------------------------------- stable compaction (ballot + prefix), three passes:
  * per-block counts, one-block exclusive scan of the counts, scatter.  keep(i) decides. */
 #define RRT_CBLOCK 1024
+/* Tile (tx, ty) belongs to rank (tx + ty * stride) % world, stride = rrt_shard_stride(world): the smallest integer >= round(sqrt(world))
+ * that is coprime with world (8 -> 3, 4 -> 3, 2 -> 1, 6 -> 5).  Every run of `world` consecutive tiles of a row AND of a column then holds
+ * every rank once, whatever the frame width.  (Round 1 used ty * tiles-per-row: with 1920 / 16 = 120 tiles per row and 8 ranks that is
+ * tx % 8 — vertical stripes, 3 or 4 of the 30 tile columns the Cornell box covers per rank: 476-590 ms per rank on C4, SCALE 5.9x at N = 8.) */
+__host__ __device__ inline int rrt_shard_stride(int world) {
+  int s = 1;
+  while ((s + 1) * (s + 1) <= world + s) ++s;     /* s = round(sqrt(world)) for the small counts that matter; any s >= 1 works */
+  for (;; ++s) {
+    int a = s, b = world;
+    while (b) { int t = a % b; a = b; b = t; }
+    if (a == 1) return s;
+  }
+}
 struct KeepOwned {  // pixel belongs to this shard and to the render cell
-  int W, x0, y0, x1, y1, tile, ntx, rank, world;
+  int W, x0, y0, x1, y1, tile, ntx /* = shard stride */, rank, world;
   __device__ bool operator()(uint32_t p, uint32_t) const {
     int x = (int)(p % (uint32_t)W), y = (int)(p / (uint32_t)W);
     if (x < x0 || x >= x1 || y < y0 || y >= y1) return false;

@@ -17,7 +17,11 @@
 #ifndef RRT_BLOCK
 #define RRT_BLOCK 128
 #endif
-#define RRT_POOL 128  /* queue entries a warp reserves per atomic */
+#ifndef RRT_POOL
+#define RRT_POOL 32   /* queue entries a warp reserves per atomic.  Entries a warp has reserved but not started are invisible to the other warps: at the
+                         end of a launch they are worked off lane by lane while the rest of the GPU idles.  128 -> 32 on B200 (profiles/r02_c_*): C4 on
+                         8 GPUs 513 -> 477 ms per frame (small launches: 3 rays per lane), single GPU bunny 207.1 -> 204.5, C2 33.5 -> 32.5, C5 53.9 -> 51.4 */
+#endif
 #ifndef RRT_MINB
 #define RRT_MINB 6     /* resident blocks per SM the trace kernels are compiled for */
 #endif

@@ -7,18 +7,30 @@ needs no queue and no communication while rendering: a pixel's estimate depends 
 """
 import numpy as np
 
-DEFAULT_TILE = 16
+DEFAULT_TILE = 8
+
+
+def shard_stride(world):
+    """Row-to-row shift of the owner pattern: the smallest integer >= round(sqrt(world)) coprime with world (mirrors
+    rrt_shard_stride in csrc/rrt_kernels.cuh): 1 -> 1, 2 -> 1, 3 -> 2, 4 -> 3, 6 -> 5, 8 -> 3."""
+    s = 1
+    while (s + 1) * (s + 1) <= world + s:
+        s += 1
+    while np.gcd(s, world) != 1:
+        s += 1
+    return int(s)
 
 
 def tile_owner(width, height, tile=DEFAULT_TILE, world=1):
-    """[height, width] int32: rank that renders each pixel.  Mirrors KeepOwned in csrc/rrt_kernels.cuh
-    (tile index = (x / tile) + (y / tile) * ceil(width / tile), owner = index % world)."""
+    """[height, width] int32: rank that renders each pixel.  Mirrors KeepOwned in csrc/rrt_kernels.cuh:
+    owner of tile (tx, ty) = (tx + ty * shard_stride(world)) % world — every run of `world` tiles along a row or a column holds
+    every rank once, whatever the frame width (the tile index of round 1, tx + ty * tiles_per_row, degenerates into vertical
+    stripes when tiles_per_row is a multiple of world: 1920 / 16 = 120 tiles with 8 ranks)."""
     if width <= 0 or height <= 0 or tile <= 0 or world <= 0:
         raise ValueError("tile_owner: width, height, tile and world must be positive")
-    ntx = (width + tile - 1) // tile
     x = np.arange(width, dtype=np.int64) // tile
     y = np.arange(height, dtype=np.int64) // tile
-    return ((x[None, :] + y[:, None] * ntx) % world).astype(np.int32)
+    return ((x[None, :] + y[:, None] * shard_stride(world)) % world).astype(np.int32)
 
 
 def owned_pixels(width, height, tile, rank, world):

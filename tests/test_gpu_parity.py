@@ -315,6 +315,12 @@ def test_c2_full_size_properties(api):
     p2 = sc.make_params(ns_aa=16, max_ray_depth=5, ns_area_light=4, seed=7, max_paths_in_flight=300000)
     hdr3, _, st3 = c.render(p2)
     assert np.array_equal(hdr, hdr3) and st3["rays"] == st["rays"]
+    # the round's chunks dealt over 1, 3 or 4 streams instead of 2: not a bit may change
+    for ns in (1, 3, 4):
+        c.set_option(api.OPT_STREAMS, ns)
+        hn, cn, stn = c.render(p2)
+        assert np.array_equal(hdr, hn) and np.array_equal(cnt, cn) and stn["rays"] == st["rays"], ns
+    c.set_option(api.OPT_STREAMS, 2)
     # interleaved tile shards: the union of the ranks' frames is the single-GPU frame (multi-GPU contract)
     acc = np.zeros_like(hdr); accn = np.zeros_like(cnt)
     for r in range(3):

@@ -24,12 +24,25 @@ def test_tile_owner_is_a_disjoint_cover(w, h, tile, world):
     if w > tile:
         assert own[0, tile] == (own[0, 0] + 1) % world
     ntx = (w + tile - 1) // tile
+    stride = shard.shard_stride(world)
+    assert np.gcd(stride, world) == 1
     if h > tile:
-        assert own[tile, 0] == ntx % world
+        assert own[tile, 0] == stride % world        # the next tile row is shifted by the stride, whatever the frame width
     # balance: no rank holds more than one tile row's worth above the mean
     counts = np.bincount(own.ravel(), minlength=world)
     if w * h >= world * tile * tile * 4:
         assert counts.max() - counts.min() <= tile * tile * (ntx + 1)
+    # any window of `world` tiles along a row or along a column holds every rank once (what round 1's index rule lost at 1920 / 16 = 120)
+    if w >= world * tile and h >= world * tile:
+        assert sorted(own[0, ::tile][:world].tolist()) == list(range(world))
+        assert sorted(own[::tile, 0][:world].tolist()) == list(range(world))
+
+
+def test_box_region_of_the_1080p_frame_is_balanced_over_8_ranks():
+    """the pixels that carry the work of C4 (the central 480x360 cell, bench.py ADAPTIVE) split within 0.5 % over 8 ranks"""
+    own = shard.tile_owner(1920, 1080, shard.DEFAULT_TILE, 8)[360:720, 720:1200]
+    counts = np.bincount(own.ravel(), minlength=8)
+    assert counts.max() - counts.min() <= 0.005 * counts.mean()
 
 
 def test_tile_owner_rejects_bad_arguments():
