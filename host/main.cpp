@@ -35,7 +35,7 @@ static void usage(const char* binary) {
   printf("  -b  <FLOAT>      Lens radius      -d  <FLOAT>  Focal distance\n");
   printf("  -e  <FILENAME>   Environment map (uncompressed .exr or .pfm)\n");
   printf("  -B  <x> <y> <z> <r> <dtheta>  Black hole centre, Schwarzschild radius, angular step\n");
-  printf("  -F               Flat spacetime (no hole)      -S <INT> RNG seed      -G <INT> CUDA device\n");
+  printf("  -F               Flat spacetime (no hole)      -S <INT> RNG seed      -G <INT[,INT...]> CUDA device(s)\n");
   printf("  --progress <PREFIX> [--progress-every <INT>]  write <PREFIX>_<samples>.png after every n-th adaptive batch\n");
   printf("  --thin-lens      sample the lens (-b, -d) for every camera ray\n");
   printf("  --stepper <fp64|fp32>   geodesic stepper: fp64 = bit-identical to the reference (default), fp32 = within 1e-4, faster\n");
@@ -52,7 +52,7 @@ int main(int argc, char** argv) {
   size_t w = 0, h = 0, x = (size_t)-1, y = 0, dx = 0, dy = 0;
   std::string filename, cam_settings, dump_scene, dump_camera, scene_path, envmap_path;
   Vector3D bh_c(0, 1, 0); double bh_r = 0.1, bh_dtheta = 0.1;
-  unsigned long long seed = 0; int device = 0;
+  unsigned long long seed = 0; int device = 0; std::vector<int> devices;
   std::string progress_prefix; int progress_every = 1; bool thin_lens = false; bool stepper_fp32 = false; int bvh_builder = 0;
 
   auto need = [&](int i, int k) { if (i + k >= argc) { usage(argv[0]); exit(1); } };
@@ -77,7 +77,13 @@ int main(int argc, char** argv) {
     }
     else if (a == "-F") flat = true;
     else if (a == "-S") { need(i, 1); seed = strtoull(argv[++i], nullptr, 10); }
-    else if (a == "-G") { need(i, 1); device = atoi(argv[++i]); }
+    else if (a == "-G") {   // one CUDA device, or a comma-separated list: the frame's tiles are dealt over those GPUs
+      need(i, 1);
+      devices.clear();
+      for (const char* q = argv[++i]; *q;) { devices.push_back(atoi(q)); while (*q && *q != ',') ++q; if (*q == ',') ++q; }
+      if (devices.empty()) { usage(argv[0]); return 1; }
+      device = devices[0];
+    }
     else if (a == "--progress") { need(i, 1); progress_prefix = argv[++i]; }
     else if (a == "--progress-every") { need(i, 1); progress_every = atoi(argv[++i]); }
     else if (a == "--thin-lens") thin_lens = true;
@@ -132,7 +138,8 @@ int main(int argc, char** argv) {
 
   PathTracer pt(ns_aa, max_ray_depth, ns_area_light, 1, 1, 1, num_threads, samples_per_batch, max_tolerance, nullptr, hemisphere,
                 scene_file, lens_radius, focal_distance);
-  pt.set_device(device); pt.set_seed(seed); pt.set_blackhole(bh_c, bh_r, bh_dtheta, flat);
+  pt.set_device(device); if (devices.size() > 1) pt.set_devices(devices);
+  pt.set_seed(seed); pt.set_blackhole(bh_c, bh_r, bh_dtheta, flat);
   pt.set_option(RRT_OPT_STEPPER, stepper_fp32 ? 1 : 0); pt.set_option(RRT_OPT_BVH_BUILDER, bvh_builder);
   if (!envmap_path.empty()) {
     int ew = 0, eh = 0; std::vector<float> env;

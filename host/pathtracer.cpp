@@ -96,7 +96,9 @@ bool PathTracer::has_valid_configuration() const { return have_scene_ && camera_
 
 void PathTracer::set_scene(const FlatScene* scene) {
   if (state_ != INIT) return;
-  if (!ctx_ && rrt_create(&ctx_, device_) != RRT_OK) { error_ = rrt_last_error(nullptr); ctx_ = nullptr; return; }
+  if (!ctx_ && (devices_.size() > 1 ? rrt_create_multi(&ctx_, (int)devices_.size(), devices_.data()) : rrt_create(&ctx_, device_)) != RRT_OK) {
+    error_ = rrt_last_error(nullptr); ctx_ = nullptr; return;
+  }
   for (const auto& o : options_) if (rrt_set_option(ctx_, o.first, o.second) != RRT_OK) { error_ = rrt_last_error(ctx_); return; }
   fprintf(stdout, "[PathTracer] Collecting primitives... Done! (%.4f sec)\n", 0.0);
   fprintf(stdout, "[PathTracer] Building BVH from %lu primitives... ", (unsigned long)scene->n_prims()); fflush(stdout);
@@ -149,7 +151,8 @@ void PathTracer::worker() {
   if (rrt_set_camera(ctx_, &cam) != RRT_OK) return finish("rrt_set_camera");
   if (rrt_set_frame(ctx_, (int)W_, (int)H_) != RRT_OK) return finish("rrt_set_frame");
   if (rrt_set_blackhole(ctx_, ctr, bh_r_, bh_dtheta_, bh_flat_ ? RRT_MODE_FLAT : RRT_MODE_LITERAL) != RRT_OK) return finish("rrt_set_blackhole");
-  if (rrt_set_tile_shard(ctx_, tile_, rank_, world_) != RRT_OK) return finish("rrt_set_tile_shard");
+  const bool multi = rrt_gpu_count(ctx_) > 1;   // a multi-GPU context deals the tiles over its own GPUs
+  if (rrt_set_tile_shard(ctx_, tile_, multi ? 0 : rank_, multi ? 1 : world_) != RRT_OK) return finish("rrt_set_tile_shard");
   int rc = render_cell ? rrt_set_cell(ctx_, (int)cell_tl[0], (int)cell_tl[1], (int)(cell_br[0] - cell_tl[0]), (int)(cell_br[1] - cell_tl[1]))
                        : rrt_set_cell(ctx_, 0, 0, 0, 0);
   if (rc != RRT_OK) return finish("rrt_set_cell");
@@ -158,7 +161,8 @@ void PathTracer::worker() {
   p.samples_per_batch = (int32_t)samples_per_batch_; p.max_tolerance = max_tolerance_; p.direct_hemisphere_sample = hemisphere_ ? 1 : 0;
   p.thin_lens = use_thin_lens ? 1 : 0; p.seed = seed_;
   snap_calls_ = 0; snaps_written_ = 0;
-  if (rrt_set_progress(ctx_, &PathTracer::progress_trampoline, this) != RRT_OK) return finish("rrt_set_progress");
+  // progressive output and stop() work between adaptive batches of ONE GPU; a multi-GPU context renders its tiles independently
+  if (!multi && rrt_set_progress(ctx_, &PathTracer::progress_trampoline, this) != RRT_OK) return finish("rrt_set_progress");
   if (rrt_render(ctx_, &p, hdr_.data(), counts_.data(), &stats_) != RRT_OK) return finish("rrt_render");
   if (rrt_tonemap(ctx_, (int64_t)(W_ * H_), hdr_.data(), frame_.data()) != RRT_OK) return finish("rrt_tonemap");
   finish(nullptr);

@@ -146,7 +146,9 @@ class PathTracer {
   void set_seed(uint64_t seed) { seed_ = seed; }
   // rrt_set_option pass-through (RRT_OPT_*: stepper, BVH builder, A/B variants); applied before the next set_scene
   void set_option(int option, int64_t value) { options_.push_back({option, value}); }
-  void set_device(int device) { device_ = device; }
+  void set_device(int device) { device_ = device; devices_.clear(); }
+  // several GPUs of this box (rrt_create_multi): the reference's N worker threads become N GPUs, tiles interleaved, one NCCL reduce per frame
+  void set_devices(const std::vector<int>& devices) { devices_ = devices; if (!devices.empty()) device_ = devices[0]; }
   void set_tile_shard(int tile, int rank, int world) { tile_ = tile; rank_ = rank; world_ = world; }
   void start_raytracing();                   // asynchronous: returns at once, state becomes DONE when the frame is ready
   void stop();                               // abandons a running render after its current adaptive batch (reference: continueRaytracing
@@ -178,7 +180,8 @@ class PathTracer {
   std::atomic<bool> stop_requested_{false};
   std::string snap_prefix_; int snap_every_ = 1, snap_calls_ = 0, snaps_written_ = 0;
   rrt_ctx* ctx_ = nullptr;
-  int device_ = 0, tile_ = 16, rank_ = 0, world_ = 1;
+  int device_ = 0, tile_ = 8, rank_ = 0, world_ = 1;
+  std::vector<int> devices_;
   bool have_scene_ = false;
   Camera* camera_ = nullptr;
   size_t W_ = 0, H_ = 0;

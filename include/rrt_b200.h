@@ -7,10 +7,11 @@
  * is available from rrt_last_error().  There is no CPU fallback: without a CUDA device every
  * compute entry point fails with RRT_E_CUDA.
  *
- * A context (rrt_ctx) is bound to ONE GPU and is driven by one host thread at a time.  Multi-GPU
- * runs use one context (one process) per GPU; each renders the interleaved tiles it owns
- * (rrt_set_tile_shard) into a zero-initialised frame and the caller combines the frames with a
- * single sum-reduce (NCCL) — see INTEGRATION.md.
+ * A context (rrt_ctx) is driven by one host thread at a time.  rrt_create binds it to ONE GPU;
+ * rrt_create_multi makes one context drive several GPUs of the box from one process (tiles dealt
+ * over the GPUs, scene replicated and the frame combined with NCCL inside the library).  Multi-
+ * process runs (one context per rank) use rrt_set_tile_shard and combine the frames with a single
+ * sum-reduce themselves — see INTEGRATION.md.
  *
  * Reference interfaces replaced (paths relative to /root/reference/pathtracer):
  *   PathTracer::set_scene  + build_accel   src/pathtracer.cpp:95-117,304-328   -> rrt_upload_scene
@@ -39,7 +40,7 @@
 extern "C" {
 #endif
 
-#define RRT_ABI_VERSION 4
+#define RRT_ABI_VERSION 5
 
 /* error codes */
 #define RRT_OK 0
@@ -187,6 +188,15 @@ enum {
 int rrt_abi_version(void);
 int rrt_device_count(void);
 int rrt_create(rrt_ctx** out, int device);
+/* One context driving n_gpus GPUs of this box from one process (devices == NULL: 0 .. n_gpus-1).  Replaces the reference's pool of N worker
+ * threads pulling tiles from one queue (src/pathtracer.cpp:224-282, 611-644): GPU k renders the interleaved 8x8 tiles it owns
+ * ((tx + ty * s) % n_gpus == k, see rrt_set_tile_shard), the scene is built once on the first GPU and replicated with ncclBroadcast,
+ * and ONE ncclReduce per frame sums the per-GPU frames onto the first GPU, where rrt_render reads them back (rrt_render_device: d_rgbn /
+ * d_counts must live on the first GPU).  Every other call behaves as on a single-GPU context (configuration goes to every GPU, parity
+ * hooks run on the first); rrt_set_progress / rrt_snapshot are not available.  Results are bit-identical to a single-GPU context.
+ * NCCL (libnccl.so.2) is loaded at this call; n_gpus == 1 is rrt_create. */
+int rrt_create_multi(rrt_ctx** out, int n_gpus, const int* devices);
+int rrt_gpu_count(const rrt_ctx* ctx);
 void rrt_destroy(rrt_ctx* ctx);
 const char* rrt_last_error(const rrt_ctx* ctx); /* ctx may be NULL: last creation error */
 int rrt_set_option(rrt_ctx* ctx, int option, int64_t value);

@@ -31,7 +31,7 @@ OPT_STEPPER = 8   # 0 = FP64 bit-exact stepper (default), 1 = FP32 state-carryin
 EXPORTS = ["rrt_abi_version", "rrt_device_count", "rrt_create", "rrt_destroy", "rrt_last_error", "rrt_set_option", "rrt_upload_scene",
            "rrt_set_camera", "rrt_set_blackhole", "rrt_set_frame", "rrt_set_cell", "rrt_set_tile_shard", "rrt_render", "rrt_render_device",
            "rrt_trace_rays", "rrt_geodesic", "rrt_generate_rays", "rrt_generate_rays_thin_lens", "rrt_set_progress", "rrt_snapshot", "rrt_bsdf_sample", "rrt_bsdf_eval", "rrt_light_sample", "rrt_philox",
-           "rrt_tonemap", "rrt_bvh_info", "rrt_bvh_build_host", "rrt_chords_per_ray", "rrt_set_envmap", "rrt_env_lookup", "rrt_trace_rays_static"]
+           "rrt_tonemap", "rrt_bvh_info", "rrt_bvh_build_host", "rrt_chords_per_ray", "rrt_set_envmap", "rrt_env_lookup", "rrt_trace_rays_static", "rrt_create_multi", "rrt_gpu_count"]
 STATIC_MAX_RAYS = 65536  # RRT_STATIC_MAX_RAYS
 
 
@@ -54,6 +54,8 @@ def lib():
         L.rrt_last_error.argtypes = [C.c_void_p]
         L.rrt_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]
         L.rrt_destroy.argtypes = [C.c_void_p]
+        L.rrt_create_multi.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_int)]
+        L.rrt_gpu_count.argtypes = [C.c_void_p]
         L.rrt_destroy.restype = None
         L.rrt_set_option.argtypes = [C.c_void_p, C.c_int, C.c_int64]
         L.rrt_upload_scene.argtypes = [C.c_void_p, C.POINTER(_sc.Scene)]
@@ -103,15 +105,23 @@ def bvh_build_host(scene, topology=0):
 
 
 class Context:
-    """One rrt_ctx: one GPU, one host thread at a time."""
+    """One rrt_ctx, one host thread at a time: one GPU (device = int) or, with a list of devices, a multi-GPU context
+    (rrt_create_multi: the frame's interleaved tiles are dealt over the GPUs, one NCCL reduce per frame onto the first)."""
 
     def __init__(self, device=0):
         self.h = C.c_void_p()
-        rc = lib().rrt_create(C.byref(self.h), int(device))
+        if isinstance(device, (list, tuple)):
+            devs = (C.c_int * len(device))(*[int(d) for d in device])
+            rc = lib().rrt_create_multi(C.byref(self.h), len(device), devs)
+        else:
+            rc = lib().rrt_create(C.byref(self.h), int(device))
         if rc != 0:
             raise RrtError("rrt_create failed (%d): %s" % (rc, lib().rrt_last_error(None).decode()))
         self.W = self.H = 0
         self.scene = None
+
+    def gpu_count(self):
+        return int(lib().rrt_gpu_count(self.h))
 
     def close(self):
         if getattr(self, "h", None) and self.h.value:

@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -57,6 +58,9 @@ struct rrt_ctx {
   std::vector<cudaEvent_t> events;
   size_t events_used = 0;
   uint32_t* h_pinned = nullptr;  // small pinned scratch for counts
+  // multi-GPU context (rrt_create_multi): this object only owns the per-GPU contexts and their NCCL communicators
+  std::vector<rrt_ctx*> subs;
+  std::vector<void*> comms;      // ncclComm_t per sub-context
 };
 
 #define CK(call)                                                                                           \
@@ -68,6 +72,24 @@ struct rrt_ctx {
     }                                                                                                      \
   } while (0)
 #define FAIL(code, msg) do { ctx->err = (msg); return (code); } while (0)
+/* multi-GPU contexts: calls that concern one GPU (parity hooks, introspection) go to the first sub-context */
+#define RRT_MULTI_FWD(ctx, CALL)                                         \
+  if ((ctx) && !(ctx)->subs.empty()) {                                   \
+    rrt_ctx* m_ = (ctx); rrt_ctx* ctx0 = m_->subs[0];                    \
+    int rc_ = (CALL);                                                    \
+    if (rc_ < 0) m_->err = ctx0->err;                                    \
+    return rc_;                                                          \
+  }
+/* ... and configuration calls go to every sub-context */
+#define RRT_MULTI_ALL(ctx, CALL)                                         \
+  if ((ctx) && !(ctx)->subs.empty()) {                                   \
+    rrt_ctx* m_ = (ctx);                                                 \
+    for (rrt_ctx* sub : m_->subs) { int rc_ = (CALL); if (rc_ < 0) { m_->err = sub->err; return rc_; } } \
+    return RRT_OK;                                                       \
+  }
+static int multi_upload_scene(rrt_ctx* m, const rrt_scene* s);
+static int multi_render(rrt_ctx* m, const rrt_params* p, float* hdr_rgb, int32_t* sample_counts, void* d_rgbn_user, void* d_counts_user, rrt_stats* stats);
+static void multi_destroy(rrt_ctx* m);
 
 static int chords_for(double dtheta) {
   int j = 0;
@@ -134,6 +156,7 @@ int rrt_create(rrt_ctx** out, int device) {
 
 void rrt_destroy(rrt_ctx* ctx) {
   if (!ctx) return;
+  if (!ctx->subs.empty()) { multi_destroy(ctx); return; }
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   DevBuf* bufs[] = {&ctx->d_env, &ctx->d_env_pdf, &ctx->d_env_cond, &ctx->d_env_marg, &ctx->d_grid, &ctx->d_nodes, &ctx->d_tripos, &ctx->d_build, &ctx->d_wide, &ctx->d_leaf, &ctx->d_nrm, &ctx->d_kind, &ctx->d_index, &ctx->d_pmat, &ctx->d_sph, &ctx->d_mats, &ctx->d_lights,
@@ -150,6 +173,7 @@ void rrt_destroy(rrt_ctx* ctx) {
 
 int rrt_set_option(rrt_ctx* ctx, int option, int64_t value) {
   if (!ctx) return RRT_E_ARG;
+  RRT_MULTI_ALL(ctx, rrt_set_option(sub, option, value));
   if (option < 0 || option > RRT_OPT_STREAMS) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
 #if !RRT_AB
   if ((option == RRT_OPT_TRACE_KERNEL && value != 0) || (option == RRT_OPT_BVH_WIDTH && value == 4))
@@ -307,6 +331,7 @@ static int build_bvh_on_device(rrt_ctx* ctx, const rrt_scene* s, bool* built) {
 extern "C" {
 int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   if (!ctx || !s) return RRT_E_ARG;
+  if (!ctx->subs.empty()) return multi_upload_scene(ctx, s);
   CK(cudaSetDevice(ctx->device));
   if (s->n_prims && (!s->prim_kind || !s->prim_index)) FAIL(RRT_E_ARG, "rrt_upload_scene: primitive arrays missing");
   if ((s->n_tris && (!s->tri_pos || !s->tri_nrm || !s->tri_mat)) || (s->n_spheres && (!s->sph || !s->sph_mat)))
@@ -391,6 +416,7 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
 
 int rrt_set_camera(rrt_ctx* ctx, const rrt_camera* cam) {
   if (!ctx || !cam) return RRT_E_ARG;
+  RRT_MULTI_ALL(ctx, rrt_set_camera(sub, cam));
   memcpy(ctx->cam.pos, cam->pos, sizeof cam->pos); memcpy(ctx->cam.c2w, cam->c2w, sizeof cam->c2w);
   ctx->cam.hFov = cam->hFov; ctx->cam.vFov = cam->vFov; ctx->cam.nClip = cam->nClip; ctx->cam.fClip = cam->fClip;
   ctx->cam.lensRadius = cam->lensRadius; ctx->cam.focalDistance = cam->focalDistance;
@@ -400,6 +426,7 @@ int rrt_set_camera(rrt_ctx* ctx, const rrt_camera* cam) {
 
 int rrt_set_blackhole(rrt_ctx* ctx, const double c[3], double r, double dtheta, int mode) {
   if (!ctx || !c) return RRT_E_ARG;
+  RRT_MULTI_ALL(ctx, rrt_set_blackhole(sub, c, r, dtheta, mode));
   if (mode != RRT_MODE_FLAT && mode != RRT_MODE_LITERAL) FAIL(RRT_E_ARG, "rrt_set_blackhole: unknown mode");
   ctx->bh.cx = c[0]; ctx->bh.cy = c[1]; ctx->bh.cz = c[2]; ctx->bh.r = r; ctx->bh.r2 = r * r; ctx->bh.h = dtheta;
   ctx->bh.cos_h = cos(dtheta); ctx->bh.sin_h = sin(dtheta);  /* host libm, as the reference evaluates them (src/static_scene/blackhole.cpp:34-35) */
@@ -410,6 +437,8 @@ int rrt_set_blackhole(rrt_ctx* ctx, const double c[3], double r, double dtheta, 
 
 int rrt_set_frame(rrt_ctx* ctx, int w, int h) {
   if (!ctx) return RRT_E_ARG;
+  if (!ctx->subs.empty()) { ctx->W = w; ctx->H = h; }
+  RRT_MULTI_ALL(ctx, rrt_set_frame(sub, w, h));
   if (w <= 0 || h <= 0 || (int64_t)w * h >= (1ll << 31)) FAIL(RRT_E_ARG, "rrt_set_frame: bad size");
   ctx->W = w; ctx->H = h; ctx->cell_w = 0;
   return RRT_OK;
@@ -417,12 +446,14 @@ int rrt_set_frame(rrt_ctx* ctx, int w, int h) {
 
 int rrt_set_cell(rrt_ctx* ctx, int x, int y, int w, int h) {
   if (!ctx) return RRT_E_ARG;
+  RRT_MULTI_ALL(ctx, rrt_set_cell(sub, x, y, w, h));
   ctx->cell_x = x; ctx->cell_y = y; ctx->cell_w = w; ctx->cell_h = h;
   return RRT_OK;
 }
 
 int rrt_set_progress(rrt_ctx* ctx, rrt_progress_fn fn, void* user) {
   if (!ctx) return RRT_E_ARG;
+  if (!ctx->subs.empty()) { if (!fn) return RRT_OK; FAIL(RRT_E_ARG, "rrt_set_progress: not available on a multi-GPU context (the GPUs render their tiles independently)"); }
   if (ctx->in_progress_cb) FAIL(RRT_E_STATE, "rrt_set_progress: called from inside the callback");
   ctx->progress_fn = fn; ctx->progress_user = user;
   return RRT_OK;
@@ -430,6 +461,7 @@ int rrt_set_progress(rrt_ctx* ctx, rrt_progress_fn fn, void* user) {
 
 int rrt_snapshot(rrt_ctx* ctx, float* hdr_rgb, int32_t* sample_counts) {
   if (!ctx) return RRT_E_ARG;
+  if (!ctx->subs.empty()) FAIL(RRT_E_STATE, "rrt_snapshot: not available on a multi-GPU context");
   if (!ctx->in_progress_cb) FAIL(RRT_E_STATE, "rrt_snapshot: only valid inside an rrt_progress_fn call");
   const size_t npix = ctx->snap_npix;
   CK(cudaSetDevice(ctx->device));
@@ -444,6 +476,11 @@ int rrt_snapshot(rrt_ctx* ctx, float* hdr_rgb, int32_t* sample_counts) {
 
 int rrt_set_tile_shard(rrt_ctx* ctx, int tile, int rank, int world) {
   if (!ctx) return RRT_E_ARG;
+  if (!ctx->subs.empty()) {   /* the context deals its own GPUs; only the tile size can be chosen */
+    if (tile <= 0 || rank != 0 || world != 1) FAIL(RRT_E_ARG, "rrt_set_tile_shard: a multi-GPU context shards over its own GPUs; pass (tile, 0, 1)");
+    for (size_t k = 0; k < ctx->subs.size(); ++k) { ctx->subs[k]->tile = tile; }
+    return RRT_OK;
+  }
   if (tile <= 0 || world <= 0 || rank < 0 || rank >= world) FAIL(RRT_E_ARG, "rrt_set_tile_shard: bad arguments");
   ctx->tile = tile; ctx->rank = rank; ctx->world = world;
   return RRT_OK;
@@ -459,10 +496,11 @@ int rrt_bvh_build_host(const rrt_scene* scene, int topology, int32_t info[8], ui
   return RRT_OK;
 }
 
-int rrt_chords_per_ray(rrt_ctx* ctx) { return ctx ? ctx->bh.nchords : RRT_E_ARG; }
+int rrt_chords_per_ray(rrt_ctx* ctx) { if (ctx && !ctx->subs.empty()) return rrt_chords_per_ray(ctx->subs[0]); return ctx ? ctx->bh.nchords : RRT_E_ARG; }
 
 int rrt_bvh_info(rrt_ctx* ctx, int32_t* n_nodes, int32_t* n_leaves, int32_t* depth, uint32_t* dfs_rank) {
   if (!ctx) return RRT_E_ARG;
+  RRT_MULTI_FWD(ctx, rrt_bvh_info(ctx0, n_nodes, n_leaves, depth, dfs_rank));
   if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_bvh_info: no scene");
   if (n_nodes) *n_nodes = ctx->bvh.ref_nodes;
   if (n_leaves) *n_leaves = ctx->bvh.ref_leaves;
@@ -833,6 +871,7 @@ extern "C" {
 
 int rrt_render(rrt_ctx* ctx, const rrt_params* p, float* hdr_rgb, int32_t* sample_counts, rrt_stats* stats) {
   if (!ctx || !p) return RRT_E_ARG;
+  if (!ctx->subs.empty()) return multi_render(ctx, p, hdr_rgb, sample_counts, nullptr, nullptr, stats);
   const size_t npix = (size_t)ctx->W * ctx->H;
   CK(cudaSetDevice(ctx->device));
   CK(ctx->d_out_rgb.ensure(12 * npix)); CK(ctx->d_out_cnt.ensure(4 * npix));
@@ -845,6 +884,11 @@ int rrt_render(rrt_ctx* ctx, const rrt_params* p, float* hdr_rgb, int32_t* sampl
 
 int rrt_render_device(rrt_ctx* ctx, const rrt_params* p, void* d_rgbn, void* d_counts, void* stream, rrt_stats* stats) {
   if (!ctx || !p) return RRT_E_ARG;
+  if (!ctx->subs.empty()) {
+    if (!d_rgbn) FAIL(RRT_E_ARG, "rrt_render_device: d_rgbn is NULL");
+    if (stream) CK(cudaStreamSynchronize((cudaStream_t)stream));
+    return multi_render(ctx, p, nullptr, nullptr, d_rgbn, d_counts, stats);
+  }
   if (stream) CK(cudaStreamSynchronize((cudaStream_t)stream));
   return render_impl(ctx, p, nullptr, (int*)d_counts, (float4*)d_rgbn, (cudaStream_t)stream, stats);
 }
@@ -876,6 +920,7 @@ static int grid_for(long long n, int block) { long long g = (n + block - 1) / bl
 
 int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, const double* min_t, const double* max_t, int any_hit, rrt_hit* out,
                    rrt_stats* stats) {
+  RRT_MULTI_FWD(ctx, rrt_trace_rays(ctx0, n, o, d, min_t, max_t, any_hit, out, stats));
   if (!ctx || n < 0 || (n && (!o || !d || !out))) return RRT_E_ARG;
   if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_trace_rays: no scene");
   if (stats) memset(stats, 0, sizeof *stats);
@@ -911,6 +956,7 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
 }
 
 int rrt_geodesic(rrt_ctx* ctx, int64_t n, const double* o, const double* d, int nsteps, double* seg_out) {
+  RRT_MULTI_FWD(ctx, rrt_geodesic(ctx0, n, o, d, nsteps, seg_out));
   if (!ctx || n < 0 || nsteps < 0 || (n && (!o || !d || !seg_out))) return RRT_E_ARG;
   if (n == 0 || nsteps == 0) return RRT_OK;
   size_t ob = 64 * (size_t)n * nsteps;
@@ -928,6 +974,7 @@ int rrt_geodesic(rrt_ctx* ctx, int64_t n, const double* o, const double* d, int 
 }
 
 int rrt_generate_rays(rrt_ctx* ctx, int64_t n, const double* xy, double* o, double* d) {
+  RRT_MULTI_FWD(ctx, rrt_generate_rays(ctx0, n, xy, o, d));
   if (!ctx || n < 0 || (n && (!xy || !o || !d))) return RRT_E_ARG;
   if (!ctx->have_cam) FAIL(RRT_E_STATE, "rrt_generate_rays: no camera");
   if (n == 0) return RRT_OK;
@@ -945,6 +992,7 @@ int rrt_generate_rays(rrt_ctx* ctx, int64_t n, const double* xy, double* o, doub
 }
 
 int rrt_generate_rays_thin_lens(rrt_ctx* ctx, int64_t n, const double* xy, const double* lens, double* o, double* d) {
+  RRT_MULTI_FWD(ctx, rrt_generate_rays_thin_lens(ctx0, n, xy, lens, o, d));
   if (!ctx || n < 0 || (n && (!xy || !lens || !o || !d))) return RRT_E_ARG;
   if (!ctx->have_cam) FAIL(RRT_E_STATE, "rrt_generate_rays_thin_lens: no camera");
   if (n == 0) return RRT_OK;
@@ -981,16 +1029,19 @@ static int bsdf_hook(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const d
 }
 
 int rrt_bsdf_sample(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const double* u, float* f, double* wi, float* pdf) {
+  RRT_MULTI_FWD(ctx, rrt_bsdf_sample(ctx0, mat, n, wo, u, f, wi, pdf));
   if (!ctx || n < 0 || (n && (!wo || !u || !f || !wi || !pdf))) return RRT_E_ARG;
   return bsdf_hook(ctx, mat, n, wo, nullptr, u, f, wi, pdf);
 }
 
 int rrt_bsdf_eval(rrt_ctx* ctx, int mat, int64_t n, const double* wo, const double* wi, float* f) {
+  RRT_MULTI_FWD(ctx, rrt_bsdf_eval(ctx0, mat, n, wo, wi, f));
   if (!ctx || n < 0 || (n && (!wo || !wi || !f))) return RRT_E_ARG;
   return bsdf_hook(ctx, mat, n, wo, wi, nullptr, f, nullptr, nullptr);
 }
 
 int rrt_light_sample(rrt_ctx* ctx, int light, int64_t n, const double* p, const double* u, float* radiance, double* wi, float* dist, float* pdf) {
+  RRT_MULTI_FWD(ctx, rrt_light_sample(ctx0, light, n, p, u, radiance, wi, dist, pdf));
   if (!ctx || n < 0 || (n && (!p || !u || !radiance || !wi || !dist || !pdf))) return RRT_E_ARG;
   if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_light_sample: no scene");
   const bool is_env = ctx->have_env && light == ctx->ds.n_lights;   /* the environment light is the last light */
@@ -1017,6 +1068,7 @@ int rrt_light_sample(rrt_ctx* ctx, int light, int64_t n, const double* p, const 
  * sampling tables (per-texel pdf, per-row conditional CDF, marginal CDF of the rows), built on the host in the reference's
  * summation order and kept on the device. */
 int rrt_set_envmap(rrt_ctx* ctx, int width, int height, const float* rgb) {
+  RRT_MULTI_ALL(ctx, rrt_set_envmap(sub, width, height, rgb));
   if (!ctx) return RRT_E_ARG;
   DevScene& d = ctx->ds;
   if (!rgb || width <= 0 || height <= 0) {
@@ -1057,6 +1109,7 @@ int rrt_set_envmap(rrt_ctx* ctx, int width, int height, const float* rgb) {
 
 /* EnvironmentLight::sample_dir for n directions d [n*3] -> radiance [n*3] (parity hook) */
 int rrt_env_lookup(rrt_ctx* ctx, int64_t n, const double* dir, float* radiance) {
+  RRT_MULTI_FWD(ctx, rrt_env_lookup(ctx0, n, dir, radiance));
   if (!ctx || n < 0 || (n && (!dir || !radiance))) return RRT_E_ARG;
   if (!ctx->have_env) FAIL(RRT_E_STATE, "rrt_env_lookup: no environment map");
   if (n == 0) return RRT_OK;
@@ -1073,6 +1126,7 @@ int rrt_env_lookup(rrt_ctx* ctx, int64_t n, const double* dir, float* radiance) 
 }
 
 int rrt_philox(rrt_ctx* ctx, uint64_t seed, int64_t n, const uint32_t* counters, uint32_t* out) {
+  RRT_MULTI_FWD(ctx, rrt_philox(ctx0, seed, n, counters, out));
   if (!ctx || n < 0 || (n && (!counters || !out))) return RRT_E_ARG;
   if (n == 0) return RRT_OK;
   int rc = hook_begin(ctx, 16 * (size_t)n, 16 * (size_t)n);
@@ -1088,6 +1142,7 @@ int rrt_philox(rrt_ctx* ctx, uint64_t seed, int64_t n, const uint32_t* counters,
 }
 
 int rrt_tonemap(rrt_ctx* ctx, int64_t n, const float* hdr_rgb, uint32_t* rgba) {
+  RRT_MULTI_FWD(ctx, rrt_tonemap(ctx0, n, hdr_rgb, rgba));
   if (!ctx || n < 0 || (n && (!hdr_rgb || !rgba))) return RRT_E_ARG;
   if (n == 0) return RRT_OK;
   int rc = hook_begin(ctx, 12 * (size_t)n, 4 * (size_t)n);
@@ -1134,6 +1189,7 @@ static int static_scratch_for(rrt_ctx* ctx, unsigned char** out) {
 
 extern "C" int rrt_trace_rays_static(rrt_ctx* ctx, int64_t n, const double* o, const double* d, const double* min_t, const double* max_t, int any_hit,
                                      rrt_hit* out) {
+  RRT_MULTI_FWD(ctx, rrt_trace_rays_static(ctx0, n, o, d, min_t, max_t, any_hit, out));
   if (!ctx || n < 0 || (n && (!o || !d || !out))) return RRT_E_ARG;
   if (!ctx->have_scene) FAIL(RRT_E_STATE, "rrt_trace_rays_static: no scene");
   if (n > RRT_STATIC_MAX_RAYS) {
@@ -1160,5 +1216,209 @@ extern "C" int rrt_trace_rays_static(rrt_ctx* ctx, int64_t n, const double* o, c
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(out, d_out, sizeof(rrt_hit) * (size_t)n, cudaMemcpyDefault, st));
   CK(cudaStreamSynchronize(st));
+  return RRT_OK;
+}
+
+/* ---------------------------------------------------------------- multi-GPU context (rrt_create_multi)
+ * One process drives G GPUs (the reference's N worker threads pulling tiles from one queue, src/pathtracer.cpp:224-282,
+ * 611-644, become G GPUs each owning the interleaved tiles (tx + ty * stride) % G == k, KeepOwned in rrt_kernels.cuh).
+ *   scene   built once on GPU 0 (BVH build included), then replicated to the other GPUs by ncclBroadcast of the device arrays
+ *   render  one host thread per GPU runs the same wavefront loop on its tiles: no exchange while rendering, a pixel's estimate
+ *           depends only on (seed, pixel, sample)
+ *   frame   ONE collective per frame: ncclReduce(sum) of the per-GPU float4 frames (mean r, g, b, sample count; pixels a GPU
+ *           does not own are zero) onto GPU 0, then one kernel there splits it into the reference's sampleBuffer /
+ *           sampleCountBuffer layout.
+ * NCCL is loaded with dlopen at rrt_create_multi time, so single-GPU users of the library do not need it installed. */
+#include <dlfcn.h>
+#include <nccl.h>
+#include <thread>
+
+namespace {
+struct NcclApi {
+  void* lib = nullptr;
+  ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*Reduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi g_nccl;
+std::mutex g_nccl_mu;
+
+const char* load_nccl() {   /* nullptr = ok, else what went wrong */
+  std::lock_guard<std::mutex> lk(g_nccl_mu);
+  if (g_nccl.lib) return nullptr;
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) return "libnccl.so.2 could not be loaded (multi-GPU contexts need NCCL)";
+  NcclApi a; a.lib = h;
+#define RRT_SYM(field, name) *(void**)(&a.field) = dlsym(h, name); if (!a.field) { dlclose(h); return "libnccl.so.2 lacks " name; }
+  RRT_SYM(CommInitAll, "ncclCommInitAll") RRT_SYM(CommDestroy, "ncclCommDestroy") RRT_SYM(Reduce, "ncclReduce") RRT_SYM(Broadcast, "ncclBroadcast")
+  RRT_SYM(GroupStart, "ncclGroupStart") RRT_SYM(GroupEnd, "ncclGroupEnd") RRT_SYM(GetErrorString, "ncclGetErrorString")
+#undef RRT_SYM
+  g_nccl = a;
+  return nullptr;
+}
+}  // namespace
+
+#define NCK(call)                                                                                         \
+  do {                                                                                                    \
+    ncclResult_t r_ = (call);                                                                             \
+    if (r_ != ncclSuccess) {                                                                              \
+      char b_[512]; snprintf(b_, sizeof b_, "%s:%d: %s: %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(r_)); \
+      ctx->err = b_; return RRT_E_CUDA;                                                                   \
+    }                                                                                                     \
+  } while (0)
+
+/* float4 (mean r, g, b, n) -> sampleBuffer rgb + sampleCountBuffer (either may be NULL); n is an exact small integer in float */
+__global__ void __launch_bounds__(256) k_split_rgbn(size_t npix, const float4* __restrict__ rgbn, float* __restrict__ rgb, int* __restrict__ counts) {
+  for (size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x; p < npix; p += (size_t)gridDim.x * blockDim.x) {
+    const float4 v = rgbn[p];
+    if (rgb) { rgb[3 * p] = v.x; rgb[3 * p + 1] = v.y; rgb[3 * p + 2] = v.z; }
+    if (counts) counts[p] = (int)v.w;
+  }
+}
+
+extern "C" int rrt_create_multi(rrt_ctx** out, int n_gpus, const int* devices) {
+  if (!out) { g_create_error = "rrt_create_multi: out is NULL"; return RRT_E_ARG; }
+  *out = nullptr;
+  if (n_gpus <= 0 || n_gpus > 64) { g_create_error = "rrt_create_multi: n_gpus must be 1..64"; return RRT_E_ARG; }
+  std::vector<int> devs(n_gpus);
+  for (int k = 0; k < n_gpus; ++k) devs[k] = devices ? devices[k] : k;
+  for (int k = 0; k < n_gpus; ++k)
+    for (int j = 0; j < k; ++j)
+      if (devs[j] == devs[k]) { g_create_error = "rrt_create_multi: a device is listed twice"; return RRT_E_ARG; }
+  if (n_gpus == 1) return rrt_create(out, devs[0]);   /* nothing to shard, no NCCL needed */
+  if (const char* why = load_nccl()) { g_create_error = std::string("rrt_create_multi: ") + why; return RRT_E_CUDA; }
+  rrt_ctx* m = new rrt_ctx();
+  memset(m->opt, 0, sizeof m->opt);
+  for (int k = 0; k < n_gpus; ++k) {
+    rrt_ctx* sub = nullptr;
+    int rc = rrt_create(&sub, devs[k]);
+    if (rc) { for (rrt_ctx* s : m->subs) rrt_destroy(s); delete m; return rc; }
+    sub->tile = 8; sub->rank = k; sub->world = n_gpus;
+    m->subs.push_back(sub);
+  }
+  m->device = devs[0];
+  std::vector<ncclComm_t> comms(n_gpus);
+  ncclResult_t r = g_nccl.CommInitAll(comms.data(), n_gpus, devs.data());
+  if (r != ncclSuccess) {
+    g_create_error = std::string("rrt_create_multi: ncclCommInitAll: ") + g_nccl.GetErrorString(r);
+    for (rrt_ctx* s : m->subs) rrt_destroy(s);
+    delete m; return RRT_E_CUDA;
+  }
+  for (ncclComm_t c : comms) m->comms.push_back((void*)c);
+  *out = m;
+  return RRT_OK;
+}
+
+extern "C" int rrt_gpu_count(const rrt_ctx* ctx) { return !ctx ? RRT_E_ARG : ctx->subs.empty() ? 1 : (int)ctx->subs.size(); }
+
+static void multi_destroy(rrt_ctx* m) {
+  for (size_t k = 0; k < m->comms.size(); ++k) { cudaSetDevice(m->subs[k]->device); cudaStreamSynchronize(m->subs[k]->stream); g_nccl.CommDestroy((ncclComm_t)m->comms[k]); }
+  for (rrt_ctx* s : m->subs) rrt_destroy(s);
+  for (cudaEvent_t ev : m->events) cudaEventDestroy(ev);
+  delete m;
+}
+
+/* device pointers of the scene arrays of ctx (everything rrt_upload_scene fills) */
+static void bind_scene_pointers(rrt_ctx* c) {
+  DevScene& d = c->ds;
+  d.nodes = c->d_nodes.as<float4>(); d.leaf = c->d_leaf.as<double2>(); d.tri_nrm = c->d_nrm.as<double>();
+  d.prim_kind = c->d_kind.as<uint8_t>(); d.prim_index = c->d_index.as<uint32_t>(); d.prim_mat = c->d_pmat.as<int32_t>();
+  d.sph = c->d_sph.as<double>(); d.mats = c->d_mats.as<rrt_material>(); d.lights = c->d_lights.as<rrt_light>();
+}
+
+static int multi_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
+  rrt_ctx* root = ctx->subs[0];
+  int rc = rrt_upload_scene(root, s);
+  if (rc) { ctx->err = root->err; return rc; }
+  const size_t G = ctx->subs.size();
+  /* the arrays the kernels read, as rrt_upload_scene left them on GPU 0 (capacities can exceed the bytes in use: harmless) */
+  DevBuf rrt_ctx::* const bufs[] = {&rrt_ctx::d_nodes, &rrt_ctx::d_wide, &rrt_ctx::d_leaf, &rrt_ctx::d_nrm, &rrt_ctx::d_kind, &rrt_ctx::d_index, &rrt_ctx::d_pmat,
+                                    &rrt_ctx::d_sph, &rrt_ctx::d_mats, &rrt_ctx::d_lights, &rrt_ctx::d_grid};
+  for (size_t k = 1; k < G; ++k) {
+    rrt_ctx* c = ctx->subs[k];
+    CK(cudaSetDevice(c->device));
+    for (auto mp : bufs) CK((c->*mp).ensure((root->*mp).bytes));
+  }
+  for (auto mp : bufs) {
+    const size_t bytes = (root->*mp).bytes;
+    if (!bytes) continue;
+    NCK(g_nccl.GroupStart());
+    for (size_t k = 0; k < G; ++k) {
+      rrt_ctx* c = ctx->subs[k];
+      NCK(g_nccl.Broadcast((root->*mp).p, (c->*mp).p, bytes, ncclUint8, 0, (ncclComm_t)ctx->comms[k], c->stream));
+    }
+    NCK(g_nccl.GroupEnd());
+  }
+  for (size_t k = 0; k < G; ++k) { CK(cudaSetDevice(ctx->subs[k]->device)); CK(cudaStreamSynchronize(ctx->subs[k]->stream)); }
+  for (size_t k = 1; k < G; ++k) {
+    rrt_ctx* c = ctx->subs[k];
+    const DevScene keep = c->ds;           /* the environment light lives in the same struct and survives rrt_upload_scene */
+    c->ds = root->ds;
+    c->ds.env = keep.env; c->ds.env_pdf = keep.env_pdf; c->ds.env_cond = keep.env_cond; c->ds.env_marg = keep.env_marg; c->ds.env_w = keep.env_w; c->ds.env_h = keep.env_h;
+    bind_scene_pointers(c);
+    c->ds.wide = root->ds.wide ? c->d_wide.as<float>() : nullptr;
+    c->ds.clearance = root->ds.clearance ? c->d_grid.as<float>() : nullptr;
+    c->n_lights = root->n_lights; c->n_delta_lights = root->n_delta_lights; c->host_lights = root->host_lights; c->has_microfacet = root->has_microfacet;
+    c->have_scene = true;
+  }
+  return RRT_OK;
+}
+
+static int multi_render(rrt_ctx* ctx, const rrt_params* p, float* hdr_rgb, int32_t* sample_counts, void* d_rgbn_user, void* d_counts_user, rrt_stats* stats) {
+  const size_t G = ctx->subs.size();
+  rrt_ctx* root = ctx->subs[0];
+  const size_t npix = (size_t)root->W * root->H;
+  if (!root->have_scene || !root->have_cam || root->W <= 0) FAIL(RRT_E_STATE, "rrt_render: scene, camera and frame must be set first");
+  for (size_t k = 0; k < G; ++k) { rrt_ctx* c = ctx->subs[k]; CK(cudaSetDevice(c->device)); CK(c->d_out_rgbn.ensure(16 * npix)); }
+  std::vector<int> rcs(G, 0);
+  std::vector<rrt_stats> sts(G);
+  std::vector<std::thread> th;
+  for (size_t k = 0; k < G; ++k)
+    th.emplace_back([&, k]() { rrt_ctx* c = ctx->subs[k]; rcs[k] = render_impl(c, p, nullptr, nullptr, c->d_out_rgbn.as<float4>(), nullptr, stats ? &sts[k] : nullptr); });
+  for (auto& t : th) t.join();
+  for (size_t k = 0; k < G; ++k) if (rcs[k]) { ctx->err = ctx->subs[k]->err; return rcs[k]; }
+  /* the frame's one collective */
+  CK(cudaSetDevice(root->device));
+  ctx->events_used = 0;
+  cudaEvent_t e0 = next_event(ctx), e1 = next_event(ctx);
+  CK(cudaEventRecord(e0, root->stream));
+  float4* dst = d_rgbn_user ? (float4*)d_rgbn_user : root->d_out_rgbn.as<float4>();
+  NCK(g_nccl.GroupStart());
+  for (size_t k = 0; k < G; ++k) {
+    rrt_ctx* c = ctx->subs[k];
+    NCK(g_nccl.Reduce(c->d_out_rgbn.p, k == 0 ? (void*)dst : c->d_out_rgbn.p, 4 * npix, ncclFloat, ncclSum, 0, (ncclComm_t)ctx->comms[k], c->stream));
+  }
+  NCK(g_nccl.GroupEnd());
+  CK(cudaSetDevice(root->device));
+  float* d_rgb = nullptr; int* d_cnt = (int*)d_counts_user;
+  if (!d_rgbn_user) {
+    CK(root->d_out_rgb.ensure(12 * npix)); CK(root->d_out_cnt.ensure(4 * npix));
+    d_rgb = root->d_out_rgb.as<float>(); d_cnt = root->d_out_cnt.as<int>();
+  }
+  if (d_rgb || d_cnt) k_split_rgbn<<<root->sm_count * 8, 256, 0, root->stream>>>(npix, dst, d_rgb, d_cnt);
+  CK(cudaEventRecord(e1, root->stream));
+  if (hdr_rgb) CK(cudaMemcpyAsync(hdr_rgb, d_rgb, 12 * npix, cudaMemcpyDeviceToHost, root->stream));
+  if (sample_counts) CK(cudaMemcpyAsync(sample_counts, d_cnt, 4 * npix, cudaMemcpyDeviceToHost, root->stream));
+  for (size_t k = 0; k < G; ++k) { CK(cudaSetDevice(ctx->subs[k]->device)); CK(cudaStreamSynchronize(ctx->subs[k]->stream)); }
+  CK(cudaSetDevice(root->device));
+  CK(cudaGetLastError());
+  if (stats) {
+    memset(stats, 0, sizeof *stats);
+    float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+    for (size_t k = 0; k < G; ++k) {
+      const rrt_stats& a = sts[k];
+      stats->seconds = std::max(stats->seconds, a.seconds); stats->trace_seconds = std::max(stats->trace_seconds, a.trace_seconds);
+      stats->paths += a.paths; stats->rays += a.rays; stats->geodesic_steps += a.geodesic_steps; stats->node_visits += a.node_visits;
+      stats->tri_tests += a.tri_tests; stats->sphere_tests += a.sphere_tests; stats->kernel_launches += a.kernel_launches;
+      stats->trace_launches += a.trace_launches; stats->algorithmic_bytes += a.algorithmic_bytes;
+    }
+    stats->seconds += ms * 1e-3;      /* slowest GPU + the reduce and the split on GPU 0 */
+    stats->kernel_launches += 1;
+  }
   return RRT_OK;
 }

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     assert len(names) >= 24 and set(names) == set(api.EXPORTS)
     for n in names:
         assert hasattr(L, n), n
-    assert L.rrt_abi_version() == 4
+    assert L.rrt_abi_version() == 5
 
 
 def test_struct_layouts_match_header():
