@@ -53,4 +53,5 @@ $CXX -O3 -fopenmp -o "$OUT/ref_probe_flat" $NOMAINBVH "$OUT/gen/bvh_flat.o" "$OU
 for f in CBspheres_lambertian CBspheres CBspheres_microfacet_al_ag CBbunny CBbunny_microfacet_cu CBgems CBcoil CBempty; do
   cp -f "$REF/dae/sky/$f.dae" "$OUT/dae/" 2>/dev/null || true
 done
+cp -f "$REF/dae/keenan/banana.dae" "$OUT/dae/" 2>/dev/null || true   # <ambient> + <directional> lights
 echo "[build_ref] built $(ls $OUT | tr '\n' ' ')"

@@ -66,6 +66,10 @@ SCENES = {  # name -> (dae, W, H, screenDist scale)
     # C5's generator at 4,608 triangles, exported as COLLADA (synth.write_c5_dae) and loaded by the reference's own loader
     "cbsynth_480x360": ("_generated_CBsynth_mesh.dae", 480, 360, None),
     "cbsynth_96x72": ("_generated_CBsynth_mesh.dae", 96, 72, 0.2),
+    # dae/keenan/banana.dae: the bundled scene with the two light classes no Cornell box has — <ambient> = InfiniteHemisphereLight,
+    # <directional> = DirectionalLight (reference src/static_scene/light.cpp:17-42)
+    "banana_480x360": ("banana.dae", 480, 360, None),
+    "banana_96x72": ("banana.dae", 96, 72, 0.2),
 }
 SYNTH_MESH = (48, 49)   # n_u, n_v of the exported mesh
 
@@ -207,7 +211,8 @@ def kat_bsdf(scene, seed):
     print("kat_bsdf", scene, len(s.mats), "materials")
 
 
-def kat_light(scene, seed):
+def kat_light(scene, seed, lights=(0,)):
+    """SceneLight::sample_L of the scene's lights `lights` for seeded points and uniforms: `out` = light lights[0], `out_<k>` = light k"""
     dae, w, h, _ = SCENES[scene]
     dae = os.path.join(DAE, dae)
     rng = np.random.default_rng(seed)
@@ -216,9 +221,12 @@ def kat_light(scene, seed):
     r = rng.integers(0, RAND_MAX, (n, 2), endpoint=True).astype(np.float64)
     r[0] = [0, 0]; r[1] = [RAND_MAX, RAND_MAX]
     inp = np.concatenate([p, r], 1)
-    probe("bh", "light", dae, w, h, 0, wr("light_in.bin", inp), tmpf("light_out.bin"))
-    np.savez_compressed(os.path.join(HERE, "kat_light_%s.npz" % scene), inp=inp, out=rd("light_out.bin", 10))
-    print("kat_light", scene)
+    outs = {}
+    for k in lights:
+        probe("bh", "light", dae, w, h, k, wr("light_in.bin", inp), tmpf("light_out.bin"))
+        outs["out" if k == lights[0] else "out_%d" % k] = rd("light_out.bin", 10)
+    np.savez_compressed(os.path.join(HERE, "kat_light_%s.npz" % scene), inp=inp, lights=np.array(lights), **outs)
+    print("kat_light", scene, lights)
 
 
 # ---------------------------------------------------------------- environment map (the reference ships none)
@@ -280,6 +288,9 @@ def make_kat(only=None):
     if only and "thin_lens" in only:
         kat_thin_lens("cbspheres_lambertian_480x360", 23)
         return
+    if only and "keenan" in only:
+        kat_light("banana_480x360", 25, lights=(0, 1))
+        return
     kat_thin_lens("cbspheres_lambertian_480x360", 23)
     kat_geodesic()
     kat_trace("cbspheres_lambertian_480x360", 96, 72, 2000, 1, bh_alt=(0.2, 0.8, -0.1, 0.05, 0.2))
@@ -289,6 +300,7 @@ def make_kat(only=None):
         kat_bsdf(sname, 10 + i)
     kat_light("cbspheres_lambertian_480x360", 20)
     kat_light("cbempty_480x360", 21)
+    kat_light("banana_480x360", 25, lights=(0, 1))
     kat_envmap("cbspheres_lambertian_480x360", 22)
 
 
@@ -321,6 +333,9 @@ RENDERS = {  # name -> (scene, mode, spp, l, m, batch, tol, seed, extra args)
     # the procedural mesh (C5's generator), through the reference's loader and raytrace_pixel
     "flat_synth_mesh": ("cbsynth_96x72", "flat", 8, 2, 4, 32, 0.05, 23, []),
     "bh_synth_mesh": ("cbsynth_96x72", "bh", 4, 2, 4, 32, 0.05, 24, []),
+    # InfiniteHemisphereLight + DirectionalLight (dae/keenan/banana.dae)
+    "flat_keenan_lights": ("banana_96x72", "flat", 16, 2, 4, 32, 0.05, 26, []),
+    "bh_keenan_lights": ("banana_96x72", "bh", 8, 2, 3, 32, 0.05, 27, []),
 }
 
 
@@ -351,6 +366,6 @@ if __name__ == "__main__":
     if "scenes" in what:
         make_scenes([w for w in what if w in SCENES] or None)
     if "kat" in what:
-        make_kat([w for w in what if w == "thin_lens"])
+        make_kat([w for w in what if w in ("thin_lens", "keenan")])
     if "render" in what:
         make_render([w for w in what if w in RENDERS] or None)

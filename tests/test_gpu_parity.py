@@ -196,6 +196,20 @@ def test_light_sample_L(api, scene):
     assert same(dist.astype(np.float64), ref[:, 6]) and same(pdf.astype(np.float64), ref[:, 7])
 
 
+def test_hemisphere_and_directional_light_sample_L(api):
+    """InfiniteHemisphereLight (uniform hemisphere sample through the reference's fixed sampleToWorld) and DirectionalLight: vectors from
+    the reference's own objects on dae/keenan/banana.dae"""
+    g = golden("kat_light_banana_480x360")
+    c = make_ctx(api, "banana_480x360")
+    inp = g["inp"]
+    for k, key in ((0, "out"), (1, "out_1")):
+        ref = g[key]
+        rad, wi, dist, pdf = c.light_sample(k, inp[:, 0:3], inp[:, 3:5] / RAND_MAX)
+        assert same(rad.astype(np.float64), ref[:, 0:3]) and same(dist.astype(np.float64), ref[:, 6]) and same(pdf.astype(np.float64), ref[:, 7]), k
+        np.testing.assert_allclose(wi, ref[:, 3:6], rtol=0, atol=2e-16)   # hemisphere: cos / sin of 2 pi xi through CUDA's libm; directional: exact
+    assert same(c.light_sample(1, inp[:, 0:3], inp[:, 3:5] / RAND_MAX)[1], g["out_1"][:, 3:6])
+
+
 def test_environment_light_matches_reference_vectors(api):
     """EnvironmentLight::sample_L / sample_dir (golden vectors made by the reference's own class, tests/golden/kat_envmap.npz)"""
     g = golden("kat_envmap")

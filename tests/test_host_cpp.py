@@ -32,7 +32,8 @@ def exe():
 
 PAIRS = [("CBspheres_lambertian.dae", "cbspheres_lambertian_480x360"), ("CBempty.dae", "cbempty_480x360"),
          ("CBspheres.dae", "cbspheres_480x360"), ("CBspheres_microfacet_al_ag.dae", "cbspheres_microfacet_480x360"),
-         ("CBgems.dae", "cbgems_480x360"), ("CBbunny_microfacet_cu.dae", "cbbunny_microfacet_480x360")]
+         ("CBgems.dae", "cbgems_480x360"), ("CBbunny_microfacet_cu.dae", "cbbunny_microfacet_480x360"),
+         ("banana.dae", "banana_480x360")]   # <ambient> + <directional> lights, three materials, no Cornell box
 
 
 @pytest.mark.parametrize("dae,gold", PAIRS)

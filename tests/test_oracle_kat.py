@@ -109,6 +109,24 @@ def test_light_sample_L(scene):
     assert same(dist.astype(np.float64), ref[:, 6]) and same(pdf.astype(np.float64), ref[:, 7])
 
 
+def test_hemisphere_and_directional_light_sample_L():
+    """InfiniteHemisphereLight and DirectionalLight (reference src/static_scene/light.cpp:34-42, 17-23): the two on-path light classes
+    no Cornell box has; vectors from the reference's own objects on dae/keenan/banana.dae (<ambient> and <directional>)"""
+    g = golden("kat_light_banana_480x360")
+    s = load_scene("banana_480x360")
+    assert [int(l["type"]) for l in s.lights] == [1, 0] and [int(l["is_delta"]) for l in s.lights] == [0, 1]   # RRT_LIGHT_HEMISPHERE, RRT_LIGHT_DIRECTIONAL
+    o = orc.Oracle(s)
+    inp = g["inp"]
+    for k, key in ((0, "out"), (1, "out_1")):
+        ref = g[key]
+        rad, wi, dist, pdf = o.light_sample(k, inp[:, 0:3], inp[:, 3:5] / RAND_MAX)
+        assert same(rad.astype(np.float64), ref[:, 0:3]) and same(wi, ref[:, 3:6]), k
+        assert same(dist.astype(np.float64), ref[:, 6]) and same(pdf.astype(np.float64), ref[:, 7]), k
+    hemi, dirl = g["out"], g["out_1"]
+    assert np.isinf(hemi[:, 6]).all() and np.allclose(hemi[:, 7], 1 / (2 * np.pi)) and (hemi[:, 4] >= -1e-7).all()   # uniform over the +y hemisphere (the reference's sampleToWorld has float-rounded zeros)
+    assert np.isinf(dirl[:, 6]).all() and (dirl[:, 7] == 1).all() and (dirl[:, 3:6] == dirl[0, 3:6]).all()        # one fixed direction, pdf 1
+
+
 def test_environment_light_sample_L_and_sample_dir():
     """EnvironmentLight (reference src/static_scene/environment_light.cpp) as the last light of the scene: importance
     sampling through the marginal / conditional tables, and the direction lookup used for camera rays that miss"""

@@ -10,7 +10,7 @@ from oracle import orc
 RENDERS = ["c1_flat_lambertian", "c2_bh_lambertian", "bh_glass_mirror", "flat_glass_mirror", "flat_microfacet", "bh_microfacet",
            "flat_gems", "flat_bunny_microfacet", "bh_bunny_microfacet", "flat_adaptive", "bh_adaptive", "flat_depth0",
            "flat_depth1", "bh_depth1_spp1", "flat_pointlight", "flat_hemisphere", "bh_alt_hole", "flat_envmap", "bh_envmap", "bh_envmap_gems",
-           "flat_thin_lens", "bh_thin_lens", "flat_synth_mesh", "bh_synth_mesh"]
+           "flat_thin_lens", "bh_thin_lens", "flat_synth_mesh", "bh_synth_mesh", "flat_keenan_lights", "bh_keenan_lights"]
 
 
 def setup_from_golden(g, obj):
