@@ -125,12 +125,17 @@ bool load_exr(const std::vector<uint8_t>& b, int* w, int* h, std::vector<float>*
     if (name == "channels") {
       size_t p = 0;
       while (p < (size_t)size && v[p]) {
-        Channel c; c.name = (const char*)v + p; p += c.name.size() + 1;
-        int32_t t; memcpy(&t, v + p, 4); c.type = t; p += 16;   // pixel type, pLinear + reserved, xSampling, ySampling
+        size_t e = p;
+        while (e < (size_t)size && v[e]) ++e;                    // the name must end inside the attribute
+        if (e >= (size_t)size || e + 1 + 16 > (size_t)size) { *err = "truncated OpenEXR channel list"; return false; }
+        Channel c; c.name.assign((const char*)v + p, e - p); p = e + 1;
+        int32_t t, xs, ys; memcpy(&t, v + p, 4); memcpy(&xs, v + p + 8, 4); memcpy(&ys, v + p + 12, 4);
+        c.type = t; p += 16;   // pixel type, pLinear + reserved, xSampling, ySampling
+        if (xs != 1 || ys != 1) { *err = "sub-sampled OpenEXR channels are not supported"; return false; }
         chans.push_back(c);
       }
-    } else if (name == "compression") compression = v[0];
-    else if (name == "dataWindow") memcpy(dw, v, 16);
+    } else if (name == "compression") { if (size < 1) { *err = "truncated OpenEXR attribute"; return false; } compression = v[0]; }
+    else if (name == "dataWindow") { if (size < 16) { *err = "truncated OpenEXR attribute"; return false; } memcpy(dw, v, 16); }
     pos += (size_t)size;
   }
   if (compression < 0 || compression > 3) {
@@ -139,8 +144,10 @@ bool load_exr(const std::vector<uint8_t>& b, int* w, int* h, std::vector<float>*
            " is not supported (NONE, RLE, ZIPS and ZIP are): re-save the map with one of those, or as .pfm";
     return false;
   }
-  *w = dw[2] - dw[0] + 1; *h = dw[3] - dw[1] + 1;
-  if (*w <= 0 || *h <= 0 || chans.empty()) { *err = "OpenEXR header without channels / data window"; return false; }
+  const int64_t w64 = (int64_t)dw[2] - dw[0] + 1, h64 = (int64_t)dw[3] - dw[1] + 1;
+  if (w64 <= 0 || h64 <= 0 || chans.empty()) { *err = "OpenEXR header without channels / data window"; return false; }
+  if (w64 > 65536 || h64 > 65536 || w64 * h64 >= ((int64_t)1 << 31)) { *err = "OpenEXR data window too large (rrt_set_envmap takes width * height < 2^31)"; return false; }
+  *w = (int)w64; *h = (int)h64;
   std::map<std::string, int> slot = {{"R", 0}, {"G", 1}, {"B", 2}};
   size_t row_bytes = 0;
   for (const Channel& c : chans) {

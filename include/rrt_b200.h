@@ -177,6 +177,8 @@ enum {
                                  chords within ~1e-6 of the reference's (bound asserted: 1e-4), NOT bit-identical; trace kernel 0 only */
   RRT_OPT_STREAMS = 10,       /* CUDA streams the wavefront chunks of one adaptive round are dealt over (1..4, default 2): a trace launch ends ragged
                                  (rays need 1..63 chords) and another stream's kernels fill the idle SMs; bit-identical results for any value */
+  RRT_OPT_ESCAPE = 11,        /* A/B builds only (otherwise RRT_E_ARG for a non-zero value): 1 = rays that have left the scene box are parked by the trace kernel
+                                 and carried on by a lean kernel (stepper + horizon + root-box test only); measured slower, default 0.  Bit-identical results */
   RRT_OPT_BVH_BUILDER = 9     /* where the BVH is built.  1 = on the device: the reference's depth-first ranks by level-synchronous stable partition
                                  + an LBVH for the traversal (scenes of >= 64 primitives, binary nodes; falls back to the host if the tree comes
                                  out deeper than the traversal stack); 2 = on the host (reference tree shape or binned SAH, threaded);
@@ -204,9 +206,11 @@ int rrt_set_option(rrt_ctx* ctx, int option, int64_t value);
 /* ---- configuration (host buffers) ---- */
 int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* scene);
 int rrt_set_camera(rrt_ctx* ctx, const rrt_camera* cam);
+/* centre, r finite, r >= 0; delta_theta finite and >= 2 pi / 65536 (RRT_E_ARG otherwise: with a NaN or non-positive step the reference's
+ * loop `j * delta_theta < 2 pi`, src/bvh.cpp:105, never ends) */
 int rrt_set_blackhole(rrt_ctx* ctx, const double centre[3], double r, double delta_theta, int mode);
 int rrt_set_frame(rrt_ctx* ctx, int width, int height);
-/* cell render (-p x y dx dy); w<=0 restores the full frame */
+/* cell render (-p x y dx dy); w <= 0 restores the full frame; w > 0 needs h > 0 */
 int rrt_set_cell(rrt_ctx* ctx, int x, int y, int w, int h);
 /* Environment light, the reference's -e <map.exr> (src/main.cpp:42-79, src/static_scene/environment_light.cpp):
  * rgb = [height*width*3] floats, row 0 = top of the lat-long map (theta = 0 is +y).  The light is appended after the
@@ -224,8 +228,10 @@ int rrt_set_tile_shard(rrt_ctx* ctx, int tile_size, int rank, int world);
  * Either output may be NULL.  Host buffers; the copies are inside the call. */
 int rrt_render(rrt_ctx* ctx, const rrt_params* p, float* hdr_rgb, int32_t* sample_counts, rrt_stats* stats);
 /* Same, results left on the device: d_rgbn is a CUDA device pointer to [W*H] float4 (mean r,g,b, sample
- * count as float), d_counts a device pointer to [W*H] int32 or NULL.  Runs on `stream` (a cudaStream_t
- * passed as void*, NULL = the context's own stream) and synchronises it before returning. */
+ * count as float), d_counts a device pointer to [W*H] int32 or NULL.  BLOCKING: the call first synchronises
+ * `stream` (a cudaStream_t passed as void*, may be NULL: work the caller queued there, e.g. clearing d_rgbn, is
+ * finished before the render starts), renders on the context's own non-blocking streams (the adaptive rounds need host
+ * read-backs), and returns when d_rgbn / d_counts are complete — any stream may read them afterwards. */
 int rrt_render_device(rrt_ctx* ctx, const rrt_params* p, void* d_rgbn, void* d_counts, void* stream, rrt_stats* stats);
 
 /* ---- parity hooks: the same device code the render uses, on caller-supplied inputs ---- */

@@ -62,7 +62,8 @@ static inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
 }
 
 struct RandState {
-  int mode = 0;  // 0 queue, 1 philox stream
+  int mode = 0;  // 0 queue, 1 philox stream, 2 glibc's own generator (random_r: the algorithm behind rand(), per-thread state, no lock)
+  struct random_data rdata; char rstate[128]; bool rinit = false;
   std::vector<int> queue; size_t qpos = 0;
   uint64_t seed = 0; uint32_t pixel = 0, sample = 0, n = 0;
   uint64_t draws = 0;
@@ -77,6 +78,7 @@ extern "C" int rand(void) {
     if (s.qpos >= s.queue.size()) { fprintf(stderr, "[ref_probe] rand queue exhausted\n"); abort(); }
     return s.queue[s.qpos++];
   }
+  if (s.mode == 2) { int32_t r = 0; random_r(&s.rdata, &r); return (int)r; }
   uint32_t c[4] = {s.pixel, s.sample, s.n >> 2, 0u};
   philox4x32_10(c, (uint32_t)s.seed, (uint32_t)(s.seed >> 32));
   uint32_t w = c[s.n & 3];
@@ -418,6 +420,36 @@ static int cmd_order(int, char**) {
   return 0;
 }
 
+// bvhorder: the reference's OWN tree (BVHAccel::construct_bvh, src/bvh.cpp:49-96) walked as intersect_micro walks it (left, then right; a
+// leaf's primitives in vector order, src/bvh.cpp:120-135): out = [nodes, leaves, depth, rank of primitive 0, rank of primitive 1, ...] as
+// doubles, rank = position of the primitive in that depth-first leaf order.  Pins the tie-break ranks (Triangle::intersect keeps the LAST
+// primitive among equal t, src/static_scene/triangle.cpp:43-45) to the reference's tree itself rather than to a restatement of its builder.
+static void walk_bvh(const BVHNode* n, int depth, const std::map<const Primitive*, size_t>& idx, std::vector<double>& rank, size_t& next, size_t& nodes,
+                     size_t& leaves, int& maxdepth) {
+  ++nodes; maxdepth = std::max(maxdepth, depth);
+  if (n->isLeaf()) {
+    ++leaves;
+    for (const Primitive* p : *n->prims) rank[idx.at(p)] = (double)next++;
+    return;
+  }
+  if (n->l) walk_bvh(n->l, depth + 1, idx, rank, next, nodes, leaves, maxdepth);
+  if (n->r) walk_bvh(n->r, depth + 1, idx, rank, next, nodes, leaves, maxdepth);
+}
+static int cmd_bvhorder(int argc, char** argv) {
+  if (argc < 6) return 1;
+  Ctx c = load(argv[2], atoi(argv[3]), atoi(argv[4]));
+  std::map<const Primitive*, size_t> idx;
+  for (size_t i = 0; i < c.prims.size(); ++i) idx[c.prims[i]] = i;
+  std::vector<double> rank(c.prims.size(), -1.0);
+  size_t next = 0, nodes = 0, leaves = 0; int depth = 0;
+  walk_bvh(c.pt->bvh->get_root(), 0, idx, rank, next, nodes, leaves, depth);
+  std::vector<double> out = {(double)nodes, (double)leaves, (double)depth};
+  out.insert(out.end(), rank.begin(), rank.end());
+  write_doubles(argv[5], out);
+  fprintf(stderr, "[ref_probe] bvhorder: %zu nodes, %zu leaves, depth %d, %zu primitives ranked\n", nodes, leaves, depth, next);
+  return next == c.prims.size() ? 0 : 2;
+}
+
 // render: the reference's own PathTracer::raytrace_pixel (src/part1_code.cpp:125-163) for every pixel
 // (or rows [y0,y1) with RRT_PROBE_ROWS=y0:y1), its rand() fed by the per-path Philox stream.
 // out = W*H x [r g b count] doubles (row 0 = bottom, sampleBuffer layout) followed by
@@ -443,14 +475,21 @@ static int cmd_render(int argc, char** argv) {
   c.pt->gridSampler = new StreamSwitchSampler();
   int y0 = 0, y1 = H;
   if (const char* rows = getenv("RRT_PROBE_ROWS")) sscanf(rows, "%d:%d", &y0, &y1);
+  const bool glibc_rand = getenv("RRT_PROBE_GLIBC_RAND") != nullptr;
+  int x0 = 0, x1 = W;   /* with RRT_PROBE_COLS=x0:x1 a cell of the frame (pixels outside stay zero) */
+  if (const char* cols = getenv("RRT_PROBE_COLS")) sscanf(cols, "%d:%d", &x0, &x1);
   std::vector<double> out((size_t)W * H * 4 + 4, 0.0);
   uint64_t draws = 0;
   double t0 = omp_get_wtime();
 #pragma omp parallel for schedule(dynamic, 1) reduction(+ : draws)
   for (int y = y0; y < y1; ++y) {
-    for (int x = 0; x < W; ++x) {
+    for (int x = x0; x < x1; ++x) {
       RandState& s = g_rs;
       s.mode = 1; s.seed = seed; s.pixel = (uint32_t)(x + y * W); s.n = 0; s.draws = 0;
+      if (glibc_rand) {   /* RRT_PROBE_GLIBC_RAND=1: an RNG that shares nothing with the product's Philox streams (statistical parity check) */
+        if (!s.rinit) { memset(&s.rdata, 0, sizeof s.rdata); initstate_r((unsigned)(seed * 2654435761u + 977u * (unsigned)omp_get_thread_num() + 1u), s.rstate, sizeof s.rstate, &s.rdata); s.rinit = true; }
+        s.mode = 2;
+      }
       // ns_aa == 1: no jitter draw, the stream of sample 0 starts at the first light sample.
       s.sample = cfg.pathtracer_ns_aa == 1 ? 0u : (uint32_t)-1;
       s.grid_calls = 0; s.grid_calls_per_sample = cfg.pathtracer_ns_aa == 1 ? 0 : (lens ? 2 : 1);
@@ -490,10 +529,12 @@ int main(int argc, char** argv) {
     else if (cmd == "envdir") rc = cmd_envdir(argc, argv);
     else if (cmd == "render") rc = cmd_render(argc, argv);
     else if (cmd == "order") rc = cmd_order(argc, argv);
+    else if (cmd == "bvhorder") rc = cmd_bvhorder(argc, argv);
   }
   if (rc == 1)
     fprintf(stderr,
             "usage: ref_probe scene <dae> W H out.rrtscene\n"
+            "       ref_probe bvhorder <dae> W H out.bin\n"
             "       ref_probe trace <dae> W H rays.bin out.bin [-B cx cy cz r dtheta]\n"
             "       ref_probe geodesic rays.bin nsteps out.bin [-B ...]\n"
             "       ref_probe camrays <dae> W H xy.bin out.bin\n"

@@ -785,7 +785,11 @@ int orc_render(orc_ctx* c, const rrt_params* p, float* hdr_rgb, int32_t* counts,
   if (c->cell_w > 0) { x0 = c->cell_x; y0 = c->cell_y; x1 = x0 + c->cell_w; y1 = y0 + c->cell_h; if (x1 > c->W) x1 = c->W; if (y1 > c->H) y1 = c->H; }
   if (hdr_rgb) memset(hdr_rgb, 0, sizeof(float) * 3 * (size_t)c->W * c->H);
   if (counts) memset(counts, 0, sizeof(int32_t) * (size_t)c->W * c->H);
-  int ntx = (c->W + g_shard_tile - 1) / g_shard_tile;
+  /* owner of tile (tx, ty) = (tx + ty * stride) % world, stride = the smallest integer >= round(sqrt(world)) coprime with world
+   * (the product's rule, include/rrt_b200.h rrt_set_tile_shard) */
+  int ntx = 1;
+  while ((ntx + 1) * (ntx + 1) <= g_shard_world + ntx) ++ntx;
+  for (;; ++ntx) { int a = ntx, b = g_shard_world; while (b) { int t = a % b; a = b; b = t; } if (a == 1) break; }
   cnt_t tot = {0, 0, 0, 0, 0}; uint64_t paths = 0;
   double t0 = 0, t1 = 0;
 #ifdef _OPENMP

@@ -139,6 +139,7 @@ int rrt_create(rrt_ctx** out, int device) {
   ctx->opt[RRT_OPT_BVH_WIDTH] = 0;
   ctx->opt[RRT_OPT_SHADE_SPLIT] = 2;
   ctx->opt[RRT_OPT_STREAMS] = 2;
+  ctx->opt[RRT_OPT_ESCAPE] = 0;
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaMallocHost((void**)&ctx->h_pinned, 4096)) != cudaSuccess) {
@@ -174,9 +175,9 @@ void rrt_destroy(rrt_ctx* ctx) {
 int rrt_set_option(rrt_ctx* ctx, int option, int64_t value) {
   if (!ctx) return RRT_E_ARG;
   RRT_MULTI_ALL(ctx, rrt_set_option(sub, option, value));
-  if (option < 0 || option > RRT_OPT_STREAMS) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
+  if (option < 0 || option > RRT_OPT_ESCAPE) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
 #if !RRT_AB
-  if ((option == RRT_OPT_TRACE_KERNEL && value != 0) || (option == RRT_OPT_BVH_WIDTH && value == 4))
+  if ((option == RRT_OPT_TRACE_KERNEL && value != 0) || (option == RRT_OPT_BVH_WIDTH && value == 4) || (option == RRT_OPT_ESCAPE && value != 0))
     FAIL(RRT_E_ARG, "rrt_set_option: this variant is compiled only into A/B builds (make EXTRA=-DRRT_AB=1)");
 #endif
   ctx->opt[option] = value;
@@ -428,6 +429,11 @@ int rrt_set_blackhole(rrt_ctx* ctx, const double c[3], double r, double dtheta, 
   if (!ctx || !c) return RRT_E_ARG;
   RRT_MULTI_ALL(ctx, rrt_set_blackhole(sub, c, r, dtheta, mode));
   if (mode != RRT_MODE_FLAT && mode != RRT_MODE_LITERAL) FAIL(RRT_E_ARG, "rrt_set_blackhole: unknown mode");
+  /* a NaN or non-positive step makes `j * dtheta < 2 pi` true for ever (reference src/bvh.cpp:105: the reference would hang); a tiny one
+   * makes every ray walk millions of chords.  2 pi / 65536 is 650 times finer than the reference's default of 0.1 */
+  if (!(dtheta >= 9.5873799e-5) || !std::isfinite(dtheta)) FAIL(RRT_E_ARG, "rrt_set_blackhole: delta_theta must be a finite number >= 2 pi / 65536");
+  if (!(r >= 0.0) || !std::isfinite(r) || !std::isfinite(c[0]) || !std::isfinite(c[1]) || !std::isfinite(c[2]))
+    FAIL(RRT_E_ARG, "rrt_set_blackhole: centre and radius must be finite, radius >= 0");
   ctx->bh.cx = c[0]; ctx->bh.cy = c[1]; ctx->bh.cz = c[2]; ctx->bh.r = r; ctx->bh.r2 = r * r; ctx->bh.h = dtheta;
   ctx->bh.cos_h = cos(dtheta); ctx->bh.sin_h = sin(dtheta);  /* host libm, as the reference evaluates them (src/static_scene/blackhole.cpp:34-35) */
   ctx->bh.mode = mode; ctx->bh.nchords = chords_for(dtheta);
@@ -447,6 +453,7 @@ int rrt_set_frame(rrt_ctx* ctx, int w, int h) {
 int rrt_set_cell(rrt_ctx* ctx, int x, int y, int w, int h) {
   if (!ctx) return RRT_E_ARG;
   RRT_MULTI_ALL(ctx, rrt_set_cell(sub, x, y, w, h));
+  if (w > 0 && h <= 0) FAIL(RRT_E_ARG, "rrt_set_cell: a cell needs a positive height (w <= 0 restores the full frame)");
   ctx->cell_x = x; ctx->cell_y = y; ctx->cell_w = w; ctx->cell_h = h;
   return RRT_OK;
 }
@@ -562,89 +569,156 @@ static int trace_step_mode(const rrt_ctx* ctx) {
   if (fast_stepper(ctx)) return 1;
   return (RRT_AB && ctx->opt[RRT_OPT_TRACE_KERNEL] == 2) ? 3 : 0;
 }
-typedef void (*closest_fn)(const DevScene, const DevHole, const double*, size_t, const int*, int*, int*, double*, Counters*);
-typedef void (*shadow_fn)(const DevScene, const DevHole, const double*, size_t, const int*, int*, const uint32_t*, int*, Counters*);
-typedef void (*hook_fn)(const DevScene, const DevHole, int, const double*, const double*, const double*, const double*, rrt_hit*, int*, Counters*);
+typedef void (*closest_fn)(const DevScene, const DevHole, const double*, size_t, const int*, int*, int*, double*, Counters*, const ParkQ);
+typedef void (*shadow_fn)(const DevScene, const DevHole, const double*, size_t, const int*, int*, const uint32_t*, int*, Counters*, const ParkQ);
+typedef void (*hook_fn)(const DevScene, const DevHole, int, const double*, const double*, const double*, const double*, rrt_hit*, int*, Counters*, const ParkQ);
 
-template <bool COUNT, int V> static closest_fn closest_of_step(int step) {
+/* park: 0 = rays run to their end in the trace kernel, 1 = escaping rays are parked for k_escape, 2 = the re-entry pass (rrt_wavetrace.cuh ParkQ);
+ * 1 and 2 exist for STEP 0 (hole on, FP64 stepper, lockstep loop) over binary and 8-wide nodes */
+template <bool COUNT, int V> static closest_fn closest_of_step(int step, int park) {
   switch (step) {
     case 1: if constexpr (V != 4) return k_trace_closest<COUNT, V, 1>; else return k_trace_closest<COUNT, V, 0>;
     case 2: return k_trace_closest<COUNT, V, 2>;
 #if RRT_AB
     case 3: return k_trace_closest<COUNT, V, 3>;
 #endif
-    default: return k_trace_closest<COUNT, V, 0>;
+    default:
+#if RRT_AB
+      if constexpr (V != 4) { if (park == 1) return k_trace_closest<COUNT, V, 0, 1>; if (park == 2) return k_trace_closest<COUNT, V, 0, 2>; }
+#endif
+      return k_trace_closest<COUNT, V, 0>;
   }
 }
-template <bool COUNT> static closest_fn closest_kernel(int v, int step) {
+template <bool COUNT> static closest_fn closest_kernel(int v, int step, int park) {
   switch (v) {
 #if RRT_AB
     case 1: return k_trace_closest<COUNT, 1, 0>;
-    case 4: return closest_of_step<COUNT, 4>(step);
+    case 4: return closest_of_step<COUNT, 4>(step, 0);
 #endif
-    case 8: return closest_of_step<COUNT, 8>(step);
-    default: return closest_of_step<COUNT, 0>(step);
+    case 8: return closest_of_step<COUNT, 8>(step, park);
+    default: return closest_of_step<COUNT, 0>(step, park);
   }
 }
-template <bool ANY, bool COUNT, int V> static shadow_fn shadow_of_step(int step) {
+template <bool ANY, bool COUNT, int V> static shadow_fn shadow_of_step(int step, int park) {
   switch (step) {
     case 1: if constexpr (V != 4) return k_trace_shadow<ANY, COUNT, V, 1>; else return k_trace_shadow<ANY, COUNT, V, 0>;
     case 2: return k_trace_shadow<ANY, COUNT, V, 2>;
 #if RRT_AB
     case 3: return k_trace_shadow<ANY, COUNT, V, 3>;
 #endif
-    default: return k_trace_shadow<ANY, COUNT, V, 0>;
+    default:
+#if RRT_AB
+      if constexpr (V != 4) { if (park == 1) return k_trace_shadow<ANY, COUNT, V, 0, 1>; if (park == 2) return k_trace_shadow<ANY, COUNT, V, 0, 2>; }
+#endif
+      return k_trace_shadow<ANY, COUNT, V, 0>;
   }
 }
-template <bool ANY, bool COUNT> static shadow_fn shadow_kernel(int v, int step) {
+template <bool ANY, bool COUNT> static shadow_fn shadow_kernel(int v, int step, int park) {
   switch (v) {
 #if RRT_AB
     case 1: return k_trace_shadow<ANY, COUNT, 1, 0>;
-    case 4: return shadow_of_step<ANY, COUNT, 4>(step);
+    case 4: return shadow_of_step<ANY, COUNT, 4>(step, 0);
 #endif
-    case 8: return shadow_of_step<ANY, COUNT, 8>(step);
-    default: return shadow_of_step<ANY, COUNT, 0>(step);
+    case 8: return shadow_of_step<ANY, COUNT, 8>(step, park);
+    default: return shadow_of_step<ANY, COUNT, 0>(step, park);
   }
 }
-template <bool ANY, int V> static hook_fn hook_of_step(int step) {
+template <bool ANY, int V> static hook_fn hook_of_step(int step, int park) {
   switch (step) {
     case 1: if constexpr (V != 4) return k_hook_trace<ANY, V, 1>; else return k_hook_trace<ANY, V, 0>;
     case 2: return k_hook_trace<ANY, V, 2>;
 #if RRT_AB
     case 3: return k_hook_trace<ANY, V, 3>;
 #endif
-    default: return k_hook_trace<ANY, V, 0>;
+    default:
+#if RRT_AB
+      if constexpr (V != 4) { if (park == 1) return k_hook_trace<ANY, V, 0, 1>; if (park == 2) return k_hook_trace<ANY, V, 0, 2>; }
+#endif
+      return k_hook_trace<ANY, V, 0>;
   }
 }
-template <bool ANY> static hook_fn hook_kernel(int v, int step) {
+template <bool ANY> static hook_fn hook_kernel(int v, int step, int park) {
   switch (v) {
 #if RRT_AB
     case 1: return k_hook_trace<ANY, 1, 0>;
-    case 4: return hook_of_step<ANY, 4>(step);
+    case 4: return hook_of_step<ANY, 4>(step, 0);
 #endif
-    case 8: return hook_of_step<ANY, 8>(step);
-    default: return hook_of_step<ANY, 0>(step);
+    case 8: return hook_of_step<ANY, 8>(step, park);
+    default: return hook_of_step<ANY, 0>(step, park);
   }
+}
+/* the escape hand-off applies to the default trace loop with the hole on and the FP64 stepper (RRT_OPT_ESCAPE, default 1) */
+static bool escape_on(const rrt_ctx* ctx) {
+#if RRT_AB
+  const int v = trace_variant(ctx);
+  return ctx->opt[RRT_OPT_ESCAPE] != 0 && trace_step_mode(ctx) == 0 && (v == 0 || v == 8);
+#else
+  (void)ctx; return false;   /* measured slower (rrt_wavetrace.cuh, ParkQ): compiled into A/B builds only */
+#endif
+}
+/* park + re-entry queues in one allocation: 2 x (7 doubles + 2 ints) per ray + 4 counters; returns the bytes used */
+static size_t park_bytes(size_t cap) { return 256 + 2 * (align_up(56 * cap) + align_up(8 * cap)); }
+static void park_carve(char* base, size_t cap, ParkQ* park, ParkQ* reentry) {
+  int* cnt = (int*)base; char* p = base + 256;
+  park->cnt = cnt; reentry->cnt = cnt + 2; park->cap = reentry->cap = cap;
+  park->st = (double*)p; p += align_up(56 * cap); park->meta = (int*)p; p += align_up(8 * cap);
+  reentry->st = (double*)p; p += align_up(56 * cap); reentry->meta = (int*)p;
 }
 
 static void launch_closest(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, const double* ray, size_t cap, const int* cnt_ptr, int* cursor, int* h_prim,
-                           double* h_geo, Counters* gc) {
+                           double* h_geo, Counters* gc, const ParkQ* park = nullptr, const ParkQ* reentry = nullptr) {
   const int v = trace_variant(ctx), step = trace_step_mode(ctx);
-  closest_fn fn = count ? closest_kernel<true>(v, step) : closest_kernel<false>(v, step);
-  fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc);
+  const bool esc = park && escape_on(ctx);
+  closest_fn fn = count ? closest_kernel<true>(v, step, esc ? 1 : 0) : closest_kernel<false>(v, step, esc ? 1 : 0);
+  if (!esc) { fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc, ParkQ()); return; }
+#if RRT_AB
+  cudaMemsetAsync(park->cnt, 0, 16, st);
+  fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc, *park);
+  const int ge = ctx->sm_count * RRT_MINB_ESCAPE;
+  if (count) k_escape_closest<true><<<ge, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, cap, h_prim, h_geo, gc, *park, *reentry);
+  else k_escape_closest<false><<<ge, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, cap, h_prim, h_geo, gc, *park, *reentry);
+  closest_fn fr = count ? closest_kernel<true>(v, step, 2) : closest_kernel<false>(v, step, 2);
+  fr<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, h_prim, h_geo, gc, *reentry);
+#else
+  (void)reentry;
+#endif
 }
 template <bool ANY>
 static void launch_shadow(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, const double* ray, size_t cap, const int* cnt_ptr, int* cursor,
-                          const uint32_t* cidx, int* res, Counters* gc) {
+                          const uint32_t* cidx, int* res, Counters* gc, const ParkQ* park = nullptr, const ParkQ* reentry = nullptr) {
   const int v = trace_variant(ctx), step = trace_step_mode(ctx);
-  shadow_fn fn = count ? shadow_kernel<ANY, true>(v, step) : shadow_kernel<ANY, false>(v, step);
-  fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc);
+  const bool esc = park && escape_on(ctx);
+  shadow_fn fn = count ? shadow_kernel<ANY, true>(v, step, esc ? 1 : 0) : shadow_kernel<ANY, false>(v, step, esc ? 1 : 0);
+  if (!esc) { fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc, ParkQ()); return; }
+#if RRT_AB
+  cudaMemsetAsync(park->cnt, 0, 16, st);
+  fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc, *park);
+  const int ge = ctx->sm_count * RRT_MINB_ESCAPE;
+  if (count) k_escape_shadow<true><<<ge, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, cap, cidx, res, gc, *park, *reentry);
+  else k_escape_shadow<false><<<ge, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, cap, cidx, res, gc, *park, *reentry);
+  shadow_fn fr = count ? shadow_kernel<ANY, true>(v, step, 2) : shadow_kernel<ANY, false>(v, step, 2);
+  fr<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc, *reentry);
+#else
+  (void)reentry;
+#endif
 }
 static void launch_hook(rrt_ctx* ctx, bool any_hit, int grid, cudaStream_t st, int n, const double* d_o, const double* d_d, const double* d_mn, const double* d_mx,
-                        rrt_hit* d_out, int* d_cursor, Counters* gc) {
+                        rrt_hit* d_out, int* d_cursor, Counters* gc, const ParkQ* park = nullptr, const ParkQ* reentry = nullptr) {
   const int v = trace_variant(ctx), step = trace_step_mode(ctx);
-  hook_fn fn = any_hit ? hook_kernel<true>(v, step) : hook_kernel<false>(v, step);
-  fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc);
+  const bool esc = park && escape_on(ctx);
+  hook_fn fn = any_hit ? hook_kernel<true>(v, step, esc ? 1 : 0) : hook_kernel<false>(v, step, esc ? 1 : 0);
+  if (!esc) { fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc, ParkQ()); return; }
+#if RRT_AB
+  cudaMemsetAsync(park->cnt, 0, 16, st);
+  fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc, *park);
+  const int ge = ctx->sm_count * RRT_MINB_ESCAPE;
+  if (any_hit) k_escape_hook<true><<<ge, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, d_out, gc, *park, *reentry);
+  else k_escape_hook<false><<<ge, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, d_out, gc, *park, *reentry);
+  hook_fn fr = any_hit ? hook_kernel<true>(v, step, 2) : hook_kernel<false>(v, step, 2);
+  fr<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc, *reentry);
+#else
+  (void)reentry;
+#endif
 }
 
 static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_counts, float4* d_rgbn, cudaStream_t user_stream, rrt_stats* stats) {
@@ -678,7 +752,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   const int iters = std::max(rk.D, 1);
 
   /* ---- work buffers: capacity from the in-flight budget */
-  const size_t per_path = 2 * (8 * 8 + 4 + 4 + 4 + 12) + 4 + 72 + 12 + 1 + 12 + (size_t)S * (56 + 4 + 4 + 16);
+  const size_t per_path = 2 * (8 * 8 + 4 + 4 + 4 + 12) + 4 + 72 + 12 + 1 + 12 + (size_t)S * (56 + 4 + 4 + 16) + (escape_on(ctx) ? (size_t)S * 128 : 0);
   size_t want = p->max_paths_in_flight > 0 ? (size_t)p->max_paths_in_flight : (size_t)4 << 20;
   size_t budget = (size_t)(ctx->opt[RRT_OPT_WORK_BYTES] > 0 ? ctx->opt[RRT_OPT_WORK_BYTES] : (int64_t)12 << 30);
   want = std::min(want, std::max<size_t>(budget / per_path / (size_t)std::min<int64_t>(std::max<int64_t>(ctx->opt[RRT_OPT_STREAMS], 1), 4), 1024));
@@ -700,6 +774,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   }
   if (!ctx->ev_fork) CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
   Queues qs[4]; memset(qs, 0, sizeof qs);
+  ParkQ parks[4], reents[4];
   size_t off = 0;
   auto carve = [&](size_t bytes) { size_t o = off; off += align_up(bytes); return o; };
   size_t o_ray[2], o_slot[2], o_rngn[2], o_flags[2], o_beta[2];
@@ -708,6 +783,9 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
          o_scidx = carve(4 * capS), o_sres = carve(4 * capS), o_scon = carve(16 * capS), o_L = carve(12 * cap);
   const int ctl_stride = iters + 2;
   size_t o_ctl = carve(4 * 4 * (size_t)ctl_stride);
+  const bool esc = escape_on(ctx);
+  const size_t cap_park = std::max(cap, capS);
+  size_t o_park = esc ? carve(park_bytes(cap_park)) : 0;
   const size_t per_stream = off;
   CK(ctx->d_work.ensure(per_stream * NS));
   for (int k = 0; k < NS; ++k) {
@@ -721,6 +799,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
     q.h_prim = (int*)(wb + o_hprim); q.h_geo = (double*)(wb + o_hgeo); q.dbeta = (float*)(wb + o_dbeta); q.vflag = (uint8_t*)(wb + o_vflag);
     q.sray = (double*)(wb + o_sray); q.s_cidx = (uint32_t*)(wb + o_scidx); q.s_res = (int*)(wb + o_sres); q.s_contrib = (float4*)(wb + o_scon);
     q.Lsample = (float*)(wb + o_L); q.ctl = (int*)(wb + o_ctl);
+    if (esc) park_carve(wb + o_park, cap_park, &parks[k], &reents[k]);
   }
   const size_t ctl_bytes = 4 * 4 * (size_t)ctl_stride;
 
@@ -784,22 +863,24 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
         const int cur = it & 1;
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, cs)); }
-        launch_closest(ctx, count, grid_trace, cs, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt);
+        launch_closest(ctx, count, grid_trace, cs, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt, esc ? &parks[si] : nullptr,
+                       esc ? &reents[si] : nullptr);
         if (stats) { CK(cudaEventRecord(e1, cs)); trace_ev.push_back({e0, e1}); }
         k_shade<<<grid_small, RRT_BLOCK, 0, cs>>>(ctx->ds, ctx->bh, rk, q, chunk, base_sample, nb, it);
         if (rk.split && rk.D >= 1 && rk.S > 0) {
           k_shade_direct<<<ctx->sm_count * 2 * RRT_DIRECT_MINB, 256, 0, cs>>>(ctx->ds, rk, q, chunk, base_sample, nb, it);
           launches++;
         }
-        launches += 2; trace_launches++;
+        launches += 2 + (esc ? 2 : 0); trace_launches++;
         if (rk.D >= 1 && rk.S > 0) {
           if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, cs)); }
           int* scount = q.ctl + q.ctl_stride + it; int* scursor = q.ctl + 3 * q.ctl_stride + it;
-          if (rk.hemi) launch_shadow<false>(ctx, count, grid_trace, cs, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
-          else launch_shadow<true>(ctx, count, grid_trace, cs, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt);
+          const ParkQ* pkq = esc ? &parks[si] : nullptr; const ParkQ* req = esc ? &reents[si] : nullptr;
+          if (rk.hemi) launch_shadow<false>(ctx, count, grid_trace, cs, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt, pkq, req);
+          else launch_shadow<true>(ctx, count, grid_trace, cs, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt, pkq, req);
           if (stats) { CK(cudaEventRecord(e1, cs)); trace_ev.push_back({e0, e1}); }
           k_accumulate<<<grid_small, 256, 0, cs>>>(ctx->ds, rk, q, it);
-          launches += 2; trace_launches++;
+          launches += 2 + (esc ? 2 : 0); trace_launches++;
         }
         if (iters > 8 && it + 1 < iters && (it & 3) == 3) {  /* long depth budgets (-m 100): stop once every path has died */
           CK(cudaMemcpyAsync(ctx->h_pinned, q.ctl + it + 1, 4, cudaMemcpyDeviceToHost, cs));
@@ -926,7 +1007,8 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
   if (stats) memset(stats, 0, sizeof *stats);
   if (n == 0) return RRT_OK;
   if (n >= ((int64_t)1 << 30)) FAIL(RRT_E_ARG, "rrt_trace_rays: at most 2^30 rays per call");
-  int rc = hook_begin(ctx, 64 * (size_t)n + 4096, sizeof(rrt_hit) * (size_t)n + 1024);
+  const bool esc = escape_on(ctx);
+  int rc = hook_begin(ctx, 64 * (size_t)n + 4096, sizeof(rrt_hit) * (size_t)n + 1024 + (esc ? park_bytes((size_t)n) + 512 : 0));
   if (rc) return rc;
   size_t io = 0, oo = 0;
   double* d_o = (double*)hook_in(ctx, io, o, 24 * (size_t)n); double* d_d = (double*)hook_in(ctx, io, d, 24 * (size_t)n);
@@ -934,12 +1016,14 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
   rrt_hit* d_out = (rrt_hit*)hook_out(ctx, oo, sizeof(rrt_hit) * (size_t)n);
   Counters* gc = (Counters*)hook_out(ctx, oo, sizeof(Counters));
   int* d_cursor = (int*)hook_out(ctx, oo, 256);
+  ParkQ park, reentry;
+  if (esc) park_carve((char*)hook_out(ctx, oo, park_bytes((size_t)n)), (size_t)n, &park, &reentry);
   CK(cudaMemsetAsync(gc, 0, sizeof(Counters), ctx->stream));
   CK(cudaMemsetAsync(d_cursor, 0, 4, ctx->stream));
   cudaEvent_t e0, e1; ctx->events_used = 0; e0 = next_event(ctx); e1 = next_event(ctx);
   CK(cudaEventRecord(e0, ctx->stream));
   int grid = (int)std::min<int64_t>((n + RRT_BLOCK - 1) / RRT_BLOCK, (int64_t)ctx->sm_count * 4);
-  launch_hook(ctx, any_hit != 0, grid, ctx->stream, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc);
+  launch_hook(ctx, any_hit != 0, grid, ctx->stream, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc, esc ? &park : nullptr, esc ? &reentry : nullptr);
   CK(cudaEventRecord(e1, ctx->stream));
   CK(cudaMemcpyAsync(out, d_out, sizeof(rrt_hit) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
@@ -949,7 +1033,7 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
     float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
     stats->seconds = stats->trace_seconds = ms * 1e-3;
     stats->rays = hc.rays; stats->geodesic_steps = hc.steps; stats->node_visits = hc.nodes; stats->tri_tests = hc.tris; stats->sphere_tests = hc.sph;
-    stats->kernel_launches = stats->trace_launches = 1;
+    stats->kernel_launches = esc ? 3 : 1; stats->trace_launches = 1;
     stats->algorithmic_bytes = node_record_bytes(ctx) * hc.nodes + 80 * hc.tris + 32 * hc.sph + 160 * hc.rays;
   }
   return RRT_OK;

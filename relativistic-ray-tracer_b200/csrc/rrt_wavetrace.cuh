@@ -114,9 +114,49 @@ __device__ __forceinline__ void wt_flush_counters(const Counters& c, Counters* g
   }
 }
 
+/* FP32, conservative: true when every point within `len` of p is outside the (outward-rounded) root box.  |p - fl(p)| <=
+ * sqrt(3) 2^-24 max|p_i| < 1.04e-7 m enters the reach L; the float evaluation of the box distance is good to a few 2^-24
+ * relative, covered by the 1e-5 margins.  NaN / inf anywhere compares false: the chord takes the traversal path. */
+__device__ __forceinline__ bool chord_outside_root(const DevScene& sc, const d3& p, double len) {
+  const float px = (float)p.x, py = (float)p.y, pz = (float)p.z;
+  const float m = fmaxf(fmaxf(fabsf(px), fabsf(py)), fabsf(pz));
+  const float ex = fmaxf(fmaxf(sc.root_lo[0] - px, px - sc.root_hi[0]), 0.f);
+  const float ey = fmaxf(fmaxf(sc.root_lo[1] - py, py - sc.root_hi[1]), 0.f);
+  const float ez = fmaxf(fmaxf(sc.root_lo[2] - pz, pz - sc.root_hi[2]), 0.f);
+  const float d2 = ex * ex + ey * ey + ez * ez;
+  const float L = __double2float_ru(len) * 1.00001f + m * 2.4e-7f;
+  return d2 * 0.99999f > L * L;
+}
+
+
+/* ---------------------------------------------------------------- escape hand-off (round 2; VERDICT r01 item 3: "two-phase trace for rays outside the scene box")
+ * A ray that has left the scene box keeps being integrated for all of its 63 chords (the reference never stops), and none of
+ * those chords can hit anything while the box is out of their reach.  Carrying such a ray in the trace kernel wastes a lane of a warp whose
+ * other lanes traverse the BVH, in an 80-register kernel that cannot reach the stepper's own throughput (28 vs 47 G chords/s).
+ * So the trace kernel PARKS a ray at the first chord that starts outside the root box and is shorter than its distance to it
+ * (chord_outside_root): (o, d, len, j, queue index) go to a park queue and the lane takes a fresh ray.  k_escape — stepper, horizon test and the
+ * conservative root-box test only, no BVH, no stack, 8+ blocks per SM — then carries the parked rays on: captured -> result; out of chords ->
+ * miss; a chord that passes the SAME root-box slab test traverse() starts with -> re-entry queue, finished by a second, small launch of the trace
+ * kernel that starts with that chord's traversal (no parking there).  Every chord, horizon test and primitive test is the same arithmetic in the
+ * same order; only chords that provably reach no primitive skip their (empty) traversal: results are bit-identical.
+ * MEASURED SLOWER on B200 (profiles/r02_d_ab_escape.jsonl, ms per frame, off -> on): bunny 1080p 16 spp 83.9 -> 86.0, C5 51.0 -> 51.4, C2 32.2 -> 34.6,
+ * bunny 480x360 64 spp 200.9 -> 212.1, C4 3311 -> 3422.  Escaped rays already run at 34 G chords/s in the trace kernel (2 streams, 32-entry pools) against
+ * 48.5 G for stepper + horizon test ALONE from registers (tools/ilp_probe.cu): the lean kernel still pays the clear test, the queue round trip (128 B per
+ * ray) and two more launch tails per trace phase, and the trace kernel pays the clear test on every chord.  The FP64 stepper, not the traversal state that
+ * travels with it, bounds these rays.  Kept behind RRT_AB (RRT_OPT_ESCAPE = 1 in A/B builds). */
+struct ParkQ {
+  double* st;    /* 7 x cap: o.xyz d.xyz len of the last chord made */
+  int* meta;     /* 2 x cap: caller's queue index, chords done so far (j) */
+  int* cnt;      /* [0] entries written, [1] consumer cursor */
+  size_t cap;
+};
+
 /* ---------------------------------------------------------------- variant 0 (default): chord-lockstep loop */
-template <bool ANY, bool COUNT, int W, int STEP, class IO>
-__device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHole& bh, const IO& io, const int n, int* cursor, Counters* gcnt) {
+/* PARK: 0 = every ray runs to its end here; 1 = escaping rays are parked in `pk` (hole on, FP64 stepper); 2 = the queue IS `pk` (re-entries from
+ * k_escape: state + a chord whose traversal is pending), no parking */
+template <bool ANY, bool COUNT, int W, int STEP, class IO, int PARK = 0>
+__device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHole& bh, const IO& io, const int n, int* cursor, Counters* gcnt,
+                                                 const ParkQ pk = ParkQ()) {
   __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
   __shared__ CoopScratch coop_mem[ANY ? RRT_BLOCK / 32 : 1];
   int* stack = stack_mem + threadIdx.x;
@@ -129,7 +169,7 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
   const unsigned lt_mask = (1u << wt_lane()) - 1u;
   int pool_next = 0, pool_end = 0;   /* warp-uniform */
   bool more = true;                  /* warp-uniform: the global queue may still have entries */
-  bool has = false;
+  bool has = false, skip = false;    /* skip (PARK 2): the loaded chord is already made and horizon-tested, its traversal comes first */
   int idx = 0, j = 0;
   FastRay fr; fr.xx = fr.xy = fr.xz = fr.yx = fr.yy = fr.yz = fr.u = fr.up = 0.f;
   float e0x = 0.f, e0y = 0.f, e0z = 0.f;   /* STEP 1: (double origin) - (float origin of the first chord) */
@@ -150,16 +190,23 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
       const int avail = pool_end - pool_next;
       const int rank = __popc(need & lt_mask);
       if (!has && rank < avail) {
+        if constexpr (PARK == 2) {
+          const size_t q = (size_t)(pool_next + rank);
+          o = D3(pk.st[q], pk.st[pk.cap + q], pk.st[2 * pk.cap + q]); d = D3(pk.st[3 * pk.cap + q], pk.st[4 * pk.cap + q], pk.st[5 * pk.cap + q]);
+          len = pk.st[6 * pk.cap + q]; idx = pk.meta[q]; j = pk.meta[pk.cap + q];
+          has = true; skip = true; tmin = 0.0; tmax = len;
+        } else {
         idx = pool_next + rank;
         io.load(idx, o, d, tmin, tmax);
         has = true; j = 0; len = 0.0;
+        }
         if (STEP == 1) {
           fast_init(bh, o, d, fr);
           const float rho = fast_rcp(fr.u);   /* the float origin fast_step is about to form, to the bit */
           e0x = (float)(o.x - (double)__fmaf_rn(rho, fr.xx, bh.f_cx)); e0y = (float)(o.y - (double)__fmaf_rn(rho, fr.xy, bh.f_cy));
           e0z = (float)(o.z - (double)__fmaf_rn(rho, fr.xz, bh.f_cz));
         }
-        if (COUNT) cnt.rays++;
+        if (COUNT && PARK != 2) cnt.rays++;
       }
       pool_next += min(__popc(need), avail);
       need = __ballot_sync(0xffffffffu, !has);
@@ -191,13 +238,34 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
       }
     } else {
       Seg s; s.o = o; s.d = d; s.tmin = tmin; s.tmax = tmax;
-      if (has) {
+      bool parked = false;
+      if (has && !(PARK == 2 && skip)) {
         if (!flat) {
           next_micro_ray(bh, o, d, len);
           s.o = o; s.d = d; s.tmin = 0.0; s.tmax = len;
           if (horizon_hit(bh, o, d, len)) { h.status = 2; h.prim = -1; h.chord = j; h.steps = j + 1; h.t = 0.0; }
+          else if (PARK == 1 && chord_outside_root(sc, o, len)) {   /* this chord reaches nothing: on to the next one, in k_escape */
+            ++j;
+            if (j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = j - 1; h.steps = j; h.t = 0.0; }
+            else parked = true;
+          }
         }
         if (COUNT) cnt.steps++;
+      }
+      skip = false;
+      if constexpr (PARK == 1) {
+        const unsigned pm = __ballot_sync(0xffffffffu, parked);
+        if (pm) {
+          int base = 0;
+          if (wt_lane() == __ffs(pm) - 1) base = atomicAdd(pk.cnt, __popc(pm));
+          base = __shfl_sync(0xffffffffu, base, __ffs(pm) - 1);
+          if (parked) {
+            const size_t q = (size_t)(base + __popc(pm & lt_mask));
+            pk.st[q] = o.x; pk.st[pk.cap + q] = o.y; pk.st[2 * pk.cap + q] = o.z; pk.st[3 * pk.cap + q] = d.x; pk.st[4 * pk.cap + q] = d.y; pk.st[5 * pk.cap + q] = d.z;
+            pk.st[6 * pk.cap + q] = len; pk.meta[q] = idx; pk.meta[pk.cap + q] = j;
+            has = false;
+          }
+        }
       }
       const bool want = has && h.status < 0 && !chord_is_clear(sc, s.o, s.tmax);
       const bool live = has && h.status < 0;
@@ -216,6 +284,78 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
     }
     if (has && h.status >= 0) { io.store(idx, h); has = false; }
     __syncwarp();
+  }
+  if (COUNT) wt_flush_counters(cnt, gcnt);
+}
+
+/* the lean loop that carries parked rays: see ParkQ above */
+template <bool COUNT, class IO>
+__device__ __forceinline__ void escape_persistent(const DevScene& sc, const DevHole& bh, const IO& io, const ParkQ in, const ParkQ out, Counters* gcnt) {
+  Counters cnt = {0, 0, 0, 0, 0, 0};
+  const int n = in.cnt[0];
+  int* cursor = in.cnt + 1;
+  const unsigned lt_mask = (1u << wt_lane()) - 1u;
+  int pool_next = 0, pool_end = 0;
+  bool more = true, has = false;
+  int idx = 0, j = 0;
+  d3 o = D3(0, 0, 0), d = D3(0, 0, 0);
+  double len = 0.0;
+  while (true) {
+    unsigned need = __ballot_sync(0xffffffffu, !has);
+    while (need) {
+      if (pool_next >= pool_end) {
+        if (!more) break;
+        int base = 0;
+        if (wt_lane() == 0) base = atomicAdd(cursor, RRT_POOL);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) { more = false; break; }
+        pool_next = base; pool_end = min(base + RRT_POOL, n);
+      }
+      const int avail = pool_end - pool_next;
+      const int rank = __popc(need & lt_mask);
+      if (!has && rank < avail) {
+        const size_t q = (size_t)(pool_next + rank);
+        o = D3(in.st[q], in.st[in.cap + q], in.st[2 * in.cap + q]); d = D3(in.st[3 * in.cap + q], in.st[4 * in.cap + q], in.st[5 * in.cap + q]);
+        len = in.st[6 * in.cap + q]; idx = in.meta[q]; j = in.meta[in.cap + q];
+        has = true;
+      }
+      pool_next += min(__popc(need), avail);
+      need = __ballot_sync(0xffffffffu, !has);
+    }
+    if (!__any_sync(0xffffffffu, has)) break;
+    Hit h; h.status = -1;
+    bool reenter = false;
+    if (has) {
+      next_micro_ray(bh, o, d, len);
+      if (COUNT) cnt.steps++;
+      if (horizon_hit(bh, o, d, len)) { h.status = 2; h.prim = -1; h.chord = j; h.steps = j + 1; h.t = 0.0; }
+      else {
+        bool clear = chord_outside_root(sc, o, len);
+        if (!clear) {   /* the test traverse() starts with: a chord that fails it visits no node */
+          Seg s; s.o = o; s.d = d; s.tmin = 0.0; s.tmax = len;
+          BoxCtx bc; float tmaxf, tn;
+          seg_boxctx(sc, s, bc, tmaxf);
+          clear = !box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tn);
+        }
+        if (clear) {
+          ++j;
+          if (j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = j - 1; h.steps = j; h.t = 0.0; }
+        } else reenter = true;
+      }
+    }
+    const unsigned rm = __ballot_sync(0xffffffffu, reenter);
+    if (rm) {
+      int base = 0;
+      if (wt_lane() == __ffs(rm) - 1) base = atomicAdd(out.cnt, __popc(rm));
+      base = __shfl_sync(0xffffffffu, base, __ffs(rm) - 1);
+      if (reenter) {
+        const size_t q = (size_t)(base + __popc(rm & lt_mask));
+        out.st[q] = o.x; out.st[out.cap + q] = o.y; out.st[2 * out.cap + q] = o.z; out.st[3 * out.cap + q] = d.x; out.st[4 * out.cap + q] = d.y; out.st[5 * out.cap + q] = d.z;
+        out.st[6 * out.cap + q] = len; out.meta[q] = idx; out.meta[out.cap + q] = j;
+        has = false;
+      }
+    }
+    if (has && h.status >= 0) { io.store(idx, h); has = false; }
   }
   if (COUNT) wt_flush_counters(cnt, gcnt);
 }
@@ -239,20 +379,6 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
 #ifndef RRT_S_THRESH
 #define RRT_S_THRESH 8
 #endif
-/* FP32, conservative: true when every point within `len` of p is outside the (outward-rounded) root box.  |p - fl(p)| <=
- * sqrt(3) 2^-24 max|p_i| < 1.04e-7 m enters the reach L; the float evaluation of the box distance is good to a few 2^-24
- * relative, covered by the 1e-5 margins.  NaN / inf anywhere compares false: the chord takes the traversal path. */
-__device__ __forceinline__ bool chord_outside_root(const DevScene& sc, const d3& p, double len) {
-  const float px = (float)p.x, py = (float)p.y, pz = (float)p.z;
-  const float m = fmaxf(fmaxf(fabsf(px), fabsf(py)), fabsf(pz));
-  const float ex = fmaxf(fmaxf(sc.root_lo[0] - px, px - sc.root_hi[0]), 0.f);
-  const float ey = fmaxf(fmaxf(sc.root_lo[1] - py, py - sc.root_hi[1]), 0.f);
-  const float ez = fmaxf(fmaxf(sc.root_lo[2] - pz, pz - sc.root_hi[2]), 0.f);
-  const float d2 = ex * ex + ey * ey + ez * ez;
-  const float L = __double2float_ru(len) * 1.00001f + m * 2.4e-7f;
-  return d2 * 0.99999f > L * L;
-}
-
 template <bool ANY, bool COUNT, int W, class IO>
 __device__ __forceinline__ void trace_decoupled(const DevScene& sc, const DevHole& bh, const IO& io, const int n, int* cursor, Counters* gcnt) {
   __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
@@ -476,43 +602,66 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
            the binary one stays at 6 (5: bunny 1080p 103.8 -> 104.8, C5 68.6 -> 70.4) */
 #define RRT_MINB_CLOSEST(V, STEP) (((V) >= 4 && (STEP) != 1) ? 5 : RRT_MINBLOCKS(V, STEP))
 #endif
-template <bool COUNT, int V, int STEP = 0>
+template <bool COUNT, int V, int STEP = 0, int PARK = 0>
 __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB_CLOSEST(V, STEP)) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                 const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
-                                                                int* cursor, int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt) {
+                                                                int* cursor, int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt, const ParkQ pk) {
   ClosestIO io; io.ray = ray; io.cap = cap; io.h_prim = h_prim; io.h_geo = h_geo;
 #if RRT_AB
   if constexpr (V == 1) trace_sched<false, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
   else if constexpr (STEP == 3) trace_decoupled<false, COUNT, (V == 0 ? 2 : V)>(sc, bh, io, *count_ptr, cursor, gcnt);
   else
 #endif
-  trace_persistent<false, COUNT, (V == 0 ? 2 : V), STEP>(sc, bh, io, *count_ptr, cursor, gcnt);
+  trace_persistent<false, COUNT, (V == 0 ? 2 : V), STEP, ClosestIO, PARK>(sc, bh, io, PARK == 2 ? pk.cnt[0] : *count_ptr, PARK == 2 ? pk.cnt + 1 : cursor, gcnt, pk);
 }
 
 /* shadow rays: BVHAccel::intersect(ray) (any hit), or closest hit when the hemisphere estimator needs the emitter */
-template <bool ANY, bool COUNT, int V, int STEP = 0>
+template <bool ANY, bool COUNT, int V, int STEP = 0, int PARK = 0>
 __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINBLOCKS(V, STEP)) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
-                                                               int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt) {
+                                                               int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt, const ParkQ pk) {
   ShadowIO io; io.ray = ray; io.cap = cap; io.cidx = cidx; io.res = res;
 #if RRT_AB
   if constexpr (V == 1) trace_sched<ANY, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
   else if constexpr (STEP == 3) trace_decoupled<ANY, COUNT, (V == 0 ? 2 : V)>(sc, bh, io, *count_ptr, cursor, gcnt);
   else
 #endif
-  trace_persistent<ANY, COUNT, (V == 0 ? 2 : V), STEP>(sc, bh, io, *count_ptr, cursor, gcnt);
+  trace_persistent<ANY, COUNT, (V == 0 ? 2 : V), STEP, ShadowIO, PARK>(sc, bh, io, PARK == 2 ? pk.cnt[0] : *count_ptr, PARK == 2 ? pk.cnt + 1 : cursor, gcnt, pk);
 }
 
 /* parity hook: the same loop on caller-supplied rays */
-template <bool ANY, int V, int STEP = 0>
+template <bool ANY, int V, int STEP = 0, int PARK = 0>
 __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINBLOCKS(V, STEP)) k_hook_trace(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, int n,
                                                             const double* __restrict__ o, const double* __restrict__ d, const double* __restrict__ tmin,
-                                                            const double* __restrict__ tmax, rrt_hit* __restrict__ out, int* cursor, Counters* gcnt) {
+                                                            const double* __restrict__ tmax, rrt_hit* __restrict__ out, int* cursor, Counters* gcnt, const ParkQ pk) {
   HookIO<ANY> io; io.o = o; io.d = d; io.tmin = tmin; io.tmax = tmax; io.out = out;
 #if RRT_AB
   if constexpr (V == 1) trace_sched<ANY, true>(sc, bh, io, n, cursor, gcnt);
   else if constexpr (STEP == 3) trace_decoupled<ANY, true, (V == 0 ? 2 : V)>(sc, bh, io, n, cursor, gcnt);
   else
 #endif
-  trace_persistent<ANY, true, (V == 0 ? 2 : V), STEP>(sc, bh, io, n, cursor, gcnt);
+  trace_persistent<ANY, true, (V == 0 ? 2 : V), STEP, HookIO<ANY>, PARK>(sc, bh, io, PARK == 2 ? pk.cnt[0] : n, PARK == 2 ? pk.cnt + 1 : cursor, gcnt, pk);
+}
+
+/* k_escape: carries the rays the trace kernel parked (ParkQ above).  No BVH, no stack: 58 registers, 8 blocks of 128 threads per SM */
+#ifndef RRT_MINB_ESCAPE
+#define RRT_MINB_ESCAPE 8
+#endif
+template <bool COUNT>
+__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB_ESCAPE) k_escape_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, size_t cap,
+                                                                               int* __restrict__ h_prim, double* __restrict__ h_geo, Counters* gcnt, const ParkQ in, const ParkQ out) {
+  ClosestIO io; io.ray = nullptr; io.cap = cap; io.h_prim = h_prim; io.h_geo = h_geo;
+  escape_persistent<COUNT>(sc, bh, io, in, out, gcnt);
+}
+template <bool COUNT>
+__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB_ESCAPE) k_escape_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, size_t cap,
+                                                                              const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt, const ParkQ in, const ParkQ out) {
+  ShadowIO io; io.ray = nullptr; io.cap = cap; io.cidx = cidx; io.res = res;
+  escape_persistent<COUNT>(sc, bh, io, in, out, gcnt);
+}
+template <bool ANY>
+__global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB_ESCAPE) k_escape_hook(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, rrt_hit* __restrict__ hits,
+                                                                            Counters* gcnt, const ParkQ in, const ParkQ out) {
+  HookIO<ANY> io; io.o = io.d = io.tmin = io.tmax = nullptr; io.out = hits;
+  escape_persistent<true>(sc, bh, io, in, out, gcnt);
 }

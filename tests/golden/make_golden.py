@@ -3,7 +3,7 @@
 oracle/build_ref.sh from /root/reference).  Runs only in the build container; the fixtures it writes are
 committed so that the GPU box (no /root/reference) can check against them.
 
-    python tests/golden/make_golden.py [kat] [render] [scenes]
+    python tests/golden/make_golden.py [kat] [render] [scenes] [fullsize] [bvhorder] [rng]
 
 Inputs are seeded numpy draws; outputs are what the reference's BVHAccel::intersect, BlackHole::next_micro_ray,
 Camera::generate_ray, BSDF::f/sample_f, SceneLight::sample_L and PathTracer::raytrace_pixel return for them.
@@ -70,6 +70,9 @@ SCENES = {  # name -> (dae, W, H, screenDist scale)
     # <directional> = DirectionalLight (reference src/static_scene/light.cpp:17-42)
     "banana_480x360": ("banana.dae", 480, 360, None),
     "banana_96x72": ("banana.dae", 96, 72, 0.2),
+    # the frames of BASELINE.json configs 3 and 4 (camera blocks only: -r crops / extends the view, the geometry is the 480x360 dump)
+    "cbbunny_microfacet_1280x720": ("CBbunny_microfacet_cu.dae", 1280, 720, None),
+    "cbbunny_microfacet_1920x1080": ("CBbunny_microfacet_cu.dae", 1920, 1080, None),
 }
 SYNTH_MESH = (48, 49)   # n_u, n_v of the exported mesh
 
@@ -361,6 +364,65 @@ def make_render(only=None):
         print("render", name, "mean radiance %.5f  paths %d" % (img[..., :3].mean(), img[..., 3].sum()))
 
 
+# ---------------------------------------------------------------- the reference's own BVH, walked (tie-break ranks)
+def kat_bvh_order():
+    out = {}
+    for scene in ("cbspheres_lambertian_480x360", "cbgems_480x360", "cbbunny_microfacet_480x360", "banana_480x360", "cbsynth_480x360"):
+        dae, w, h, _ = SCENES[scene]
+        probe("bh", "bvhorder", os.path.join(DAE, dae), w, h, tmpf("order.bin"))
+        a = np.fromfile(tmpf("order.bin"), np.float64)
+        out[scene + "_info"] = a[:3].astype(np.int64)          # nodes, leaves, depth of BVHAccel::get_root()'s tree
+        out[scene + "_rank"] = a[3:].astype(np.uint32)         # per primitive (reference order): position in the depth-first leaf order
+        print("kat_bvh_order", scene, a[:3], len(a) - 3)
+    np.savez_compressed(os.path.join(HERE, "kat_bvh_order.npz"), **out)
+
+
+# ---------------------------------------------------------------- independent-RNG reference image (statistical parity)
+def render_independent_rng():
+    """The reference's raytrace_pixel driven by glibc's OWN generator (random_r, the algorithm behind rand(); nothing shared with the product's
+    Philox streams), adaptive stop off, 96x72, 4096 spp, hole on: what a converged run of the unmodified binary estimates, kept as HDR."""
+    scene, spp, l, m = "cbspheres_lambertian_96x72", 4096, 2, 4
+    dae, w, h, _ = SCENES[scene]
+    env = dict(scene_env(scene)); env["RRT_PROBE_GLIBC_RAND"] = "1"
+    out = tmpf("render_rng.bin")
+    probe("bh", "render", os.path.join(DAE, dae), w, h, spp, l, m, spp + 1, 0.0, 12345, out, env=env)
+    a = np.fromfile(out, np.float64)
+    img = a[: w * h * 4].reshape(h, w, 4)
+    np.savez_compressed(os.path.join(HERE, "render_independent_rng.npz"), hdr=img[..., :3].astype(np.float32), counts=img[..., 3].astype(np.int32),
+                        scene=scene, mode="bh", params=np.array([spp, l, m, spp + 1, 0.0, 0], np.float64))
+    print("render_independent_rng mean radiance %.5f  paths %d  %.1f s" % (img[..., :3].mean(), img[..., 3].sum(), a[w * h * 4 + 3]))
+
+
+# ---------------------------------------------------------------- full-size frames of BASELINE.json's own configs
+FULLSIZE = {  # name -> (scene, mode, spp, l, m, batch, tol, seed, cell (x0, y0, w, h) or None = whole frame)
+    "c1": ("cbspheres_lambertian_480x360", "flat", 16, 4, 5, 32, 0.05, 1, None),
+    "c2": ("cbspheres_lambertian_480x360", "bh", 16, 4, 5, 32, 0.05, 1, None),
+    # C3: a 256x144 cell of the 1280x720 frame over the bunny (flat, 256 spp; the adaptive rule acts from 32 spp on)
+    "c3_cell": ("cbbunny_microfacet_1280x720", "flat", 256, 4, 5, 32, 0.05, 1, (512, 216, 256, 144)),
+    # C4: a 256x144 cell of the 1920x1080 hole frame, left of the hole's image: mesh, walls, lensed region (64 spp, two adaptive batches)
+    "c4_cell": ("cbbunny_microfacet_1920x1080", "bh", 64, 4, 5, 32, 0.05, 1, (736, 468, 256, 144)),
+}
+
+
+def make_fullsize(only=None):
+    """Rendered by the reference's own raytrace_pixel (Philox-fed rand()) at the configs' real frame sizes; minutes of CPU each."""
+    for name, (scene, mode, spp, l, m, batch, tol, seed, cell) in FULLSIZE.items():
+        if only and name not in only:
+            continue
+        dae, w, h, _ = SCENES[scene]
+        out = tmpf("render_full.bin")
+        env = dict(scene_env(scene))
+        x0, y0, cw, ch = cell if cell else (0, 0, w, h)
+        env["RRT_PROBE_ROWS"] = "%d:%d" % (y0, y0 + ch); env["RRT_PROBE_COLS"] = "%d:%d" % (x0, x0 + cw)
+        probe(mode, "render", os.path.join(DAE, dae), w, h, spp, l, m, batch, tol, seed, out, env=env)
+        a = np.fromfile(out, np.float64)
+        img = a[: w * h * 4].reshape(h, w, 4)[y0:y0 + ch, x0:x0 + cw]
+        np.savez_compressed(os.path.join(HERE, "render_full_%s.npz" % name), hdr=img[..., :3].astype(np.float32), counts=img[..., 3].astype(np.int32),
+                            scene=scene, mode=mode, params=np.array([spp, l, m, batch, tol, seed], np.float64), frame=np.array([w, h]),
+                            cell=np.array([x0, y0, cw, ch]), seconds=a[w * h * 4 + 3])
+        print("render_full", name, "mean radiance %.5f  paths %d  %.1f s" % (img[..., :3].mean(), img[..., 3].sum(), a[w * h * 4 + 3]), flush=True)
+
+
 if __name__ == "__main__":
     what = sys.argv[1:] or ["scenes", "kat", "render"]
     if "scenes" in what:
@@ -369,3 +431,9 @@ if __name__ == "__main__":
         make_kat([w for w in what if w in ("thin_lens", "keenan")])
     if "render" in what:
         make_render([w for w in what if w in RENDERS] or None)
+    if "bvhorder" in what:
+        kat_bvh_order()
+    if "rng" in what:
+        render_independent_rng()
+    if "fullsize" in what:
+        make_fullsize([w for w in what if w in FULLSIZE] or None)

@@ -60,3 +60,21 @@ def test_survey_bvh_shapes():
     assert api.bvh_build_host(load_scene("cbspheres_lambertian_480x360"))["n_nodes"] == 7
     b = api.bvh_build_host(load_scene("cbbunny_microfacet_480x360"))
     assert (b["n_nodes"], b["n_leaves"], b["depth"]) == (19103, 9552, 19)
+
+
+@pytest.mark.parametrize("scene", ["cbspheres_lambertian_480x360", "cbgems_480x360", "cbbunny_microfacet_480x360", "banana_480x360", "cbsynth_480x360"])
+def test_dfs_rank_equals_the_reference_trees_own_leaf_order(scene):
+    """tests/golden/kat_bvh_order.npz: BVHAccel::get_root() of the reference's OWN tree (src/bvh.cpp:49-96) walked left-then-right as intersect_micro
+    walks it (src/bvh.cpp:120-135), primitives of a leaf in vector order.  The tie-break ranks (Triangle::intersect keeps the last primitive among
+    equal t) of the host builder and of the oracle restatement equal that order, node / leaf counts and depth included."""
+    from util import golden
+    g = golden("kat_bvh_order")
+    s = load_scene(scene)
+    nodes, leaves, depth = [int(v) for v in g[scene + "_info"]]
+    for topology in (0, 1):
+        got = api.bvh_build_host(s, topology)
+        assert (got["n_nodes"], got["n_leaves"], got["depth"]) == (nodes, leaves, depth)
+        assert np.array_equal(got["dfs_rank"], g[scene + "_rank"])
+    ref = orc.Oracle(s).bvh_info()
+    assert np.array_equal(ref["dfs_rank"], g[scene + "_rank"]) and (ref["n_nodes"], ref["n_leaves"], ref["depth"]) == (nodes, leaves, depth)
+    assert sorted(g[scene + "_rank"].tolist()) == list(range(s.n_prims))

@@ -42,3 +42,61 @@ def test_oracle_render_matches_reference(name):
     # identical IEEE operations: expect equality; allow 2 float ulps for libm (glibc here vs glibc at golden time is the same)
     np.testing.assert_allclose(hdr, ref, rtol=3e-7, atol=1e-9)
     assert st["paths"] == int(cnt.sum())
+
+
+FULLSIZE = ["c1", "c2", "c3_cell", "c4_cell"]
+
+
+def setup_full(g, obj, sub=None):
+    """frame, hole mode and parameters of a full-size golden (tests/golden/render_full_*.npz, rendered by the reference's own raytrace_pixel at
+    the frame sizes of BASELINE.json's configs); sub = (dx, dy, w, h) restricts the render to a sub-cell of the golden's cell"""
+    W, H = [int(v) for v in g["frame"]]
+    x0, y0, cw, ch = [int(v) for v in g["cell"]]
+    obj.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_FLAT if str(g["mode"]) == "flat" else sc.MODE_LITERAL)
+    obj.set_frame(W, H)
+    if sub:
+        x0, y0, cw, ch = x0 + sub[0], y0 + sub[1], sub[2], sub[3]
+    if (cw, ch) != (W, H):
+        obj.set_cell(x0, y0, cw, ch)
+    spp, l, m, batch, tol, seed = g["params"]
+    return sc.make_params(ns_aa=spp, max_ray_depth=m, ns_area_light=l, samples_per_batch=batch, max_tolerance=tol, seed=int(seed)), (x0, y0, cw, ch)
+
+
+@pytest.mark.parametrize("name", FULLSIZE)
+def test_oracle_matches_a_cell_of_the_full_size_reference_frames(name):
+    """C1 / C2 at 480x360 / 16 spp, a cell of C3's 1280x720 / 256 spp frame and of the 1080p hole frame: the oracle on a 24x12 sub-cell
+    (the whole frames take the CPU minutes; the GPU tests compare every pixel)"""
+    g = golden("render_full_" + name)
+    o = orc.Oracle(load_scene(str(g["scene"])))
+    sub = (g["hdr"].shape[1] // 2 - 12, g["hdr"].shape[0] // 2 - 6, 24, 12)
+    p, (x0, y0, cw, ch) = setup_full(g, o, sub)
+    hdr, cnt, st = o.render(p)
+    ref = g["hdr"][sub[1]:sub[1] + ch, sub[0]:sub[0] + cw]; refc = g["counts"][sub[1]:sub[1] + ch, sub[0]:sub[0] + cw]
+    assert np.array_equal(cnt[y0:y0 + ch, x0:x0 + cw], refc)
+    np.testing.assert_allclose(hdr[y0:y0 + ch, x0:x0 + cw], ref, rtol=3e-7, atol=1e-9)
+    assert cnt.sum() == refc.sum()      # nothing rendered outside the cell
+
+
+def stat_blocks(a, by=12, bx=16):
+    """means over blocks of by x bx pixels"""
+    h, w, c = a.shape
+    return a.reshape(h // by, by, w // bx, bx, c).mean((1, 3))
+
+
+def test_oracle_agrees_statistically_with_the_reference_driven_by_glibcs_own_generator():
+    """Every image golden feeds the SAME Philox stream to both sides; here the reference's raytrace_pixel ran on glibc's own generator
+    (random_r, the algorithm behind rand(); tests/golden/render_independent_rng.npz, 96x72, 4096 spp, hole on, adaptive stop off), which
+    shares nothing with the Philox streams or with how they are consumed.  The oracle at 192 spp: frame mean within 2 %, 16x12-pixel block
+    means within a few standard errors (the GPU test does this at 16 k spp against the 1 % bound)."""
+    g = golden("render_independent_rng")
+    ref = g["hdr"].astype(np.float64)
+    spp, l, m = int(g["params"][0]), int(g["params"][1]), int(g["params"][2])
+    o = orc.Oracle(load_scene(str(g["scene"])))
+    o.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_LITERAL); o.set_frame(96, 72)
+    n = 192
+    hdr, cnt, st = o.render(sc.make_params(ns_aa=n, max_ray_depth=m, ns_area_light=l, samples_per_batch=n + 1, max_tolerance=0.0, seed=4242))
+    assert (cnt == n).all() and (g["counts"] == spp).all()
+    M = ref.mean()
+    assert abs(hdr.mean() / M - 1) < 0.02
+    d = stat_blocks(hdr.astype(np.float64)) - stat_blocks(ref)
+    assert np.sqrt((d ** 2).mean()) < 0.06 * M          # 192 spp: noise, not bias, sets this bound (9 % at 48 spp measured)
