@@ -179,6 +179,8 @@ enum {
                                  (rays need 1..63 chords) and another stream's kernels fill the idle SMs; bit-identical results for any value */
   RRT_OPT_ESCAPE = 11,        /* A/B builds only (otherwise RRT_E_ARG for a non-zero value): 1 = rays that have left the scene box are parked by the trace kernel
                                  and carried on by a lean kernel (stepper + horizon + root-box test only); measured slower, default 0.  Bit-identical results */
+  RRT_OPT_TOP_NODE = 12,      /* binary trees: 1 (default) = the top of the tree is also kept as ONE 8-wide record (groupings of large primitives opened into
+                                 their flat boxes + the root of the rest) that every traversal tests first; 0 = start at the binary root.  Same results; next rrt_upload_scene */
   RRT_OPT_BVH_BUILDER = 9     /* where the BVH is built.  1 = on the device: the reference's depth-first ranks by level-synchronous stable partition
                                  + an LBVH for the traversal (scenes of >= 64 primitives, binary nodes; falls back to the host if the tree comes
                                  out deeper than the traversal stack); 2 = on the host (reference tree shape or binned SAH, threaded);

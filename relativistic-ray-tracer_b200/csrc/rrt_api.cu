@@ -53,7 +53,7 @@ struct rrt_ctx {
   // device memory
   DevBuf d_env, d_env_pdf, d_env_cond, d_env_marg;
   bool have_env = false;
-  DevBuf d_tripos, d_build, d_grid, d_nodes, d_wide, d_leaf, d_nrm, d_kind, d_index, d_pmat, d_sph, d_mats, d_lights;
+  DevBuf d_top, d_tripos, d_build, d_grid, d_nodes, d_wide, d_leaf, d_nrm, d_kind, d_index, d_pmat, d_sph, d_mats, d_lights;
   DevBuf d_work, d_px, d_act, d_blk, d_cnt, d_out_rgb, d_out_cnt, d_out_rgbn, d_hook_in, d_hook_out;
   std::vector<cudaEvent_t> events;
   size_t events_used = 0;
@@ -140,6 +140,7 @@ int rrt_create(rrt_ctx** out, int device) {
   ctx->opt[RRT_OPT_SHADE_SPLIT] = 2;
   ctx->opt[RRT_OPT_STREAMS] = 2;
   ctx->opt[RRT_OPT_ESCAPE] = 0;
+  ctx->opt[RRT_OPT_TOP_NODE] = 1;
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaMallocHost((void**)&ctx->h_pinned, 4096)) != cudaSuccess) {
@@ -160,7 +161,7 @@ void rrt_destroy(rrt_ctx* ctx) {
   if (!ctx->subs.empty()) { multi_destroy(ctx); return; }
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->d_env, &ctx->d_env_pdf, &ctx->d_env_cond, &ctx->d_env_marg, &ctx->d_grid, &ctx->d_nodes, &ctx->d_tripos, &ctx->d_build, &ctx->d_wide, &ctx->d_leaf, &ctx->d_nrm, &ctx->d_kind, &ctx->d_index, &ctx->d_pmat, &ctx->d_sph, &ctx->d_mats, &ctx->d_lights,
+  DevBuf* bufs[] = {&ctx->d_top, &ctx->d_env, &ctx->d_env_pdf, &ctx->d_env_cond, &ctx->d_env_marg, &ctx->d_grid, &ctx->d_nodes, &ctx->d_tripos, &ctx->d_build, &ctx->d_wide, &ctx->d_leaf, &ctx->d_nrm, &ctx->d_kind, &ctx->d_index, &ctx->d_pmat, &ctx->d_sph, &ctx->d_mats, &ctx->d_lights,
                     &ctx->d_work, &ctx->d_px, &ctx->d_act, &ctx->d_blk, &ctx->d_cnt, &ctx->d_out_rgb, &ctx->d_out_cnt, &ctx->d_out_rgbn,
                     &ctx->d_hook_in, &ctx->d_hook_out};
   for (DevBuf* b : bufs) b->release();
@@ -175,7 +176,7 @@ void rrt_destroy(rrt_ctx* ctx) {
 int rrt_set_option(rrt_ctx* ctx, int option, int64_t value) {
   if (!ctx) return RRT_E_ARG;
   RRT_MULTI_ALL(ctx, rrt_set_option(sub, option, value));
-  if (option < 0 || option > RRT_OPT_ESCAPE) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
+  if (option < 0 || option > RRT_OPT_TOP_NODE) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
 #if !RRT_AB
   if ((option == RRT_OPT_TRACE_KERNEL && value != 0) || (option == RRT_OPT_BVH_WIDTH && value == 4) || (option == RRT_OPT_ESCAPE && value != 0))
     FAIL(RRT_E_ARG, "rrt_set_option: this variant is compiled only into A/B builds (make EXTRA=-DRRT_AB=1)");
@@ -329,6 +330,54 @@ static int build_bvh_on_device(rrt_ctx* ctx, const rrt_scene* s, bool* built) {
   return RRT_OK;
 }
 
+/* The top of a binary tree as one 8-wide record (rrt_trace.cuh traverse()).  Starting from the root's two children, the interior child with the
+ * largest surface area that is not flat (a grouping of walls, not the two coplanar triangles of one wall) is replaced by its two children until 8
+ * slots are used or nothing is left to open.  `fetch(i, rec)` delivers the
+ * 64-byte record of interior node i.  out: 6 arrays of 8 floats (lo.x lo.y lo.z hi.x hi.y hi.z) + 8 child codes + 8 pad; returns the child count. */
+template <class Fetch>
+static int build_top_record(Fetch fetch, int32_t root_code, float out[64], int max_children = 8) {
+  struct Child { int32_t code; float lo[3], hi[3]; };
+  auto area = [](const Child& c) {
+    const double dx = (double)c.hi[0] - c.lo[0], dy = (double)c.hi[1] - c.lo[1], dz = (double)c.hi[2] - c.lo[2];
+    return (dx < 0 || dy < 0 || dz < 0) ? 0.0 : 2.0 * (dx * dy + dy * dz + dz * dx);
+  };
+  auto kids_of = [&](int32_t node, Child* L, Child* R) {
+    float q[16]; fetch(node, q);
+    L->lo[0] = q[0]; L->lo[1] = q[1]; L->lo[2] = q[2]; L->hi[0] = q[3]; L->hi[1] = q[4]; L->hi[2] = q[5];
+    R->lo[0] = q[6]; R->lo[1] = q[7]; R->lo[2] = q[8]; R->hi[0] = q[9]; R->hi[1] = q[10]; R->hi[2] = q[11];
+    memcpy(&L->code, &q[12], 4); memcpy(&R->code, &q[13], 4);
+  };
+  std::vector<Child> ch(2);
+  kids_of(root_code, &ch[0], &ch[1]);
+  auto flat = [](const Child& c) {   /* a wall: opening it yields two triangles with the same box */
+    const double e[3] = {(double)c.hi[0] - c.lo[0], (double)c.hi[1] - c.lo[1], (double)c.hi[2] - c.lo[2]};
+    const double mx = std::max(e[0], std::max(e[1], e[2])), mn = std::min(e[0], std::min(e[1], e[2]));
+    return mn <= 1e-3 * mx;
+  };
+  while ((int)ch.size() < max_children) {
+    int pick = -1; double best = 0.0;
+    for (size_t k = 0; k < ch.size(); ++k) {
+      if (ch[k].code < 0 || flat(ch[k])) continue;
+      const double a = area(ch[k]);
+      if (a > best) { best = a; pick = (int)k; }
+    }
+    if (pick < 0) break;
+    Child l, r; kids_of(ch[pick].code, &l, &r);
+    ch[pick] = l; ch.push_back(r);
+  }
+  for (int k = 0; k < 8; ++k) {
+    int32_t code = rrt::kEmptyChild;
+    if (k < (int)ch.size()) {
+      for (int a = 0; a < 3; ++a) { out[a * 8 + k] = ch[k].lo[a]; out[(3 + a) * 8 + k] = ch[k].hi[a]; }
+      code = ch[k].code;
+    } else {
+      for (int a = 0; a < 3; ++a) { out[a * 8 + k] = INFINITY; out[(3 + a) * 8 + k] = -INFINITY; }
+    }
+    memcpy(&out[48 + k], &code, 4); out[56 + k] = 0.f;
+  }
+  return (int)ch.size();
+}
+
 extern "C" {
 int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   if (!ctx || !s) return RRT_E_ARG;
@@ -395,6 +444,27 @@ int rrt_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   d.n_prims = (int)s->n_prims; d.n_mats = (int)s->n_mats; d.n_lights = (int)s->n_lights;
   d.width = b.width; d.wide = b.width > 2 ? ctx->d_wide.as<float>() : nullptr;
   d.root = b.root; d.wroot = b.wide_root;
+  d.top = nullptr;
+  {
+    const int tree_depth = on_device ? b.device_depth : flat_depth(b);
+    /* stack: the top visit leaves at most (children - 1) entries below whatever the binary descent pushes (<= tree_depth - 1) */
+    const int max_children = std::min(8, RRT_STACK - tree_depth + 1);
+    if (ctx->opt[RRT_OPT_TOP_NODE] != 0 && b.width <= 2 && b.root >= 0 && b.n_nodes >= 8 && max_children >= 3 && ctx->opt[RRT_OPT_TRACE_KERNEL] != 1) {
+      float rec[64];
+      cudaError_t fe = cudaSuccess;
+      auto fetch = [&](int32_t node, float* q) {
+        if (on_device) { cudaError_t e = cudaMemcpy(q, ctx->d_nodes.as<float>() + 16 * (size_t)node, 64, cudaMemcpyDeviceToHost); if (e != cudaSuccess) fe = e; }
+        else memcpy(q, &b.nodes[16 * (size_t)node], 64);
+      };
+      const int nch = build_top_record(fetch, b.root, rec, max_children);
+      CK(fe);
+      if (nch > 2) {
+        if ((rc = upload(ctx, ctx->d_top, rec, sizeof rec))) return rc;
+        CK(cudaStreamSynchronize(ctx->stream));
+        d.top = ctx->d_top.as<float>();
+      }
+    }
+  }
   for (int k = 0; k < 3; ++k) { d.root_lo[k] = rrt::round_down_f(b.root_lo[k]); d.root_hi[k] = rrt::round_up_f(b.root_hi[k]); }
   {
     double r2 = 0.0;
@@ -1421,7 +1491,7 @@ static int multi_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
   if (rc) { ctx->err = root->err; return rc; }
   const size_t G = ctx->subs.size();
   /* the arrays the kernels read, as rrt_upload_scene left them on GPU 0 (capacities can exceed the bytes in use: harmless) */
-  DevBuf rrt_ctx::* const bufs[] = {&rrt_ctx::d_nodes, &rrt_ctx::d_wide, &rrt_ctx::d_leaf, &rrt_ctx::d_nrm, &rrt_ctx::d_kind, &rrt_ctx::d_index, &rrt_ctx::d_pmat,
+  DevBuf rrt_ctx::* const bufs[] = {&rrt_ctx::d_top, &rrt_ctx::d_nodes, &rrt_ctx::d_wide, &rrt_ctx::d_leaf, &rrt_ctx::d_nrm, &rrt_ctx::d_kind, &rrt_ctx::d_index, &rrt_ctx::d_pmat,
                                     &rrt_ctx::d_sph, &rrt_ctx::d_mats, &rrt_ctx::d_lights, &rrt_ctx::d_grid};
   for (size_t k = 1; k < G; ++k) {
     rrt_ctx* c = ctx->subs[k];
@@ -1446,6 +1516,7 @@ static int multi_upload_scene(rrt_ctx* ctx, const rrt_scene* s) {
     c->ds.env = keep.env; c->ds.env_pdf = keep.env_pdf; c->ds.env_cond = keep.env_cond; c->ds.env_marg = keep.env_marg; c->ds.env_w = keep.env_w; c->ds.env_h = keep.env_h;
     bind_scene_pointers(c);
     c->ds.wide = root->ds.wide ? c->d_wide.as<float>() : nullptr;
+    c->ds.top = root->ds.top ? c->d_top.as<float>() : nullptr;
     c->ds.clearance = root->ds.clearance ? c->d_grid.as<float>() : nullptr;
     c->n_lights = root->n_lights; c->n_delta_lights = root->n_delta_lights; c->host_lights = root->host_lights; c->has_microfacet = root->has_microfacet;
     c->have_scene = true;

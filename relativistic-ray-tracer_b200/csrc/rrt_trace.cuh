@@ -32,6 +32,8 @@ struct DevScene {
   // environment light (rrt_set_envmap): map [h][w][3] row 0 = top, and the reference's sampling tables
   const float* env; const double* env_pdf; const double* env_cond; const double* env_marg;
   int env_w, env_h;
+  const float* top;               // binary trees: the top of the tree collapsed into ONE 8-wide record (64 floats, layout of `wide`; child codes
+                                  // are binary node indices / leaf codes), or nullptr: see traverse()
   const float* wide;              // wide nodes (rrt_bvh.h): 8 * width floats each
   int32_t wroot;                  // child code of the wide root
   int width;                      // 2: `nodes`; 4 / 8: `wide`
@@ -67,6 +69,51 @@ struct Best { double t, b1, b2; int prim; int rank; int kind; };
 /* BlackHole::f (reference src/static_scene/blackhole.cpp:13-15) */
 __device__ __forceinline__ double bh_f(double r, double u) { return -u + 3.0 * r * u * u / 2.0; }
 
+/* Two of the stepper's six divisions have a divisor whose correctly rounded reciprocal is already at hand, and for those the IEEE quotient
+ * RN(a / b) can be had from FMAs instead of the ~14 FP64-pipe slots of a division (MUFU seed + Newton steps + range check):
+ *   y = RN(1 / b) exactly;  q0 = RN(a y);  r0 = RN(a - b q0);  q1 = RN(q0 + r0 y);  r1 = a - b q1 (exact);  q = RN(q1 + r1 y).
+ * q1 is within 1 ulp of a / b (|a y - a / b| <= |a / b| 2^-53, one rounding, one correction); with q1 faithful, r1 exact and y the correctly
+ * rounded reciprocal, RN(q1 + r1 y) = RN(a / b) (Markstein 1990, Theorem on the final division step; Cornea, Harrison, Tang, "Scientific
+ * computing on Itanium-based systems", Thm 8.1): q1 + r1 y differs from a / b by |r1| |y - 1 / b| < 2^-53 ulp, while a quotient of two doubles is
+ * never closer than 2^-53 ulp to a rounding boundary without lying on it.  Operands outside [1e-140, 1e140] (and inf / NaN / 0) take the
+ * division itself.  For the constant divisor 6 three steps suffice: a / 6 is at least ulp / 6 away from every rounding boundary (6 M = a has no
+ * solution with M a midpoint: 3 x odd needs 55 bits), q0 + r0 y is within 1.5 x 2^-53 ulp of a / 6.
+ * tools/div_check.cu compares both against `/` on the device for 2^36 operand pairs incl. adversarial significands: 0 mismatches
+ * (profiles/r02_e_div_check.txt); the chord goldens (bit-exact against the reference's own chords) run through this code. */
+#ifndef RRT_FAST_DIV
+#define RRT_FAST_DIV 0   /* exact (0 mismatches in 2.7e11 pairs) but NOT faster on B200: tools/ilp_probe 46.5 -> 43.3 G chords/s at 6 blocks per SM, frames
+                          unchanged (C2 32.0 / 32.2 ms, C5 51.1 / 50.9): the two divisions are not what the stepper waits for.  A/B record. */
+#endif
+__device__ __forceinline__ bool div_safe(double x) {   /* 1e-140 < |x| < 1e140, finite, non-zero: biased exponent in [558, 1488] */
+  const unsigned e = ((unsigned)__double2hiint(x) >> 20) & 0x7ffu;
+  return e - 558u <= 930u;
+}
+/* RN(a / b) given rb == RN(1 / b) */
+__device__ __forceinline__ double div_known_rcp(double a, double b, double rb) {
+#if RRT_FAST_DIV
+  const double q0 = a * rb;
+  if (div_safe(b) && div_safe(q0)) {
+    const double r0 = __fma_rn(-b, q0, a);
+    const double q1 = __fma_rn(r0, rb, q0);
+    const double r1 = __fma_rn(-b, q1, a);
+    return __fma_rn(r1, rb, q1);
+  }
+#endif
+  return a / b;
+}
+/* RN(a / 6) */
+__device__ __forceinline__ double div_by_6(double a) {
+#if RRT_FAST_DIV
+  const double y = 0.16666666666666666;   /* RN(1 / 6) */
+  if (div_safe(a)) {
+    const double q0 = a * y;
+    const double r0 = __fma_rn(-6.0, q0, a);
+    return __fma_rn(r0, y, q0);
+  }
+#endif
+  return a / 6.0;
+}
+
 /* BlackHole::next_micro_ray (reference src/static_scene/blackhole.cpp:17-40).  In: previous chord (o, d, len).
  * Out: next chord.  The conserved plane (x_axis, y_axis) is re-derived from the chord each call, exactly as the
  * reference does; nothing but (o, d, len) is carried. */
@@ -83,11 +130,11 @@ __device__ __forceinline__ void next_micro_ray(const DevHole& bh, d3& o, d3& d, 
   double dy = vnorm(y_axis);
   double rdy = 1.0 / dy;
   y_axis = D3(y_axis.x * rdy, y_axis.y * rdy, y_axis.z * rdy);
-  double up = -u * dx / dy;
+  double up = div_known_rcp(-u * dx, dy, rdy);   /* -u * dx / dy */
   double f1 = bh_f(bh.r, u);
   double f2 = bh_f(bh.r, u + up * h / 2.0);
   double f3 = bh_f(bh.r, u + up * h / 2.0 + f1 * h * h / 4.0);
-  u += up * h + (f1 + f2 + f3) * h * h / 6.0;
+  u += up * h + div_by_6((f1 + f2 + f3) * h * h);   /* ... * h * h / 6.0 */
   double dn = 1.0 / u;
   double next_x = dn * bh.cos_h;
   double next_y = dn * bh.sin_h;
@@ -319,12 +366,31 @@ __device__ __forceinline__ Seg seg_exact(const SegF& s) {
   r.d = D3((double)s.dx, (double)s.dy, (double)s.dz); r.tmin = 0.0; r.tmax = (double)s.tmax;
   return r;
 }
+/* Chord kept in shared memory (RRT_SEG_SMEM, rrt_wavetrace.cuh): 7 doubles per thread, stride RRT_SEG_STRIDE doubles; the traversal reads them
+ * only where it needs them (box context, exact leaf tests), so they occupy no registers while nodes are visited. */
+#ifndef RRT_SEG_STRIDE
+#define RRT_SEG_STRIDE 128
+#endif
+struct SegS { const double* p; };
+__device__ __forceinline__ Seg seg_exact(const SegS& s) {
+  Seg r;
+  r.o = D3(s.p[0], s.p[RRT_SEG_STRIDE], s.p[2 * RRT_SEG_STRIDE]); r.d = D3(s.p[3 * RRT_SEG_STRIDE], s.p[4 * RRT_SEG_STRIDE], s.p[5 * RRT_SEG_STRIDE]);
+  r.tmin = 0.0; r.tmax = s.p[6 * RRT_SEG_STRIDE];
+  return r;
+}
+__device__ __forceinline__ double seg_tmax(const SegS& s) { return s.p[6 * RRT_SEG_STRIDE]; }
 __device__ __forceinline__ double seg_tmax(const Seg& s) { return s.tmax; }
 __device__ __forceinline__ double seg_tmax(const SegF& s) { return (double)s.tmax; }
 /* box context + float upper end of the range; returns whether the far-chord origin shift is in effect */
 __device__ __forceinline__ bool seg_boxctx(const DevScene& sc, const Seg& s, BoxCtx& bc, float& tmaxf) {
   const double T = boxctx_make(sc, s.o, s.d, s.tmin, bc);
   tmaxf = boxctx_tmax(s.tmax, T);
+  return T != 0.0;
+}
+__device__ __forceinline__ bool seg_boxctx(const DevScene& sc, const SegS& s, BoxCtx& bc, float& tmaxf) {
+  const Seg e = seg_exact(s);
+  const double T = boxctx_make(sc, e.o, e.d, 0.0, bc);
+  tmaxf = boxctx_tmax(e.tmax, T);
   return T != 0.0;
 }
 __device__ __forceinline__ void boxctx_axis_f(float of, float df, float slack, float& inv, float& cn, float& cf, bool& neg) {
@@ -503,6 +569,40 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const SEG& s, Best&
   if (active) {
     shifted = seg_boxctx(sc, s, bc, tmaxf);
     if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tl)) cur = sc.root;
+  }
+  /* Top of the tree as one 8-wide record.  The boxes near the root of a Cornell-box scene are the groupings of its walls: each spans most of
+   * the room, so a chord anywhere inside used to walk 5-6 binary nodes only to learn that it touches no wall (6.0 node visits per chord on the
+   * bunny scene, 56 % of the trace kernel's instructions, profiles/r02_f_attribution_c4_shadow.txt).  rrt_upload_scene opens those nodes
+   * (largest drop in surface area first) into up to 8 children — the flat per-wall boxes and the root of the mesh — and one straight-line visit
+   * tests all of them; what passes goes on the stack and the binary loop below carries on.  Same boxes, same leaves: results unchanged. */
+  if (sc.top != nullptr) {
+    if (cur != DONE && cur >= 0) {
+      const float R = 9.5367431640625e-7f;
+      const float* nd = sc.top;
+      if (COUNT) cnt.nodes += 4;     /* a 256-byte record */
+      cur = DONE;
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        const float4 a = __ldg((const float4*)(nd + (RRT_NEGX(bc) ? 24 : 0)) + g), b = __ldg((const float4*)(nd + (RRT_NEGX(bc) ? 0 : 24)) + g);
+        const float4 c = __ldg((const float4*)(nd + (RRT_NEGY(bc) ? 32 : 8)) + g), d = __ldg((const float4*)(nd + (RRT_NEGY(bc) ? 8 : 32)) + g);
+        const float4 e = __ldg((const float4*)(nd + (RRT_NEGZ(bc) ? 40 : 16)) + g), f = __ldg((const float4*)(nd + (RRT_NEGZ(bc) ? 16 : 40)) + g);
+        const int4 k = __ldg((const int4*)(nd + 48) + g);
+        auto child = [&](float pnx, float pfx, float pny, float pfy, float pnz, float pfz, int code) {
+          float tn = fmaxf(fmaxf(__fmaf_rn(pnx, bc.ix, bc.nx_), __fmaf_rn(pny, bc.iy, bc.ny_)), __fmaf_rn(pnz, bc.iz, bc.nz_));
+          float tf = fminf(fminf(__fmaf_rn(pfx, bc.ix, bc.fx_), __fmaf_rn(pfy, bc.iy, bc.fy_)), __fmaf_rn(pfz, bc.iz, bc.fz_));
+          tn = __fmaf_rn(fabsf(tn), -R, tn);
+          tf = __fmaf_rn(fabsf(tf), R, tf);
+          if (tn <= tf && tn <= tmaxf && tf >= bc.tmin && code != DONE) {
+            if (cur != DONE) stack[(sp++) * stride] = cur;
+            cur = code;
+          }
+        };
+        child(a.x, b.x, c.x, d.x, e.x, f.x, k.x);
+        child(a.y, b.y, c.y, d.y, e.y, f.y, k.y);
+        child(a.z, b.z, c.z, d.z, e.z, f.z, k.z);
+        child(a.w, b.w, c.w, d.w, e.w, f.w, k.w);
+      }
+    }
   }
   auto visit = [&]() {
     const float4* nd = sc.nodes + 4 * (size_t)cur;

@@ -28,6 +28,9 @@
 #ifndef RRT_COOP_LEAVES
 #define RRT_COOP_LEAVES 0   /* 1 = any-hit leaf tests deferred and shared across the warp (rrt_trace.cuh coop_*): measured SLOWER, C2 41.4 vs 37.1 ms */
 #endif
+#ifndef RRT_SEG_SMEM
+#define RRT_SEG_SMEM 0   /* A/B: 1 = the current chord (o, d, len) of the hole-on FP64 loop is kept in shared memory between steps */
+#endif
 #ifndef RRT_MINB_FP32
 #define RRT_MINB_FP32 5   /* resident blocks per SM for the FP32-stepper variants (STEP = 1): 4 / 5 / 6 / 7 / 8 measured, see DESIGN.md 6.2 */
 #endif
@@ -159,6 +162,9 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
                                                  const ParkQ pk = ParkQ()) {
   __shared__ int stack_mem[RRT_STACK * RRT_BLOCK];
   __shared__ CoopScratch coop_mem[ANY ? RRT_BLOCK / 32 : 1];
+  constexpr bool SMEM = RRT_SEG_SMEM && STEP == 0 && PARK == 0 && !RRT_COOP_LEAVES;   /* the chord lives in shared memory, not in registers */
+  __shared__ double seg_mem[SMEM ? 7 * RRT_SEG_STRIDE : 1];
+  double* sm = seg_mem + (SMEM ? threadIdx.x : 0);
   int* stack = stack_mem + threadIdx.x;
   constexpr bool COOP = ANY && RRT_COOP_LEAVES;
   CoopScratch* coop = &coop_mem[COOP ? threadIdx.x >> 5 : 0];
@@ -199,6 +205,10 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
         idx = pool_next + rank;
         io.load(idx, o, d, tmin, tmax);
         has = true; j = 0; len = 0.0;
+        if constexpr (SMEM) {
+          sm[0] = o.x; sm[RRT_SEG_STRIDE] = o.y; sm[2 * RRT_SEG_STRIDE] = o.z; sm[3 * RRT_SEG_STRIDE] = d.x; sm[4 * RRT_SEG_STRIDE] = d.y; sm[5 * RRT_SEG_STRIDE] = d.z;
+          sm[6 * RRT_SEG_STRIDE] = 0.0;
+        }
         }
         if (STEP == 1) {
           fast_init(bh, o, d, fr);
@@ -231,6 +241,28 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
         if (found) {
           h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
           if (IO::GEO) fill_geo(sc, seg_exact(sf), best, h);
+        } else {
+          ++j;
+          if (j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = j - 1; h.steps = j; h.t = 0.0; }
+        }
+      }
+    } else if constexpr (SMEM) {
+      SegS ss; ss.p = sm;
+      if (has) {
+        Seg e = seg_exact(ss);
+        next_micro_ray(bh, e.o, e.d, e.tmax);
+        sm[0] = e.o.x; sm[RRT_SEG_STRIDE] = e.o.y; sm[2 * RRT_SEG_STRIDE] = e.o.z; sm[3 * RRT_SEG_STRIDE] = e.d.x; sm[4 * RRT_SEG_STRIDE] = e.d.y; sm[5 * RRT_SEG_STRIDE] = e.d.z;
+        sm[6 * RRT_SEG_STRIDE] = e.tmax;
+        if (horizon_hit(bh, e.o, e.d, e.tmax)) { h.status = 2; h.prim = -1; h.chord = j; h.steps = j + 1; h.t = 0.0; }
+        if (COUNT) cnt.steps++;
+      }
+      const bool live = has && h.status < 0;
+      if (W == 2) found = traverse<ANY, COUNT, false, true, SegS>(sc, ss, best, stack, RRT_BLOCK, cnt, live, coop);
+      else found = traverse_wide<ANY, COUNT, (W == 2 ? 4 : W), false, true, SegS>(sc, ss, best, stack, RRT_BLOCK, cnt, live, coop);
+      if (live) {
+        if (found) {
+          h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
+          if (IO::GEO) fill_geo(sc, seg_exact(ss), best, h);
         } else {
           ++j;
           if (j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = j - 1; h.steps = j; h.t = 0.0; }
