@@ -340,6 +340,7 @@ def main():
     ap.add_argument("--builder", default="auto", choices=["auto", "host", "device"], help="BVH construction (RRT_OPT_BVH_BUILDER): auto = device LBVH for >= 4096 primitives, else host binned SAH")
     ap.add_argument("--batch", type=int, default=0, help="override samples_per_batch (the reference's -a batch; default rule: shard.weak_scaling_params)")
     ap.add_argument("--streams", type=int, default=0, help="RRT_OPT_STREAMS override (0 = library default)")
+    ap.add_argument("--no-overlap", action="store_true", help="RRT_OPT_OVERLAP = 0")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -388,6 +389,8 @@ def main():
     ctx.set_option(api.OPT_BVH_BUILDER, {"auto": 0, "device": 1, "host": 2}[args.builder])
     if args.streams:
         ctx.set_option(api.OPT_STREAMS, args.streams)
+    if args.no_overlap:
+        ctx.set_option(api.OPT_OVERLAP, 0)
     ctx.upload_scene(s)
     ctx.set_blackhole((0.0, 1.0, 0.0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
     ctx.set_frame(W, H)

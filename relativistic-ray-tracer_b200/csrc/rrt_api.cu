@@ -35,6 +35,8 @@ struct rrt_ctx {
   cudaStream_t stream = nullptr;
   cudaStream_t aux[3] = {nullptr, nullptr, nullptr};   /* wavefront chunks of one round are dealt over stream + aux[0 .. n-2] (RRT_OPT_STREAMS) */
   cudaEvent_t ev_fork = nullptr, ev_join[3] = {nullptr, nullptr, nullptr};
+  cudaStream_t shadow_stream[4] = {nullptr, nullptr, nullptr, nullptr};   /* RRT_OPT_OVERLAP: shadow rays of depth i beside extension rays of depth i + 1 */
+  std::vector<cudaEvent_t> sync_events; size_t sync_used = 0;
   std::string err;
   // configuration
   bool have_scene = false, have_cam = false;
@@ -141,6 +143,7 @@ int rrt_create(rrt_ctx** out, int device) {
   ctx->opt[RRT_OPT_STREAMS] = 2;
   ctx->opt[RRT_OPT_ESCAPE] = 0;
   ctx->opt[RRT_OPT_TOP_NODE] = 1;
+  ctx->opt[RRT_OPT_OVERLAP] = 1;
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaMallocHost((void**)&ctx->h_pinned, 4096)) != cudaSuccess) {
@@ -169,6 +172,8 @@ void rrt_destroy(rrt_ctx* ctx) {
   if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
   for (int k = 0; k < 3; ++k) { if (ctx->aux[k]) cudaStreamDestroy(ctx->aux[k]); if (ctx->ev_join[k]) cudaEventDestroy(ctx->ev_join[k]); }
   if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+  for (int k = 0; k < 4; ++k) if (ctx->shadow_stream[k]) cudaStreamDestroy(ctx->shadow_stream[k]);
+  for (cudaEvent_t ev : ctx->sync_events) cudaEventDestroy(ev);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -176,7 +181,7 @@ void rrt_destroy(rrt_ctx* ctx) {
 int rrt_set_option(rrt_ctx* ctx, int option, int64_t value) {
   if (!ctx) return RRT_E_ARG;
   RRT_MULTI_ALL(ctx, rrt_set_option(sub, option, value));
-  if (option < 0 || option > RRT_OPT_TOP_NODE) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
+  if (option < 0 || option > RRT_OPT_OVERLAP) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
 #if !RRT_AB
   if ((option == RRT_OPT_TRACE_KERNEL && value != 0) || (option == RRT_OPT_BVH_WIDTH && value == 4) || (option == RRT_OPT_ESCAPE && value != 0))
     FAIL(RRT_E_ARG, "rrt_set_option: this variant is compiled only into A/B builds (make EXTRA=-DRRT_AB=1)");
@@ -589,6 +594,10 @@ int rrt_bvh_info(rrt_ctx* ctx, int32_t* n_nodes, int32_t* n_leaves, int32_t* dep
 }  // extern "C"
 
 /* ---------------------------------------------------------------- render */
+static cudaEvent_t next_sync_event(rrt_ctx* ctx) {   /* ordering only, no timing */
+  if (ctx->sync_used == ctx->sync_events.size()) { cudaEvent_t ev; cudaEventCreateWithFlags(&ev, cudaEventDisableTiming); ctx->sync_events.push_back(ev); }
+  return ctx->sync_events[ctx->sync_used++];
+}
 static cudaEvent_t next_event(rrt_ctx* ctx) {
   if (ctx->events_used == ctx->events.size()) {
     cudaEvent_t ev; cudaEventCreate(&ev); ctx->events.push_back(ev);
@@ -843,6 +852,16 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
     streams[k] = ctx->aux[k - 1];
   }
   if (!ctx->ev_fork) CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+  /* Shadow rays of depth i only feed k_accumulate(i), so they run on a stream of their own beside the extension rays of depth i + 1: two big
+   * persistent launches in flight, the second fills the SMs the first one's ragged end leaves idle (10 -> ~6 exposed tails per round).
+   * k_shade(i + 1) waits for k_accumulate(i): the order of every float addition is what it was, results are bit-identical. */
+  const bool overlap = ctx->opt[RRT_OPT_OVERLAP] != 0 && !escape_on(ctx) && rk.D >= 2 && rk.S > 0;
+  cudaStream_t sstreams[4] = {nullptr, nullptr, nullptr, nullptr};
+  for (int k = 0; k < NS; ++k) {
+    if (overlap && !ctx->shadow_stream[k]) CK(cudaStreamCreateWithFlags(&ctx->shadow_stream[k], cudaStreamNonBlocking));
+    sstreams[k] = overlap ? ctx->shadow_stream[k] : streams[k];
+  }
+  ctx->sync_used = 0;
   Queues qs[4]; memset(qs, 0, sizeof qs);
   ParkQ parks[4], reents[4];
   size_t off = 0;
@@ -912,7 +931,9 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
     const int nb = std::min(rk.batch, rk.ns_aa - base_sample);
     /* chunks of this round: as few as the buffers allow, but a multiple of NS of equal size once every chunk still fills the machine */
     size_t nchunks = (n_act + pix_per_chunk - 1) / pix_per_chunk;
-    const int ns_round = (NS > 1 && (size_t)n_act * nb >= (size_t)NS * 65536) ? NS : 1;
+    /* (a chunk below ~1 M paths leaves under 10 rays per resident lane: launches that small are mostly ragged end, and splitting them over streams makes
+     * them smaller still: C4 on 8 GPUs, 691 k paths per rank and round: 416 ms per frame in two chunks, 402 ms in one) */
+    const int ns_round = (NS > 1 && (size_t)n_act * nb >= (size_t)NS * ((size_t)1 << 20)) ? NS : 1;
     nchunks = (nchunks + ns_round - 1) / ns_round * ns_round;
     const size_t chunk_px = ((size_t)n_act + nchunks - 1) / nchunks;
     if (ns_round > 1) {
@@ -924,8 +945,9 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
       const int npx = (int)std::min(chunk_px, (size_t)n_act - c0);
       const uint32_t* chunk = act[a] + c0;
       const int si = (int)(ci % ns_round);
-      cudaStream_t cs = streams[si];
+      cudaStream_t cs = streams[si], ss = sstreams[si];
       const Queues& q = qs[si];
+      cudaEvent_t ev_acc = nullptr;   /* k_accumulate of the previous depth, on ss */
       CK(cudaMemsetAsync(q.ctl, 0, ctl_bytes, cs));
       k_generate<<<grid_small, 256, 0, cs>>>(ctx->cam, rk, q, chunk, npx, base_sample, nb);
       launches++;
@@ -936,6 +958,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
         launch_closest(ctx, count, grid_trace, cs, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt, esc ? &parks[si] : nullptr,
                        esc ? &reents[si] : nullptr);
         if (stats) { CK(cudaEventRecord(e1, cs)); trace_ev.push_back({e0, e1}); }
+        if (ev_acc) { CK(cudaStreamWaitEvent(cs, ev_acc, 0)); ev_acc = nullptr; }
         k_shade<<<grid_small, RRT_BLOCK, 0, cs>>>(ctx->ds, ctx->bh, rk, q, chunk, base_sample, nb, it);
         if (rk.split && rk.D >= 1 && rk.S > 0) {
           k_shade_direct<<<ctx->sm_count * 2 * RRT_DIRECT_MINB, 256, 0, cs>>>(ctx->ds, rk, q, chunk, base_sample, nb, it);
@@ -943,13 +966,15 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
         }
         launches += 2 + (esc ? 2 : 0); trace_launches++;
         if (rk.D >= 1 && rk.S > 0) {
-          if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, cs)); }
+          if (ss != cs) { cudaEvent_t ev = next_sync_event(ctx); CK(cudaEventRecord(ev, cs)); CK(cudaStreamWaitEvent(ss, ev, 0)); }
+          if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, ss)); }
           int* scount = q.ctl + q.ctl_stride + it; int* scursor = q.ctl + 3 * q.ctl_stride + it;
           const ParkQ* pkq = esc ? &parks[si] : nullptr; const ParkQ* req = esc ? &reents[si] : nullptr;
-          if (rk.hemi) launch_shadow<false>(ctx, count, grid_trace, cs, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt, pkq, req);
-          else launch_shadow<true>(ctx, count, grid_trace, cs, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt, pkq, req);
-          if (stats) { CK(cudaEventRecord(e1, cs)); trace_ev.push_back({e0, e1}); }
-          k_accumulate<<<grid_small, 256, 0, cs>>>(ctx->ds, rk, q, it);
+          if (rk.hemi) launch_shadow<false>(ctx, count, grid_trace, ss, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt, pkq, req);
+          else launch_shadow<true>(ctx, count, grid_trace, ss, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt, pkq, req);
+          if (stats) { CK(cudaEventRecord(e1, ss)); trace_ev.push_back({e0, e1}); }
+          k_accumulate<<<grid_small, 256, 0, ss>>>(ctx->ds, rk, q, it);
+          if (ss != cs) { ev_acc = next_sync_event(ctx); CK(cudaEventRecord(ev_acc, ss)); }
           launches += 2 + (esc ? 2 : 0); trace_launches++;
         }
         if (iters > 8 && it + 1 < iters && (it & 3) == 3) {  /* long depth budgets (-m 100): stop once every path has died */
@@ -958,6 +983,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
           if (ctx->h_pinned[0] == 0) break;
         }
       }
+      if (ev_acc) CK(cudaStreamWaitEvent(cs, ev_acc, 0));
       k_resolve<<<grid_small, 256, 0, cs>>>(rk, q, px, chunk, npx, nb);
       launches++;
     }

@@ -459,6 +459,10 @@ def test_c2_full_size_properties(api):
         assert all(ste[k] == st[k] for k in ("rays", "geodesic_steps", "tri_tests", "sphere_tests", "paths"))
     except api.RrtError as e:
         assert "A/B builds" in str(e)
+    c.set_option(api.OPT_OVERLAP, 0)          # shadow rays of depth i no longer beside the extension rays of depth i + 1
+    ho, co, sto = c.render(p)
+    c.set_option(api.OPT_OVERLAP, 1)
+    assert np.array_equal(hdr, ho) and np.array_equal(cnt, co) and sto["rays"] == st["rays"]
     # the round's chunks dealt over 1, 3 or 4 streams instead of 2: not a bit may change
     for ns in (1, 3, 4):
         c.set_option(api.OPT_STREAMS, ns)
@@ -563,7 +567,7 @@ def test_empty_and_degenerate_inputs(api):
             c.set_blackhole((0, 1, 0), bad_r, 0.1, sc.MODE_LITERAL)
     c.set_blackhole((0, 1, 0), 0.0, 0.1, sc.MODE_LITERAL)      # r = 0 is legal (the reference's -B 0 1 0 0 0.1)
     with pytest.raises(api.RrtError, match="unknown option"):
-        c.set_option(13, 1)
+        c.set_option(14, 1)
     with pytest.raises(api.RrtError, match="positive height"):
         c.set_cell(0, 0, 16, 0)
     c.set_cell(0, 0, 0, 0)

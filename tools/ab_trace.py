@@ -10,7 +10,7 @@ import bench
 from util import sc
 api = importlib.import_module("relativistic-ray-tracer_b200.api")
 OPT = dict(kernel=api.OPT_TRACE_KERNEL, grid=api.OPT_CLEARANCE_GRID, width=api.OPT_BVH_WIDTH, builder=api.OPT_BVH_BUILDER, leaf=api.OPT_LEAF_SIZE,
-           topology=api.OPT_BVH_TOPOLOGY, stepper=api.OPT_STEPPER, streams=api.OPT_STREAMS, escape=api.OPT_ESCAPE, top=api.OPT_TOP_NODE)
+           topology=api.OPT_BVH_TOPOLOGY, stepper=api.OPT_STEPPER, streams=api.OPT_STREAMS, escape=api.OPT_ESCAPE, top=api.OPT_TOP_NODE, overlap=api.OPT_OVERLAP)
 sets = []
 for part in (sys.argv[2] if len(sys.argv) > 2 else "default:").split(";"):
     name, _, kv = part.partition(":")
