@@ -14,6 +14,7 @@
 #include <string.h>
 
 #include <string>
+#include <thread>
 
 #include "rrt_host.h"
 
@@ -45,6 +46,7 @@ static void usage(const char* binary) {
 }
 
 int main(int argc, char** argv) {
+  rrt_host_tick("main");
   size_t ns_aa = 1, max_ray_depth = 1, ns_area_light = 1, num_threads = 1, samples_per_batch = 32;
   float max_tolerance = 0.05f;
   bool hemisphere = false, write_to_file = false, flat = false;
@@ -118,6 +120,17 @@ int main(int argc, char** argv) {
   std::string scene_file = scene_path.substr(scene_path.find_last_of('/') + 1);
   scene_file = scene_file.substr(0, scene_file.find(".dae"));
 
+  // The first CUDA call of a process (driver initialisation + primary context) takes 1.2 - 2.5 s on a B200 box — 20x everything else a C2 frame
+  // needs (profiles/r02_j_cli_timing.txt) — and needs nothing from the scene: it runs on a thread of its own while the .dae is parsed and flattened.
+  rrt_ctx* warm_ctx = nullptr; std::string warm_err;
+  std::thread warm;
+  if (dump_scene.empty())
+    warm = std::thread([&]() {
+      const int rc = devices.size() > 1 ? rrt_create_multi(&warm_ctx, (int)devices.size(), devices.data()) : rrt_create(&warm_ctx, device);
+      if (rc != RRT_OK) { warm_err = rrt_last_error(nullptr); warm_ctx = nullptr; }
+      rrt_host_tick("context ready (warm-up thread)");
+    });
+  struct Joiner { std::thread& t; ~Joiner() { if (t.joinable()) t.join(); } } joiner{warm};
   FlatScene scene; Camera camera; std::string err;
   bool is_dae = scene_path.size() >= 4 && scene_path.compare(scene_path.size() - 4, 4, ".dae") == 0;
   bool ok = is_dae ? load_dae(scene_path, &scene, &camera, &err) : load_rrtscene(scene_path, &scene, &camera, &err);
@@ -136,9 +149,13 @@ int main(int argc, char** argv) {
     return 0;
   }
 
+  rrt_host_tick("scene file loaded and flattened");
   PathTracer pt(ns_aa, max_ray_depth, ns_area_light, 1, 1, 1, num_threads, samples_per_batch, max_tolerance, nullptr, hemisphere,
                 scene_file, lens_radius, focal_distance);
+  if (warm.joinable()) warm.join();
+  if (!warm_ctx && !warm_err.empty()) { fprintf(stderr, "[PathTracer] %s\n", warm_err.c_str()); return 3; }
   pt.set_device(device); if (devices.size() > 1) pt.set_devices(devices);
+  pt.adopt_context(warm_ctx);
   pt.set_seed(seed); pt.set_blackhole(bh_c, bh_r, bh_dtheta, flat);
   pt.set_option(RRT_OPT_STEPPER, stepper_fp32 ? 1 : 0); pt.set_option(RRT_OPT_BVH_BUILDER, bvh_builder);
   if (!envmap_path.empty()) {
@@ -152,6 +169,7 @@ int main(int argc, char** argv) {
   pt.set_frame_size(camera.screenW, camera.screenH);
   if (!pt.error().empty()) { fprintf(stderr, "[PathTracer] %s\n", pt.error().c_str()); return 3; }
   pt.render_to_file(write_to_file ? filename : std::string(""), x, y, dx, dy);
+  rrt_host_tick("render_to_file returned (PNG written)");
   if (!pt.error().empty()) { fprintf(stderr, "[PathTracer] %s\n", pt.error().c_str()); return 3; }
   return 0;
 }

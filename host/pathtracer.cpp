@@ -87,18 +87,31 @@ PathTracer::PathTracer(size_t ns_aa, size_t max_ray_depth, size_t ns_area_light,
   (void)envmap;   /* the pixels come through set_envmap: an opaque HDRImageBuffer* cannot cross this boundary */
 }
 
+void rrt_host_tick(const char* what) {
+  static const bool on = getenv("RRT_HOST_TIMING") != nullptr;
+  static struct timespec t0; static bool have = false;
+  if (!on) return;
+  struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t);
+  if (!have) { t0 = t; have = true; }
+  fprintf(stderr, "[timing] %8.1f ms  %s\n", 1e3 * (t.tv_sec - t0.tv_sec) + 1e-6 * (t.tv_nsec - t0.tv_nsec), what);
+}
+
 PathTracer::~PathTracer() {
+  rrt_host_tick("~PathTracer: before rrt_destroy");
   if (thread_.joinable()) thread_.join();
   if (ctx_) rrt_destroy(ctx_);
+  rrt_host_tick("~PathTracer: after rrt_destroy");
 }
 
 bool PathTracer::has_valid_configuration() const { return have_scene_ && camera_ && W_ && H_; }
 
 void PathTracer::set_scene(const FlatScene* scene) {
   if (state_ != INIT) return;
+  rrt_host_tick("set_scene: before rrt_create");
   if (!ctx_ && (devices_.size() > 1 ? rrt_create_multi(&ctx_, (int)devices_.size(), devices_.data()) : rrt_create(&ctx_, device_)) != RRT_OK) {
     error_ = rrt_last_error(nullptr); ctx_ = nullptr; return;
   }
+  rrt_host_tick("set_scene: context created");
   for (const auto& o : options_) if (rrt_set_option(ctx_, o.first, o.second) != RRT_OK) { error_ = rrt_last_error(ctx_); return; }
   fprintf(stdout, "[PathTracer] Collecting primitives... Done! (%.4f sec)\n", 0.0);
   fprintf(stdout, "[PathTracer] Building BVH from %lu primitives... ", (unsigned long)scene->n_prims()); fflush(stdout);
@@ -112,6 +125,7 @@ void PathTracer::set_scene(const FlatScene* scene) {
     if (rrt_set_envmap(ctx_, env_w_, env_h_, env_.data()) != RRT_OK) { error_ = rrt_last_error(ctx_); fprintf(stdout, "failed: %s\n", error_.c_str()); return; }
     fprintf(stdout, "done.\n");
   }
+  rrt_host_tick("set_scene: scene uploaded, BVH built");
   have_scene_ = true; n_prims_ = scene->n_prims();
   if (has_valid_configuration()) state_ = READY;
 }
@@ -163,7 +177,9 @@ void PathTracer::worker() {
   snap_calls_ = 0; snaps_written_ = 0;
   // progressive output and stop() work between adaptive batches of ONE GPU; a multi-GPU context renders its tiles independently
   if (!multi && rrt_set_progress(ctx_, &PathTracer::progress_trampoline, this) != RRT_OK) return finish("rrt_set_progress");
+  rrt_host_tick("worker: before rrt_render");
   if (rrt_render(ctx_, &p, hdr_.data(), counts_.data(), &stats_) != RRT_OK) return finish("rrt_render");
+  rrt_host_tick("worker: rrt_render returned");
   if (rrt_tonemap(ctx_, (int64_t)(W_ * H_), hdr_.data(), frame_.data()) != RRT_OK) return finish("rrt_tonemap");
   finish(nullptr);
 }

@@ -126,6 +126,9 @@ class BVHAccel {
   Vector3D lo_, hi_;
 };
 
+// RRT_HOST_TIMING=1: wall-clock milestones of a run on stderr (tools/cli_timing.sh)
+void rrt_host_tick(const char* what);
+
 class PathTracer {
  public:
   enum State { INIT, READY, RENDERING, DONE };
@@ -147,6 +150,8 @@ class PathTracer {
   // rrt_set_option pass-through (RRT_OPT_*: stepper, BVH builder, A/B variants); applied before the next set_scene
   void set_option(int option, int64_t value) { options_.push_back({option, value}); }
   void set_device(int device) { device_ = device; devices_.clear(); }
+  // hand over a context created elsewhere (host/main.cpp creates it on a thread while the scene file is parsed); owned from here on
+  void adopt_context(rrt_ctx* ctx) { if (!ctx_) ctx_ = ctx; }
   // several GPUs of this box (rrt_create_multi): the reference's N worker threads become N GPUs, tiles interleaved, one NCCL reduce per frame
   void set_devices(const std::vector<int>& devices) { devices_ = devices; if (!devices.empty()) device_ = devices[0]; }
   void set_tile_shard(int tile, int rank, int world) { tile_ = tile; rank_ = rank; world_ = world; }

@@ -837,6 +837,11 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   want = std::min(want, std::max<size_t>(budget / per_path / (size_t)std::min<int64_t>(std::max<int64_t>(ctx->opt[RRT_OPT_STREAMS], 1), 4), 1024));
   size_t pix_per_chunk = std::max<size_t>(want / nb_max, 1);
   pix_per_chunk = std::min(pix_per_chunk, npix);
+  /* buffers follow the frame, not a fixed budget: when rounds are split over NS streams no chunk is larger than a stream's share (or the
+   * 1 M-path threshold below which a round stays whole), and a frame too small to ever be split gets ONE set of queues */
+  const int NS_opt = (int)std::min<int64_t>(std::max<int64_t>(ctx->opt[RRT_OPT_STREAMS], 1), 4);
+  const bool ever_split = NS_opt > 1 && npix * (size_t)nb_max >= (size_t)NS_opt * ((size_t)1 << 20);
+  if (ever_split) pix_per_chunk = std::min(pix_per_chunk, std::max((npix + NS_opt - 1) / NS_opt, (((size_t)NS_opt << 20) + nb_max - 1) / nb_max));
   const size_t cap = pix_per_chunk * nb_max, capS = cap * S;
   if (capS >= ((size_t)1 << 31)) FAIL(RRT_E_ARG, "rrt_render: max_paths_in_flight x light samples exceeds 2^31");
   rk.cap = (int)cap;
@@ -845,7 +850,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
    * NS streams, each with its own queues: a trace launch ends ragged — rays need 1 to 63 chords, and the last ones keep a few lanes alive —
    * and the other stream's kernels fill the SMs that tail leaves idle.  Matters most where launches are small: strong scaling (C4 on 8 GPUs:
    * 20 k pixels per rank and round).  RRT_OPT_STREAMS (1..4, default 2); results are bit-identical for any value. */
-  const int NS = (int)std::min<int64_t>(std::max<int64_t>(ctx->opt[RRT_OPT_STREAMS], 1), 4);
+  const int NS = ever_split ? NS_opt : 1;
   cudaStream_t streams[4] = {st, nullptr, nullptr, nullptr};
   for (int k = 1; k < NS; ++k) {
     if (!ctx->aux[k - 1]) { CK(cudaStreamCreateWithFlags(&ctx->aux[k - 1], cudaStreamNonBlocking)); CK(cudaEventCreateWithFlags(&ctx->ev_join[k - 1], cudaEventDisableTiming)); }
