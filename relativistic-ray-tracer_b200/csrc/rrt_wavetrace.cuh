@@ -23,13 +23,17 @@
                          8 GPUs 513 -> 477 ms per frame (small launches: 3 rays per lane), single GPU bunny 207.1 -> 204.5, C2 33.5 -> 32.5, C5 53.9 -> 51.4 */
 #endif
 #ifndef RRT_MINB
-#define RRT_MINB 6     /* resident blocks per SM the trace kernels are compiled for */
+#define RRT_MINB 7     /* resident blocks per SM the binary-node trace kernels are compiled for (72 registers).  6 until the chord moved to shared
+                          memory (RRT_SEG_SMEM) and the tree-top record brought spills back at 80 registers: 6 -> 7 with the chord in shared memory:
+                          bunny in-box 174.4 -> 171.5 ms, C5 50.8 -> 50.0, bunny 1080p 77.8 -> 77.1 (profiles/r02_k_ab_smem_minb.jsonl) */
 #endif
 #ifndef RRT_COOP_LEAVES
 #define RRT_COOP_LEAVES 0   /* 1 = any-hit leaf tests deferred and shared across the warp (rrt_trace.cuh coop_*): measured SLOWER, C2 41.4 vs 37.1 ms */
 #endif
 #ifndef RRT_SEG_SMEM
-#define RRT_SEG_SMEM 0   /* A/B: 1 = the current chord (o, d, len) of the hole-on FP64 loop is kept in shared memory between steps */
+#define RRT_SEG_SMEM 1   /* the current chord (o, d, len) of the hole-on FP64 loop lives in shared memory between steps (7 KB per block): it is read by the
+                            stepper, the box context and the leaf tests only, and holds no registers while nodes are visited.  Alone (6 blocks per SM) it
+                            changes nothing; it is what lets a 7th block in without spills in the shadow kernel (RRT_MINB) */
 #endif
 #ifndef RRT_MINB_FP32
 #define RRT_MINB_FP32 5   /* resident blocks per SM for the FP32-stepper variants (STEP = 1): 4 / 5 / 6 / 7 / 8 measured, see DESIGN.md 6.2 */

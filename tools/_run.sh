@@ -1,15 +1,5 @@
-python -m pytest tests/test_host_gpu.py tests/test_multi_gpu.py -x -q -m gpu 2>&1 | tail -2
-python - <<'PY'
-import importlib,os,sys
-sys.path.insert(0,"."); sys.path.insert(0,"tests")
-synth = importlib.import_module("relativistic-ray-tracer_b200.synth")
-os.makedirs("/tmp/x",exist_ok=True)
-synth.write_c5_dae("/tmp/x/c5.dae", open("oracle/_ref/dae/CBspheres_lambertian.dae").read())
-PY
-S=tests/golden/cbspheres_lambertian_480x360.rrtscene
-{
-for i in 1 2; do s=$(date +%s%N); RRT_HOST_TIMING=1 host/pathtracer -s 16 -l 4 -m 5 -r 480 360 -f gpurun_out/cli_c2.png $S 2>&1 | grep "timing"; e=$(date +%s%N); echo "$(( (e - s) / 1000000 )) ms wall: C2 command line"; done
-for i in 1 2; do s=$(date +%s%N); RRT_HOST_TIMING=1 host/pathtracer -s 4 -l 4 -m 5 -r 3840 2160 -f gpurun_out/cli_c5.png /tmp/x/c5.dae 2>&1 | grep "timing"; e=$(date +%s%N); echo "$(( (e - s) / 1000000 )) ms wall: C5 .dae (52 MB, 1 M triangles) at 4K / 4 spp"; done
-} > gpurun_out/cli_timing2.txt 2>&1
-cat gpurun_out/cli_timing2.txt
-rm -f gpurun_out/cli_c5.png gpurun_out/cli_c5_rate.png
+python -m pytest tests -x -q -m gpu > gpurun_out/t_gpu12.log 2>&1; echo "gpu rc=$?"; tail -2 gpurun_out/t_gpu12.log
+python tools/ab_trace.py c2,bunny_box,c3@32,c1 "default:" > gpurun_out/ab11.jsonl 2>&1
+grep -o '"workload": "[a-z0-9_]*"\|"ms": [0-9.]*\|"trace_ms": [0-9.]*' gpurun_out/ab11.jsonl | paste -sd' ' | sed 's/"workload"/\n"workload"/g'
+python bench.py --steps 3 --warmup 2 --no-cpu-baseline > gpurun_out/b9_c4.json 2> gpurun_out/b9_c4.err; python -c "
+import json; j=json.loads(open('gpurun_out/b9_c4.json').read().strip().splitlines()[-1]); print('c4', j['value'], j['ms_per_step'], j['roofline']['frac'], j['e2e']['value'])"
