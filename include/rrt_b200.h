@@ -181,8 +181,9 @@ enum {
                                  and carried on by a lean kernel (stepper + horizon + root-box test only); measured slower, default 0.  Bit-identical results */
   RRT_OPT_TOP_NODE = 12,      /* binary trees: 1 (default) = the top of the tree is also kept as ONE 8-wide record (groupings of large primitives opened into
                                  their flat boxes + the root of the rest) that every traversal tests first; 0 = start at the binary root.  Same results; next rrt_upload_scene */
-  RRT_OPT_OVERLAP = 13,       /* 1 (default) = the shadow rays of depth i are traced on their own stream beside the extension rays of depth i + 1 (they only feed
-                                 k_accumulate(i); k_shade(i + 1) waits for it, so every addition keeps its order); 0 = one kernel at a time per chunk.  Bit-identical */
+  RRT_OPT_OVERLAP = 13,       /* 1 (default) = the shadow rays of depth i are traced on their own stream beside the extension rays of depths i + 1 and i + 2 (they only feed
+                                 k_accumulate(i), which makes every addition into a path's radiance, in vertex order; the shadow side of the queues is double-buffered and
+                                 k_shade(i + 2) waits for k_accumulate(i)); 0 = one kernel at a time per chunk.  Bit-identical */
   RRT_OPT_BVH_BUILDER = 9     /* where the BVH is built.  1 = on the device: the reference's depth-first ranks by level-synchronous stable partition
                                  + an LBVH for the traversal (scenes of >= 64 primitives, binary nodes; falls back to the host if the tree comes
                                  out deeper than the traversal stack); 2 = on the host (reference tree shape or binned SAH, threaded);

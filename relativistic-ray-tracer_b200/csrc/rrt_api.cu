@@ -818,6 +818,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   if (rk.D == 0) rk.S = 0;
   /* 2 = choose: the per-sample kernel pays when evaluating the BSDF is expensive (microfacet: C3 34.2 -> 26.6 ms per
    * 32 spp) and costs a little when it is not (diffuse C1: 4.43 -> 4.74 ms), DESIGN.md section 4.4 */
+  rk.defer_emit = (rk.D >= 1 && rk.S > 0) ? 1 : 0;   /* k_accumulate runs for every vertex index */
   rk.split = ctx->opt[RRT_OPT_SHADE_SPLIT] == 2 ? (ctx->has_microfacet ? 1 : 0) : (ctx->opt[RRT_OPT_SHADE_SPLIT] != 0);
   rk.direct_draws = 0;
   if (rk.hemi) rk.direct_draws = 2 * rk.S;
@@ -831,7 +832,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   const int iters = std::max(rk.D, 1);
 
   /* ---- work buffers: capacity from the in-flight budget */
-  const size_t per_path = 2 * (8 * 8 + 4 + 4 + 4 + 12) + 4 + 72 + 12 + 1 + 12 + (size_t)S * (56 + 4 + 4 + 16) + (escape_on(ctx) ? (size_t)S * 128 : 0);
+  const size_t per_path = 2 * (8 * 8 + 4 + 4 + 4 + 12) + 4 + 72 + 12 + 2 * (12 + 1 + 12 + 4) + 2 * (size_t)S * (56 + 4 + 4 + 16) + (escape_on(ctx) ? (size_t)S * 128 : 0);
   size_t want = p->max_paths_in_flight > 0 ? (size_t)p->max_paths_in_flight : (size_t)4 << 20;
   size_t budget = (size_t)(ctx->opt[RRT_OPT_WORK_BYTES] > 0 ? ctx->opt[RRT_OPT_WORK_BYTES] : (int64_t)12 << 30);
   want = std::min(want, std::max<size_t>(budget / per_path / (size_t)std::min<int64_t>(std::max<int64_t>(ctx->opt[RRT_OPT_STREAMS], 1), 4), 1024));
@@ -857,9 +858,12 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
     streams[k] = ctx->aux[k - 1];
   }
   if (!ctx->ev_fork) CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
-  /* Shadow rays of depth i only feed k_accumulate(i), so they run on a stream of their own beside the extension rays of depth i + 1: two big
-   * persistent launches in flight, the second fills the SMs the first one's ragged end leaves idle (10 -> ~6 exposed tails per round).
-   * k_shade(i + 1) waits for k_accumulate(i): the order of every float addition is what it was, results are bit-identical. */
+  /* Shadow rays of depth i only feed k_accumulate(i), so they run on a stream of their own beside the extension rays of the NEXT TWO depths: the
+   * shadow side of the queues (rays, contribution table, verdicts, the vertex's throughput / slot / emission term) exists once per parity of the
+   * vertex index, so k_shade(i + 1) and k_shade_direct(i + 1) fill the other set while shadow(i) and k_accumulate(i) still read theirs, and
+   * k_shade(i + 2) waits for k_accumulate(i).  Two or three big persistent launches are in flight and fill the SMs each other's ragged ends leave
+   * idle.  Every addition into a path's radiance is made by k_accumulate, in vertex order, on one stream (k_shade hands the emission term of a
+   * vertex reached through a delta BSDF over instead of adding it): the order of every float addition is what it was, results are bit-identical. */
   const bool overlap = ctx->opt[RRT_OPT_OVERLAP] != 0 && !escape_on(ctx) && rk.D >= 2 && rk.S > 0;
   cudaStream_t sstreams[4] = {nullptr, nullptr, nullptr, nullptr};
   for (int k = 0; k < NS; ++k) {
@@ -873,8 +877,12 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   auto carve = [&](size_t bytes) { size_t o = off; off += align_up(bytes); return o; };
   size_t o_ray[2], o_slot[2], o_rngn[2], o_flags[2], o_beta[2];
   for (int b = 0; b < 2; ++b) { o_ray[b] = carve(64 * cap); o_slot[b] = carve(4 * cap); o_rngn[b] = carve(4 * cap); o_flags[b] = carve(4 * cap); o_beta[b] = carve(12 * cap); }
-  size_t o_hprim = carve(4 * cap), o_hgeo = carve(72 * cap), o_dbeta = carve(12 * cap), o_vflag = carve(cap), o_sray = carve(56 * capS),
-         o_scidx = carve(4 * capS), o_sres = carve(4 * capS), o_scon = carve(16 * capS), o_L = carve(12 * cap);
+  size_t o_hprim = carve(4 * cap), o_hgeo = carve(72 * cap), o_L = carve(12 * cap);
+  size_t o_dbeta[2], o_vflag[2], o_emit[2], o_aslot[2], o_sray[2], o_scidx[2], o_sres[2], o_scon[2];   /* shadow side: one set per parity of the vertex index */
+  for (int b = 0; b < 2; ++b) {
+    o_dbeta[b] = carve(12 * cap); o_vflag[b] = carve(cap); o_emit[b] = carve(12 * cap); o_aslot[b] = carve(4 * cap);
+    o_sray[b] = carve(56 * capS); o_scidx[b] = carve(4 * capS); o_sres[b] = carve(4 * capS); o_scon[b] = carve(16 * capS);
+  }
   const int ctl_stride = iters + 2;
   size_t o_ctl = carve(4 * 4 * (size_t)ctl_stride);
   const bool esc = escape_on(ctx);
@@ -890,8 +898,11 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
       q.ray[b] = (double*)(wb + o_ray[b]); q.slot[b] = (uint32_t*)(wb + o_slot[b]); q.rngn[b] = (uint32_t*)(wb + o_rngn[b]);
       q.flags[b] = (uint32_t*)(wb + o_flags[b]); q.beta[b] = (float*)(wb + o_beta[b]);
     }
-    q.h_prim = (int*)(wb + o_hprim); q.h_geo = (double*)(wb + o_hgeo); q.dbeta = (float*)(wb + o_dbeta); q.vflag = (uint8_t*)(wb + o_vflag);
-    q.sray = (double*)(wb + o_sray); q.s_cidx = (uint32_t*)(wb + o_scidx); q.s_res = (int*)(wb + o_sres); q.s_contrib = (float4*)(wb + o_scon);
+    q.h_prim = (int*)(wb + o_hprim); q.h_geo = (double*)(wb + o_hgeo);
+    for (int b = 0; b < 2; ++b) {
+      q.dbeta[b] = (float*)(wb + o_dbeta[b]); q.vflag[b] = (uint8_t*)(wb + o_vflag[b]); q.emit[b] = (float*)(wb + o_emit[b]); q.aslot[b] = (uint32_t*)(wb + o_aslot[b]);
+      q.sray[b] = (double*)(wb + o_sray[b]); q.s_cidx[b] = (uint32_t*)(wb + o_scidx[b]); q.s_res[b] = (int*)(wb + o_sres[b]); q.s_contrib[b] = (float4*)(wb + o_scon[b]);
+    }
     q.Lsample = (float*)(wb + o_L); q.ctl = (int*)(wb + o_ctl);
     if (esc) park_carve(wb + o_park, cap_park, &parks[k], &reents[k]);
   }
@@ -952,7 +963,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
       const int si = (int)(ci % ns_round);
       cudaStream_t cs = streams[si], ss = sstreams[si];
       const Queues& q = qs[si];
-      cudaEvent_t ev_acc = nullptr;   /* k_accumulate of the previous depth, on ss */
+      cudaEvent_t ev_acc[2] = {nullptr, nullptr};   /* k_accumulate(it - 1), k_accumulate(it - 2) on ss: the latter frees the shadow-side buffers k_shade(it) fills */
       CK(cudaMemsetAsync(q.ctl, 0, ctl_bytes, cs));
       k_generate<<<grid_small, 256, 0, cs>>>(ctx->cam, rk, q, chunk, npx, base_sample, nb);
       launches++;
@@ -963,7 +974,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
         launch_closest(ctx, count, grid_trace, cs, q.ray[cur], cap, q.ctl + it, q.ctl + 2 * q.ctl_stride + it, q.h_prim, q.h_geo, gcnt, esc ? &parks[si] : nullptr,
                        esc ? &reents[si] : nullptr);
         if (stats) { CK(cudaEventRecord(e1, cs)); trace_ev.push_back({e0, e1}); }
-        if (ev_acc) { CK(cudaStreamWaitEvent(cs, ev_acc, 0)); ev_acc = nullptr; }
+        if (ev_acc[1]) { CK(cudaStreamWaitEvent(cs, ev_acc[1], 0)); ev_acc[1] = nullptr; }
         k_shade<<<grid_small, RRT_BLOCK, 0, cs>>>(ctx->ds, ctx->bh, rk, q, chunk, base_sample, nb, it);
         if (rk.split && rk.D >= 1 && rk.S > 0) {
           k_shade_direct<<<ctx->sm_count * 2 * RRT_DIRECT_MINB, 256, 0, cs>>>(ctx->ds, rk, q, chunk, base_sample, nb, it);
@@ -975,11 +986,13 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
           if (stats) { e0 = next_event(ctx); e1 = next_event(ctx); CK(cudaEventRecord(e0, ss)); }
           int* scount = q.ctl + q.ctl_stride + it; int* scursor = q.ctl + 3 * q.ctl_stride + it;
           const ParkQ* pkq = esc ? &parks[si] : nullptr; const ParkQ* req = esc ? &reents[si] : nullptr;
-          if (rk.hemi) launch_shadow<false>(ctx, count, grid_trace, ss, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt, pkq, req);
-          else launch_shadow<true>(ctx, count, grid_trace, ss, q.sray, capS, scount, scursor, q.s_cidx, q.s_res, gcnt, pkq, req);
+          const int sp = it & 1;
+          if (rk.hemi) launch_shadow<false>(ctx, count, grid_trace, ss, q.sray[sp], capS, scount, scursor, q.s_cidx[sp], q.s_res[sp], gcnt, pkq, req);
+          else launch_shadow<true>(ctx, count, grid_trace, ss, q.sray[sp], capS, scount, scursor, q.s_cidx[sp], q.s_res[sp], gcnt, pkq, req);
           if (stats) { CK(cudaEventRecord(e1, ss)); trace_ev.push_back({e0, e1}); }
           k_accumulate<<<grid_small, 256, 0, ss>>>(ctx->ds, rk, q, it);
-          if (ss != cs) { ev_acc = next_sync_event(ctx); CK(cudaEventRecord(ev_acc, ss)); }
+          ev_acc[1] = ev_acc[0];
+          if (ss != cs) { ev_acc[0] = next_sync_event(ctx); CK(cudaEventRecord(ev_acc[0], ss)); }
           launches += 2 + (esc ? 2 : 0); trace_launches++;
         }
         if (iters > 8 && it + 1 < iters && (it & 3) == 3) {  /* long depth budgets (-m 100): stop once every path has died */
@@ -988,7 +1001,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
           if (ctx->h_pinned[0] == 0) break;
         }
       }
-      if (ev_acc) CK(cudaStreamWaitEvent(cs, ev_acc, 0));
+      if (ev_acc[0]) CK(cudaStreamWaitEvent(cs, ev_acc[0], 0));   /* stream order on ss: every earlier k_accumulate is done too */
       k_resolve<<<grid_small, 256, 0, cs>>>(rk, q, px, chunk, npx, nb);
       launches++;
     }

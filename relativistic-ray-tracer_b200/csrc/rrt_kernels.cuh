@@ -21,6 +21,8 @@ struct RenderK {      // per-render constants (reference PathTracer members, src
   int cap;            // queue capacity = SoA stride
   int direct_draws;   // uniforms one direct-lighting estimate consumes (fixed per scene: 2 per sample of an area / hemisphere / environment light)
   int split;          // 1: direct lighting in k_shade_direct (one thread per light sample), k_shade does emission + bounce only
+  int defer_emit;     // 1: k_accumulate runs for every vertex index (D >= 1 and S > 0), so the emission term of a vertex reached through a delta BSDF is
+                      //    handed to it (Queues::emit) instead of being added by k_shade: k_shade(it + 1) then touches nothing k_accumulate(it) touches
 };
 
 struct Queues {
@@ -31,12 +33,16 @@ struct Queues {
   float* beta[2];       // 3 x cap: throughput
   int* h_prim;          // closest-hit result per queue position: prim >= 0, -1 miss, -2 captured
   double* h_geo;        // 9 x cap: hit_p, w_out, n
-  float* dbeta;         // 3 x cap: throughput at the vertex whose direct light is pending
-  uint8_t* vflag;       // bit0: vertex took light samples
-  double* sray;         // 7 x capS: shadow rays o d tmax
-  uint32_t* s_cidx;     // contribution-table index of each shadow ray
-  int* s_res;           // capS: -2 no ray, -1 unoccluded, >= 0 prim hit
-  float4* s_contrib;    // capS: contribution (rgb), w = cos term (hemisphere mode)
+  /* shadow side, double-buffered by the parity of the vertex index `it`: the shadow rays of vertex it are traced (and folded by k_accumulate(it)) on
+   * their own stream while k_shade / k_shade_direct already fill the buffers of vertex it + 1 (rrt_api.cu, RRT_OPT_OVERLAP) */
+  float* dbeta[2];      // 3 x cap: throughput at the vertex whose direct light is pending
+  uint8_t* vflag[2];    // bit0: vertex took light samples; bit1: an emission term waits in `emit` (previous vertex was a delta BSDF)
+  float* emit[2];       // 3 x cap: Le * throughput of such a vertex, added by k_accumulate BEFORE the vertex's direct light (the reference's order)
+  uint32_t* aslot[2];   // path slot of the vertex, for k_accumulate
+  double* sray[2];      // 7 x capS: shadow rays o d tmax
+  uint32_t* s_cidx[2];  // contribution-table index of each shadow ray
+  int* s_res[2];        // capS: -2 no ray, -1 unoccluded, >= 0 prim hit
+  float4* s_contrib[2]; // capS: contribution (rgb), w = cos term (hemisphere mode)
   float* Lsample;       // 3 x cap: radiance of each path slot
   int* ctl;             // [4][D+2]: queue counts, shadow counts, trace cursors, shadow cursors
   int ctl_stride;
@@ -116,20 +122,23 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_SHADE_MINB) k_shade(const __gri
                                                      const __grid_constant__ RenderK rk, const __grid_constant__ Queues q,
                                                      const uint32_t* __restrict__ act, int base_sample, int nb, int it) {
   const int cur = it & 1, nxt = cur ^ 1;
+  const int sp = it & 1;            /* parity of the shadow-side buffers */
   const size_t cap = (size_t)rk.cap;
   const int count = q.ctl[it];
   int* next_count = q.ctl + (it + 1);
   int* sh_count = q.ctl + q.ctl_stride + it;
+  uint8_t* const vflag = q.vflag[sp]; float* const dbeta = q.dbeta[sp];
+  double* const sray = q.sray[sp]; uint32_t* const s_cidx = q.s_cidx[sp]; int* const s_res = q.s_res[sp]; float4* const s_contrib = q.s_contrib[sp];
   const int nwarps = (gridDim.x * blockDim.x) >> 5, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   for (int base = warp * 32; base < count; base += nwarps * 32) {
     const int i = base + lane_id();
     bool ext = false;
+    uint8_t vf_out = 0;
     d3 eo = D3(0, 0, 0), ed = D3(0, 0, 0);
     f3 ebeta = F3(0, 0, 0);
     uint32_t slot = 0, en = 0, eflags = 0;
     if (i < count) {
       const int prim = q.h_prim[i];
-      q.vflag[i] = 0;
       if (prim < 0 && it == 0 && sc.env) {
         /* camera ray that hit nothing (or fell into the hole): the environment seen along its own, unbent direction
          * (reference src/part1_code.cpp:106-107) */
@@ -147,8 +156,10 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_SHADE_MINB) k_shade(const __gri
         if (it == 0) { q.Lsample[slot] = Le.r; q.Lsample[cap + slot] = Le.g; q.Lsample[2 * cap + slot] = Le.b; }
         else if (flags & 1u) {
           f3 a = s_mul(Le, beta);
-          q.Lsample[slot] += a.r; q.Lsample[cap + slot] += a.g; q.Lsample[2 * cap + slot] += a.b;
+          if (rk.defer_emit) { vf_out |= 2; q.emit[sp][i] = a.r; q.emit[sp][cap + i] = a.g; q.emit[sp][2 * cap + i] = a.b; }
+          else { q.Lsample[slot] += a.r; q.Lsample[cap + slot] += a.g; q.Lsample[2 * cap + slot] += a.b; }
         }
+        q.aslot[sp][i] = slot;
         if (rk.D >= 1) {
           const uint32_t pixel = act[slot / (uint32_t)nb];
           Rng g = rng_make(rk.seed, pixel, (uint32_t)(base_sample + slot % (uint32_t)nb), q.rngn[cur][i]);
@@ -160,8 +171,8 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_SHADE_MINB) k_shade(const __gri
           const bool delta = mat_is_delta(m);
           if (rk.D == 1 || !delta) {
             /* one_bounce_radiance: light samples -> shadow queue, contributions -> table row i */
-            q.vflag[i] = 1;
-            q.dbeta[i] = beta.r; q.dbeta[cap + i] = beta.g; q.dbeta[2 * cap + i] = beta.b;
+            vf_out |= 1;
+            dbeta[i] = beta.r; dbeta[cap + i] = beta.g; dbeta[2 * cap + i] = beta.b;
             int k = 0;
             if (rk.split) {
               g.n += (uint32_t)rk.direct_draws;   /* k_shade_direct takes these draws, one thread per sample */
@@ -172,15 +183,15 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_SHADE_MINB) k_shade(const __gri
                 d3 wi_world = mat_mul(o2w, w_in);
                 f3 f = bsdf_f(m, w_out, w_in);
                 const size_t ci = (size_t)i * rk.S + k;
-                q.s_contrib[ci] = make_float4(f.r, f.g, f.b, (float)w_in.z);
-                q.s_res[ci] = -1;
+                s_contrib[ci] = make_float4(f.r, f.g, f.b, (float)w_in.z);
+                s_res[ci] = -1;
                 int pos = append_pos(sh_count);
                 const size_t cs = cap * (size_t)rk.S;
                 d3 so = vadd(hit_p, smul(RRT_EPS_D, wi_world));
-                q.sray[pos] = so.x; q.sray[cs + pos] = so.y; q.sray[2 * cs + pos] = so.z;
-                q.sray[3 * cs + pos] = wi_world.x; q.sray[4 * cs + pos] = wi_world.y; q.sray[5 * cs + pos] = wi_world.z;
-                q.sray[6 * cs + pos] = INFINITY;
-                q.s_cidx[pos] = (uint32_t)ci;
+                sray[pos] = so.x; sray[cs + pos] = so.y; sray[2 * cs + pos] = so.z;
+                sray[3 * cs + pos] = wi_world.x; sray[4 * cs + pos] = wi_world.y; sray[5 * cs + pos] = wi_world.z;
+                sray[6 * cs + pos] = INFINITY;
+                s_cidx[pos] = (uint32_t)ci;
               }
             } else {
               /* estimate_direct_lighting_importance (reference src/part1_code.cpp:33-57) */
@@ -193,20 +204,20 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_SHADE_MINB) k_shade(const __gri
                   d3 wi_world; float dist, pdf;
                   f3 Li = is_env ? env_sample_L(sc, wi_world, dist, pdf, g) : light_sample_L(l, hit_p, wi_world, dist, pdf, g);
                   const size_t ci = (size_t)i * rk.S + k;
-                  q.s_res[ci] = -2;
+                  s_res[ci] = -2;
                   if (!is_env && l.type == RRT_LIGHT_NULL) continue;
                   d3 w_in = mat_tmul(o2w, wi_world);
                   if (w_in.z < 0) continue;
                   f3 c = s_divf(s_mulf(s_mul(Li, bsdf_f(m, w_out, w_in)), (float)w_in.z), pdf);
-                  q.s_contrib[ci] = make_float4(c.r, c.g, c.b, 0.f);
-                  q.s_res[ci] = -1;
+                  s_contrib[ci] = make_float4(c.r, c.g, c.b, 0.f);
+                  s_res[ci] = -1;
                   int pos = append_pos(sh_count);
                   const size_t cs = cap * (size_t)rk.S;
                   d3 so = vadd(hit_p, smul(RRT_EPS_D, wi_world));
-                  q.sray[pos] = so.x; q.sray[cs + pos] = so.y; q.sray[2 * cs + pos] = so.z;
-                  q.sray[3 * cs + pos] = wi_world.x; q.sray[4 * cs + pos] = wi_world.y; q.sray[5 * cs + pos] = wi_world.z;
-                  q.sray[6 * cs + pos] = (double)dist;
-                  q.s_cidx[pos] = (uint32_t)ci;
+                  sray[pos] = so.x; sray[cs + pos] = so.y; sray[2 * cs + pos] = so.z;
+                  sray[3 * cs + pos] = wi_world.x; sray[4 * cs + pos] = wi_world.y; sray[5 * cs + pos] = wi_world.z;
+                  sray[6 * cs + pos] = (double)dist;
+                  s_cidx[pos] = (uint32_t)ci;
                 }
               }
             }
@@ -230,6 +241,7 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_SHADE_MINB) k_shade(const __gri
         }
       }
     }
+    if (i < count) vflag[i] = vf_out;
     __syncwarp();
     /* compaction of survivors: warp ballot + prefix, one atomic per warp */
     unsigned mask = __ballot_sync(0xffffffffu, ext);
@@ -260,8 +272,9 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_SHADE_MINB) k_shade(const __gri
 #endif
 __global__ void __launch_bounds__(256, RRT_DIRECT_MINB) k_shade_direct(const __grid_constant__ DevScene sc, const __grid_constant__ RenderK rk,
                                                       const __grid_constant__ Queues q, const uint32_t* __restrict__ act, int base_sample, int nb, int it) {
-  const int cur = it & 1;
+  const int cur = it & 1, sp = it & 1;
   const size_t cap = (size_t)rk.cap;
+  double* const sray = q.sray[sp]; uint32_t* const s_cidx = q.s_cidx[sp]; int* const s_res = q.s_res[sp]; float4* const s_contrib = q.s_contrib[sp];
   const int count = q.ctl[it];
   int* sh_count = q.ctl + q.ctl_stride + it;
   const int S = rk.S;
@@ -292,8 +305,8 @@ __global__ void __launch_bounds__(256, RRT_DIRECT_MINB) k_shade_direct(const __g
             d3 w_in = hemisphere_sample(g);
             wi_world = mat_mul(o2w, w_in);
             f3 f = bsdf_f(m, w_out, w_in);
-            q.s_contrib[ci] = make_float4(f.r, f.g, f.b, (float)w_in.z);
-            q.s_res[ci] = -1;
+            s_contrib[ci] = make_float4(f.r, f.g, f.b, (float)w_in.z);
+            s_res[ci] = -1;
             dist_d = INFINITY; emit = true;
           } else {
             /* which light, which of its samples, and how many draws precede it */
@@ -317,11 +330,11 @@ __global__ void __launch_bounds__(256, RRT_DIRECT_MINB) k_shade_direct(const __g
               d3 w_in = mat_tmul(o2w, wi_world);
               if (!(w_in.z < 0)) {
                 f3 c = s_divf(s_mulf(s_mul(Li, bsdf_f(m, w_out, w_in)), (float)w_in.z), pdf);
-                q.s_contrib[ci] = make_float4(c.r, c.g, c.b, 0.f);
+                s_contrib[ci] = make_float4(c.r, c.g, c.b, 0.f);
                 verdict = -1; dist_d = (double)dist; emit = true;
               }
             }
-            q.s_res[ci] = verdict;
+            s_res[ci] = verdict;
           }
           so = vadd(hit_p, smul(RRT_EPS_D, wi_world));
         }
@@ -335,10 +348,10 @@ __global__ void __launch_bounds__(256, RRT_DIRECT_MINB) k_shade_direct(const __g
       if (emit) {
         const int pos = base + __popc(mask & ((1u << lane_id()) - 1u));
         const size_t cs = cap * (size_t)S;
-        q.sray[pos] = so.x; q.sray[cs + pos] = so.y; q.sray[2 * cs + pos] = so.z;
-        q.sray[3 * cs + pos] = wi_world.x; q.sray[4 * cs + pos] = wi_world.y; q.sray[5 * cs + pos] = wi_world.z;
-        q.sray[6 * cs + pos] = dist_d;
-        q.s_cidx[pos] = (uint32_t)ci;
+        sray[pos] = so.x; sray[cs + pos] = so.y; sray[2 * cs + pos] = so.z;
+        sray[3 * cs + pos] = wi_world.x; sray[4 * cs + pos] = wi_world.y; sray[5 * cs + pos] = wi_world.z;
+        sray[6 * cs + pos] = dist_d;
+        s_cidx[pos] = (uint32_t)ci;
       }
     }
   }
@@ -348,30 +361,37 @@ __global__ void __launch_bounds__(256, RRT_DIRECT_MINB) k_shade_direct(const __g
  * `it` into each path's radiance, in the reference's sample order */
 __global__ void __launch_bounds__(256) k_accumulate(const __grid_constant__ DevScene sc, const __grid_constant__ RenderK rk,
                                                     const __grid_constant__ Queues q, int it) {
-  const int cur = it & 1;
+  const int sp = it & 1;
   const size_t cap = (size_t)rk.cap;
   const int count = q.ctl[it];
+  const uint8_t* const vflag = q.vflag[sp]; const float* const dbeta = q.dbeta[sp]; const float* const emit = q.emit[sp];
+  const int* const s_res = q.s_res[sp]; const float4* const s_contrib = q.s_contrib[sp];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-    if (!(q.vflag[i] & 1)) continue;
+    const uint8_t vf = vflag[i];
+    if (!vf) continue;
+    const uint32_t slot = q.aslot[sp][i];
+    if (vf & 2) {   /* emission of a vertex reached through a delta BSDF (reference src/part1_code.cpp:94-95): before this vertex's direct light */
+      q.Lsample[slot] += emit[i]; q.Lsample[cap + slot] += emit[cap + i]; q.Lsample[2 * cap + slot] += emit[2 * cap + i];
+    }
+    if (!(vf & 1)) continue;
     f3 L = F3(0, 0, 0);
     for (int k = 0; k < rk.S; ++k) {
       const size_t ci = (size_t)i * rk.S + k;
-      const int r = q.s_res[ci];
+      const int r = s_res[ci];
       if (rk.hemi) {
         if (r >= 0) {
-          float4 c = q.s_contrib[ci];
+          float4 c = s_contrib[ci];
           f3 Le = mat_emission(sc.mats[sc.prim_mat[r]]);
           L = s_add(L, s_mulf(s_mul(Le, F3(c.x, c.y, c.z)), c.w));
         }
       } else if (r == -1) {
-        float4 c = q.s_contrib[ci];
+        float4 c = s_contrib[ci];
         L = s_add(L, F3(c.x, c.y, c.z));
       }
     }
     if (rk.hemi) L = s_divf(s_mulf(s_mulf(L, 2.f), (float)RRT_PI), (float)rk.total);
     else L = s_divf(L, (float)rk.total);
-    const f3 beta = F3(q.dbeta[i], q.dbeta[cap + i], q.dbeta[2 * cap + i]);
-    const uint32_t slot = q.slot[cur][i];
+    const f3 beta = F3(dbeta[i], dbeta[cap + i], dbeta[2 * cap + i]);
     f3 a = s_mul(L, beta);
     q.Lsample[slot] += a.r; q.Lsample[cap + slot] += a.g; q.Lsample[2 * cap + slot] += a.b;
   }

@@ -636,7 +636,10 @@ __device__ __forceinline__ void trace_sched(const DevScene& sc, const DevHole& b
 #define RRT_MINB_CLOSEST(V, STEP) RRT_MINB_CLOSEST_N
 #else   /* wide closest-hit kernel: 5 blocks at 96 registers (fewer spills around Best / fill_geo): C2 37.08 -> 36.51 ms, C1 4.47 -> 4.42;
            the binary one stays at 6 (5: bunny 1080p 103.8 -> 104.8, C5 68.6 -> 70.4) */
-#define RRT_MINB_CLOSEST(V, STEP) (((V) >= 4 && (STEP) != 1) ? 5 : RRT_MINBLOCKS(V, STEP))
+#ifndef RRT_MINB_CLOSEST_BIN
+#define RRT_MINB_CLOSEST_BIN RRT_MINB   /* A/B: resident blocks of the binary-node closest-hit kernel alone */
+#endif
+#define RRT_MINB_CLOSEST(V, STEP) (((V) >= 4 && (STEP) != 1) ? 5 : ((V) < 4 && (STEP) != 1) ? RRT_MINB_CLOSEST_BIN : RRT_MINBLOCKS(V, STEP))
 #endif
 template <bool COUNT, int V, int STEP = 0, int PARK = 0>
 __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB_CLOSEST(V, STEP)) k_trace_closest(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
