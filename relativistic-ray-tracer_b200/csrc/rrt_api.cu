@@ -370,6 +370,17 @@ static int build_top_record(Fetch fetch, int32_t root_code, float out[64], int m
     Child l, r; kids_of(ch[pick].code, &l, &r);
     ch[pick] = l; ch.push_back(r);
   }
+  /* a child whose two children are leaves with adjacent records (the two triangles of one wall) becomes that leaf itself: one binary visit less
+   * for every chord that comes near the wall */
+  for (Child& c : ch) {
+    if (c.code < 0) continue;
+    Child l, r; kids_of(c.code, &l, &r);
+    if (l.code >= 0 || r.code >= 0 || l.code == rrt::kEmptyChild || r.code == rrt::kEmptyChild) continue;
+    const uint32_t bl = (uint32_t)~l.code, br = (uint32_t)~r.code;
+    uint32_t f0 = bl >> 3, n0 = bl & 7u, f1 = br >> 3, n1 = br & 7u;
+    if (f1 + n1 == f0) { std::swap(f0, f1); std::swap(n0, n1); }
+    if (f0 + n0 == f1 && n0 + n1 <= 7u) c.code = ~(int32_t)((f0 << 3) | (n0 + n1));
+  }
   for (int k = 0; k < 8; ++k) {
     int32_t code = rrt::kEmptyChild;
     if (k < (int)ch.size()) {

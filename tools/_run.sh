@@ -1,5 +1,3 @@
-python bench.py > gpurun_out/final_c4.json 2> gpurun_out/final_c4.err; echo "c4 rc=$?"
-python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/final_c4_ref.json 2> gpurun_out/final_c4_ref.err; echo "ref rc=$?"
-python bench.py --workload c5 --spp 64 --steps 3 --warmup 2 --no-cpu-baseline > gpurun_out/final_c5_64spp.json 2> gpurun_out/final_c5.err; echo "c5 rc=$?"
-python bench.py --workload c2 --steps 5 --warmup 3 > gpurun_out/final_c2.json 2> gpurun_out/final_c2.err; echo "c2 rc=$?"
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
+python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "oracle_records or bvh_intersect or full_size or device_bvh or far_origin" > gpurun_out/t_gpu14.log 2>&1; echo "gpu rc=$?"; tail -2 gpurun_out/t_gpu14.log
+python tools/ab_trace.py bunny_box,bunny_bh,c5,c3@32 "default:" > gpurun_out/ab14.jsonl 2>&1
+grep -o '"workload": "[a-z0-9_]*"\|"ms": [0-9.]*\|"trace_ms": [0-9.]*\|"nodes": [0-9]*' gpurun_out/ab14.jsonl | paste -sd' ' | sed 's/"workload"/\n"workload"/g'
