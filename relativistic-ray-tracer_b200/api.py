@@ -107,6 +107,30 @@ def bvh_build_host(scene, topology=0):
                 dfs_rank=rank[:scene.n_prims])
 
 
+_NCCL = None
+
+
+def _preload_nccl():
+    """rrt_create_multi dlopen()s libnccl.so.2.  In a Python process that (later) imports torch, the NCCL torch ships (site-packages/nvidia/nccl) must be
+    the one the process holds: the loader identifies libraries by SONAME, and an older system libnccl.so.2 loaded first would be handed to
+    libtorch_cuda.so in place of its own (ImportError: undefined symbol ncclDevCommCreate).  So that copy, when present, is loaded first; the library
+    then finds it already there.  RRT_NCCL_LIB overrides."""
+    global _NCCL
+    if _NCCL is not None or os.environ.get("RRT_NCCL_LIB"):
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for base in (list(spec.submodule_search_locations) if spec and spec.submodule_search_locations else []):
+            cand = os.path.join(base, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                _NCCL = C.CDLL(cand, mode=os.RTLD_LOCAL)
+                return
+    except Exception:
+        pass
+    _NCCL = False
+
+
 class Context:
     """One rrt_ctx, one host thread at a time: one GPU (device = int) or, with a list of devices, a multi-GPU context
     (rrt_create_multi: the frame's interleaved tiles are dealt over the GPUs, one NCCL reduce per frame onto the first)."""
@@ -114,6 +138,7 @@ class Context:
     def __init__(self, device=0):
         self.h = C.c_void_p()
         if isinstance(device, (list, tuple)):
+            _preload_nccl()
             devs = (C.c_int * len(device))(*[int(d) for d in device])
             rc = lib().rrt_create_multi(C.byref(self.h), len(device), devs)
         else:

@@ -1459,8 +1459,14 @@ std::mutex g_nccl_mu;
 const char* load_nccl() {   /* nullptr = ok, else what went wrong */
   std::lock_guard<std::mutex> lk(g_nccl_mu);
   if (g_nccl.lib) return nullptr;
-  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
-  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  /* An NCCL the process already holds (a Python caller that imported torch, or api.py's pre-load of the NCCL torch ships) is used as it is: the
+   * loader identifies libraries by SONAME, and a second, older libnccl.so.2 loaded first would later be handed to torch in place of its own
+   * (undefined symbol ncclDevCommCreate).  RRT_NCCL_LIB names a specific file.  RTLD_LOCAL: nothing of NCCL leaks into the global scope. */
+  void* h = nullptr;
+  if (const char* path = getenv("RRT_NCCL_LIB")) h = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL | RTLD_NOLOAD);
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
   if (!h) return "libnccl.so.2 could not be loaded (multi-GPU contexts need NCCL)";
   NcclApi a; a.lib = h;
 #define RRT_SYM(field, name) *(void**)(&a.field) = dlsym(h, name); if (!a.field) { dlclose(h); return "libnccl.so.2 lacks " name; }

@@ -56,6 +56,22 @@ def test_multi_gpu_frame_equals_single_gpu_frame(api, scene, mode):
     assert np.array_equal(one.render(p2)[0], m.render(p2)[0])
 
 
+def test_multi_gpu_render_device_leaves_the_frame_on_the_first_gpu(api):
+    """rrt_render_device on a multi-GPU context: d_rgbn / d_counts live on the first GPU and receive the reduced frame"""
+    import torch
+    s = load_scene("cbspheres_lambertian_96x72")
+    p = sc.make_params(ns_aa=8, max_ray_depth=3, ns_area_light=2, seed=4)
+    m = api.Context([0, 1]); m.upload_scene(s); m.set_frame(96, 72)
+    hdr, cnt, _ = m.render(p)
+    frame = torch.zeros((72, 96, 4), dtype=torch.float32, device="cuda:0")
+    counts = torch.zeros((72, 96), dtype=torch.int32, device="cuda:0")
+    torch.cuda.synchronize()
+    st = m.render_device(p, frame.data_ptr(), counts.data_ptr())
+    f = frame.cpu().numpy()
+    assert np.array_equal(f[..., :3], hdr) and np.array_equal(f[..., 3], cnt.astype(np.float32)) and np.array_equal(counts.cpu().numpy(), cnt)
+    assert st["paths"] == int(cnt.sum())
+
+
 def test_multi_gpu_context_rejects_what_it_cannot_do(api):
     with pytest.raises(api.RrtError, match="listed twice"):
         api.Context([0, 0])

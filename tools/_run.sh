@@ -1,2 +1,9 @@
-RRT_B200_LIB=build_ab/lib_ab.so python tools/ab_trace.py bunny_box,bunny_bh,c2 "escape:escape=1,overlap=0;noescape:escape=0,overlap=0;noescape_overlap:escape=0" > gpurun_out/ab15.jsonl 2>&1
-grep -o '"workload": "[a-z0-9_]*"\|"options": "[a-z_]*"\|"ms": [0-9.]*\|"trace_ms": [0-9.]*' gpurun_out/ab15.jsonl | paste -sd' ' | sed 's/"workload"/\n"workload"/g'; tail -2 gpurun_out/ab15.jsonl | cut -c1-200
+python -m pytest tests/test_multi_gpu.py -x -q -m gpu 2>&1 | tail -3
+python -c "
+import importlib, sys
+sys.path.insert(0,'tests')
+api=importlib.import_module('relativistic-ray-tracer_b200.api')
+m=api.Context([0,1]); print('multi ctx ok', m.gpu_count())
+import torch; print('torch imported after rrt_create_multi:', torch.cuda.device_count(), 'GPUs')
+" 2>&1 | tail -3
+host/pathtracer -s 4 -l 2 -m 3 -G 0,1 -f gpurun_out/cli_multi.png tests/golden/cbspheres_lambertian_480x360.rrtscene 2>&1 | tail -2
