@@ -8,9 +8,18 @@
 // of the reference's, and the primitive tests alone decide the hit.  Equal-t ties go to the primitive
 // with the higher reference depth-first rank (the reference keeps the last one it visits).
 #pragma once
+#include <type_traits>
 #include "rrt_math.cuh"
 #include "../../include/rrt_b200.h"
 
+#ifndef RRT_TOP_AABB
+#define RRT_TOP_AABB 0            /* A/B: 1 = short chords test the tree-top record with their bounding box (traverse()).  Bit-identical, and not a gain on
+                                     B200 (profiles/r02_r_ab_top_aabb.jsonl): bunny in-box 165.5 -> 164.5 ms, bunny 1080p 75.4 -> 76.2, C5 51.3 -> 52.0 with ten times
+                                     the triangle tests (380 M against 39 M): what the cheaper test saves in the record it loses in leaves it lets through */
+#endif
+#ifndef RRT_TOP_AABB_MAXLEN
+#define RRT_TOP_AABB_MAXLEN 0.5f  /* ... "short": up to this length; longer chords (escaped rays coming back through the scene) keep the slab test */
+#endif
 #ifndef RRT_STACK
 #define RRT_STACK 40
 #define RRT_SPILL 136   /* wide traversal: entries beyond the shared-memory stack go to local memory (never seen in practice) */
@@ -576,7 +585,52 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const SEG& s, Best&
    * (largest drop in surface area first) into up to 8 children — the flat per-wall boxes and the root of the mesh — and one straight-line visit
    * tests all of them; what passes goes on the stack and the binary loop below carries on.  Same boxes, same leaves: results unchanged. */
   if (sc.top != nullptr) {
-    if (cur != DONE && cur >= 0) {
+    const bool need_top = cur != DONE && cur >= 0;
+#if RRT_TOP_AABB
+    /* Short chords (everything inside the scene: a few centimetres) take a cheaper test of the same record: the chord's own bounding box against
+     * the child boxes, 6 compares per child instead of 6 FFMA + 2 three-way min / max + 2 FFMA + 3 compares.  Conservative like the slab test (a
+     * chord that meets a box has a bounding box that overlaps it; the box is widened by the rounding of its corners), exact for the walls (a
+     * full-wall rectangle: every chord inside the room that reaches the wall's plane does so within it), and the children it lets through are
+     * tested exactly further down.  The choice is made per WARP (all of its chords short, none far-shifted), so there is one code path per trip. */
+    bool aabb_ok = true;
+    if constexpr (!std::is_same<SEG, SegF>::value) aabb_ok = !need_top || (!shifted && tmaxf <= RRT_TOP_AABB_MAXLEN && bc.tmin <= 0.f);
+    else aabb_ok = !need_top;
+    if (__all_sync(0xffffffffu, aabb_ok)) {
+      if constexpr (!std::is_same<SEG, SegF>::value) {
+        if (need_top) {
+          const Seg& e = seg_exact(s);
+          const float ox = (float)e.o.x, oy = (float)e.o.y, oz = (float)e.o.z;
+          const float ex = __fmaf_rn((float)e.d.x, tmaxf, ox), ey = __fmaf_rn((float)e.d.y, tmaxf, oy), ez = __fmaf_rn((float)e.d.z, tmaxf, oz);
+          /* corners of the chord's box: |fl(o) - o| <= 2^-24 |o|, the far end lies between o and o + d tmaxf (tmaxf >= len) up to
+           * 2^-24 (|o| + 2 tmaxf + |end|); 2^-21 (...) covers both with an 8x margin */
+          const float mx = 4.7683716e-7f * (fabsf(ox) + fabsf(ex) + tmaxf), my = 4.7683716e-7f * (fabsf(oy) + fabsf(ey) + tmaxf),
+                      mz = 4.7683716e-7f * (fabsf(oz) + fabsf(ez) + tmaxf);
+          const float lx = fminf(ox, ex) - mx, hx = fmaxf(ox, ex) + mx, ly = fminf(oy, ey) - my, hy = fmaxf(oy, ey) + my,
+                      lz = fminf(oz, ez) - mz, hz = fmaxf(oz, ez) + mz;
+          const float* nd = sc.top;
+          if (COUNT) cnt.nodes += 4;
+          cur = DONE;
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            const float4 a = __ldg((const float4*)(nd + 0) + g), b = __ldg((const float4*)(nd + 8) + g), c = __ldg((const float4*)(nd + 16) + g);
+            const float4 d = __ldg((const float4*)(nd + 24) + g), f = __ldg((const float4*)(nd + 32) + g), h = __ldg((const float4*)(nd + 40) + g);
+            const int4 k = __ldg((const int4*)(nd + 48) + g);
+            auto child = [&](float blx, float bly, float blz, float bhx, float bhy, float bhz, int code) {
+              if (lx <= bhx && hx >= blx && ly <= bhy && hy >= bly && lz <= bhz && hz >= blz && code != DONE) {
+                if (cur != DONE) stack[(sp++) * stride] = cur;
+                cur = code;
+              }
+            };
+            child(a.x, b.x, c.x, d.x, f.x, h.x, k.x);
+            child(a.y, b.y, c.y, d.y, f.y, h.y, k.y);
+            child(a.z, b.z, c.z, d.z, f.z, h.z, k.z);
+            child(a.w, b.w, c.w, d.w, f.w, h.w, k.w);
+          }
+        }
+      }
+    } else
+#endif
+    if (need_top) {
       const float R = 9.5367431640625e-7f;
       const float* nd = sc.top;
       if (COUNT) cnt.nodes += 4;     /* a 256-byte record */

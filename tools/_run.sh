@@ -1,9 +1,3 @@
-python -m pytest tests/test_multi_gpu.py -x -q -m gpu 2>&1 | tail -3
-python -c "
-import importlib, sys
-sys.path.insert(0,'tests')
-api=importlib.import_module('relativistic-ray-tracer_b200.api')
-m=api.Context([0,1]); print('multi ctx ok', m.gpu_count())
-import torch; print('torch imported after rrt_create_multi:', torch.cuda.device_count(), 'GPUs')
-" 2>&1 | tail -3
-host/pathtracer -s 4 -l 2 -m 3 -G 0,1 -f gpurun_out/cli_multi.png tests/golden/cbspheres_lambertian_480x360.rrtscene 2>&1 | tail -2
+python -m pytest tests -x -q -m gpu > gpurun_out/t_gpu16.log 2>&1; echo "gpu rc=$?"; tail -2 gpurun_out/t_gpu16.log
+python tools/ab_trace.py bunny_box,bunny_bh,c5,c3@32 "default:" > gpurun_out/ab16.jsonl 2>&1
+grep -o '"workload": "[a-z0-9_]*"\|"ms": [0-9.]*\|"trace_ms": [0-9.]*\|"tri_records": [0-9]*' gpurun_out/ab16.jsonl | paste -sd' ' | sed 's/"workload"/\n"workload"/g'
