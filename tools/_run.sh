@@ -1,3 +1,2 @@
-python -m pytest tests -x -q -m gpu > gpurun_out/t_gpu16.log 2>&1; echo "gpu rc=$?"; tail -2 gpurun_out/t_gpu16.log
-python tools/ab_trace.py bunny_box,bunny_bh,c5,c3@32 "default:" > gpurun_out/ab16.jsonl 2>&1
-grep -o '"workload": "[a-z0-9_]*"\|"ms": [0-9.]*\|"trace_ms": [0-9.]*\|"tri_records": [0-9]*' gpurun_out/ab16.jsonl | paste -sd' ' | sed 's/"workload"/\n"workload"/g'
+python -m pytest tests -x -q -m gpu > gpurun_out/t_gpu17.log 2>&1; echo "gpu rc=$?"; tail -2 gpurun_out/t_gpu17.log
+bash tools/ncu_heaviest.sh r02_c4_shadow_final 'k_trace_shadow' python tools/one_frame.py c4 fp64 1; tail -1 gpurun_out/r02_c4_shadow_final_plain.log | cut -c200-
