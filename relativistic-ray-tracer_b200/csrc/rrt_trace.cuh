@@ -563,7 +563,7 @@ __device__ __forceinline__ bool coop_flush(const DevScene& sc, CoopScratch* cs, 
  * per-thread stack in shared memory.  ANY = shadow-ray form (stop at the first accepted primitive). */
 template <bool ANY, bool COUNT, bool COOP = false, bool UNITD = true, class SEG = Seg>
 __device__ __forceinline__ bool traverse(const DevScene& sc, const SEG& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt, bool active,
-                                         CoopScratch* cs = nullptr) {
+                                         CoopScratch* cs = nullptr, bool* root_miss = nullptr) {
   /* Called by ALL 32 lanes of the warp, converged; lanes without a chord pass active = false and idle through.
    * while-while: every lane first descends until it holds a leaf (or runs out of nodes), the warp re-converges, then
    * the lanes that hold a leaf test its records.  (Measured alternatives, C2 on B200, ms per frame: single if/else
@@ -578,6 +578,7 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const SEG& s, Best&
   if (active) {
     shifted = seg_boxctx(sc, s, bc, tmaxf);
     if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tl)) cur = sc.root;
+    else if (root_miss) *root_miss = true;   /* the chord does not reach the scene box at all */
   }
   /* Top of the tree as one 8-wide record.  The boxes near the root of a Cornell-box scene are the groupings of its walls: each spans most of
    * the room, so a chord anywhere inside used to walk 5-6 binary nodes only to learn that it touches no wall (6.0 node visits per chord on the
@@ -721,7 +722,7 @@ __device__ __forceinline__ bool traverse(const DevScene& sc, const SEG& s, Best&
  * shared memory as before, anything beyond (never observed) in a local-memory array; rrt_upload_scene checks the bound. */
 template <bool ANY, bool COUNT, int W, bool COOP = false, bool UNITD = true, class SEG = Seg>
 __device__ __forceinline__ bool traverse_wide(const DevScene& sc, const SEG& s, Best& best, int* __restrict__ stack, int stride, Counters& cnt, bool active,
-                                              CoopScratch* cs = nullptr) {
+                                              CoopScratch* cs = nullptr, bool* root_miss = nullptr) {
   const int DONE = (int)0x80000000;   /* also the code of an unused child slot (kEmptyChild) */
   const float R = 9.5367431640625e-7f; /* 2^-20 */
   best.t = seg_tmax(s); best.rank = -1; best.prim = -1; best.kind = 0; best.b1 = best.b2 = 0.0;
@@ -739,6 +740,7 @@ __device__ __forceinline__ bool traverse_wide(const DevScene& sc, const SEG& s, 
     if (bc.ny) { ony = 4 * W; ofy = W; }
     if (bc.nz) { onz = 5 * W; ofz = 2 * W; }
     if (box_hit(sc.root_lo[0], sc.root_lo[1], sc.root_lo[2], sc.root_hi[0], sc.root_hi[1], sc.root_hi[2], bc, tmaxf, tl)) cur = sc.wroot;
+    else if (root_miss) *root_miss = true;
   }
   auto visit = [&]() {
     const float* nd = sc.wide + (size_t)(8 * W) * (size_t)cur;

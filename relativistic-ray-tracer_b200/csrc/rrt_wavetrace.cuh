@@ -159,6 +159,26 @@ struct ParkQ {
 };
 
 /* ---------------------------------------------------------------- variant 0 (default): chord-lockstep loop */
+/* Escape warp (RRT_ESCAPE_WARP = 1; hole on, FP64 stepper).  MEASURED SLOWER, off by default, kept as the record of the experiment.
+ * In a launch of in-box rays a third of all chords belong to rays that have left the scene box through the open front and still walk their 63
+ * chords (the reference never stops): they need no traversal, but each of them holds a lane of a warp whose other lanes do — the tree-top record
+ * is visited at 20 of 32 lanes (profiles/r02_s_attribution_c4_shadow_final.txt).  With the flag on, warp 0 of every block takes such rays over: a
+ * lane of the other warps whose chord missed the root box on two chords in a row hands its ray (chord, index, chord count: 64 B) to a 32-entry ring
+ * in shared memory and takes a fresh one; warp 0 refills its lanes from that ring first and from the launch's queue otherwise.  Who executes a
+ * chord changes, nothing else: frames are bit-identical (same SHA-256 on bunny_box, C2, C4).  A full ring leaves the ray where it is, and once the
+ * launch's queue is exhausted nobody hands over any more.  Time, B200, same box, best of 3: bunny_box 165.3 -> 180.7 ms, C2 32.4 -> 35.7 ms,
+ * C4 2684 -> 2925 ms (profiles/r02_u_escape_warp.txt): the traversal of a warp costs its slowest lane, so filling the idle lanes with in-box
+ * rays lengthens every trip of three warps in four by more than the trips of the fourth get shorter. */
+#ifndef RRT_ESCAPE_WARP
+#define RRT_ESCAPE_WARP 0
+#endif
+#define RRT_EQ_CAP 32
+struct EscQ {
+  double st[7][RRT_EQ_CAP];
+  int idx[RRT_EQ_CAP], j[RRT_EQ_CAP], flag[RRT_EQ_CAP];   /* flag: 1 = entry published */
+  int head, tail, count, producers;                      /* head: consumer only; count >= tail - head at all times; producers: warps that may still publish */
+};
+
 /* PARK: 0 = every ray runs to its end here; 1 = escaping rays are parked in `pk` (hole on, FP64 stepper); 2 = the queue IS `pk` (re-entries from
  * k_escape: state + a chord whose traversal is pending), no parking */
 template <bool ANY, bool COUNT, int W, int STEP, class IO, int PARK = 0>
@@ -170,6 +190,16 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
   __shared__ double seg_mem[SMEM ? 7 * RRT_SEG_STRIDE : 1];
   double* sm = seg_mem + (SMEM ? threadIdx.x : 0);
   int* stack = stack_mem + threadIdx.x;
+  constexpr bool EW = RRT_ESCAPE_WARP && SMEM && RRT_BLOCK >= 64;
+  __shared__ EscQ eq_mem[1];   /* unreferenced, hence dropped, when EW is false */
+  EscQ& eq = eq_mem[0];
+  const bool esc_warp = EW && (threadIdx.x >> 5) == 0;
+  int out_streak = 0;                /* consecutive chords that missed the root box */
+  if constexpr (EW) {
+    if (threadIdx.x < RRT_EQ_CAP) eq.flag[threadIdx.x] = 0;
+    if (threadIdx.x == 0) { eq.head = 0; eq.tail = 0; eq.count = 0; eq.producers = RRT_BLOCK / 32 - 1; }
+    __syncthreads();
+  }
   constexpr bool COOP = ANY && RRT_COOP_LEAVES;
   CoopScratch* coop = &coop_mem[COOP ? threadIdx.x >> 5 : 0];
   if (COOP) coop_init(coop);
@@ -188,6 +218,36 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
   while (true) {
     /* ---- hand queue entries to the lanes that have none */
     unsigned need = __ballot_sync(0xffffffffu, !has);
+    if constexpr (EW) {
+      if (esc_warp && need) {   /* the ring first: rays the other warps of the block handed over */
+        int h0 = 0, k = 0;
+        if (wt_lane() == 0) {
+          h0 = eq.head;
+          const int want = __popc(need);
+          while (k < want && ((volatile int*)eq.flag)[(h0 + k) % RRT_EQ_CAP] == 1) ++k;
+        }
+        h0 = __shfl_sync(0xffffffffu, h0, 0); k = __shfl_sync(0xffffffffu, k, 0);
+        if (k > 0) {
+          __threadfence_block();
+          const int rank = __popc(need & lt_mask);
+          if (!has && rank < k) {
+            const int q = (h0 + rank) % RRT_EQ_CAP;
+#pragma unroll
+            for (int c = 0; c < 7; ++c) sm[c * RRT_SEG_STRIDE] = ((volatile double*)eq.st[c])[q];
+            idx = ((volatile int*)eq.idx)[q]; j = ((volatile int*)eq.j)[q];
+            has = true; out_streak = 2;
+          }
+          __syncwarp();
+          if (wt_lane() == 0) {
+            for (int r = 0; r < k; ++r) ((volatile int*)eq.flag)[(h0 + r) % RRT_EQ_CAP] = 0;
+            eq.head = h0 + k;
+            __threadfence_block();
+            atomicSub(&eq.count, k);
+          }
+          need = __ballot_sync(0xffffffffu, !has);
+        }
+      }
+    }
     while (need) {
       if (pool_next >= pool_end) {
         if (!more) break;
@@ -208,7 +268,7 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
         } else {
         idx = pool_next + rank;
         io.load(idx, o, d, tmin, tmax);
-        has = true; j = 0; len = 0.0;
+        has = true; j = 0; len = 0.0; out_streak = 0;
         if constexpr (SMEM) {
           sm[0] = o.x; sm[RRT_SEG_STRIDE] = o.y; sm[2 * RRT_SEG_STRIDE] = o.z; sm[3 * RRT_SEG_STRIDE] = d.x; sm[4 * RRT_SEG_STRIDE] = d.y; sm[5 * RRT_SEG_STRIDE] = d.z;
           sm[6 * RRT_SEG_STRIDE] = 0.0;
@@ -225,7 +285,19 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
       pool_next += min(__popc(need), avail);
       need = __ballot_sync(0xffffffffu, !has);
     }
-    if (!__any_sync(0xffffffffu, has)) break;
+    if (!__any_sync(0xffffffffu, has)) {
+      if constexpr (EW) {
+        if (esc_warp) {   /* nothing to do right now: done only when no warp of the block can publish any more and the ring is empty */
+          int fin = 0;
+          if (wt_lane() == 0) fin = (!more && *(volatile int*)&eq.producers == 0 && *(volatile int*)&eq.count == 0) ? 1 : 0;
+          fin = __shfl_sync(0xffffffffu, fin, 0);
+          if (fin) break;
+          __nanosleep(200);
+          continue;
+        }
+      }
+      break;
+    }
     /* ---- one chord for every lane that holds a ray */
     Hit h; h.status = -1;
     Best best;
@@ -261,8 +333,9 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
         if (COUNT) cnt.steps++;
       }
       const bool live = has && h.status < 0;
-      if (W == 2) found = traverse<ANY, COUNT, false, true, SegS>(sc, ss, best, stack, RRT_BLOCK, cnt, live, coop);
-      else found = traverse_wide<ANY, COUNT, (W == 2 ? 4 : W), false, true, SegS>(sc, ss, best, stack, RRT_BLOCK, cnt, live, coop);
+      bool root_miss = false;
+      if (W == 2) found = traverse<ANY, COUNT, false, true, SegS>(sc, ss, best, stack, RRT_BLOCK, cnt, live, coop, &root_miss);
+      else found = traverse_wide<ANY, COUNT, (W == 2 ? 4 : W), false, true, SegS>(sc, ss, best, stack, RRT_BLOCK, cnt, live, coop, &root_miss);
       if (live) {
         if (found) {
           h.status = 1; h.prim = best.prim; h.chord = j; h.steps = j + 1; h.t = best.t;
@@ -270,6 +343,23 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
         } else {
           ++j;
           if (j >= bh.nchords) { h.status = 0; h.prim = -1; h.chord = j - 1; h.steps = j; h.t = 0.0; }
+        }
+        out_streak = root_miss ? out_streak + 1 : 0;
+      }
+      if constexpr (EW) {
+        /* hand a ray that has left the scene box over to warp 0 (see EscQ): not from warp 0 itself, not once the launch's queue is exhausted */
+        if (!esc_warp && more && has && h.status < 0 && out_streak >= 2) {
+          const int c = atomicAdd(&eq.count, 1);
+          if (c >= RRT_EQ_CAP) atomicSub(&eq.count, 1);          /* ring full: the ray stays here */
+          else {
+            const int q = atomicAdd(&eq.tail, 1) % RRT_EQ_CAP;
+#pragma unroll
+            for (int cc = 0; cc < 7; ++cc) ((volatile double*)eq.st[cc])[q] = sm[cc * RRT_SEG_STRIDE];
+            ((volatile int*)eq.idx)[q] = idx; ((volatile int*)eq.j)[q] = j;
+            __threadfence_block();
+            ((volatile int*)eq.flag)[q] = 1;
+            has = false;
+          }
         }
       }
     } else {
@@ -320,6 +410,9 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
     }
     if (has && h.status >= 0) { io.store(idx, h); has = false; }
     __syncwarp();
+  }
+  if constexpr (EW) {
+    if (!esc_warp && wt_lane() == 0) { __threadfence_block(); atomicSub(&eq.producers, 1); }
   }
   if (COUNT) wt_flush_counters(cnt, gcnt);
 }

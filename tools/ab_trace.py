@@ -2,7 +2,7 @@
 warm-up), trace time, and the instrumented counts.  Images must be identical across every option set of a workload.
 usage: ab_trace.py workload[,workload...] "name:opt=val,opt=val;name2:..."     (opt = kernel | grid | width | builder | leaf | topology | streams | overlap | top | escape | shard=N: rank 0 of N)
 workloads: c2, bunny_box (bunny at 480x360: the in-box pixels of the 1080p frame), bunny_bh, c5, or any bench.py workload; [@spp]"""
-import importlib, json, os, sys
+import hashlib, importlib, json, os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -45,5 +45,5 @@ for wl in sys.argv[1].split(","):
         print(json.dumps(dict(workload=wl, spp=spp, options=name, ms=round(best["seconds"] * 1e3, 3), trace_ms=round(best["trace_seconds"] * 1e3, 3),
                               mpaths_s=round(st["paths"] / best["seconds"] / 1e6, 1), upload_s=round(up, 3), rays=st["rays"], chords=st["geodesic_steps"],
                               nodes=st["node_visits"], tri_records=st["tri_tests"], sphere_tests=st["sphere_tests"],
-                              identical=bool(exact))), flush=True)
+                              identical=bool(exact), sha=hashlib.sha256(np.ascontiguousarray(hdr).tobytes()).hexdigest()[:16])), flush=True)
         c.close()
