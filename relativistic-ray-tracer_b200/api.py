@@ -28,6 +28,7 @@ OPT_BVH_BUILDER = 9  # 0 = auto (device for >= 4096 primitives), 1 = device (ref
 OPT_ESCAPE = 11   # escape hand-off: rays outside the scene box continue in a lean kernel (default 1)
 OPT_TOP_NODE = 12  # 8-wide record for the top of a binary tree (default 1)
 OPT_OVERLAP = 13  # shadow rays of depth i beside extension rays of depth i + 1 (default 1)
+OPT_SORT_SHADOW = 14  # hole on, meshes: shadow rays handed to the trace kernel cell by cell of their origin (1 = chunks < 2 M paths, default; 2 = always; 0 = never)
 OPT_STREAMS = 10  # wavefront chunks of a round dealt over this many CUDA streams (default 2)
 OPT_STEPPER = 8   # 0 = FP64 bit-exact stepper (default), 1 = FP32 state-carrying stepper (include/rrt_b200.h)
 

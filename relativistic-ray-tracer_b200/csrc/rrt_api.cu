@@ -144,6 +144,7 @@ int rrt_create(rrt_ctx** out, int device) {
   ctx->opt[RRT_OPT_ESCAPE] = 0;
   ctx->opt[RRT_OPT_TOP_NODE] = 1;
   ctx->opt[RRT_OPT_OVERLAP] = 1;
+  ctx->opt[RRT_OPT_SORT_SHADOW] = 1;
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaMallocHost((void**)&ctx->h_pinned, 4096)) != cudaSuccess) {
@@ -181,7 +182,7 @@ void rrt_destroy(rrt_ctx* ctx) {
 int rrt_set_option(rrt_ctx* ctx, int option, int64_t value) {
   if (!ctx) return RRT_E_ARG;
   RRT_MULTI_ALL(ctx, rrt_set_option(sub, option, value));
-  if (option < 0 || option > RRT_OPT_OVERLAP) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
+  if (option < 0 || option > RRT_OPT_SORT_SHADOW) FAIL(RRT_E_ARG, "rrt_set_option: unknown option");
 #if !RRT_AB
   if ((option == RRT_OPT_TRACE_KERNEL && value != 0) || (option == RRT_OPT_BVH_WIDTH && value == 4) || (option == RRT_OPT_ESCAPE && value != 0))
     FAIL(RRT_E_ARG, "rrt_set_option: this variant is compiled only into A/B builds (make EXTRA=-DRRT_AB=1)");
@@ -660,7 +661,7 @@ static int trace_step_mode(const rrt_ctx* ctx) {
   return (RRT_AB && ctx->opt[RRT_OPT_TRACE_KERNEL] == 2) ? 3 : 0;
 }
 typedef void (*closest_fn)(const DevScene, const DevHole, const double*, size_t, const int*, int*, int*, double*, Counters*, const ParkQ);
-typedef void (*shadow_fn)(const DevScene, const DevHole, const double*, size_t, const int*, int*, const uint32_t*, int*, Counters*, const ParkQ);
+typedef void (*shadow_fn)(const DevScene, const DevHole, const double*, size_t, const int*, int*, const uint32_t*, int*, const uint32_t*, Counters*, const ParkQ);
 typedef void (*hook_fn)(const DevScene, const DevHole, int, const double*, const double*, const double*, const double*, rrt_hit*, int*, Counters*, const ParkQ);
 
 /* park: 0 = rays run to their end in the trace kernel, 1 = escaping rays are parked for k_escape, 2 = the re-entry pass (rrt_wavetrace.cuh ParkQ);
@@ -775,19 +776,19 @@ static void launch_closest(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, 
 }
 template <bool ANY>
 static void launch_shadow(rrt_ctx* ctx, bool count, int grid, cudaStream_t st, const double* ray, size_t cap, const int* cnt_ptr, int* cursor,
-                          const uint32_t* cidx, int* res, Counters* gc, const ParkQ* park = nullptr, const ParkQ* reentry = nullptr) {
+                          const uint32_t* cidx, int* res, const uint32_t* perm, Counters* gc, const ParkQ* park = nullptr, const ParkQ* reentry = nullptr) {
   const int v = trace_variant(ctx), step = trace_step_mode(ctx);
   const bool esc = park && escape_on(ctx);
   shadow_fn fn = count ? shadow_kernel<ANY, true>(v, step, esc ? 1 : 0) : shadow_kernel<ANY, false>(v, step, esc ? 1 : 0);
-  if (!esc) { fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc, ParkQ()); return; }
+  if (!esc) { fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, perm, gc, ParkQ()); return; }
 #if RRT_AB
   cudaMemsetAsync(park->cnt, 0, 16, st);
-  fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc, *park);
+  fn<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, nullptr, gc, *park);
   const int ge = ctx->sm_count * RRT_MINB_ESCAPE;
   if (count) k_escape_shadow<true><<<ge, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, cap, cidx, res, gc, *park, *reentry);
   else k_escape_shadow<false><<<ge, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, cap, cidx, res, gc, *park, *reentry);
   shadow_fn fr = count ? shadow_kernel<ANY, true>(v, step, 2) : shadow_kernel<ANY, false>(v, step, 2);
-  fr<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, gc, *reentry);
+  fr<<<grid, RRT_BLOCK, 0, st>>>(ctx->ds, ctx->bh, ray, cap, cnt_ptr, cursor, cidx, res, nullptr, gc, *reentry);
 #else
   (void)reentry;
 #endif
@@ -843,7 +844,7 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   const int iters = std::max(rk.D, 1);
 
   /* ---- work buffers: capacity from the in-flight budget */
-  const size_t per_path = 2 * (8 * 8 + 4 + 4 + 4 + 12) + 4 + 72 + 12 + 2 * (12 + 1 + 12 + 4) + 2 * (size_t)S * (56 + 4 + 4 + 16) + (escape_on(ctx) ? (size_t)S * 128 : 0);
+  const size_t per_path = 2 * (8 * 8 + 4 + 4 + 4 + 12) + 4 + 72 + 12 + 2 * (12 + 1 + 12 + 4) + 2 * (size_t)S * (56 + 4 + 4 + 16 + 2 + 4) + (escape_on(ctx) ? (size_t)S * 128 : 0);
   size_t want = p->max_paths_in_flight > 0 ? (size_t)p->max_paths_in_flight : (size_t)4 << 20;
   size_t budget = (size_t)(ctx->opt[RRT_OPT_WORK_BYTES] > 0 ? ctx->opt[RRT_OPT_WORK_BYTES] : (int64_t)12 << 30);
   want = std::min(want, std::max<size_t>(budget / per_path / (size_t)std::min<int64_t>(std::max<int64_t>(ctx->opt[RRT_OPT_STREAMS], 1), 4), 1024));
@@ -897,6 +898,18 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   const int ctl_stride = iters + 2;
   size_t o_ctl = carve(4 * 4 * (size_t)ctl_stride);
   const bool esc = escape_on(ctx);
+  /* shadow rays handed out cell by cell (rrt_kernels.cuh, k_bin_*): hole on — a flat shadow ray is one traversal, too short to repay a sort */
+  const bool sort_sh = ctx->opt[RRT_OPT_SORT_SHADOW] != 0 && ctx->bh.mode != RRT_MODE_FLAT && !esc && rk.D >= 1 && rk.S > 0 && trace_variant(ctx) == 0;   /* meshes */
+  /* 1: only chunks under 2 M paths.  What the sort buys is mostly a shorter ragged end — rays that start together end together — and that is a
+   * visible share of a small launch only: C4 whole, 4 M-path chunks, +-0; an 8-GPU rank's share of it, rounds of 8 M paths shrinking to 0.2 M, -2.3 % */
+  const size_t sort_below = ctx->opt[RRT_OPT_SORT_SHADOW] == 1 ? ((size_t)2 << 20) : ~(size_t)0;
+  size_t o_sbin[2] = {0, 0}, o_sperm[2] = {0, 0}, o_shist[2] = {0, 0};
+  if (sort_sh) for (int b = 0; b < 2; ++b) { o_sbin[b] = carve(2 * capS); o_sperm[b] = carve(4 * capS); o_shist[b] = carve(8 * RRT_BINS); }
+  BinGrid bing;
+  for (int a3 = 0; a3 < 3; ++a3) {
+    const float ext = ctx->ds.root_hi[a3] - ctx->ds.root_lo[a3];
+    bing.lo[a3] = ctx->ds.root_lo[a3]; bing.inv[a3] = ext > 0.f ? (float)(1 << RRT_BIN_BITS) / ext : 0.f;
+  }
   const size_t cap_park = std::max(cap, capS);
   size_t o_park = esc ? carve(park_bytes(cap_park)) : 0;
   const size_t per_stream = off;
@@ -915,6 +928,10 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
       q.sray[b] = (double*)(wb + o_sray[b]); q.s_cidx[b] = (uint32_t*)(wb + o_scidx[b]); q.s_res[b] = (int*)(wb + o_sres[b]); q.s_contrib[b] = (float4*)(wb + o_scon[b]);
     }
     q.Lsample = (float*)(wb + o_L); q.ctl = (int*)(wb + o_ctl);
+    if (sort_sh) for (int b = 0; b < 2; ++b) {
+      q.s_bin[b] = (uint16_t*)(wb + o_sbin[b]); q.s_perm[b] = (uint32_t*)(wb + o_sperm[b]); q.s_hist[b] = (uint32_t*)(wb + o_shist[b]);
+      CK(cudaMemsetAsync(q.s_hist[b], 0, 8 * RRT_BINS, st));   /* k_bin_scan leaves the counts at zero after every use */
+    }
     if (esc) park_carve(wb + o_park, cap_park, &parks[k], &reents[k]);
   }
   const size_t ctl_bytes = 4 * 4 * (size_t)ctl_stride;
@@ -998,8 +1015,15 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
           int* scount = q.ctl + q.ctl_stride + it; int* scursor = q.ctl + 3 * q.ctl_stride + it;
           const ParkQ* pkq = esc ? &parks[si] : nullptr; const ParkQ* req = esc ? &reents[si] : nullptr;
           const int sp = it & 1;
-          if (rk.hemi) launch_shadow<false>(ctx, count, grid_trace, ss, q.sray[sp], capS, scount, scursor, q.s_cidx[sp], q.s_res[sp], gcnt, pkq, req);
-          else launch_shadow<true>(ctx, count, grid_trace, ss, q.sray[sp], capS, scount, scursor, q.s_cidx[sp], q.s_res[sp], gcnt, pkq, req);
+          const uint32_t* perm = nullptr;
+          if (sort_sh && (size_t)npx * nb < sort_below) {
+            k_bin_count<<<grid_small, 256, 0, ss>>>(q.sray[sp], capS, scount, bing, q.s_hist[sp], q.s_bin[sp]);
+            k_bin_scan<<<1, 1024, 0, ss>>>(q.s_hist[sp], q.s_hist[sp] + RRT_BINS);
+            k_bin_scatter<<<grid_small, 256, 0, ss>>>(q.s_bin[sp], scount, q.s_hist[sp] + RRT_BINS, q.s_perm[sp]);
+            perm = q.s_perm[sp]; launches += 3;
+          }
+          if (rk.hemi) launch_shadow<false>(ctx, count, grid_trace, ss, q.sray[sp], capS, scount, scursor, q.s_cidx[sp], q.s_res[sp], perm, gcnt, pkq, req);
+          else launch_shadow<true>(ctx, count, grid_trace, ss, q.sray[sp], capS, scount, scursor, q.s_cidx[sp], q.s_res[sp], perm, gcnt, pkq, req);
           if (stats) { CK(cudaEventRecord(e1, ss)); trace_ev.push_back({e0, e1}); }
           k_accumulate<<<grid_small, 256, 0, ss>>>(ctx->ds, rk, q, it);
           ev_acc[1] = ev_acc[0];
@@ -1147,7 +1171,8 @@ int rrt_trace_rays(rrt_ctx* ctx, int64_t n, const double* o, const double* d, co
   CK(cudaMemsetAsync(d_cursor, 0, 4, ctx->stream));
   cudaEvent_t e0, e1; ctx->events_used = 0; e0 = next_event(ctx); e1 = next_event(ctx);
   CK(cudaEventRecord(e0, ctx->stream));
-  int grid = (int)std::min<int64_t>((n + RRT_BLOCK - 1) / RRT_BLOCK, (int64_t)ctx->sm_count * 4);
+  /* as many resident blocks as a render's trace launches get, so that a timing taken through this hook reads like theirs */
+  int grid = (int)std::min<int64_t>((n + RRT_BLOCK - 1) / RRT_BLOCK, (int64_t)ctx->sm_count * (trace_variant(ctx) >= 4 ? RRT_MINB_WIDE : RRT_MINB));
   launch_hook(ctx, any_hit != 0, grid, ctx->stream, (int)n, d_o, d_d, d_mn, d_mx, d_out, d_cursor, gc, esc ? &park : nullptr, esc ? &reentry : nullptr);
   CK(cudaEventRecord(e1, ctx->stream));
   CK(cudaMemcpyAsync(out, d_out, sizeof(rrt_hit) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));

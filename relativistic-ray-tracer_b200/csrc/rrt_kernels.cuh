@@ -43,6 +43,9 @@ struct Queues {
   uint32_t* s_cidx[2];  // contribution-table index of each shadow ray
   int* s_res[2];        // capS: -2 no ray, -1 unoccluded, >= 0 prim hit
   float4* s_contrib[2]; // capS: contribution (rgb), w = cos term (hemisphere mode)
+  uint16_t* s_bin[2];   // capS: origin cell of each shadow ray       } RRT_OPT_SORT_SHADOW, k_bin_* below
+  uint32_t* s_perm[2];  // capS: launch order -> shadow-queue position }
+  uint32_t* s_hist[2];  // 2 x RRT_BINS: rays per cell (zero between uses), first launch position of each cell
   float* Lsample;       // 3 x cap: radiance of each path slot
   int* ctl;             // [4][D+2]: queue counts, shadow counts, trace cursors, shadow cursors
   int ctl_stride;
@@ -354,6 +357,124 @@ __global__ void __launch_bounds__(256, RRT_DIRECT_MINB) k_shade_direct(const __g
         s_cidx[pos] = (uint32_t)ci;
       }
     }
+  }
+}
+
+/* ---------------------------------------------------------------- shadow rays in the order of their origin's cell (RRT_OPT_SORT_SHADOW).
+ * The shadow rays of the second and later vertices of a path start anywhere in the scene, in the order the paths happen to sit in the queue:
+ * the 32 rays a warp of the trace kernel holds have nothing in common, each needs the tree in a different place and for a different number of
+ * visits, and a warp's trip through the traversal lasts as long as its slowest lane.  Handing the same rays out cell by cell — a 16 x 16 x 16
+ * grid over the scene box, cells in Morton order, 12 cm at Cornell-box scale — makes the launch 10-12 % shorter (tools/sort_probe.py: finer
+ * cells and the direction octant add nothing).  The rays stay where k_shade_direct put them; a counting sort over the cell numbers builds the
+ * launch order `perm`, and the trace kernel's IO policy reads ray perm[i] where it read ray i.  Which lane traces a ray changes, no result does.
+ * Three small kernels per launch, the queue's length read on the device like everywhere else: cell numbers + per-block histogram in shared
+ * memory, a one-block scan of the 4096 counts, and the scatter (one atomic per group of lanes of a warp that share a cell). */
+#define RRT_BIN_BITS 4
+#define RRT_BINS (1 << (3 * RRT_BIN_BITS))
+struct BinGrid { float lo[3], inv[3]; };   /* cell coordinate = (p - lo) * inv, clamped to the grid */
+
+__device__ __forceinline__ uint32_t bin_spread(uint32_t v) {   /* bit k -> bit 3k */
+  uint32_t r = 0;
+#pragma unroll
+  for (int k = 0; k < RRT_BIN_BITS; ++k) r |= ((v >> k) & 1u) << (3 * k);
+  return r;
+}
+__device__ __forceinline__ uint32_t bin_of(const BinGrid& g, double x, double y, double z) {
+  const int m = (1 << RRT_BIN_BITS) - 1;
+  const int ix = min(max((int)(((float)x - g.lo[0]) * g.inv[0]), 0), m), iy = min(max((int)(((float)y - g.lo[1]) * g.inv[1]), 0), m),
+            iz = min(max((int)(((float)z - g.lo[2]) * g.inv[2]), 0), m);   /* a NaN lands in cell 0 */
+  return bin_spread((uint32_t)ix) | (bin_spread((uint32_t)iy) << 1) | (bin_spread((uint32_t)iz) << 2);
+}
+/* lanes of a warp that hold the same cell make ONE addition between them (rays reach the queue vertex by vertex and pixel by pixel: most of a warp
+ * usually shares its cell, and 32 atomics on one word are 32 turns); returns the value before the addition + this lane's rank among its peers */
+__device__ __forceinline__ uint32_t bin_add_grouped(uint32_t* counters, uint32_t b, unsigned act) {
+  const unsigned peers = __match_any_sync(act, b);
+  const int leader = __ffs(peers) - 1;
+  uint32_t pos = 0;
+  if (lane_id() == leader) pos = atomicAdd(&counters[b], (uint32_t)__popc(peers));
+  pos = __shfl_sync(peers, pos, leader);
+  return pos + (uint32_t)__popc(peers & ((1u << lane_id()) - 1u));
+}
+__global__ void __launch_bounds__(256) k_bin_count(const double* __restrict__ sray, size_t cs, const int* __restrict__ count_ptr, const BinGrid g,
+                                                   uint32_t* __restrict__ hist, uint16_t* __restrict__ bin) {
+  __shared__ uint32_t h[RRT_BINS];
+  for (int t = threadIdx.x; t < RRT_BINS; t += blockDim.x) h[t] = 0;
+  __syncthreads();
+  const int n = *count_ptr;
+  const int span = (n + 31) & ~31;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < span; i += gridDim.x * blockDim.x) {
+    const bool ok = i < n;
+    const unsigned act = __ballot_sync(0xffffffffu, ok);
+    if (ok) {
+      const uint32_t b = bin_of(g, sray[i], sray[cs + i], sray[2 * cs + i]);
+      bin[i] = (uint16_t)b;
+      bin_add_grouped(h, b, act);
+    }
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < RRT_BINS; t += blockDim.x)
+    if (h[t]) atomicAdd(&hist[t], h[t]);
+}
+/* one block of 1024 threads: exclusive scan of the counts into `base`, and the counts back to zero for the next launch */
+__global__ void __launch_bounds__(1024) k_bin_scan(uint32_t* __restrict__ hist, uint32_t* __restrict__ base) {
+  constexpr int PER = RRT_BINS / 1024;
+  static_assert(RRT_BINS % 1024 == 0, "k_bin_scan: 1024 threads, a whole number of cells each");
+  __shared__ uint32_t wsum[32];
+  uint32_t v[PER], sum = 0;
+#pragma unroll
+  for (int k = 0; k < PER; ++k) { v[k] = hist[threadIdx.x * PER + k]; hist[threadIdx.x * PER + k] = 0; sum += v[k]; }
+  uint32_t inc = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o); if (lane_id() >= o) inc += y; }
+  if (lane_id() == 31) wsum[threadIdx.x >> 5] = inc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    uint32_t w = wsum[threadIdx.x], wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, wi, o); if (lane_id() >= o) wi += y; }
+    wsum[threadIdx.x] = wi - w;
+  }
+  __syncthreads();
+  uint32_t ex = wsum[threadIdx.x >> 5] + inc - sum;
+#pragma unroll
+  for (int k = 0; k < PER; ++k) { base[threadIdx.x * PER + k] = ex; ex += v[k]; }
+}
+/* scatter, a tile of 4096 consecutive rays per block and turn: ranks within the tile from a histogram in shared memory, then ONE reservation per
+ * (tile, cell) in the global table — the rays of a tile share a handful of cells when the queue is in pixel order, and an atomic per group of lanes
+ * on those few words would run one after the other across the whole grid */
+#define RRT_BIN_RPT 16
+__global__ void __launch_bounds__(256) k_bin_scatter(const uint16_t* __restrict__ bin, const int* __restrict__ count_ptr, uint32_t* __restrict__ base,
+                                                     uint32_t* __restrict__ perm) {
+  __shared__ uint32_t h[RRT_BINS];
+  const int n = *count_ptr;
+  constexpr int TILE = 256 * RRT_BIN_RPT;
+  for (int t0 = blockIdx.x * TILE; t0 < n; t0 += gridDim.x * TILE) {
+    for (int t = threadIdx.x; t < RRT_BINS; t += 256) h[t] = 0;
+    __syncthreads();
+    uint32_t br[RRT_BIN_RPT];   /* cell << 16 | rank within (tile, cell) */
+#pragma unroll
+    for (int k = 0; k < RRT_BIN_RPT; ++k) {
+      const int i = t0 + k * 256 + (int)threadIdx.x;
+      const bool ok = i < n;
+      const unsigned act = __ballot_sync(0xffffffffu, ok);
+      br[k] = 0;
+      if (ok) {
+        const uint32_t b = bin[i];
+        br[k] = (b << 16) | bin_add_grouped(h, b, act);
+      }
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < RRT_BINS; t += 256) {
+      const uint32_t c = h[t];
+      if (c) h[t] = atomicAdd(&base[t], c);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RRT_BIN_RPT; ++k) {
+      const int i = t0 + k * 256 + (int)threadIdx.x;
+      if (i < n) perm[h[br[k] >> 16] + (br[k] & 0xffffu)] = (uint32_t)i;
+    }
+    __syncthreads();
   }
 }
 

@@ -81,12 +81,14 @@ struct ClosestIO {   // extension queue -> hit records for the shade kernel
 
 struct ShadowIO {    // shadow queue -> verdict in the contribution table
   const double* ray; size_t cap; const uint32_t* cidx; int* res;
+  const uint32_t* perm;   // launch order -> queue position (RRT_OPT_SORT_SHADOW, rrt_kernels.cuh k_bin_*), or nullptr: ray i is the i-th of the queue
   static constexpr bool GEO = false;
   __device__ __forceinline__ void load(int i, d3& o, d3& d, double& tmin, double& tmax) const {
-    o = D3(ray[i], ray[cap + i], ray[2 * cap + i]); d = D3(ray[3 * cap + i], ray[4 * cap + i], ray[5 * cap + i]);
-    tmin = 0.0; tmax = ray[6 * cap + i];
+    const size_t q = perm ? (size_t)perm[i] : (size_t)i;
+    o = D3(ray[q], ray[cap + q], ray[2 * cap + q]); d = D3(ray[3 * cap + q], ray[4 * cap + q], ray[5 * cap + q]);
+    tmin = 0.0; tmax = ray[6 * cap + q];
   }
-  __device__ __forceinline__ void store(int i, const Hit& h) const { res[cidx[i]] = h.status == 1 ? h.prim : -1; }
+  __device__ __forceinline__ void store(int i, const Hit& h) const { res[cidx[perm ? (size_t)perm[i] : (size_t)i]] = h.status == 1 ? h.prim : -1; }
 };
 
 template <bool ANY>
@@ -751,8 +753,9 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB_CLOSEST(V, STEP)) k_trace_
 template <bool ANY, bool COUNT, int V, int STEP = 0, int PARK = 0>
 __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINBLOCKS(V, STEP)) k_trace_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh,
                                                                const double* __restrict__ ray, size_t cap, const int* __restrict__ count_ptr,
-                                                               int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt, const ParkQ pk) {
-  ShadowIO io; io.ray = ray; io.cap = cap; io.cidx = cidx; io.res = res;
+                                                               int* cursor, const uint32_t* __restrict__ cidx, int* __restrict__ res,
+                                                               const uint32_t* __restrict__ perm, Counters* gcnt, const ParkQ pk) {
+  ShadowIO io; io.ray = ray; io.cap = cap; io.cidx = cidx; io.res = res; io.perm = perm;
 #if RRT_AB
   if constexpr (V == 1) trace_sched<ANY, COUNT>(sc, bh, io, *count_ptr, cursor, gcnt);
   else if constexpr (STEP == 3) trace_decoupled<ANY, COUNT, (V == 0 ? 2 : V)>(sc, bh, io, *count_ptr, cursor, gcnt);
@@ -788,7 +791,7 @@ __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB_ESCAPE) k_escape_closest(c
 template <bool COUNT>
 __global__ void __launch_bounds__(RRT_BLOCK, RRT_MINB_ESCAPE) k_escape_shadow(const __grid_constant__ DevScene sc, const __grid_constant__ DevHole bh, size_t cap,
                                                                               const uint32_t* __restrict__ cidx, int* __restrict__ res, Counters* gcnt, const ParkQ in, const ParkQ out) {
-  ShadowIO io; io.ray = nullptr; io.cap = cap; io.cidx = cidx; io.res = res;
+  ShadowIO io; io.ray = nullptr; io.cap = cap; io.cidx = cidx; io.res = res; io.perm = nullptr;
   escape_persistent<COUNT>(sc, bh, io, in, out, gcnt);
 }
 template <bool ANY>

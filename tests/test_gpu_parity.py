@@ -415,6 +415,30 @@ def test_converged_image_against_the_reference_on_an_independent_rng(api):
     assert np.median(np.abs(z)) < 1.2 and (np.abs(z) > 6).mean() < 0.01
 
 
+def test_shadow_rays_sorted_by_origin_cell_give_the_same_frame(api):
+    """RRT_OPT_SORT_SHADOW (meshes, hole on): the shadow rays of a launch handed to the trace kernel cell by cell of their origin instead of
+    in queue order.  Which lane traces a ray changes; frame, sample counts and every counter must not."""
+    s = load_scene("cbbunny_microfacet_480x360")
+    p = sc.make_params(ns_aa=40, max_ray_depth=4, ns_area_light=2, samples_per_batch=16, max_tolerance=0.2, seed=11)   # adaptive stop acts: 3 rounds
+    out = {}
+    for sort in (0, 1, 2):
+        c = api.Context(0); c.set_option(api.OPT_SORT_SHADOW, sort); c.upload_scene(s); c.set_frame(240, 180)
+        c.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_LITERAL)
+        out[sort] = c.render(p)
+        c.close()
+    h0, c0, st0 = out[0]
+    assert 0 < c0.min() < 40 and c0.max() == 40 and np.isfinite(h0).all() and h0.max() > 0
+    for sort in (1, 2):
+        h, cn, st = out[sort]
+        assert np.array_equal(h, h0) and np.array_equal(cn, c0), sort
+        assert all(st[k] == st0[k] for k in ("paths", "rays", "geodesic_steps", "node_visits", "tri_tests")), sort
+        assert st["kernel_launches"] > st0["kernel_launches"] and st["trace_launches"] == st0["trace_launches"]
+    # not for flat spacetime (a flat shadow ray is one traversal: nothing to repay a sort) and not for the 8-wide kernel of small scenes
+    c = api.Context(0); c.set_option(api.OPT_SORT_SHADOW, 2); c.upload_scene(s); c.set_frame(240, 180); c.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_FLAT)
+    cf = api.Context(0); cf.set_option(api.OPT_SORT_SHADOW, 0); cf.upload_scene(s); cf.set_frame(240, 180); cf.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_FLAT)
+    assert c.render(p)[2]["kernel_launches"] == cf.render(p)[2]["kernel_launches"]
+
+
 def test_c2_full_size_properties(api):
     """BASELINE config 2 at full size: size-independent properties instead of a CPU run."""
     c, s = c2_setup(api)
@@ -567,7 +591,7 @@ def test_empty_and_degenerate_inputs(api):
             c.set_blackhole((0, 1, 0), bad_r, 0.1, sc.MODE_LITERAL)
     c.set_blackhole((0, 1, 0), 0.0, 0.1, sc.MODE_LITERAL)      # r = 0 is legal (the reference's -B 0 1 0 0 0.1)
     with pytest.raises(api.RrtError, match="unknown option"):
-        c.set_option(14, 1)
+        c.set_option(15, 1)
     with pytest.raises(api.RrtError, match="positive height"):
         c.set_cell(0, 0, 16, 0)
     c.set_cell(0, 0, 0, 0)

@@ -1,6 +1,6 @@
 """A/B of trace-kernel options on a GPU box: per (workload, option set) the frame time with counters off (best of 3 after a
 warm-up), trace time, and the instrumented counts.  Images must be identical across every option set of a workload.
-usage: ab_trace.py workload[,workload...] "name:opt=val,opt=val;name2:..."     (opt = kernel | grid | width | builder | leaf | topology | streams | overlap | top | escape | shard=N: rank 0 of N)
+usage: ab_trace.py workload[,workload...] "name:opt=val,opt=val;name2:..."     (opt = kernel | grid | width | builder | leaf | topology | streams | overlap | top | escape | sort | shard=N: rank 0 of N | m=N: max ray depth)
 workloads: c2, bunny_box (bunny at 480x360: the in-box pixels of the 1080p frame), bunny_bh, c5, or any bench.py workload; [@spp]"""
 import hashlib, importlib, json, os, sys
 import numpy as np
@@ -10,7 +10,7 @@ import bench
 from util import sc
 api = importlib.import_module("relativistic-ray-tracer_b200.api")
 OPT = dict(kernel=api.OPT_TRACE_KERNEL, grid=api.OPT_CLEARANCE_GRID, width=api.OPT_BVH_WIDTH, builder=api.OPT_BVH_BUILDER, leaf=api.OPT_LEAF_SIZE,
-           topology=api.OPT_BVH_TOPOLOGY, stepper=api.OPT_STEPPER, streams=api.OPT_STREAMS, escape=api.OPT_ESCAPE, top=api.OPT_TOP_NODE, overlap=api.OPT_OVERLAP)
+           topology=api.OPT_BVH_TOPOLOGY, stepper=api.OPT_STEPPER, streams=api.OPT_STREAMS, escape=api.OPT_ESCAPE, top=api.OPT_TOP_NODE, overlap=api.OPT_OVERLAP, sort=api.OPT_SORT_SHADOW)
 sets = []
 for part in (sys.argv[2] if len(sys.argv) > 2 else "default:").split(";"):
     name, _, kv = part.partition(":")
@@ -33,11 +33,12 @@ for wl in sys.argv[1].split(","):
             c.set_tile_shard(8, 0, extra["shard"])     # rank 0's share of an N-GPU strong-scaling run, on one GPU
         c.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
         ad = bench.ADAPTIVE.get(wl) if not spp_s else None
-        p = sc.make_params(ns_aa=spp, max_ray_depth=m, ns_area_light=l, seed=3, samples_per_batch=ad["batch"] if ad else spp + 1, max_tolerance=ad["tol"] if ad else 0.05)
+        p = sc.make_params(ns_aa=spp, max_ray_depth=extra.get("m", m), ns_area_light=l, seed=3, samples_per_batch=ad["batch"] if ad else spp + 1, max_tolerance=ad["tol"] if ad else 0.05)
         hdr, _, st = c.render(p)
         c.set_option(api.OPT_COUNTERS, 0)
         best = min((c.render(p)[2] for _ in range(3)), key=lambda s: s["seconds"])
         exact = api.OPT_STEPPER not in opts
+        exact = exact and "m" not in extra
         if exact:
             if base is None:
                 base = hdr
