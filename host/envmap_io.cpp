@@ -1,7 +1,8 @@
 // envmap_io.cpp — environment maps for -e (reference src/main.cpp:42-79 reads them through tinyexr).
 // Two containers:
-//   * OpenEXR scanline files with compression NONE, RLE, ZIPS or ZIP (zlib) and HALF / FLOAT / UINT channels R, G, B; the wavelet
-//     and lossy codecs (PIZ, PXR24, B44, DWA) and tiled / deep / multi-part files are reported, not guessed at;
+//   * OpenEXR scanline files with compression NONE, RLE, ZIPS, ZIP (zlib) or PIZ (wavelet + Huffman, below) and HALF / FLOAT / UINT channels
+//     R, G, B — a superset of what the reference's tinyexr reads (NONE, ZIPS, ZIP, PIZ); the lossy codecs (PXR24, B44, DWA) and tiled / deep /
+//     multi-part files are reported, not guessed at;
 //   * PFM ("PF", little- or big-endian, bottom row first).
 // Output: [h][w][3] floats, row 0 = top, the layout rrt_set_envmap takes.
 #include <stdio.h>
@@ -10,6 +11,7 @@
 
 #include <algorithm>
 #include <map>
+#include <memory>
 
 #include <zlib.h>
 
@@ -100,6 +102,219 @@ bool exr_rle_decode(const uint8_t* in, size_t n, size_t expect, std::vector<uint
 
 struct Channel { std::string name; int type; };   // 0 uint, 1 half, 2 float
 
+// ---------------------------------------------------------------------------------------------------------------- PIZ chunks
+// The codec most HDR probes are saved with, and the one the reference's tinyexr reads beside ZIP (reference CGL/include/CGL/tinyexr.h,
+// DecompressPiz).  As OpenEXR publishes it (ImfPizCompressor, ImfHuf, ImfWav): the 16-bit words of a chunk of up to 32 scan lines — per channel
+// a plane of lines x width x (1 | 2) words — are renumbered densely (a bitmap says which of the 65536 values occur), every plane is
+// Haar-wavelet transformed, and all words are Huffman coded as one sequence with a run marker.  Decoding runs the three steps backwards.
+// A chunk is untrusted input: every read goes through a bounded cursor, every table index is checked.
+namespace piz {
+
+struct Bits {   // MSB-first bit cursor over [p, p + nbytes), never past `limit` bits
+  const uint8_t* p; size_t nbytes; uint64_t pos, limit;
+  uint64_t left() const { return limit - pos; }
+  uint64_t peek(int n) const {   // the next n bits, 1 <= n <= 57, zero-padded past the last byte
+    const size_t byte = (size_t)(pos >> 3);
+    uint64_t acc = 0;
+    for (size_t k = 0; k < 8; ++k) acc = (acc << 8) | (byte + k < nbytes ? p[byte + k] : 0);
+    acc <<= (pos & 7);           // drop what has been read of the first byte: at least 57 bits remain at the top
+    return acc >> (64 - n);
+  }
+  void skip(int n) { pos += (uint64_t)n; }
+};
+
+const int kMaxLen = 58, kSymbols = 65537, kFast = 12;
+
+struct Code {
+  uint8_t len[kSymbols];
+  uint64_t base[kMaxLen + 1]; uint32_t count[kMaxLen + 1], offset[kMaxLen + 1];
+  std::vector<uint32_t> syms;                       // symbols in (length, symbol) order: canonical codes count up along it
+  std::vector<uint32_t> fast;                       // kFast-bit prefix -> symbol << 8 | length, 0 = longer code (or none)
+};
+
+// code lengths of symbols im .. iM, 6 bits each; 59 .. 62 = 2 .. 5 zero lengths, 63 + 8 bits = 6 .. 261 zero lengths
+bool read_lengths(Bits* in, uint32_t im, uint32_t iM, Code* c) {
+  memset(c->len, 0, sizeof c->len);
+  for (uint32_t s = im; s <= iM;) {
+    if (in->left() < 6) return false;
+    const uint32_t l = (uint32_t)in->peek(6); in->skip(6);
+    if (l >= 59) {
+      uint32_t run = l - 59 + 2;
+      if (l == 63) { if (in->left() < 8) return false; run = (uint32_t)in->peek(8) + 6; in->skip(8); }
+      if (s + run > iM + 1) return false;
+      s += run;
+    } else c->len[s++] = (uint8_t)l;
+  }
+  return true;
+}
+// canonical assignment: the longest codes take the numerically smallest values, and within a length codes count up with the symbol
+bool build_code(Code* c) {
+  memset(c->count, 0, sizeof c->count);
+  for (int s = 0; s < kSymbols; ++s) c->count[c->len[s]]++;
+  c->count[0] = 0;
+  uint64_t next = 0; uint32_t off = 0;
+  for (int l = kMaxLen; l >= 1; --l) { c->base[l] = next; next = (next + c->count[l]) >> 1; }
+  for (int l = 1; l <= kMaxLen; ++l) {
+    c->offset[l] = off; off += c->count[l];
+    if (c->count[l] && c->base[l] + c->count[l] > ((uint64_t)1 << l)) return false;   // more codes than l bits hold
+  }
+  if (off < 2) return false;                         // at least one value and the run marker
+  c->syms.assign(off, 0);
+  std::vector<uint32_t> fill(c->offset, c->offset + kMaxLen + 1);
+  for (int s = 0; s < kSymbols; ++s) if (c->len[s]) c->syms[fill[c->len[s]]++] = (uint32_t)s;
+  c->fast.assign((size_t)1 << kFast, 0);
+  for (int l = 1; l <= kFast; ++l)
+    for (uint32_t k = 0; k < c->count[l]; ++k) {
+      const uint64_t code = c->base[l] + k;
+      const size_t lo = (size_t)(code << (kFast - l)), hi = (size_t)((code + 1) << (kFast - l));
+      for (size_t e = lo; e < hi; ++e) {
+        if (c->fast[e]) return false;                // two codes share a prefix: not a prefix code
+        c->fast[e] = (c->syms[c->offset[l] + k] << 8) | (uint32_t)l;
+      }
+    }
+  return true;
+}
+bool next_symbol(const Code& c, Bits* in, uint32_t* sym) {
+  const uint32_t f = c.fast[(size_t)in->peek(kFast)];
+  if (f) {
+    const int l = (int)(f & 0xFF);
+    if ((uint64_t)l > in->left()) return false;
+    in->skip(l); *sym = f >> 8;
+    return true;
+  }
+  const uint64_t window = in->peek(57);              // codes longer than 57 bits would need 2^57 symbols below them
+  for (int l = kFast + 1; l <= 57; ++l) {
+    if (!c.count[l]) continue;
+    const uint64_t code = window >> (57 - l);
+    if (code >= c.base[l] && code - c.base[l] < c.count[l]) {
+      if ((uint64_t)l > in->left()) return false;
+      in->skip(l); *sym = c.syms[c.offset[l] + (size_t)(code - c.base[l])];
+      return true;
+    }
+  }
+  return false;
+}
+// the Huffman stream of a chunk -> n words
+bool huffman_decode(const uint8_t* src, size_t size, uint16_t* out, size_t n, Code* code) {
+  if (n == 0) return true;
+  if (size < 20) return false;
+  uint32_t im, iM, nbits;
+  memcpy(&im, src, 4); memcpy(&iM, src + 4, 4); memcpy(&nbits, src + 12, 4);
+  if (im >= (uint32_t)kSymbols || iM >= (uint32_t)kSymbols || im > iM) return false;
+  Bits tb; tb.p = src + 20; tb.nbytes = size - 20; tb.pos = 0; tb.limit = 8 * (uint64_t)(size - 20);
+  if (!read_lengths(&tb, im, iM, code)) return false;
+  const size_t table_bytes = (size_t)((tb.pos + 7) >> 3);   // the data starts at the next byte
+  if (!build_code(code) || !code->len[iM]) return false;
+  Bits in; in.p = src + 20 + table_bytes; in.nbytes = size - 20 - table_bytes; in.pos = 0; in.limit = nbits;
+  if (in.limit > 8 * (uint64_t)in.nbytes) return false;
+  size_t k = 0;
+  while (k < n) {
+    uint32_t s;
+    if (!next_symbol(*code, &in, &s)) return false;
+    if (s == iM) {                                    // run marker: the previous word, `count` more times
+      if (in.left() < 8 || k == 0) return false;
+      const size_t run = (size_t)in.peek(8); in.skip(8);
+      if (k + run > n) return false;
+      for (size_t r = 0; r < run; ++r, ++k) out[k] = out[k - 1];
+    } else {
+      if (s > 0xFFFF) return false;
+      out[k++] = (uint16_t)s;
+    }
+  }
+  return true;
+}
+
+// inverse Haar steps: (average, difference) -> the two values.  14-bit form: plain integers; 16-bit form: modulo 2^16
+inline void pair14(uint16_t l, uint16_t h, uint16_t* a, uint16_t* b) {
+  const int ls = (int16_t)l, hs = (int16_t)h;
+  const int ai = ls + (hs & 1) + (hs >> 1);
+  *a = (uint16_t)ai; *b = (uint16_t)(ai - hs);
+}
+inline void pair16(uint16_t l, uint16_t h, uint16_t* a, uint16_t* b) {
+  const int bb = ((int)l - ((int)h >> 1)) & 0xFFFF;
+  *b = (uint16_t)bb; *a = (uint16_t)(((int)h + bb - 0x8000) & 0xFFFF);
+}
+// one plane: element (x, y) at a[x * ox + y * oy]; levels from the coarsest (largest power of two <= min(nx, ny)) down to 1
+template <void (*PAIR)(uint16_t, uint16_t, uint16_t*, uint16_t*)>
+void unwavelet(uint16_t* a, int nx, size_t ox, int ny, size_t oy) {
+  int p = 1;
+  while (p <= std::min(nx, ny)) p <<= 1;
+  p >>= 1;
+  for (int p2 = p, q = p >> 1; q >= 1; p2 = q, q >>= 1) {
+    int y = 0;
+    for (; y + p2 <= ny; y += p2) {
+      int x = 0;
+      for (; x + p2 <= nx; x += p2) {
+        uint16_t* v00 = a + x * ox + y * oy; uint16_t* v01 = v00 + q * ox; uint16_t* v10 = v00 + q * oy; uint16_t* v11 = v10 + q * ox;
+        uint16_t i00, i01, i10, i11;
+        PAIR(*v00, *v10, &i00, &i10); PAIR(*v01, *v11, &i01, &i11);
+        PAIR(i00, i01, v00, v01); PAIR(i10, i11, v10, v11);
+      }
+      if (nx & q) {                                   // a last column without a partner in x
+        uint16_t* v00 = a + x * ox + y * oy; uint16_t* v10 = v00 + q * oy;
+        uint16_t i00;
+        PAIR(*v00, *v10, &i00, v10); *v00 = i00;
+      }
+    }
+    if (ny & q)                                       // a last line without a partner in y
+      for (int x = 0; x + p2 <= nx; x += p2) {
+        uint16_t* v00 = a + x * ox + y * oy; uint16_t* v01 = v00 + q * ox;
+        uint16_t i00;
+        PAIR(*v00, *v01, &i00, v01); *v00 = i00;
+      }
+  }
+}
+
+// one chunk -> `expect` bytes in the uncompressed chunk layout (per scan line, per channel, the channel's row)
+bool decode_chunk(const uint8_t* src, size_t size, const std::vector<Channel>& chans, int w, int lines, size_t expect, Code* code,
+                  std::vector<uint8_t>* out, std::string* err) {
+  const size_t nwords = expect / 2;
+  if (size < 4) { *err = "truncated PIZ chunk"; return false; }
+  uint16_t lo, hi;
+  memcpy(&lo, src, 2); memcpy(&hi, src + 2, 2);
+  size_t pos = 4;
+  std::vector<uint8_t> bitmap(8192, 0);
+  if (hi >= 8192) { *err = "corrupt PIZ chunk (value bitmap)"; return false; }
+  if (lo <= hi) {
+    const size_t nb = (size_t)hi - lo + 1;
+    if (pos + nb > size) { *err = "truncated PIZ chunk"; return false; }
+    memcpy(bitmap.data() + lo, src + pos, nb); pos += nb;
+  }
+  std::vector<uint16_t> value(65536, 0);             // dense number -> value; zero is always number 0
+  uint32_t n_values = 0;
+  for (uint32_t v = 0; v < 65536; ++v)
+    if (v == 0 || (bitmap[v >> 3] & (1u << (v & 7)))) value[n_values++] = (uint16_t)v;
+  const uint32_t max_number = n_values - 1;
+  if (pos + 4 > size) { *err = "truncated PIZ chunk"; return false; }
+  int32_t hlen; memcpy(&hlen, src + pos, 4); pos += 4;
+  if (hlen < 0 || pos + (size_t)hlen > size) { *err = "truncated PIZ chunk"; return false; }
+  std::vector<uint16_t> words(nwords);
+  if (!huffman_decode(src + pos, (size_t)hlen, words.data(), nwords, code)) { *err = "corrupt Huffman data in PIZ chunk"; return false; }
+  size_t start = 0;
+  for (const Channel& c : chans) {
+    const size_t sz = c.type == 1 ? 1 : 2;
+    for (size_t j = 0; j < sz; ++j) {
+      if (max_number < (1u << 14)) unwavelet<pair14>(words.data() + start + j, w, sz, lines, (size_t)w * sz);
+      else unwavelet<pair16>(words.data() + start + j, w, sz, lines, (size_t)w * sz);
+    }
+    start += (size_t)w * lines * sz;
+  }
+  for (uint16_t& x : words) x = value[x];            // numbers past the last one map to 0, as in the format's own table
+  out->resize(expect);
+  uint8_t* q = out->data();
+  std::vector<size_t> at(chans.size());
+  start = 0;
+  for (size_t k = 0; k < chans.size(); ++k) { at[k] = start; start += (size_t)w * lines * (chans[k].type == 1 ? 1 : 2); }
+  for (int l = 0; l < lines; ++l)
+    for (size_t k = 0; k < chans.size(); ++k) {
+      const size_t n = (size_t)w * (chans[k].type == 1 ? 1 : 2);
+      memcpy(q, words.data() + at[k], 2 * n); q += 2 * n; at[k] += n;
+    }
+  return true;
+}
+
+}  // namespace piz
+
 bool load_exr(const std::vector<uint8_t>& b, int* w, int* h, std::vector<float>* rgb, std::string* err) {
   size_t pos = 8;
   uint32_t version; memcpy(&version, b.data() + 4, 4);
@@ -138,10 +353,10 @@ bool load_exr(const std::vector<uint8_t>& b, int* w, int* h, std::vector<float>*
     else if (name == "dataWindow") { if (size < 16) { *err = "truncated OpenEXR attribute"; return false; } memcpy(dw, v, 16); }
     pos += (size_t)size;
   }
-  if (compression < 0 || compression > 3) {
+  if (compression < 0 || compression > 4) {
     static const char* names[] = {"NONE", "RLE", "ZIPS", "ZIP", "PIZ", "PXR24", "B44", "B44A", "DWAA", "DWAB"};
     *err = std::string("OpenEXR compression ") + (compression >= 0 && compression < 10 ? names[compression] : "(unknown)") +
-           " is not supported (NONE, RLE, ZIPS and ZIP are): re-save the map with one of those, or as .pfm";
+           " is not supported (NONE, RLE, ZIPS, ZIP and PIZ are): re-save the map with one of those, or as .pfm";
     return false;
   }
   const int64_t w64 = (int64_t)dw[2] - dw[0] + 1, h64 = (int64_t)dw[3] - dw[1] + 1;
@@ -154,7 +369,8 @@ bool load_exr(const std::vector<uint8_t>& b, int* w, int* h, std::vector<float>*
     if (c.type < 0 || c.type > 2) { *err = "unknown OpenEXR pixel type"; return false; }
     row_bytes += (size_t)*w * (c.type == 1 ? 2 : 4);
   }
-  const int lines_per_chunk = compression == 3 ? 16 : 1;
+  const int lines_per_chunk = compression == 4 ? 32 : compression == 3 ? 16 : 1;
+  std::unique_ptr<piz::Code> piz_code(compression == 4 ? new piz::Code() : nullptr);
   const int n_chunks = (*h + lines_per_chunk - 1) / lines_per_chunk;
   if (pos + 8 * (size_t)n_chunks > b.size()) { *err = "truncated OpenEXR offset table"; return false; }
   rgb->assign((size_t)*w * *h * 3, 0.f);
@@ -169,16 +385,20 @@ bool load_exr(const std::vector<uint8_t>& b, int* w, int* h, std::vector<float>*
     const size_t expect = row_bytes * (size_t)lines;
     if (size < 0 || off + 8 + (size_t)size > b.size()) { *err = "truncated OpenEXR chunk"; return false; }
     const uint8_t* q = b.data() + off + 8;
-    if (compression != 0 && (size_t)size < expect) {      // a chunk that did not shrink is stored raw
-      if (compression == 1) {
+    // a chunk that did not shrink is stored raw (same size); a PIZ chunk LARGER than its data can only be codec output (writers without the
+    // raw fall-back exist, and the reference's reader decodes whatever it finds)
+    if (compression != 0 && ((size_t)size < expect || (compression == 4 && (size_t)size > expect))) {
+      if (compression == 4) {
+        if (!piz::decode_chunk(q, (size_t)size, chans, *w, lines, expect, piz_code.get(), &block, err)) return false;
+        q = block.data();
+      } else if (compression == 1) {
         if (!exr_rle_decode(q, (size_t)size, expect, &tmp)) { *err = "corrupt RLE data in OpenEXR chunk"; return false; }
       } else {
         tmp.resize(expect);
         uLongf got = (uLongf)expect;
         if (uncompress(tmp.data(), &got, q, (uLong)size) != Z_OK || got != expect) { *err = "corrupt zlib data in OpenEXR chunk"; return false; }
       }
-      exr_unpredict_and_interleave(tmp, &block);
-      q = block.data();
+      if (compression != 4) { exr_unpredict_and_interleave(tmp, &block); q = block.data(); }
     } else if ((size_t)size != expect) { *err = "OpenEXR chunk of unexpected size"; return false; }
     for (int l = 0; l < lines; ++l) {
       const int row = row0 + l;

@@ -5,7 +5,7 @@
 //     -b <FLOAT> -d <FLOAT> -c <camera settings file>  -B <x> <y> <z> <r> <dtheta>        exactly as the reference
 //   additions (not in the reference): -F (flat spacetime, the reference has no working switch), -S <seed>,
 //     -G <device>, --dump-scene <out.rrtscene> (load + flatten only: needs no GPU), --dump-camera <file>
-//   -e <map.exr | map.pfm>: scan-line OpenEXR (NONE / RLE / ZIPS / ZIP) or PFM.
+//   -e <map.exr | map.pfm>: scan-line OpenEXR (NONE / RLE / ZIPS / ZIP / PIZ) or PFM.
 //   not available: the interactive viewer (no graphics stack on this box): without -f the program renders to
 //     <scene>_screenshot_<time>.png instead of opening a window.
 // -t is accepted and ignored: the device replaces the worker threads.

@@ -96,7 +96,7 @@ bool save_rrtscene(const std::string& filename, const FlatScene& scene, const Ca
 bool halfedge_triangles_and_normals(const std::vector<std::vector<size_t>>& polygons, const std::vector<Vector3D>& positions,
                                     std::vector<size_t>* out_tri, std::vector<Vector3D>* out_normals, std::string* error);
 
-// ---- environment maps for -e: scan-line OpenEXR (NONE / RLE / ZIPS / ZIP; HALF / FLOAT / UINT) or PFM -> [h][w][3] floats, row 0 = top
+// ---- environment maps for -e: scan-line OpenEXR (NONE / RLE / ZIPS / ZIP / PIZ; HALF / FLOAT / UINT) or PFM -> [h][w][3] floats, row 0 = top
 bool load_envmap(const std::string& filename, int* width, int* height, std::vector<float>* rgb, std::string* error);
 
 // ---- PNG (8-bit RGBA, stored deflate blocks: no compression library in the image)

@@ -7,6 +7,7 @@
 #                         by sed into oracle/_ref/gen/ at build time.
 #   oracle/_ref/ref_probe[_flat]  our probe TU (oracle/ref_probe.cpp) linked against the reference objects:
 #                         dumps flattened scenes, KAT vectors and HDR renders for tests/golden/.
+#   oracle/_ref/exr_probe the reference's `-e map.exr` reader alone (tinyexr as vendored by the reference), for the OpenEXR fixtures
 #   oracle/_ref/dae/      the bundled scenes the configs use (data, needed by the CPU baseline on the GPU box)
 # Does not run the reference's CMake (it requires OpenGL/Freetype, absent here).
 set -euo pipefail
@@ -50,6 +51,8 @@ $CXX -O3 -fopenmp -o "$OUT/ref_bh"   $ALL   $STUBS -lpthread
 $CXX -O3 -fopenmp -o "$OUT/ref_flat" $NOBVH "$OUT/gen/bvh_flat.o" $STUBS -lpthread
 $CXX -O3 -fopenmp -o "$OUT/ref_probe"      $NOMAIN    "$OUT/gen/ref_probe.o" $STUBS -lpthread
 $CXX -O3 -fopenmp -o "$OUT/ref_probe_flat" $NOMAINBVH "$OUT/gen/bvh_flat.o" "$OUT/gen/ref_probe.o" $STUBS -lpthread
+# the reference's OpenEXR reader on its own (oracle/exr_probe.cpp): pins the PIZ fixtures of tests/golden/
+$CXX -std=gnu++11 -O2 -w -I$REF/CGL/include -o "$OUT/exr_probe" "$HERE/exr_probe.cpp"
 for f in CBspheres_lambertian CBspheres CBspheres_microfacet_al_ag CBbunny CBbunny_microfacet_cu CBgems CBcoil CBempty; do
   cp -f "$REF/dae/sky/$f.dae" "$OUT/dae/" 2>/dev/null || true
 done

@@ -3,7 +3,7 @@
 oracle/build_ref.sh from /root/reference).  Runs only in the build container; the fixtures it writes are
 committed so that the GPU box (no /root/reference) can check against them.
 
-    python tests/golden/make_golden.py [kat] [render] [scenes] [fullsize] [bvhorder] [rng]
+    python tests/golden/make_golden.py [kat] [render] [scenes] [fullsize] [bvhorder] [rng] [piz]
 
 Inputs are seeded numpy draws; outputs are what the reference's BVHAccel::intersect, BlackHole::next_micro_ray,
 Camera::generate_ray, BSDF::f/sample_f, SceneLight::sample_L and PathTracer::raytrace_pixel return for them.
@@ -423,8 +423,54 @@ def make_fullsize(only=None):
         print("render_full", name, "mean radiance %.5f  paths %d  %.1f s" % (img[..., :3].mean(), img[..., 3].sum(), a[w * h * 4 + 3]), flush=True)
 
 
+PIZ_FILES = {   # name -> (pixel type: 1 half / 2 float, what it exercises)
+    "envmap_piz_half_96x70": (1, "sun + sky + noise: three chunks (32, 32, 6 lines), 14-bit wavelet, Huffman codes well past 12 bits, runs"),
+    "envmap_piz_float_20x35": (2, "32-bit samples (two 16-bit planes per channel), noise: the chunks come out larger than their data"),
+    "envmap_piz_half_wide_200x37": (1, "19 200 distinct values in the first chunk: more than 2^14 numbers, the modulo-2^16 wavelet"),
+}
+
+
+def piz_image(name):
+    rng = np.random.default_rng(40)
+    if name == "envmap_piz_half_96x70":
+        yy, xx = np.mgrid[0:70, 0:96]
+        sun = np.exp(-((yy - 12) ** 2 + (xx - 60) ** 2) / 40.0)[..., None] * np.array([900.0, 700.0, 400.0])
+        sky = (0.2 + 0.6 * (1 - yy / 70.0))[..., None] * np.array([0.4, 0.6, 1.0])
+        return (sun + sky + rng.uniform(0, 0.02, (70, 96, 3))).astype(np.float32)
+    if name == "envmap_piz_float_20x35":
+        return rng.uniform(0, 4, (35, 20, 3)).astype(np.float32)
+    pat = rng.choice(0x7C00, size=200 * 32 * 3, replace=False).astype(np.uint16)         # distinct finite non-negative halves
+    top = pat.view(np.float16).astype(np.float32).reshape(32, 200, 3)
+    return np.concatenate([top, rng.uniform(0, 1, (5, 200, 3)).astype(np.float32)], axis=0)
+
+
+def make_piz():
+    """PIZ-compressed OpenEXR maps: written by tests/exr_piz.py (the reference's tinyexr has its PIZ encoder compiled out), read back by the
+    reference's own `-e` code path (oracle/exr_probe.cpp on the reference's vendored tinyexr); what THAT returns is the expected output."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import struct
+    import exr_piz
+    for name, (pt, _) in PIZ_FILES.items():
+        img = piz_image(name)
+        path = os.path.join(HERE, name + ".exr")
+        exr_piz.write_exr_piz(path, img, pt)
+        out = tmpf(name + ".bin")
+        run([os.path.join(REF, "exr_probe"), path, out])
+        raw = open(out, "rb").read()
+        w, h = struct.unpack("<ii", raw[:8])
+        got = np.frombuffer(raw[8:], np.float32).reshape(h, w, 3)
+        want = img.astype(np.float16).astype(np.float32) if pt == 1 else img
+        assert np.array_equal(got, want), name        # lossless codec: the reference decodes what was written
+        store = got.astype(np.float16) if pt == 1 else got
+        assert np.array_equal(store.astype(np.float32), got)
+        np.savez_compressed(os.path.join(HERE, name + ".expected.npz"), rgb=store)
+        print("%s: %d x %d, %d bytes, reference reader agrees" % (name, w, h, os.path.getsize(path)))
+
+
 if __name__ == "__main__":
     what = sys.argv[1:] or ["scenes", "kat", "render"]
+    if "piz" in what:
+        make_piz()
     if "scenes" in what:
         make_scenes([w for w in what if w in SCENES] or None)
     if "kat" in what:
