@@ -341,6 +341,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="override samples_per_batch (the reference's -a batch; default rule: shard.weak_scaling_params)")
     ap.add_argument("--streams", type=int, default=0, help="RRT_OPT_STREAMS override (0 = library default)")
     ap.add_argument("--no-overlap", action="store_true", help="RRT_OPT_OVERLAP = 0")
+    ap.add_argument("--sort-shadow", type=int, default=-1, help="RRT_OPT_SORT_SHADOW override (0 never, 1 chunks under 2 M paths, 2 always; -1 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -389,6 +390,8 @@ def main():
     ctx.set_option(api.OPT_BVH_BUILDER, {"auto": 0, "device": 1, "host": 2}[args.builder])
     if args.streams:
         ctx.set_option(api.OPT_STREAMS, args.streams)
+    if args.sort_shadow >= 0:
+        ctx.set_option(api.OPT_SORT_SHADOW, args.sort_shadow)
     if args.no_overlap:
         ctx.set_option(api.OPT_OVERLAP, 0)
     ctx.upload_scene(s)
