@@ -1,6 +1,6 @@
 """A/B of trace-kernel options on a GPU box: per (workload, option set) the frame time with counters off (best of 3 after a
 warm-up), trace time, and the instrumented counts.  Images must be identical across every option set of a workload.
-usage: ab_trace.py workload[,workload...] "name:opt=val,opt=val;name2:..."     (opt = kernel | grid | width | builder | leaf | topology | streams | overlap | top | escape | sort | shard=N: rank 0 of N | m=N: max ray depth)
+usage: ab_trace.py workload[,workload...] "name:opt=val,opt=val;name2:..."     (opt = kernel | grid | width | builder | leaf | topology | streams | overlap | top | escape | sort | shard=N: rank 0 of N | m=N: max ray depth | inflight=N: paths per chunk | workgb=N: work-buffer budget)
 workloads: c2, bunny_box (bunny at 480x360: the in-box pixels of the 1080p frame), bunny_bh, c5, or any bench.py workload; [@spp]"""
 import hashlib, importlib, json, os, sys
 import numpy as np
@@ -29,11 +29,14 @@ for wl in sys.argv[1].split(","):
         import time
         t0 = time.perf_counter(); c.upload_scene(scene); up = time.perf_counter() - t0
         c.set_frame(W, H)
+        if extra.get("workgb"):
+            c.set_option(api.OPT_WORK_BYTES, extra["workgb"] << 30)
         if extra.get("shard"):
             c.set_tile_shard(8, 0, extra["shard"])     # rank 0's share of an N-GPU strong-scaling run, on one GPU
         c.set_blackhole((0, 1, 0), 0.1, 0.1, sc.MODE_LITERAL if mode == "bh" else sc.MODE_FLAT)
         ad = bench.ADAPTIVE.get(wl) if not spp_s else None
-        p = sc.make_params(ns_aa=spp, max_ray_depth=extra.get("m", m), ns_area_light=l, seed=3, samples_per_batch=ad["batch"] if ad else spp + 1, max_tolerance=ad["tol"] if ad else 0.05)
+        p = sc.make_params(ns_aa=spp, max_ray_depth=extra.get("m", m), ns_area_light=l, seed=3, samples_per_batch=ad["batch"] if ad else spp + 1, max_tolerance=ad["tol"] if ad else 0.05,
+                           max_paths_in_flight=extra.get("inflight", 0))
         hdr, _, st = c.render(p)
         c.set_option(api.OPT_COUNTERS, 0)
         best = min((c.render(p)[2] for _ in range(3)), key=lambda s: s["seconds"])
