@@ -161,7 +161,7 @@ struct ParkQ {
 };
 
 /* ---------------------------------------------------------------- variant 0 (default): chord-lockstep loop */
-/* Escape warp (RRT_ESCAPE_WARP = 1; hole on, FP64 stepper).  MEASURED SLOWER, off by default, kept as the record of the experiment.
+/* Escape warp (RRT_AB = 1 and RRT_ESCAPE_WARP = 1; hole on, FP64 stepper).  MEASURED SLOWER, not in the default build, kept as the record of the experiment.
  * In a launch of in-box rays a third of all chords belong to rays that have left the scene box through the open front and still walk their 63
  * chords (the reference never stops): they need no traversal, but each of them holds a lane of a warp whose other lanes do — the tree-top record
  * is visited at 20 of 32 lanes (profiles/r02_s_attribution_c4_shadow_final.txt).  With the flag on, warp 0 of every block takes such rays over: a
@@ -192,7 +192,7 @@ __device__ __forceinline__ void trace_persistent(const DevScene& sc, const DevHo
   __shared__ double seg_mem[SMEM ? 7 * RRT_SEG_STRIDE : 1];
   double* sm = seg_mem + (SMEM ? threadIdx.x : 0);
   int* stack = stack_mem + threadIdx.x;
-  constexpr bool EW = RRT_ESCAPE_WARP && SMEM && RRT_BLOCK >= 64;
+  constexpr bool EW = RRT_AB && RRT_ESCAPE_WARP && SMEM && RRT_BLOCK >= 64;   /* A/B builds only: make EXTRA="-DRRT_AB=1 -DRRT_ESCAPE_WARP=1" */
   __shared__ EscQ eq_mem[1];   /* unreferenced, hence dropped, when EW is false */
   EscQ& eq = eq_mem[0];
   const bool esc_warp = EW && (threadIdx.x >> 5) == 0;
