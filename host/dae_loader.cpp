@@ -100,6 +100,9 @@ struct Loader {
   std::vector<NodeRec> nodes;
   std::string err;
 
+  // "#id" -> "id"; an empty attribute has nothing after its terminator
+  static const char* ref_id(const char* s) { return (s && *s) ? s + 1 : ""; }
+
   void uri_load(const XmlNode* e) {
     if (const char* id = e->attr("id")) sources[id] = e;
     for (const auto& c : e->children) uri_load(c.get());
@@ -112,7 +115,7 @@ struct Loader {
   const XmlNode* get_element(const XmlNode* xml, const std::string& query) const {
     const XmlNode* e = xml->path(query);
     if (e)
-      if (const char* url = e->attr("url")) e = uri_find(url + 1);
+      if (const char* url = e->attr("url")) e = uri_find(ref_id(url));
     return e;
   }
   const XmlNode* technique_common(const XmlNode* xml) const {
@@ -175,8 +178,8 @@ struct Loader {
     if (!im) return true;
     const char* target = im->attr("target");
     if (!target) return fail("no target material in instance_material");
-    const XmlNode* m = uri_find(target + 1);
-    if (!m) return fail(std::string("invalid target material id: ") + (target + 1));
+    const XmlNode* m = uri_find(ref_id(target));
+    if (!m) return fail(std::string("invalid target material id: ") + ref_id(target));
     rec->has_material = true;
     return parse_material(m, &rec->material);
   }
@@ -245,8 +248,9 @@ struct Loader {
       if (!id || !fa) continue;
       std::vector<float> floats;
       size_t count = (size_t)fa->int_attr("count");
-      floats.reserve(count);
       const char* p = text_of(fa) ? text_of(fa) : "";
+      if (count > strlen(p) + 1) return fail("float_array count exceeds its data");   // a negative or damaged count: no allocation, no endless loop
+      floats.reserve(count);
       float last = 0.f;
       for (size_t i = 0; i < count; ++i) {
         char* end = nullptr;
@@ -264,7 +268,7 @@ struct Loader {
       const char* sem = in->attr("semantic");
       if (!sem || strcmp(sem, "POSITION")) continue;
       const char* source = in->attr("source");
-      auto it = arrays.find(source ? source + 1 : "");
+      auto it = arrays.find(ref_id(source));
       if (it == arrays.end()) return fail("undefined input source for POSITION");
       const std::vector<float>& f = it->second;
       for (size_t i = 0; i + 2 < f.size(); i += 3) vertices.push_back(Vector3D(f[i], f[i + 1], f[i + 2]));
@@ -280,15 +284,21 @@ struct Loader {
       if (!sem) continue;
       if (!strcmp(sem, "VERTEX")) {
         has_v = true; v_off = off;
-        if (!source || vertices_id != source + 1) return fail("undefined source for VERTEX semantic");
+        if (!source || vertices_id != ref_id(source)) return fail("undefined source for VERTEX semantic");
         rec->vertices = vertices;
       } else if (!strcmp(sem, "NORMAL")) has_n = true;
       else if (!strcmp(sem, "TEXCOORD")) has_t = true;
     }
     size_t n_poly = (size_t)pl->int_attr("count");
     size_t stride = (has_v ? 1 : 0) + (has_n ? 1 : 0) + (has_t ? 1 : 0);
+    /* the reference indexes p[k * stride + offset] without a check; a VERTEX offset outside the stride reads past the array there */
+    if (has_v && v_off >= stride) return fail("VERTEX offset outside the polylist's index stride");
     const XmlNode* vcount = pl->child("vcount");
     if (!vcount) return fail("polygon sizes undefined in geometry");
+    const XmlNode* pe = pl->child("p");
+    if (!pe) return fail("no index array defined in geometry");
+    const size_t vcount_len = strlen(text_of(vcount) ? text_of(vcount) : ""), p_len = strlen(text_of(pe) ? text_of(pe) : "");
+    if (n_poly > vcount_len + 1) return fail("polylist count exceeds its vcount data");
     std::vector<size_t> sizes; sizes.reserve(n_poly);
     size_t n_idx = 0;
     {
@@ -298,12 +308,12 @@ struct Loader {
         char* end = nullptr;
         unsigned long long v = strtoull(p, &end, 10);
         if (end == p) v = last; else { last = (size_t)v; p = end; }
+        if (v > p_len + 1) return fail("polygon size exceeds the index data");
         sizes.push_back((size_t)v);
         n_idx += (size_t)v * stride;
+        if (n_idx > p_len + 1) return fail("polygon sizes exceed the index data");
       }
     }
-    const XmlNode* pe = pl->child("p");
-    if (!pe) return fail("no index array defined in geometry");
     std::vector<size_t> indices; indices.reserve(n_idx);
     {
       const char* p = text_of(pe) ? text_of(pe) : "";
@@ -319,7 +329,11 @@ struct Loader {
     if (has_v) {
       size_t k = 0;
       for (size_t i = 0; i < n_poly; ++i)
-        for (size_t j = 0; j < sizes[i]; ++j, ++k) rec->polygons[i].push_back(indices[k * stride + v_off]);
+        for (size_t j = 0; j < sizes[i]; ++j, ++k) {
+          const size_t v = indices[k * stride + v_off];
+          if (v >= rec->vertices.size()) return fail("polygon refers to a vertex that does not exist");
+          rec->polygons[i].push_back(v);
+        }
     }
     return true;
   }

@@ -28,6 +28,12 @@ bool put(FILE* f, const std::vector<T>& v) {
 }
 template <class T>
 bool take(FILE* f, std::vector<T>* v, size_t n) {
+  /* the count comes from the file: nothing is allocated that the rest of the file cannot fill */
+  const long here = ftell(f);
+  if (here < 0 || fseek(f, 0, SEEK_END) != 0) return false;
+  const long end = ftell(f);
+  if (end < here || fseek(f, here, SEEK_SET) != 0) return false;
+  if (n > (size_t)(end - here) / sizeof(T)) return false;
   v->resize(n);
   size_t bytes = sizeof(T) * n, pad = (8 - bytes % 8) % 8;
   char z[8];
