@@ -57,7 +57,8 @@ bool load_pfm(const std::vector<uint8_t>& b, int* w, int* h, std::vector<float>*
   *w = atoi(token().c_str()); *h = atoi(token().c_str());
   double scale = atof(token().c_str());
   ++pos;   // the single whitespace after the scale
-  if (*w <= 0 || *h <= 0 || scale == 0) { *err = "malformed PFM header"; return false; }
+  if (*w <= 0 || *h <= 0 || scale == 0 || scale != scale) { *err = "malformed PFM header"; return false; }
+  if (*w > 65536 || *h > 65536 || (int64_t)*w * *h >= ((int64_t)1 << 31)) { *err = "PFM map too large (rrt_set_envmap takes width * height < 2^31)"; return false; }
   size_t need = (size_t)*w * *h * channels * 4;
   if (b.size() < pos + need) { *err = "truncated PFM data"; return false; }
   const bool big = scale > 0;
