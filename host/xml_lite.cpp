@@ -90,7 +90,10 @@ struct Parser {
   }
 
   // parses the content of `node` up to and including its end tag (or end of input for the synthetic root)
-  bool content(XmlNode* node, bool is_root) {
+  // depth: elements open above this one.  Nesting is bounded (COLLADA needs a dozen levels): the parser, the tree's destructor and every walk of
+  // the tree recurse per level, and a file of 300 000 nested tags would otherwise end in a stack overflow instead of a message
+  bool content(XmlNode* node, bool is_root, int depth = 0) {
+    if (depth > 512) { err = "elements nested more than 512 deep"; return false; }
     bool seen_child = false;
     while (i < s.size()) {
       if (s[i] != '<') {
@@ -146,7 +149,7 @@ struct Parser {
       XmlNode* raw = c.get();
       node->children.push_back(std::move(c));
       seen_child = true;
-      if (!self_closed && !content(raw, false)) return false;
+      if (!self_closed && !content(raw, false, depth + 1)) return false;
     }
     if (!is_root) { err = "missing end tag </" + node->name + ">"; return false; }
     return true;

@@ -177,6 +177,13 @@ def test_malformed_collada_is_refused_not_followed(exe, tmp_path, change, messag
     assert r.returncode == 0 and out.exists(), r.stderr                   # the same document, undamaged, loads
 
 
+def test_deeply_nested_xml_is_refused(exe, tmp_path):
+    """the XML reader, the tree's destructor and every walk recurse per nesting level: 300 000 nested tags used to end in a stack overflow"""
+    src = tmp_path / "deep.dae"; src.write_text("<COLLADA>" + "<node>" * 300000 + "</node>" * 300000 + "</COLLADA>")
+    r = subprocess.run([exe, "--dump-scene", str(tmp_path / "o.rrtscene"), str(src)], capture_output=True, text=True, timeout=120)
+    assert r.returncode in (0, 1, 2) and "nested more than 512 deep" in r.stderr
+
+
 def test_scene_file_with_a_damaged_header_allocates_nothing(exe, tmp_path):
     """.rrtscene: array lengths come from the header; a length the rest of the file cannot fill is refused before anything is allocated"""
     src = os.path.join(ROOT, "tests", "golden", "cbempty_480x360.rrtscene")
