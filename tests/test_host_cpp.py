@@ -312,6 +312,23 @@ def test_piz_environment_maps_read_like_the_reference(exe, tmp_path, name):
     assert got.shape == want.shape and np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("name", ["envmap_piz_half_96x70", "envmap_piz_float_20x35", "envmap_piz_half_wide_200x37"])
+def test_piz_fixtures_are_what_the_reference_reader_returns(tmp_path, name):
+    """the pin itself: oracle/_ref/exr_probe (the reference's load_exr calls on the reference's vendored tinyexr, built by oracle/build_ref.sh)
+    decodes the committed maps to the committed expectation"""
+    probe = os.path.join(ROOT, "oracle", "_ref", "exr_probe")
+    if not os.path.exists(probe):
+        pytest.skip("oracle/_ref/exr_probe not built (needs the reference sources)")
+    out = str(tmp_path / "ref.bin")
+    r = subprocess.run([probe, os.path.join(ROOT, "tests", "golden", name + ".exr"), out], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    raw = open(out, "rb").read()
+    w, h = struct.unpack("<ii", raw[:8])
+    got = np.frombuffer(raw[8:], np.float32).reshape(h, w, 3)
+    want = np.load(os.path.join(ROOT, "tests", "golden", name + ".expected.npz"))["rgb"].astype(np.float32)
+    assert np.array_equal(got, want)
+
+
 def test_piz_round_trips_and_refuses_damage(exe, tmp_path):
     """fresh maps through tests/exr_piz.py (the encoder half of the codec, test infrastructure) and back through the host's reader: every shape the
     wavelet treats specially (one pixel, one column, one line, odd sizes, a partial last chunk), both sample sizes, chunks stored raw because the
