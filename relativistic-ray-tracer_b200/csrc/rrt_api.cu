@@ -9,6 +9,7 @@
 #include <mutex>
 #include <string>
 #include <vector>
+#include <chrono>
 
 #include "rrt_bvh.h"
 #include "rrt_kernels.cuh"
@@ -52,6 +53,7 @@ struct rrt_ctx {
   bool in_progress_cb = false; PixelAcc snap_px; size_t snap_npix = 0;
   int tile = 32, rank = 0, world = 1;
   int64_t opt[16];
+  double sync_wait_ms = 0;   /* host time spent blocked on the round-end read-backs of the current render (RRT_ENQUEUE_TIMING) */
   // device memory
   DevBuf d_env, d_env_pdf, d_env_cond, d_env_marg;
   bool have_env = false;
@@ -627,7 +629,9 @@ static int compact(rrt_ctx* ctx, Keep keep, const uint32_t* in, uint32_t n, uint
   k_compact_scan<<<1, 1024, 0, ctx->stream>>>(blk, nblocks, blk + nblocks);
   k_compact_scatter<<<nblocks, RRT_CBLOCK, 0, ctx->stream>>>(keep, in, n, blk, out);
   CK(cudaMemcpyAsync(ctx->h_pinned, blk + nblocks, 4, cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
+  const auto t_wait = std::chrono::steady_clock::now();
+  CK(cudaStreamSynchronize(ctx->stream));   /* the one host round trip of an adaptive round: the next round's launch sizes depend on it */
+  ctx->sync_wait_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_wait).count();
   *n_out = ctx->h_pinned[0];
   return RRT_OK;
 }
@@ -956,6 +960,8 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   cudaEvent_t ev_begin = next_event(ctx), ev_end = next_event(ctx);
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> trace_ev;
   CK(cudaEventRecord(ev_begin, st));
+  const auto t_render0 = std::chrono::steady_clock::now();
+  ctx->sync_wait_ms = 0;
 
   KeepOwned own;
   own.W = ctx->W; own.tile = ctx->tile; own.ntx = rrt_shard_stride(ctx->world); own.rank = ctx->rank; own.world = ctx->world;
@@ -1064,7 +1070,16 @@ static int render_impl(rrt_ctx* ctx, const rrt_params* p, float* d_rgb, int* d_c
   k_finalize<<<grid_small, 256, 0, st>>>(px, npix, d_rgb, d_counts, d_rgbn, gcnt);
   launches++;
   CK(cudaEventRecord(ev_end, st));
+  /* RRT_ENQUEUE_TIMING=1: how far ahead of the device the host's launch loop runs (is a frame of many small launches bound by the enqueue rate?) */
+  static const bool enqueue_timing = getenv("RRT_ENQUEUE_TIMING") != nullptr;
+  const auto t_enq = std::chrono::steady_clock::now();
   CK(cudaStreamSynchronize(st));
+  if (enqueue_timing) {
+    const auto t_done = std::chrono::steady_clock::now();
+    const double host_ms = std::chrono::duration<double, std::milli>(t_enq - t_render0).count();
+    fprintf(stderr, "[rrt] render: %llu launches; host %.2f ms in the launch loop = %.2f ms issuing + %.2f ms blocked on round-end read-backs; device done %.2f ms after the last launch\n",
+            (unsigned long long)launches, host_ms, host_ms - ctx->sync_wait_ms, ctx->sync_wait_ms, std::chrono::duration<double, std::milli>(t_done - t_enq).count());
+  }
   CK(cudaGetLastError());
   if (stats) {
     memset(stats, 0, sizeof *stats);
