@@ -113,43 +113,53 @@ struct Builder {
   }
 
   // construct_bvh (reference src/bvh.cpp:49-96).  prims[0..n) is reordered in place (stable partition, as the
-  // reference's push_back into left/right vectors is).
-  int build_ref(Tree& t, uint32_t* prims, uint32_t n, uint32_t base, int depth) {
-    int me = (int)t.nodes.size();
-    t.nodes.push_back(TNode());
-    if (tasks && n <= grain && depth > 0) {   /* subtree left to a worker thread (build_parallel) */
+  // reference's push_back into left/right vectors is).  The reference recurses; this walks the same tree with an explicit stack, nodes numbered
+  // in the same depth-first preorder: the midpoint split has no depth bound (boxes that all contain one point give a chain as deep as the scene
+  // is large — 50 000 such triangles overflowed the thread's stack here, as they would the reference's), and a scene is input, not code.
+  int build_ref(Tree& t, uint32_t* prims0, uint32_t n0, uint32_t base0, int depth0) {
+    struct Frame { int parent; bool right; uint32_t* prims; uint32_t n, base; int depth; };
+    std::vector<Frame> todo;
+    todo.push_back(Frame{-1, false, prims0, n0, base0, depth0});
+    const int first = (int)t.nodes.size();
+    while (!todo.empty()) {
+      const Frame f = todo.back(); todo.pop_back();
+      uint32_t* prims = f.prims; const uint32_t n = f.n, base = f.base; const int depth = f.depth;
+      const int me = (int)t.nodes.size();
+      t.nodes.push_back(TNode());
+      if (f.parent >= 0) { if (f.right) t.nodes[f.parent].r = me; else t.nodes[f.parent].l = me; }
       t.nodes[me].l = t.nodes[me].r = -1; t.nodes[me].start = t.nodes[me].count = 0;
-      tasks->push_back(Task{me, prims, n, base, depth});
-      return me;
+      if (tasks && n <= grain && depth > 0) {   /* subtree left to a worker thread (build_parallel) */
+        tasks->push_back(Task{me, prims, n, base, depth});
+        continue;
+      }
+      Box bb = bounds(prims, n);
+      t.nodes[me].bb = bb;
+      if (depth > t.depth) t.depth = depth;
+      if (n <= 4) {
+        t.nodes[me].start = (int)base; t.nodes[me].count = (int)n; t.leaves++;
+        continue;
+      }
+      double ex = bb.hi[0] - bb.lo[0], ey = bb.hi[1] - bb.lo[1], ez = bb.hi[2] - bb.lo[2];
+      int axis = (ex > ey && ex > ez) ? 0 : (ey > ex && ey > ez) ? 1 : 2;
+      const double half = 1.0 / 2;
+      double mid = half * (bb.lo[axis] + bb.hi[axis]);
+      uint32_t nl = 0, nr = 0;
+      for (uint32_t i = 0; i < n; ++i) {
+        if (pcen[3 * (size_t)prims[i] + axis] < mid) prims[nl++] = prims[i];   // nl <= i: safe in place
+        else tmp[base + nr++] = prims[i];
+      }
+      if (nl == 0 || nr == 0) {
+        // both vectors are rebuilt from the ORIGINAL order: first half left, rest right; the in-place pass above kept
+        // the original order in whichever side received everything
+        if (nl == 0) memcpy(prims, tmp.data() + base, sizeof(uint32_t) * n);
+        nl = n / 2; nr = n - nl;
+      } else {
+        memcpy(prims + nl, tmp.data() + base, sizeof(uint32_t) * nr);
+      }
+      todo.push_back(Frame{me, true, prims + nl, nr, base + nl, depth + 1});   // popped second: the left subtree is numbered first
+      todo.push_back(Frame{me, false, prims, nl, base, depth + 1});
     }
-    Box bb = bounds(prims, n);
-    t.nodes[me].bb = bb; t.nodes[me].l = t.nodes[me].r = -1; t.nodes[me].start = t.nodes[me].count = 0;
-    if (depth > t.depth) t.depth = depth;
-    if (n <= 4) {
-      t.nodes[me].start = (int)base; t.nodes[me].count = (int)n; t.leaves++;
-      return me;
-    }
-    double ex = bb.hi[0] - bb.lo[0], ey = bb.hi[1] - bb.lo[1], ez = bb.hi[2] - bb.lo[2];
-    int axis = (ex > ey && ex > ez) ? 0 : (ey > ex && ey > ez) ? 1 : 2;
-    const double half = 1.0 / 2;
-    double mid = half * (bb.lo[axis] + bb.hi[axis]);
-    uint32_t nl = 0, nr = 0;
-    for (uint32_t i = 0; i < n; ++i) {
-      if (pcen[3 * (size_t)prims[i] + axis] < mid) prims[nl++] = prims[i];   // nl <= i: safe in place
-      else tmp[base + nr++] = prims[i];
-    }
-    if (nl == 0 || nr == 0) {
-      // both vectors are rebuilt from the ORIGINAL order: first half left, rest right; the in-place pass above kept
-      // the original order in whichever side received everything
-      if (nl == 0) memcpy(prims, tmp.data() + base, sizeof(uint32_t) * n);
-      nl = n / 2; nr = n - nl;
-    } else {
-      memcpy(prims + nl, tmp.data() + base, sizeof(uint32_t) * nr);
-    }
-    int l = build_ref(t, prims, nl, base, depth + 1);
-    int r = build_ref(t, prims + nl, nr, base + nl, depth + 1);
-    t.nodes[me].l = l; t.nodes[me].r = r;
-    return me;
+    return first;
   }
 
   // binned SAH (16 bins per axis); leaves of <= 4 primitives like the reference

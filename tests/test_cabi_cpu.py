@@ -56,6 +56,33 @@ def test_host_bvh_matches_reference_tree(scene):
     assert sah["leaf_records"] == s.n_prims
 
 
+def _triangles_only(tri):
+    from util import sc
+    base = load_scene("cbempty_480x360")
+    n = tri.shape[0]
+    return sc.SceneData(np.zeros(n, np.uint8), np.arange(n, dtype=np.uint32), np.ascontiguousarray(tri, np.float64), np.tile([0, 0, 1.0], (n, 3)).reshape(n, 9),
+                        np.zeros(n, np.int32), np.zeros((0, 4)), np.zeros(0, np.int32), base.mats[:1], base.lights, base.camera)
+
+
+def test_host_bvh_survives_degenerate_scenes():
+    """a scene is input, not code: the reference's midpoint split has no depth bound, and triangles whose boxes all contain one point give a chain as
+    deep as the scene is large.  The reference recurses (and so did the builder here: 50 000 such triangles overflowed the stack); the builder now
+    walks the same tree with an explicit stack, and the traversal tree (binned SAH with a depth budget) stays under the device's stack regardless."""
+    n = 50000
+    chain = np.zeros((n, 9)); chain[:, 0] = np.linspace(0, 1, n)       # (t, 0, 0), (0, 0, 0), (0, 0, 0)
+    sah = api.bvh_build_host(_triangles_only(chain), 1)               # builds the reference-shape tree (ranks) and the traversal tree
+    assert sah["depth"] > 40000 and sah["leaf_records"] == n and sorted(sah["dfs_rank"].tolist()) == list(range(n))
+    assert sah["flat_depth"] < sah["stack"]
+    rng = np.random.default_rng(3)
+    for tri in (np.tile([0, 0, 0, 1, 0, 0, 0, 1, 0.0], (20000, 1)),                                                   # identical triangles
+                np.where(rng.uniform(0, 1, (5000, 9)) < 0.01, np.nan, rng.uniform(-1, 1, (5000, 9))),                 # NaN vertices
+                np.where(rng.uniform(0, 1, (5000, 9)) < 0.01, np.inf, rng.uniform(-1, 1, (5000, 9))),                 # infinite vertices
+                rng.uniform(-1, 1, (3000, 9)) * 1e300, rng.uniform(-1, 1, (1, 9)), np.zeros((0, 9))):
+        for topology in (0, 1):
+            b = api.bvh_build_host(_triangles_only(tri), topology)
+            assert b["leaf_records"] == tri.shape[0] and sorted(b["dfs_rank"].tolist()) == list(range(tri.shape[0]))
+
+
 def test_survey_bvh_shapes():
     assert api.bvh_build_host(load_scene("cbspheres_lambertian_480x360"))["n_nodes"] == 7
     b = api.bvh_build_host(load_scene("cbbunny_microfacet_480x360"))
