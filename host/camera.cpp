@@ -24,8 +24,8 @@ void Camera::configure(double hFov_deg, double vFov_deg, double nClip_, double f
   nClip = nClip_; fClip = fClip_; hFov = hFov_deg; vFov = vFov_deg;
   double ar1 = tan(radians(hFov) / 2) / tan(radians(vFov) / 2);
   ar = static_cast<double>(screenW) / screenH;
-  if (ar1 < ar) hFov = 2 * degrees(atan(tan(radians(vFov) / 2) * ar));        // hFov is too small
-  else if (ar1 > ar) vFov = 2 * degrees(atan(tan(radians(hFov) / 2) / ar));   // vFov is too small
+  if (ar1 < ar) hFov = 2 * degrees(atan(tan(radians(vFov) / 2) * ar));        // frame wider than the camera's aspect: widen the horizontal angle
+  else if (ar1 > ar) vFov = 2 * degrees(atan(tan(radians(hFov) / 2) / ar));   // frame taller: widen the vertical angle
   screenDist = ((double)screenH) / (2.0 * tan(radians(vFov) / 2));
 }
 

@@ -58,20 +58,20 @@ __device__ __forceinline__ double mf_lambda(const rrt_material& m, d3 w) {
   return 0.5 * (erf(a) - 1.0 + exp(-a * a) / (a * RRT_PI));
 }
 __device__ __forceinline__ double mf_G(const rrt_material& m, d3 wo, d3 wi) { return 1.0 / (1.0 + mf_lambda(m, wi) + mf_lambda(m, wo)); }
-__device__ __forceinline__ double mf_D(const rrt_material& m, d3 h) {
-  double theta_h = mf_theta(h), tan_theta_h = tan(theta_h), cos_theta_h = h.z, cos_theta_h2 = cos_theta_h * cos_theta_h,
+__device__ __forceinline__ double mf_D(const rrt_material& m, d3 h) {   /* Beckmann distribution of the half vector, reference src/bsdf.cpp:49-56 */
+  double ang = mf_theta(h), tg = tan(ang), cz = h.z, cz2 = cz * cz,
          alpha2 = m.alpha * m.alpha; /* float product, as in the reference */
-  return exp(-tan_theta_h * tan_theta_h / alpha2) / (RRT_PI * alpha2 * cos_theta_h2 * cos_theta_h2);
+  return exp(-tg * tg / alpha2) / (RRT_PI * alpha2 * cz2 * cz2);
 }
-__device__ __forceinline__ f3 mf_F(const rrt_material& m, d3 wi) {
+__device__ __forceinline__ f3 mf_F(const rrt_material& m, d3 wi) {       /* conductor Fresnel term per channel, reference src/bsdf.cpp:58-66 */
   f3 eta = s3(m.a), k = s3(m.b);
-  f3 eta2pk2 = s_add(s_mul(eta, eta), s_mul(k, k));
-  double cos_theta_i = wi.z, cos_theta_i2 = cos_theta_i * cos_theta_i;
-  f3 tetacos = s_mulf(s_mulf(eta, 2.f), (float)cos_theta_i);
-  f3 R_s = s_div(s_addf(s_sub(eta2pk2, tetacos), (float)cos_theta_i2), s_addf(s_add(eta2pk2, tetacos), (float)cos_theta_i2));
-  f3 R_p = s_div(s_addf(s_sub(s_mulf(eta2pk2, (float)cos_theta_i2), tetacos), 1.f),
-                 s_addf(s_add(s_mulf(eta2pk2, (float)cos_theta_i2), tetacos), 1.f));
-  return s_divf(s_add(R_s, R_p), 2.f);
+  f3 n2k2 = s_add(s_mul(eta, eta), s_mul(k, k));                         /* |eta + i k|^2 */
+  double cz = wi.z, cz2 = cz * cz;
+  f3 two_n_cos = s_mulf(s_mulf(eta, 2.f), (float)cz);
+  f3 perp = s_div(s_addf(s_sub(n2k2, two_n_cos), (float)cz2), s_addf(s_add(n2k2, two_n_cos), (float)cz2));
+  f3 para = s_div(s_addf(s_sub(s_mulf(n2k2, (float)cz2), two_n_cos), 1.f),
+                  s_addf(s_add(s_mulf(n2k2, (float)cz2), two_n_cos), 1.f));
+  return s_divf(s_add(perp, para), 2.f);
 }
 
 /* BSDF::f (reference src/part1_code.cpp:167-169 diffuse; src/bsdf.cpp:68-72 microfacet; zero for every other class) */
@@ -130,14 +130,14 @@ __device__ __forceinline__ f3 bsdf_sample_f(const rrt_material& m, d3 wo, d3& wi
     case RRT_MAT_MICROFACET: {
       double ux, uy; rng_grid2(g, ux, uy);
       double alpha2 = m.alpha * m.alpha, /* float product */
-             theta_h = atan(sqrt(-alpha2 * log(1 - ux))), phi_h = 2 * RRT_PI * uy, sin_theta_h = sin(theta_h),
-             cos_theta_h = cos(theta_h), tan_theta_h = tan(theta_h),
-             p_theta = 2 * sin_theta_h * exp(-tan_theta_h * tan_theta_h / alpha2) / (alpha2 * cos_theta_h * cos_theta_h * cos_theta_h),
-             p_phi = 0.5 / RRT_PI;
-      d3 h = D3(sin_theta_h * cos(phi_h), sin_theta_h * sin(phi_h), cos_theta_h);
+             ang = atan(sqrt(-alpha2 * log(1 - ux))), azi = 2 * RRT_PI * uy, sn = sin(ang),
+             cs = cos(ang), tg = tan(ang),
+             pdf_polar = 2 * sn * exp(-tg * tg / alpha2) / (alpha2 * cs * cs * cs),
+             pdf_azimuth = 0.5 / RRT_PI;
+      d3 h = D3(sn * cos(azi), sn * sin(azi), cs);
       wi = vsub(smul(2 * vdot(wo, h), h), wo);
       if (wi.z <= 0) { pdf = 0; return F3(0, 0, 0); }
-      pdf = (float)(p_theta * p_phi / (sin_theta_h * 4 * vdot(wi, h)));
+      pdf = (float)(pdf_polar * pdf_azimuth / (sn * 4 * vdot(wi, h)));
       return bsdf_f(m, wo, wi);
     }
     default: /* RefractionBSDF: returns Spectrum() and leaves pdf unwritten (reference src/bsdf.cpp:104-106); pdf = 0 ends the path */
